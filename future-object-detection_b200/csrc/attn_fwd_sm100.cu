@@ -1,0 +1,305 @@
+// Flash-attention forward for sm_100a: TMA-staged Q/K/V tiles, tcgen05.mma with TMEM accumulators,
+// online softmax in registers.  Head dim is 32 per "part"; NPARTS = 2 realises the ConditionalDETR
+// concatenated query/key ([content ‖ sine], head dim 64) as two accumulating MMAs into the same S tile.
+//
+//   warps 0..3 : softmax (one query row per thread; TMEM lane = row), O accumulator (32 fp32) in registers
+//   warp 4     : TMA producer  (Q once, K/V double-buffered)
+//   warp 5     : TMEM alloc + tcgen05.mma issuer:  S = Q·Kᵀ (M128 N128 K32·NPARTS),  PV = P·V (M128 N32 K128)
+//
+// Per (batch, head, 128-query tile) CTA; 2 CTAs/SM overlap one CTA's softmax with the other's MMAs.
+// Bound: MUFU ex2 (one exp per 128 flop at head dim 32) and HBM at S=350; see DESIGN.md.
+#include "fod_internal.h"
+#include "sm100_ptx.cuh"
+#include "tmap.h"
+
+namespace fod {
+
+constexpr int AT_BM = 128;  // queries per CTA
+constexpr int AT_BN = 128;  // keys per tile
+constexpr int AT_D = 32;    // head dim per part (and value head dim)
+constexpr int AT_THREADS = 192;
+constexpr int AT_TILE_BYTES = AT_BN * AT_D * 2;  // 8 KB, rows of 64 B, SWIZZLE_64B
+constexpr int AT_P_BYTES = AT_BM * AT_BN * 2;    // 32 KB, two SWIZZLE_128B slabs of [128][64]
+constexpr int AT_KV_STAGES = 2;
+
+template <int NPARTS>
+struct AttnSmem {
+    static constexpr int kQ = 0;
+    static constexpr int kK = kQ + NPARTS * AT_TILE_BYTES;
+    static constexpr int kV = kK + AT_KV_STAGES * NPARTS * AT_TILE_BYTES;
+    static constexpr int kP = kV + AT_KV_STAGES * AT_TILE_BYTES;
+    static constexpr int kBars = kP + AT_P_BYTES;
+    static constexpr int kTotal = kBars + 128 + 1024;
+};
+
+struct AttnParams {
+    __nv_bfloat16* out;
+    float* lse;
+    long long ldo, bso;
+    int B, H, Lq, Lk;
+    int bm_q1, bm_k1, bm_q2, bm_k2, bm_v;  // 1 if the tensor has a batch dimension, 0 if broadcast
+    float scale_log2;                      // scale * log2(e)
+    float scale;
+};
+
+template <int NPARTS>
+__global__ void __launch_bounds__(AT_THREADS, 2)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant__ CUtensorMap tmK1,
+                const __grid_constant__ CUtensorMap tmQ2, const __grid_constant__ CUtensorMap tmK2,
+                const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
+    using L = AttnSmem<NPARTS>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBars);
+    uint64_t* q_full = bars + 0;
+    uint64_t* kv_full = bars + 1;   // [2]
+    uint64_t* kv_empty = bars + 3;  // [2]
+    uint64_t* s_full = bars + 5;
+    uint64_t* p_full = bars + 6;
+    uint64_t* pv_full = bars + 7;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int q0 = blockIdx.x * AT_BM;
+    const int h = blockIdx.y;
+    const int b = blockIdx.z;
+    const int nkt = (p.Lk + AT_BN - 1) / AT_BN;
+
+    if (warp == 4 && lane == 0) {
+        tma_prefetch_desc(&tmQ1);
+        tma_prefetch_desc(&tmK1);
+        tma_prefetch_desc(&tmV);
+        if (NPARTS == 2) {
+            tma_prefetch_desc(&tmQ2);
+            tma_prefetch_desc(&tmK2);
+        }
+        mbar_init(q_full, 1);
+        for (int s = 0; s < AT_KV_STAGES; ++s) {
+            mbar_init(kv_full + s, 1);
+            mbar_init(kv_empty + s, 1);
+        }
+        mbar_init(s_full, 1);
+        mbar_init(p_full, 128);
+        mbar_init(pv_full, 1);
+        fence_barrier_init();
+    }
+    if (warp == 5) tmem_alloc<256>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    const uint32_t tmem_S = tmem_base;
+    const uint32_t tmem_PV = tmem_base + 128;
+
+    if (warp == 4) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(q_full, NPARTS * AT_TILE_BYTES);
+            tma_load_3d(smem + L::kQ, &tmQ1, q_full, h * AT_D, q0, b * p.bm_q1);
+            if (NPARTS == 2) tma_load_3d(smem + L::kQ + AT_TILE_BYTES, &tmQ2, q_full, h * AT_D, q0, b * p.bm_q2);
+            for (int j = 0; j < nkt; ++j) {
+                const int s = j % AT_KV_STAGES;
+                const uint32_t ph = (j / AT_KV_STAGES) & 1;
+                mbar_wait(kv_empty + s, ph ^ 1);
+                mbar_arrive_expect_tx(kv_full + s, (NPARTS + 1) * AT_TILE_BYTES);
+                uint8_t* sk = smem + L::kK + s * NPARTS * AT_TILE_BYTES;
+                tma_load_3d(sk, &tmK1, kv_full + s, h * AT_D, j * AT_BN, b * p.bm_k1);
+                if (NPARTS == 2) tma_load_3d(sk + AT_TILE_BYTES, &tmK2, kv_full + s, h * AT_D, j * AT_BN, b * p.bm_k2);
+                tma_load_3d(smem + L::kV + s * AT_TILE_BYTES, &tmV, kv_full + s, h * AT_D, j * AT_BN, b * p.bm_v);
+            }
+        }
+    } else if (warp == 5) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN, 0, 0);
+            constexpr uint32_t idesc_pv = umma_idesc_bf16(AT_BM, AT_D, 0, 1);  // B = V is MN-major
+            const uint32_t q_addr = smem_u32(smem + L::kQ);
+            const uint32_t p_addr = smem_u32(smem + L::kP);
+            auto issue_S = [&](int j) {
+                const int s = j % AT_KV_STAGES;
+                mbar_wait(kv_full + s, (j / AT_KV_STAGES) & 1);
+                tc_fence_after();
+                const uint32_t k_addr = smem_u32(smem + L::kK + s * NPARTS * AT_TILE_BYTES);
+#pragma unroll
+                for (int part = 0; part < NPARTS; ++part) {
+#pragma unroll
+                    for (int k = 0; k < AT_D / 16; ++k) {
+                        const uint64_t da = umma_smem_desc(q_addr + part * AT_TILE_BYTES + k * 32, 16, 512, 4);
+                        const uint64_t db = umma_smem_desc(k_addr + part * AT_TILE_BYTES + k * 32, 16, 512, 4);
+                        umma_bf16_ss(tmem_S, da, db, idesc_s, (part | k) ? 1u : 0u);
+                    }
+                }
+                umma_commit(s_full);
+            };
+            mbar_wait(q_full, 0);
+            issue_S(0);
+            for (int j = 0; j < nkt; ++j) {
+                const int s = j % AT_KV_STAGES;
+                mbar_wait(p_full, j & 1);
+                tc_fence_after();
+                const uint32_t v_addr = smem_u32(smem + L::kV + s * AT_TILE_BYTES);
+#pragma unroll
+                for (int kk = 0; kk < AT_BN / 16; ++kk) {
+                    const uint64_t da = umma_smem_desc(p_addr + (kk >> 2) * (AT_BM * 128) + (kk & 3) * 32, 16, 1024, 2);
+                    const uint64_t db = umma_smem_desc(v_addr + kk * 1024, 4096, 512, 4);
+                    umma_bf16_ss(tmem_PV, da, db, idesc_pv, kk ? 1u : 0u);
+                }
+                umma_commit(pv_full);
+                umma_commit(kv_empty + s);
+                if (j + 1 < nkt) issue_S(j + 1);
+            }
+        }
+    } else {
+        // ------------------------------------------------ softmax warps
+        const int row = warp * 32 + lane;  // warp == TMEM lane quarter
+        const uint32_t lane_off = uint32_t(warp * 32) << 16;
+        uint8_t* sP = smem + L::kP;
+        float m_run = -INFINITY, l_run = 0.f;
+        float o[AT_D];
+#pragma unroll
+        for (int i = 0; i < AT_D; ++i) o[i] = 0.f;
+        uint32_t v[32];
+        for (int j = 0; j < nkt; ++j) {
+            mbar_wait(s_full, j & 1);
+            tc_fence_after();
+            const int kvalid = p.Lk - j * AT_BN;  // >= 1
+            float mx = -INFINITY;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                tmem_ld_32x32b_x32(tmem_S + lane_off + c * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                    if (c * 32 + i < kvalid) mx = fmaxf(mx, __uint_as_float(v[i]));
+            }
+            const float m_new = fmaxf(m_run, mx);
+            const float alpha = fast_exp2((m_run - m_new) * p.scale_log2);
+            const float moff = m_new * p.scale_log2;
+            float rs = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                tmem_ld_32x32b_x32(tmem_S + lane_off + c * 32, v);
+                tmem_ld_wait();
+                float pr[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const float e = fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2, -moff));
+                    pr[i] = (c * 32 + i < kvalid) ? e : 0.f;
+                    rs += pr[i];
+                }
+                // 32 bf16 = four 16-byte chunks: logical chunk index within the 64-wide slab
+                uint8_t* slab = sP + (c >> 1) * (AT_BM * 128);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    uint4 u;
+                    u.x = pack_bf16x2(pr[q * 8 + 0], pr[q * 8 + 1]);
+                    u.y = pack_bf16x2(pr[q * 8 + 2], pr[q * 8 + 3]);
+                    u.z = pack_bf16x2(pr[q * 8 + 4], pr[q * 8 + 5]);
+                    u.w = pack_bf16x2(pr[q * 8 + 6], pr[q * 8 + 7]);
+                    *reinterpret_cast<uint4*>(slab + swz_off<128>(row, (c & 1) * 4 + q)) = u;
+                }
+            }
+            l_run = l_run * alpha + rs;
+            m_run = m_new;
+            fence_proxy_async_smem();
+            tc_fence_before();
+            mbar_arrive(p_full);
+            mbar_wait(pv_full, j & 1);
+            tc_fence_after();
+            tmem_ld_32x32b_x32(tmem_PV + lane_off, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < AT_D; ++i) o[i] = fmaf(o[i], alpha, __uint_as_float(v[i]));
+        }
+        const int q = q0 + row;
+        if (q < p.Lq) {
+            const float inv = 1.f / l_run;
+            __nv_bfloat16* dst = p.out + (long long)b * p.bso + (long long)q * p.ldo + h * AT_D;
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq) {
+                uint4 u;
+                u.x = pack_bf16x2(o[qq * 8 + 0] * inv, o[qq * 8 + 1] * inv);
+                u.y = pack_bf16x2(o[qq * 8 + 2] * inv, o[qq * 8 + 3] * inv);
+                u.z = pack_bf16x2(o[qq * 8 + 4] * inv, o[qq * 8 + 5] * inv);
+                u.w = pack_bf16x2(o[qq * 8 + 6] * inv, o[qq * 8 + 7] * inv);
+                reinterpret_cast<uint4*>(dst)[qq] = u;
+            }
+            if (p.lse) p.lse[((long long)b * p.H + h) * p.Lq + q] = m_run * p.scale + logf(l_run);
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 5) {
+        tc_fence_after();
+        tmem_dealloc<256>(tmem_base);
+    }
+}
+
+static int make_seq_tmap(CUtensorMap* tm, const void* base, int rowlen, int L, int B, long long ld, long long bs) {
+    const bool bcast = (bs == 0) || (B == 1);
+    uint64_t dims[3] = {(uint64_t)rowlen, (uint64_t)L, (uint64_t)(bcast ? 1 : B)};
+    uint64_t str[2] = {(uint64_t)ld * 2, (uint64_t)(bcast ? (uint64_t)ld * 2 * L : (uint64_t)bs * 2)};
+    uint32_t box[3] = {AT_D, AT_BN, 1};
+    return make_tmap_bf16(tm, base, 3, dims, str, box, 64);
+}
+
+}  // namespace fod
+
+extern "C" int fod_attn_fwd(const fod_attn_args* a, void* stream) {
+    using namespace fod;
+    if (!a || !a->q1 || !a->k1 || !a->v || !a->out) return fod_fail(FOD_E_ARG, "attn: null pointer");
+    if (a->B <= 0 || a->H <= 0 || a->Lq <= 0 || a->Lk <= 0) return fod_fail(FOD_E_ARG, "attn: empty shape");
+    if ((a->q2 == nullptr) != (a->k2 == nullptr)) return fod_fail(FOD_E_ARG, "attn: q2/k2 must come together");
+    const int two = a->q2 != nullptr;
+    const long long lds[6] = {a->ldq1, a->ldk1, a->ldv, a->ldo, two ? a->ldq2 : 8, two ? a->ldk2 : 8};
+    for (int i = 0; i < 6; ++i)
+        if (lds[i] % 8) return fod_fail(FOD_E_ARG, "attn: row strides must be multiples of 8 elements");
+    const long long bss[6] = {a->bsq1, a->bsk1, a->bsv, a->bso, two ? a->bsq2 : 0, two ? a->bsk2 : 0};
+    for (int i = 0; i < 6; ++i)
+        if (bss[i] % 8) return fod_fail(FOD_E_ARG, "attn: batch strides must be multiples of 8 elements");
+    const int rowlen = a->H * AT_D;
+    CUtensorMap tq1, tk1, tq2, tk2, tv;
+    if (make_seq_tmap(&tq1, a->q1, rowlen, a->Lq, a->B, a->ldq1, a->bsq1)) return fod_fail(FOD_E_TMAP, "attn: tmap q1");
+    if (make_seq_tmap(&tk1, a->k1, rowlen, a->Lk, a->B, a->ldk1, a->bsk1)) return fod_fail(FOD_E_TMAP, "attn: tmap k1");
+    if (make_seq_tmap(&tv, a->v, rowlen, a->Lk, a->B, a->ldv, a->bsv)) return fod_fail(FOD_E_TMAP, "attn: tmap v");
+    if (two) {
+        if (make_seq_tmap(&tq2, a->q2, rowlen, a->Lq, a->B, a->ldq2, a->bsq2)) return fod_fail(FOD_E_TMAP, "attn: tmap q2");
+        if (make_seq_tmap(&tk2, a->k2, rowlen, a->Lk, a->B, a->ldk2, a->bsk2)) return fod_fail(FOD_E_TMAP, "attn: tmap k2");
+    } else {
+        tq2 = tq1;
+        tk2 = tk1;
+    }
+    AttnParams p;
+    p.out = reinterpret_cast<__nv_bfloat16*>(a->out);
+    p.lse = a->lse;
+    p.ldo = a->ldo;
+    p.bso = a->bso;
+    p.B = a->B;
+    p.H = a->H;
+    p.Lq = a->Lq;
+    p.Lk = a->Lk;
+    auto has_b = [&](long long bs) { return (bs != 0 && a->B > 1) ? 1 : 0; };
+    p.bm_q1 = has_b(a->bsq1);
+    p.bm_k1 = has_b(a->bsk1);
+    p.bm_q2 = two ? has_b(a->bsq2) : 0;
+    p.bm_k2 = two ? has_b(a->bsk2) : 0;
+    p.bm_v = has_b(a->bsv);
+    p.scale = a->scale;
+    p.scale_log2 = a->scale * 1.4426950408889634f;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    dim3 grid((a->Lq + AT_BM - 1) / AT_BM, a->H, a->B);
+    static bool attr1 = false, attr2 = false;
+    if (two) {
+        if (!attr2) {
+            cudaFuncSetAttribute(attn_fwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnSmem<2>::kTotal);
+            attr2 = true;
+        }
+        attn_fwd_kernel<2><<<grid, AT_THREADS, AttnSmem<2>::kTotal, st>>>(tq1, tk1, tq2, tk2, tv, p);
+    } else {
+        if (!attr1) {
+            cudaFuncSetAttribute(attn_fwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnSmem<1>::kTotal);
+            attr1 = true;
+        }
+        attn_fwd_kernel<1><<<grid, AT_THREADS, AttnSmem<1>::kTotal, st>>>(tq1, tk1, tq2, tk2, tv, p);
+    }
+    return fod_check_launch("attn_fwd_kernel");
+}
