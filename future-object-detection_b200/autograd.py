@@ -1,0 +1,252 @@
+"""torch.autograd.Function wrappers: each block's forward AND backward run on the C-ABI kernels (ops.py).
+
+Conventions: activations are 2-D (rows, channels) bf16, contiguous; `w` is the fp32 weight (a Parameter, or a
+cat/pad of Parameters — it only routes the gradient), `wq` its bf16 copy that the kernels read.  Weight gradients
+are produced in fp32 by the split-K MN-major GEMM (dW = dYᵀ·X, atomically reduced), activation gradients in bf16.
+Dropout is not implemented (p = 0): parity with the reference is defined with dropout disabled.
+"""
+import torch
+from torch.autograd import Function
+
+from . import ops
+
+BF16 = torch.bfloat16
+_NUM_SMS = 148
+
+
+def _bf(t):
+    return t.to(BF16).contiguous() if t.dtype != BF16 else t.contiguous()
+
+
+def _split_k(m_out, n_out, k):
+    bn = 256 if n_out > 128 else (128 if n_out > 64 else 64)
+    tiles = ((m_out + 127) // 128) * ((n_out + bn - 1) // bn)
+    kb = (k + 63) // 64
+    return max(1, min(kb // 2 if kb >= 2 else 1, (_NUM_SMS + tiles - 1) // tiles))
+
+
+def weight_grad(dy, x):
+    """dW (N, K) fp32 = dyᵀ (N, rows) · x (rows, K), contraction over rows on the MN-major tcgen05 GEMM."""
+    n, k = dy.shape[1], x.shape[1]
+    dw = torch.zeros((n, k), dtype=torch.float32, device=dy.device)
+    ops.gemm(dy, x, a_mn=True, b_mn=True, accum_into=dw, split_k=_split_k(n, k, dy.shape[0]))
+    return dw
+
+
+def input_grad(dy, wq, **kw):
+    """dX (rows, K) bf16 = dy (rows, N) · W (N, K), W read in its nn.Linear layout (MN-major B operand)."""
+    return ops.gemm(dy, wq, b_mn=True, **kw)
+
+
+class LinearFn(Function):
+    """y = [relu](x·Wᵀ + b + residual[row % mod]) — nn.Linear (+ReLU) call sites of transformer.py / paper.py."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, wq, residual, res_row_mod, relu, out_f32):
+        y = ops.gemm(x, wq, bias=b, residual=residual, res_row_mod=res_row_mod, relu=relu, out_f32=out_f32)
+        ctx.save_for_backward(x, wq, y if relu else None)
+        ctx.cfg = (res_row_mod, relu, b is not None, residual is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, wq, y = ctx.saved_tensors
+        mod, relu, has_b, has_res = ctx.cfg
+        dy = _bf(dy)
+        if relu:
+            dy = dy * (y > 0)
+        dx = input_grad(dy, wq) if ctx.needs_input_grad[0] else None
+        dw = weight_grad(dy, x) if ctx.needs_input_grad[1] else None
+        db = ops.colsum(dy).view(-1) if has_b and ctx.needs_input_grad[2] else None
+        dres = None
+        if has_res and ctx.needs_input_grad[4]:
+            dres = dy if mod == 0 else dy.view(-1, mod, dy.shape[1]).sum(0)
+        return dx, dw, db, None, dres, None, None, None
+
+
+def linear(x, w, b, wq, residual=None, res_row_mod=0, relu=False, out_f32=False):
+    return LinearFn.apply(x, w, b, wq, residual, res_row_mod, relu, out_f32)
+
+
+class LinearLNFn(Function):
+    """y = LayerNorm(res + x·Wᵀ + b): attention out_proj + residual + norm (transformer.py:417, 272, 286)."""
+
+    @staticmethod
+    def forward(ctx, x, res, w, b, wq, gamma, beta, eps, need_grad):
+        if need_grad:
+            y, pre, mean, rstd = ops.gemm(x, wq, bias=b, residual=res, ln=(gamma, beta, eps), save_ln=True)
+            ctx.save_for_backward(x, wq, pre, mean, rstd, gamma)
+        else:
+            y = ops.gemm(x, wq, bias=b, residual=res, ln=(gamma, beta, eps))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, wq, pre, mean, rstd, gamma = ctx.saved_tensors
+        dgamma = torch.zeros_like(gamma)
+        dbeta = torch.zeros_like(gamma)
+        dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, dgamma, dbeta)
+        dx = input_grad(dz, wq)
+        dw = weight_grad(dz, x)
+        db = ops.colsum(dz).view(-1)
+        return dx, dz, dw, db, None, dgamma, dbeta, None, None
+
+
+def linear_ln(x, res, w, b, wq, gamma, beta, eps=1e-5):
+    return LinearLNFn.apply(x, res, w, b, wq, gamma, beta, eps, torch.is_grad_enabled())
+
+
+class FFNLNFn(Function):
+    """y = LayerNorm(x + W2·relu(W1·x + b1) + b2) — transformer.py:407-419 (encoder), :228-235,309-311 (decoder),
+    :103-108,116-118 (egodeep MLP).  Backward: LN bwd -> dH GEMM with fused ReLU mask -> dX GEMM with fused residual."""
+
+    @staticmethod
+    def forward(ctx, x, w1, b1, w1q, w2, b2, w2q, gamma, beta, eps, need_grad):
+        h = ops.gemm(x, w1q, bias=b1, relu=True)
+        if need_grad:
+            y, pre, mean, rstd = ops.gemm(h, w2q, bias=b2, residual=x, ln=(gamma, beta, eps), save_ln=True)
+            ctx.save_for_backward(x, h, w1q, w2q, pre, mean, rstd, gamma)
+        else:
+            y = ops.gemm(h, w2q, bias=b2, residual=x, ln=(gamma, beta, eps))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, h, w1q, w2q, pre, mean, rstd, gamma = ctx.saved_tensors
+        dgamma = torch.zeros_like(gamma)
+        dbeta = torch.zeros_like(gamma)
+        dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, dgamma, dbeta)
+        dh = input_grad(dz, w2q, relu_mask=h)
+        dw2 = weight_grad(dz, h)
+        db2 = ops.colsum(dz).view(-1)
+        dx = input_grad(dh, w1q, residual=dz)
+        dw1 = weight_grad(dh, x)
+        db1 = ops.colsum(dh).view(-1)
+        return dx, dw1, db1, None, dw2, db2, None, dgamma, dbeta, None, None
+
+
+def ffn_ln(x, w1, b1, w1q, w2, b2, w2q, gamma, beta, eps=1e-5):
+    return FFNLNFn.apply(x, w1, b1, w1q, w2, b2, w2q, gamma, beta, eps, torch.is_grad_enabled())
+
+
+class AddLNFn(Function):
+    """y = LayerNorm(x + bcast[row // rows_per_group]) — norm_eda (transformer.py:486) and decoder.norm (:386)."""
+
+    @staticmethod
+    def forward(ctx, x, bcast, rows_per_group, gamma, beta, eps, need_grad):
+        if need_grad:
+            y, mean, rstd = ops.add_ln_fwd(x, gamma, beta, eps, bcast, rows_per_group, save=True)
+            ctx.save_for_backward(x, bcast, mean, rstd, gamma)
+            ctx.rpg = rows_per_group
+        else:
+            y = ops.add_ln_fwd(x, gamma, beta, eps, bcast, rows_per_group)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, bcast, mean, rstd, gamma = ctx.saved_tensors
+        dgamma = torch.zeros_like(gamma)
+        dbeta = torch.zeros_like(gamma)
+        dz = ops.ln_bwd(_bf(dy), x, mean, rstd, gamma, dgamma, dbeta, bcast=bcast, rows_per_group=ctx.rpg)
+        db = ops.colsum(dz, ctx.rpg).to(BF16) if bcast is not None else None
+        return dz, db, None, dgamma, dbeta, None, None
+
+
+def add_ln(x, gamma, beta, bcast=None, rows_per_group=0, eps=1e-5):
+    return AddLNFn.apply(x, bcast, rows_per_group, gamma, beta, eps, torch.is_grad_enabled())
+
+
+class SelfAttnFn(Function):
+    """Multi-head self-attention core on a fused projection qkv (B, L, 768) = [q | k | v], head dim 32:
+    torch.nn.MultiheadAttention core (transformer.py:404) and SlotToSlotAttention's (transformer.py:79-81)."""
+
+    @staticmethod
+    def forward(ctx, qkv, heads, scale):
+        c = heads * 32
+        out, lse = ops.attn_fwd(qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:], scale, heads)
+        ctx.save_for_backward(qkv, out, lse)
+        ctx.cfg = (heads, scale)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, out, lse = ctx.saved_tensors
+        heads, scale = ctx.cfg
+        c = heads * 32
+        dq, _, _, _, _ = ops.attn_bwd(qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:], out, lse, _bf(dout), scale,
+                                      heads, fused="qkv")
+        return dq._base if dq._base is not None else dq, None, None
+
+
+def self_attention(qkv, heads=8, scale=32 ** -0.5):
+    return SelfAttnFn.apply(qkv, heads, scale)
+
+
+class PlainAttnFn(Function):
+    """Single-part attention on separate dense q (B,Lq,C), k, v (B,Lk,C) — EgodeepAttention with several IMU keys."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, heads, scale):
+        out, lse = ops.attn_fwd(q, k, v, scale, heads)
+        ctx.save_for_backward(q, k, v, out, lse)
+        ctx.cfg = (heads, scale)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        q, k, v, out, lse = ctx.saved_tensors
+        heads, scale = ctx.cfg
+        dq, dk, dv, _, _ = ops.attn_bwd(q, k, v, out, lse, _bf(dout), scale, heads)
+        return dq, dk, dv, None, None
+
+
+class CrossAttnFn(Function):
+    """Conditional cross-attention core (transformer.py:148-176 + attention.py:274-372): per head
+    q = [qc ‖ qs], k = [kc ‖ kp] realised as two accumulating MMAs; kv (B, S, 512) = [kc | v] fused projection;
+    kp (S, 256) batch-invariant; qs (B, M, 256) or batch-invariant (M, 256)."""
+
+    @staticmethod
+    def forward(ctx, qc, qs, kv, kp, heads, scale):
+        c = heads * 32
+        out, lse = ops.attn_fwd(qc, kv[..., :c], kv[..., c:], scale, heads, q2=qs, k2=kp, batch=kv.shape[0])
+        ctx.save_for_backward(qc, qs, kv, kp, out, lse)
+        ctx.cfg = (heads, scale)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qc, qs, kv, kp, out, lse = ctx.saved_tensors
+        heads, scale = ctx.cfg
+        c = heads * 32
+        dq1, dk1, _, dq2, dk2 = ops.attn_bwd(qc, kv[..., :c], kv[..., c:], out, lse, _bf(dout), scale, heads, q2=qs,
+                                             k2=kp, fused="kv")
+        dkv = dk1._base
+        dqs = dq2 if qs.dim() == 3 else dq2.sum(0)
+        dkp = dk2.sum(0) if kp.dim() == 2 else dk2
+        return dq1, dqs, dkv, dkp, None, None
+
+
+def cross_attention(qc, qs, kv, kp, heads=8, scale=64 ** -0.5):
+    return CrossAttnFn.apply(qc, qs, kv, kp, heads, scale)
+
+
+class SetLossFn(Function):
+    """Matching + losses (set_criterion.py:172-217): forward runs fod_match and fod_set_loss (which also produces the
+    gradients); backward scales them by the incoming gradient of the total loss."""
+
+    @staticmethod
+    def forward(ctx, logits, boxes, tgt_boxes, tgt_labels, tgt_count, num_boxes, weights, status):
+        w_ce, w_bbox, w_giou, c_class, c_bbox, c_giou, alpha = weights
+        m = ops.match(logits.detach(), boxes.detach(), tgt_boxes, tgt_labels, tgt_count, c_class, c_bbox, c_giou,
+                      alpha, want_lists=False, status=status)
+        out, dl, db = ops.set_loss(logits, boxes, m["match_tgt"], tgt_boxes, tgt_labels, tgt_count, num_boxes, w_ce,
+                                   w_bbox, w_giou, alpha, want_grads=True)
+        ctx.save_for_backward(dl, db)
+        ctx.mark_non_differentiable(m["match_tgt"])
+        return out, m["match_tgt"]
+
+    @staticmethod
+    def backward(ctx, dout, _):
+        dl, db = ctx.saved_tensors
+        g = dout[0]
+        return dl * g, db * g, None, None, None, None, None, None

@@ -13,6 +13,10 @@ namespace fod {
 struct GemmEpi {
     const float* bias;
     const __nv_bfloat16* residual;
+    const __nv_bfloat16* relu_mask;  // (M,N), ld_out: output is zeroed where mask <= 0 (ReLU backward)
+    const float* col_scale;          // optional (res_row_mod or M, N) fp32 multiplier applied after bias: y = (acc+b)*s
+    int atomic_out;                  // 1: red.add into out_f32 (split-K / gradient accumulation)
+    int kb_per_split;
     const float* ln_gamma;
     const float* ln_beta;
     __nv_bfloat16* out_bf16;
@@ -60,6 +64,12 @@ __device__ __forceinline__ void epi_bias_res(float (&z)[32], const GemmEpi& p, l
 #pragma unroll
         for (int i = 0; i < 32; ++i)
             if (col0 + i < p.N) z[i] += __ldg(p.bias + col0 + i);
+    }
+    if (p.col_scale) {
+        const float* sc = p.col_scale + res_row * (long long)p.N + col0;
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+            if (col0 + i < p.N) z[i] *= __ldg(sc + i);
     }
     if (p.residual) {
         const __nv_bfloat16* r = p.residual + res_row * p.ld_res + col0;
@@ -112,7 +122,7 @@ __device__ __forceinline__ void epi_store_f32(float* dst, const float (&z)[32], 
     }
 }
 
-template <int BN>
+template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmEpi p) {
     using Cfg = GemmCfg<BN>;
@@ -127,7 +137,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * BN;
     const int m0 = blockIdx.y * GEMM_BM;
-    const int num_kb = (p.K + GEMM_BK - 1) / GEMM_BK;
+    const int total_kb = (p.K + GEMM_BK - 1) / GEMM_BK;
+    const int kb_begin = blockIdx.z * p.kb_per_split;
+    const int kb_end = min(total_kb, kb_begin + p.kb_per_split);
+    const int num_kb = kb_end - kb_begin;  // >= 1 by construction of the grid
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -154,13 +167,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 uint8_t* sa = smem + s * Cfg::kStageBytes;
                 uint8_t* sb = sa + Cfg::kABytes;
                 mbar_arrive_expect_tx(full_bar + s, Cfg::kStageBytes);
-                tma_load_2d(sa, &tmA, full_bar + s, kb * GEMM_BK, m0);
-                tma_load_2d(sb, &tmB, full_bar + s, kb * GEMM_BK, n0);
+                const int k0 = (kb_begin + kb) * GEMM_BK;
+                if constexpr (A_MN) {  // memory is (K, M): 64x64 boxes, one per 64-wide M chunk
+#pragma unroll
+                    for (int c = 0; c < GEMM_BM / 64; ++c) tma_load_2d(sa + c * 8192, &tmA, full_bar + s, m0 + c * 64, k0);
+                } else {
+                    tma_load_2d(sa, &tmA, full_bar + s, k0, m0);
+                }
+                if constexpr (B_MN) {
+#pragma unroll
+                    for (int c = 0; c < BN / 64; ++c) tma_load_2d(sb + c * 8192, &tmB, full_bar + s, n0 + c * 64, k0);
+                } else {
+                    tma_load_2d(sb, &tmB, full_bar + s, k0, n0);
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, 0, 0);
+            constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
             for (int kb = 0; kb < num_kb; ++kb) {
                 const int s = kb % Cfg::kStages;
                 const uint32_t ph = (kb / Cfg::kStages) & 1;
@@ -170,8 +194,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 const uint32_t b_addr = a_addr + Cfg::kABytes;
 #pragma unroll
                 for (int k = 0; k < GEMM_BK / 16; ++k) {
-                    const uint64_t da = umma_smem_desc(a_addr + k * 32, 16, 1024, 2);
-                    const uint64_t db = umma_smem_desc(b_addr + k * 32, 16, 1024, 2);
+                    // K-major: 128-byte rows of 64 k, 8-row groups 1024 B apart.  MN-major: [64 k][64 mn] slabs of
+                    // 8 KB (LBO = next 64 mn), 8-k groups 1024 B apart (SBO), 16 k per instruction = 2048 B.
+                    const uint64_t da = A_MN ? umma_smem_desc(a_addr + k * 2048, 8192, 1024, 2)
+                                             : umma_smem_desc(a_addr + k * 32, 16, 1024, 2);
+                    const uint64_t db = B_MN ? umma_smem_desc(b_addr + k * 2048, 8192, 1024, 2)
+                                             : umma_smem_desc(b_addr + k * 32, 16, 1024, 2);
                     umma_bf16_ss(tmem_base, da, db, idesc, (kb | k) ? 1u : 0u);
                 }
                 umma_commit(empty_bar + s);  // frees the smem stage when these MMAs retire
@@ -206,8 +234,33 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                         for (int i = 0; i < 32; ++i) z[i] = fmaxf(z[i], 0.f);
                     }
                     const int nv = p.N - col0;
+                    if (p.relu_mask) {
+                        const __nv_bfloat16* mk = p.relu_mask + row * p.ld_out + col0;
+                        if (nv >= 32 && ((reinterpret_cast<uintptr_t>(mk) & 15) == 0)) {
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                uint4 u = __ldg(reinterpret_cast<const uint4*>(mk) + q);
+                                const __nv_bfloat16* hm = reinterpret_cast<const __nv_bfloat16*>(&u);
+#pragma unroll
+                                for (int j = 0; j < 8; ++j)
+                                    if (!(__bfloat162float(hm[j]) > 0.f)) z[q * 8 + j] = 0.f;
+                            }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (i < nv && !(__bfloat162float(mk[i]) > 0.f)) z[i] = 0.f;
+                        }
+                    }
                     if (p.out_bf16) epi_store_bf16(p.out_bf16 + row * p.ld_out + col0, z, nv);
-                    if (p.out_f32) epi_store_f32(p.out_f32 + row * p.ld_out + col0, z, nv);
+                    if (p.out_f32) {
+                        if (p.atomic_out) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (i < nv) atomicAdd(p.out_f32 + row * p.ld_out + col0 + i, z[i]);
+                        } else {
+                            epi_store_f32(p.out_f32 + row * p.ld_out + col0, z, nv);
+                        }
+                    }
                 }
             }
         } else {
@@ -269,30 +322,55 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
 }
 
-template <int BN>
-static int launch_gemm(const fod_linear_args* a, const GemmEpi& epi, cudaStream_t st) {
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     using Cfg = GemmCfg<BN>;
     CUtensorMap tmA, tmB;
-    {
+    const long long ldw = a->ldw ? a->ldw : (B_MN ? a->N : a->K);
+    if (A_MN) {
+        uint64_t dims[2] = {(uint64_t)a->M, (uint64_t)a->K};
+        uint64_t str[1] = {(uint64_t)a->ldx * 2};
+        uint32_t box[2] = {64, GEMM_BK};
+        if (make_tmap_bf16(&tmA, a->x, 2, dims, str, box, 128)) return fod_fail(FOD_E_TMAP, "gemm: tmap A (MN-major)");
+    } else {
         uint64_t dims[2] = {(uint64_t)a->K, (uint64_t)a->M};
         uint64_t str[1] = {(uint64_t)a->ldx * 2};
         uint32_t box[2] = {GEMM_BK, GEMM_BM};
-        if (make_tmap_bf16(&tmA, a->x, 2, dims, str, box, 128)) return FOD_E_TMAP;
+        if (make_tmap_bf16(&tmA, a->x, 2, dims, str, box, 128)) return fod_fail(FOD_E_TMAP, "gemm: tmap A");
     }
-    {
+    if (B_MN) {
+        uint64_t dims[2] = {(uint64_t)a->N, (uint64_t)a->K};
+        uint64_t str[1] = {(uint64_t)ldw * 2};
+        uint32_t box[2] = {64, GEMM_BK};
+        if (make_tmap_bf16(&tmB, a->w, 2, dims, str, box, 128)) return fod_fail(FOD_E_TMAP, "gemm: tmap B (MN-major)");
+    } else {
         uint64_t dims[2] = {(uint64_t)a->K, (uint64_t)a->N};
-        uint64_t str[1] = {(uint64_t)a->K * 2};
+        uint64_t str[1] = {(uint64_t)ldw * 2};
         uint32_t box[2] = {GEMM_BK, (uint32_t)BN};
-        if (make_tmap_bf16(&tmB, a->w, 2, dims, str, box, 128)) return FOD_E_TMAP;
+        if (make_tmap_bf16(&tmB, a->w, 2, dims, str, box, 128)) return fod_fail(FOD_E_TMAP, "gemm: tmap B");
     }
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(gemm_bf16_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+        cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             Cfg::kSmemBytes);
         attr_set = true;
     }
-    dim3 grid((a->N + BN - 1) / BN, (a->M + GEMM_BM - 1) / GEMM_BM);
-    gemm_bf16_kernel<BN><<<grid, GEMM_THREADS, Cfg::kSmemBytes, st>>>(tmA, tmB, epi);
+    const int total_kb = (a->K + GEMM_BK - 1) / GEMM_BK;
+    int splits = a->split_k > 1 ? a->split_k : 1;
+    if (splits > total_kb) splits = total_kb;
+    epi.kb_per_split = (total_kb + splits - 1) / splits;
+    splits = (total_kb + epi.kb_per_split - 1) / epi.kb_per_split;  // no empty split
+    dim3 grid((a->N + BN - 1) / BN, (a->M + GEMM_BM - 1) / GEMM_BM, splits);
+    gemm_bf16_kernel<BN, A_MN, B_MN><<<grid, GEMM_THREADS, Cfg::kSmemBytes, st>>>(tmA, tmB, epi);
     return fod_check_launch("gemm_bf16_kernel");
+}
+
+template <int BN>
+static int launch_gemm_major(const fod_linear_args* a, const GemmEpi& e, cudaStream_t st) {
+    if (a->a_mn && a->b_mn) return launch_gemm<BN, true, true>(a, e, st);
+    if (a->b_mn) return launch_gemm<BN, false, true>(a, e, st);
+    if (a->a_mn) return fod_fail(FOD_E_ARG, "gemm: A MN-major with B K-major is not instantiated");
+    return launch_gemm<BN, false, false>(a, e, st);
 }
 
 }  // namespace fod
@@ -300,15 +378,24 @@ static int launch_gemm(const fod_linear_args* a, const GemmEpi& epi, cudaStream_
 extern "C" int fod_linear_fwd(const fod_linear_args* a, void* stream) {
     using namespace fod;
     if (!a || !a->x || !a->w || a->M <= 0 || a->N <= 0 || a->K <= 0) return fod_fail(FOD_E_ARG, "linear: null/empty");
-    if ((a->K % 8) || (a->ldx % 8)) return fod_fail(FOD_E_ARG, "linear: K and ldx must be multiples of 8");
+    if (a->ldx % 8 || a->ldw % 8) return fod_fail(FOD_E_ARG, "linear: ldx/ldw must be multiples of 8");
+    if (!a->a_mn && (a->K % 8)) return fod_fail(FOD_E_ARG, "linear: K must be a multiple of 8");
+    if (a->a_mn && (a->M % 8)) return fod_fail(FOD_E_ARG, "linear: M must be a multiple of 8 for MN-major A");
+    if (a->b_mn ? (a->N % 8) : (a->K % 8)) return fod_fail(FOD_E_ARG, "linear: W inner extent must be a multiple of 8");
     if ((reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(a->w)) & 15)
         return fod_fail(FOD_E_ARG, "linear: x/w must be 16-byte aligned");
-    if (a->ln_gamma && (a->N != 256 || !a->ln_beta || a->relu))
-        return fod_fail(FOD_E_ARG, "linear: LayerNorm epilogue needs N == 256, beta, no relu");
+    if (a->ln_gamma && (a->N != 256 || !a->ln_beta || a->relu || a->split_k > 1 || a->relu_mask))
+        return fod_fail(FOD_E_ARG, "linear: LayerNorm epilogue needs N == 256, beta, no relu/mask/split");
     if (!a->out_bf16 && !a->out_f32) return fod_fail(FOD_E_ARG, "linear: no output");
+    if (a->split_k > 1 && (!a->atomic_out || !a->out_f32 || a->out_bf16 || a->relu || a->bias || a->residual))
+        return fod_fail(FOD_E_ARG, "linear: split_k needs atomic fp32 output and a plain epilogue");
     GemmEpi e;
     e.bias = a->bias;
     e.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual);
+    e.relu_mask = reinterpret_cast<const __nv_bfloat16*>(a->relu_mask);
+    e.col_scale = a->col_scale;
+    e.atomic_out = a->atomic_out;
+    e.kb_per_split = 0;
     e.ln_gamma = a->ln_gamma;
     e.ln_beta = a->ln_beta;
     e.out_bf16 = reinterpret_cast<__nv_bfloat16*>(a->out_bf16);
@@ -325,7 +412,7 @@ extern "C" int fod_linear_fwd(const fod_linear_args* a, void* stream) {
     e.relu = a->relu;
     e.ln_eps = a->ln_eps;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (a->ln_gamma || a->N > 128) return launch_gemm<256>(a, e, st);
-    if (a->N > 64) return launch_gemm<128>(a, e, st);
-    return launch_gemm<64>(a, e, st);
+    if (a->ln_gamma || a->N > 128) return launch_gemm_major<256>(a, e, st);
+    if (a->N > 64) return launch_gemm_major<128>(a, e, st);
+    return launch_gemm_major<64>(a, e, st);
 }

@@ -1,0 +1,218 @@
+// HBM-bound row kernels over 256-channel token rows (one warp per row, 16-byte vector loads, warp-shuffle
+// reductions; grid sized to 148 SMs x 4 CTAs):
+//   fod_add_ln_fwd : y = LayerNorm(x + bcast[row / rows_per_group])   transformer.py:486 (norm_eda), :386 (decoder norm)
+//   fod_ln_bwd     : LayerNorm backward (dz, dgamma, dbeta) for every post-norm block, transformer.py:416-419 etc.
+//   fod_colsum     : per-group column sums (bias gradients, broadcast-operand gradients)
+// Algorithmic bytes per row: fwd 512 B read + 512 B write; bwd 1024 B read + 512 B write (bf16, D = 256).
+#include "fod_internal.h"
+#include "sm100_ptx.cuh"
+
+namespace fod {
+
+constexpr int RO_D = 256;
+constexpr int RO_WARPS = 8;
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float (&f)[8]) {
+    const uint4 u = __ldg(reinterpret_cast<const uint4*>(p));
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float2 t = __bfloat1622float2(h[j]);
+        f[2 * j] = t.x;
+        f[2 * j + 1] = t.y;
+    }
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float (&f)[8]) {
+    uint4 u;
+    u.x = pack_bf16x2(f[0], f[1]);
+    u.y = pack_bf16x2(f[2], f[3]);
+    u.z = pack_bf16x2(f[4], f[5]);
+    u.w = pack_bf16x2(f[6], f[7]);
+    *reinterpret_cast<uint4*>(p) = u;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__global__ void __launch_bounds__(RO_WARPS * 32)
+add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ bcast, int rows_per_group,
+                  const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
+                  float* __restrict__ mean_out, float* __restrict__ rstd_out, long long M, float eps) {
+    const int lane = threadIdx.x & 31;
+    const int c0 = lane * 8;
+    float g[8], bt[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        g[j] = __ldg(gamma + c0 + j);
+        bt[j] = __ldg(beta + c0 + j);
+    }
+    const long long stride = (long long)gridDim.x * RO_WARPS;
+    for (long long row = (long long)blockIdx.x * RO_WARPS + (threadIdx.x >> 5); row < M; row += stride) {
+        float z[8];
+        load8(x + row * RO_D + c0, z);
+        if (bcast) {
+            float o[8];
+            load8(bcast + (row / rows_per_group) * RO_D + c0, o);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) z[j] += o[j];
+        }
+        float s = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += z[j];
+        const float mean = warp_sum(s) * (1.f / RO_D);
+        float q = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float d = z[j] - mean;
+            q += d * d;
+        }
+        const float rstd = rsqrtf(warp_sum(q) * (1.f / RO_D) + eps);
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (z[j] - mean) * rstd * g[j] + bt[j];
+        store8(y + row * RO_D + c0, o);
+        if (lane == 0) {
+            if (mean_out) mean_out[row] = mean;
+            if (rstd_out) rstd_out[row] = rstd;
+        }
+    }
+}
+
+// dz = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma,  xhat = (z - mean) * rstd,
+// z = pre (+ bcast[row / rows_per_group]).  dy may carry a second addend dy2 (two consumers of the LN output).
+__global__ void __launch_bounds__(RO_WARPS * 32)
+ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
+              const __nv_bfloat16* __restrict__ pre, const __nv_bfloat16* __restrict__ bcast, int rows_per_group,
+              const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
+              __nv_bfloat16* __restrict__ dz, float* __restrict__ dgamma, float* __restrict__ dbeta, long long M) {
+    __shared__ float red[2][RO_WARPS][RO_D];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c0 = lane * 8;
+    float g[8], ag[8], ab[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        g[j] = __ldg(gamma + c0 + j);
+        ag[j] = 0.f;
+        ab[j] = 0.f;
+    }
+    const long long stride = (long long)gridDim.x * RO_WARPS;
+    for (long long row = (long long)blockIdx.x * RO_WARPS + warp; row < M; row += stride) {
+        float d[8], z[8];
+        load8(dy + row * RO_D + c0, d);
+        if (dy2) {
+            float e[8];
+            load8(dy2 + row * RO_D + c0, e);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) d[j] += e[j];
+        }
+        load8(pre + row * RO_D + c0, z);
+        if (bcast) {
+            float o[8];
+            load8(bcast + (row / rows_per_group) * RO_D + c0, o);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) z[j] += o[j];
+        }
+        const float mean = mean_in[row], rstd = rstd_in[row];
+        float s1 = 0.f, s2 = 0.f, xh[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            xh[j] = (z[j] - mean) * rstd;
+            const float gj = d[j] * g[j];
+            s1 += gj;
+            s2 += gj * xh[j];
+            ag[j] += d[j] * xh[j];
+            ab[j] += d[j];
+        }
+        s1 = warp_sum(s1) * (1.f / RO_D);
+        s2 = warp_sum(s2) * (1.f / RO_D);
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (d[j] * g[j] - s1 - xh[j] * s2);
+        store8(dz + row * RO_D + c0, o);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        red[0][warp][c0 + j] = ag[j];
+        red[1][warp][c0 + j] = ab[j];
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < RO_D; c += RO_WARPS * 32) {
+        float sg = 0.f, sb = 0.f;
+#pragma unroll
+        for (int w = 0; w < RO_WARPS; ++w) {
+            sg += red[0][w][c];
+            sb += red[1][w][c];
+        }
+        if (dgamma) atomicAdd(dgamma + c, sg);
+        if (dbeta) atomicAdd(dbeta + c, sb);
+    }
+}
+
+// out[g][c] += sum over the rows of group g of x[row][c];  one CTA handles a strip of rows of one group.
+__global__ void __launch_bounds__(256)
+colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, float* __restrict__ out, int N, int rows_per_group,
+              int strips_per_group, int rows_per_strip) {
+    const int g = blockIdx.x / strips_per_group;
+    const int strip = blockIdx.x % strips_per_group;
+    const int r0 = strip * rows_per_strip;
+    const int r1 = min(rows_per_group, r0 + rows_per_strip);
+    for (int c = blockIdx.y * 256 + threadIdx.x; c < N; c += gridDim.y * 256) {
+        float s = 0.f;
+        const __nv_bfloat16* px = x + ((long long)g * rows_per_group + r0) * ldx + c;
+        for (int r = r0; r < r1; ++r, px += ldx) s += __bfloat162float(*px);
+        atomicAdd(out + (long long)g * N + c, s);
+    }
+}
+
+static int ro_grid(long long M) {
+    long long need = (M + RO_WARPS - 1) / RO_WARPS;
+    long long cap = 148 * 4;
+    return (int)(need < cap ? (need < 1 ? 1 : need) : cap);
+}
+
+}  // namespace fod
+
+using namespace fod;
+
+extern "C" int fod_add_ln_fwd(const void* x, const void* bcast, int32_t rows_per_group, const float* gamma,
+                              const float* beta, void* y, float* mean_out, float* rstd_out, int64_t M, float eps,
+                              void* stream) {
+    if (!x || !gamma || !beta || !y || M <= 0) return fod_fail(FOD_E_ARG, "add_ln_fwd: null/empty");
+    if (bcast && rows_per_group <= 0) return fod_fail(FOD_E_ARG, "add_ln_fwd: rows_per_group");
+    add_ln_fwd_kernel<<<ro_grid(M), RO_WARPS * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(bcast), rows_per_group,
+        gamma, beta, reinterpret_cast<__nv_bfloat16*>(y), mean_out, rstd_out, M, eps);
+    return fod_check_launch("add_ln_fwd_kernel");
+}
+
+extern "C" int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bcast, int32_t rows_per_group,
+                          const float* mean, const float* rstd, const float* gamma, void* dz, float* dgamma,
+                          float* dbeta, int64_t M, void* stream) {
+    if (!dy || !pre || !mean || !rstd || !gamma || !dz || M <= 0) return fod_fail(FOD_E_ARG, "ln_bwd: null/empty");
+    if (bcast && rows_per_group <= 0) return fod_fail(FOD_E_ARG, "ln_bwd: rows_per_group");
+    ln_bwd_kernel<<<ro_grid(M), RO_WARPS * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(dy2),
+        reinterpret_cast<const __nv_bfloat16*>(pre), reinterpret_cast<const __nv_bfloat16*>(bcast), rows_per_group, mean,
+        rstd, gamma, reinterpret_cast<__nv_bfloat16*>(dz), dgamma, dbeta, M);
+    return fod_check_launch("ln_bwd_kernel");
+}
+
+extern "C" int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int32_t rows_per_group,
+                          void* stream) {
+    if (!x || !out || M <= 0 || N <= 0) return fod_fail(FOD_E_ARG, "colsum: null/empty");
+    if (rows_per_group <= 0) rows_per_group = (int32_t)M;
+    if (M % rows_per_group) return fod_fail(FOD_E_ARG, "colsum: M must be a multiple of rows_per_group");
+    const int groups = (int)(M / rows_per_group);
+    int strips = (148 * 4 + groups - 1) / groups;
+    const int max_strips = (rows_per_group + 31) / 32;
+    if (strips > max_strips) strips = max_strips;
+    if (strips < 1) strips = 1;
+    const int rows_per_strip = (rows_per_group + strips - 1) / strips;
+    strips = (rows_per_group + rows_per_strip - 1) / rows_per_strip;
+    dim3 grid(groups * strips, (N + 255) / 256);
+    colsum_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), ldx, out, N, rows_per_group, strips, rows_per_strip);
+    return fod_check_launch("colsum_kernel");
+}

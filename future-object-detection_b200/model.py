@@ -1,0 +1,333 @@
+"""Drop-in modules for the reference's hot path, computing on the fod_b200 CUDA kernels.
+
+Module tree, constructor arguments, `state_dict` keys and forward signatures mirror
+  future_od/models/st_detr.py   (SpatioTemporalDETR, SpatioTemporalDETRArgs)
+  future_od/models/paper.py     (PositionalEncoder, CDetrBackbone, SeparateEncoder, CDetrDetectorSpatioTemporal,
+                                 FuturePredCore)
+  future_od/models/transformer.py (MLP, Encoder/Decoder layers and attention blocks)
+so a reference checkpoint loads with `load_state_dict` and `runs/_model.py:build_model` can construct this model
+unchanged (see fod_b200.build_model).  Internally tokens are batch-first (rows = batch*tokens, 256 channels, bf16)
+and every Linear / LayerNorm / attention / loss op is a C-ABI kernel call (autograd.py); torch is used for the
+ResNet body (cuDNN), for weight casts and for a few 128-row element-wise ops in the decoder.
+Dropout is not implemented: the modules behave as the reference does with dropout disabled (eval-mode numerics in
+both train and eval), which is the parity definition of SURVEY.md §8c.
+"""
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import autograd as A
+from . import ops
+
+BF16 = torch.bfloat16
+
+
+def _q(w):
+    """bf16 copy of an fp32 weight for the kernels (no autograd edge; the Function routes the gradient)."""
+    return w.detach().to(BF16).contiguous()
+
+
+def _rows(t):
+    return t.reshape(-1, t.shape[-1])
+
+
+def _xavier_(module):
+    """transformer.py:12-15 — xavier_uniform_ on every parameter with dim > 1 in the subtree."""
+    for p in module.parameters():
+        if p.dim() > 1:
+            nn.init.xavier_uniform_(p)
+
+
+def _lin(x, layer, relu=False, out_f32=False, residual=None, res_row_mod=0):
+    return A.linear(x, layer.weight, layer.bias, _q(layer.weight), residual, res_row_mod, relu, out_f32)
+
+
+def _lin_padded(x, layer, n_pad=64):
+    """Linear with fewer than 8 outputs (class / box / reference-point heads): weight rows zero-padded to n_pad so the
+    tensor-core tile and the MN-major backward apply; fp32 output, sliced back."""
+    n = layer.weight.shape[0]
+    w = F.pad(layer.weight, (0, 0, 0, n_pad - n))
+    b = F.pad(layer.bias, (0, n_pad - n))
+    return A.linear(x, w, b, _q(w), None, 0, False, True)[:, :n]
+
+
+class MLP(nn.Module):
+    """transformer.py:18-32 — Linear/ReLU stack (attribute name `layers`)."""
+
+    def __init__(self, input_dim, hidden_dim, output_dim, num_layers):
+        super().__init__()
+        h = [hidden_dim] * (num_layers - 1)
+        self.num_layers = num_layers
+        self.layers = nn.ModuleList(nn.Linear(n, k) for n, k in zip([input_dim] + h, h + [output_dim]))
+
+    def forward(self, x, out_f32_last=False):
+        for i, layer in enumerate(self.layers):
+            last = i == self.num_layers - 1
+            if last and layer.weight.shape[0] < 8:
+                x = _lin_padded(x, layer)
+            else:
+                x = _lin(x, layer, relu=not last, out_f32=last and out_f32_last)
+        return x
+
+
+# ------------------------------------------------------------------------------------------------ positional encodings
+def _sincos(angles):
+    return torch.stack((angles[..., 0::2].sin(), angles[..., 1::2].cos()), dim=-1).flatten(-2)
+
+
+class PositionalEncoder(nn.Module):
+    """paper.py:32-80.  The 2-D sine encoding is input-independent, so it is built once per (h, w) and cached."""
+
+    def __init__(self, no_temporal=False, temperature=10000.0, extra_temporal_offset=0.0):
+        super().__init__()
+        self.no_temporal = no_temporal
+        self.temperature = temperature
+        self.extra_temporal_offset = extra_temporal_offset
+        self._cache = {}
+
+    def spatial_tokens(self, h, w, c, device):
+        """(h*w, c) fp32: tokens in (h w) order, first c/2 channels encode y (paper.py:57-64, 75-80)."""
+        key = (h, w, c, str(device))
+        if key not in self._cache:
+            half = c // 2
+            ones = torch.ones((h, w), dtype=torch.float32, device=device)
+            ys, xs = ones.cumsum(0), ones.cumsum(1)
+            ys = ys / (ys[-1:, :] + 1e-6) * (2 * math.pi)
+            xs = xs / (xs[:, -1:] + 1e-6) * (2 * math.pi)
+            idx = torch.arange(half, dtype=torch.float32, device=device)
+            dim_t = self.temperature ** (2 * torch.div(idx, 2, rounding_mode="floor") / half)
+            enc = torch.cat((_sincos(ys[..., None] / dim_t), _sincos(xs[..., None] / dim_t)), dim=-1)
+            self._cache[key] = enc.reshape(h * w, c).contiguous()
+        return self._cache[key]
+
+    def temporal_channels(self, offsets, c):
+        """paper.py:66-73 — (B, L, c) sine code of the frame offsets, added to every token of the frame."""
+        idx = torch.arange(c, dtype=torch.float32, device=offsets.device)
+        dim_t = self.temperature ** (2 * torch.div(idx, 2, rounding_mode="floor") / c)
+        ang = (offsets[..., None].float() + self.extra_temporal_offset) * (2 * math.pi) / dim_t
+        return _sincos(ang)
+
+
+def gen_sineembed_for_position(ref_xy, d=256):
+    """transformer.py:35-48 — ref_xy (..., 2) in [0,1] -> (..., d) = [sine(y) ‖ sine(x)]."""
+    half = d // 2
+    idx = torch.arange(half, dtype=torch.float32, device=ref_xy.device)
+    dim_t = 10000 ** (2 * torch.div(idx, 2, rounding_mode="floor") / half)
+    ax = ref_xy[..., 0, None] * (2 * math.pi) / dim_t
+    ay = ref_xy[..., 1, None] * (2 * math.pi) / dim_t
+    return torch.cat((_sincos(ay), _sincos(ax)), dim=-1)
+
+
+def inverse_sigmoid(x, eps=1e-5):
+    """ConditionalDETR/util/misc.py:477-481."""
+    x = x.clamp(0, 1)
+    return torch.log(x.clamp(min=eps) / (1 - x).clamp(min=eps))
+
+
+# ------------------------------------------------------------------------------------------------ backbone (cuDNN)
+class FrozenBatchNorm2d(nn.Module):
+    """ConditionalDETR/models/backbone.py:27-63 — statistics and affine are buffers; eps 1e-5."""
+
+    def __init__(self, n):
+        super().__init__()
+        self.register_buffer("weight", torch.ones(n))
+        self.register_buffer("bias", torch.zeros(n))
+        self.register_buffer("running_mean", torch.zeros(n))
+        self.register_buffer("running_var", torch.ones(n))
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        state_dict.pop(prefix + "num_batches_tracked", None)
+        super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
+
+    def forward(self, x):
+        scale = self.weight * (self.running_var + 1e-5).rsqrt()
+        shift = self.bias - self.running_mean * scale
+        return x * scale.view(1, -1, 1, 1).to(x.dtype) + shift.view(1, -1, 1, 1).to(x.dtype)
+
+
+class CDetrBackbone(nn.Module):
+    """paper.py:83-116.  The ResNet body stays on torch/cuDNN (channels_last, bf16 autocast); the 1x1 `input_proj`
+    is a GEMM over NHWC rows and runs on the tcgen05 kernel, emitting encoder tokens directly."""
+
+    def __init__(self, name, train_backbone, dilation, hidden_dim, pretrained=True):
+        super().__init__()
+        import torchvision
+        from torchvision.models._utils import IntermediateLayerGetter
+
+        if pretrained:
+            raise RuntimeError("pretrained ImageNet weights need network access; load a checkpoint instead")
+        backbone = getattr(torchvision.models, name)(
+            replace_stride_with_dilation=[False, False, dilation], weights=None, norm_layer=FrozenBatchNorm2d)
+        for pname, p in backbone.named_parameters():
+            if not train_backbone or ("layer2" not in pname and "layer3" not in pname and "layer4" not in pname):
+                p.requires_grad_(False)
+        self.body = IntermediateLayerGetter(backbone, return_layers={"layer4": "0"})
+        self.num_channels = 512 if name in ("resnet18", "resnet34") else 2048
+        self.input_proj = nn.Conv2d(self.num_channels, hidden_dim, kernel_size=(1, 1))
+        self.compute_dtype = BF16
+
+    def forward_tokens(self, images):
+        """(N,3,H,W) -> tokens (N*h*w, hidden) bf16 in (n, h, w) row order, plus (h, w)."""
+        x = images.contiguous(memory_format=torch.channels_last)
+        with torch.autocast("cuda", dtype=self.compute_dtype, enabled=self.compute_dtype != torch.float32):
+            f = self.body(x)["0"]
+        n, c, h, w = f.shape
+        rows = f.permute(0, 2, 3, 1).to(BF16).contiguous().view(n * h * w, c)
+        wgt = self.input_proj.weight.view(self.input_proj.weight.shape[0], c)
+        return A.linear(rows, wgt, self.input_proj.bias, _q(wgt)), h, w
+
+    def forward(self, images):
+        t, h, w = self.forward_tokens(images)
+        return t.view(images.shape[0], h, w, -1).permute(0, 3, 1, 2).float()
+
+
+# ------------------------------------------------------------------------------------------------ encoder
+class _InProjMHA(nn.Module):
+    """Parameter holder with torch.nn.MultiheadAttention's names (transformer.py:404): packed in-proj + out_proj."""
+
+    def __init__(self, d, heads):
+        super().__init__()
+        self.embed_dim, self.num_heads = d, heads
+        self.in_proj_weight = nn.Parameter(torch.empty(3 * d, d))
+        self.in_proj_bias = nn.Parameter(torch.zeros(3 * d))
+        self.out_proj = nn.Linear(d, d)
+        nn.init.xavier_uniform_(self.in_proj_weight)
+        nn.init.zeros_(self.out_proj.bias)
+
+
+class EncoderAttention(nn.Module):
+    """transformer.py:401-419: x1 = LN(x + MHA(q=k=x+pos, v=x)); x2 = LN(x1 + W2 relu(W1 x1))."""
+
+    def __init__(self, D, Nhead, Dff, dropout=0.1):
+        super().__init__()
+        self.attn = _InProjMHA(D, Nhead)
+        self.norm1 = nn.LayerNorm(D)
+        self.mlp = nn.Sequential(nn.Linear(D, Dff), nn.ReLU(inplace=True), nn.Dropout(dropout), nn.Linear(Dff, D))
+        self.norm2 = nn.LayerNorm(D)
+        self.heads = Nhead
+
+    def forward(self, x, pos_bf, n_seq, seq_len):
+        """x (n_seq*seq_len, D) bf16; pos_bf (seq_len, D) bf16, shared by every sequence."""
+        w, b = self.attn.in_proj_weight, self.attn.in_proj_bias
+        wq = _q(w)
+        d = w.shape[1]
+        # (x + pos)·Wᵀ = x·Wᵀ + pos·Wᵀ: the positional half is batch-invariant -> a (seq_len, 3D) row-modular residual
+        pqk = A.linear(pos_bf, w[:2 * d], None, wq[:2 * d])
+        res = torch.cat((pqk, pqk.new_zeros(seq_len, d)), dim=1)
+        qkv = A.linear(x, w, b, wq, residual=res, res_row_mod=seq_len)
+        a = A.self_attention(qkv.view(n_seq, seq_len, 3 * d), self.heads, (d // self.heads) ** -0.5)
+        op = self.attn.out_proj
+        x = A.linear_ln(a.view(-1, d), x, op.weight, op.bias, _q(op.weight), self.norm1.weight, self.norm1.bias,
+                        self.norm1.eps)
+        l1, l2 = self.mlp[0], self.mlp[3]
+        return A.ffn_ln(x, l1.weight, l1.bias, _q(l1.weight), l2.weight, l2.bias, _q(l2.weight), self.norm2.weight,
+                        self.norm2.bias, self.norm2.eps)
+
+
+class _OutProjOnly(nn.Module):
+    """ConditionalDETR MultiheadAttention parameters (attention.py:52-172): no in-projection, `out_proj` only."""
+
+    def __init__(self, vdim):
+        super().__init__()
+        self.out_proj = nn.Linear(vdim, vdim)
+
+
+class _ZeroGrad(torch.autograd.Function):
+    """Gives numerically dead parameters an exact zero gradient (what the reference produces with dropout off), so
+    DDP(find_unused_parameters=False) and the 'got no gradient' check of trainer.py:181-185 behave as upstream."""
+
+    @staticmethod
+    def forward(ctx, x, *dead):
+        ctx.shapes = [(p.shape, p.dtype, p.device) for p in dead]
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return (g,) + tuple(torch.zeros(s, dtype=dt, device=dv) for s, dt, dv in ctx.shapes)
+
+
+class EgodeepAttention(nn.Module):
+    """transformer.py:85-119.  With ONE IMU key per sequence the softmax weight is exactly 1, so the block reduces to
+    o = LN2(o1 + mlp(o1)), o1 = LN1(2·out_proj(value(e))) per sequence; query_content / query_pos /
+    key cannot influence the output and receive zero gradients.  With several keys (JointEncoder) the general
+    attention path is used."""
+
+    def __init__(self, D, Nhead, Dff=None, dropout=0.1):
+        super().__init__()
+        self.query_content = nn.Linear(D, D)
+        self.query_pos = nn.Linear(D, D)
+        self.key = nn.Linear(D, D)
+        self.value = nn.Linear(D, D)
+        self.fun = _OutProjOnly(D)
+        self.heads = Nhead
+        self.use_mlp = Dff is not None
+        if self.use_mlp:
+            self.norm1 = nn.LayerNorm(D)
+            self.mlp = nn.Sequential(nn.Linear(D, Dff), nn.ReLU(inplace=True), nn.Dropout(dropout), nn.Linear(Dff, D))
+            self.norm2 = nn.LayerNorm(D)
+
+    def _post(self, o):
+        if not self.use_mlp:
+            return o
+        o = A.add_ln(o * 2, self.norm1.weight, self.norm1.bias, eps=self.norm1.eps)
+        l1, l2 = self.mlp[0], self.mlp[3]
+        return A.ffn_ln(o, l1.weight, l1.bias, _q(l1.weight), l2.weight, l2.bias, _q(l2.weight), self.norm2.weight,
+                        self.norm2.bias, self.norm2.eps)
+
+    def forward_single_key(self, ego):
+        """ego (n_seq, D) bf16 -> per-sequence update vector (n_seq, D) bf16."""
+        o = _lin(_lin(ego, self.value), self.fun.out_proj)
+        o = self._post(o)
+        dead = [p for m in (self.query_content, self.query_pos, self.key) for p in m.parameters() if p.requires_grad]
+        return _ZeroGrad.apply(o, *dead) if dead and torch.is_grad_enabled() else o
+
+    def forward_multi_key(self, x, pos_bf, ego, n_seq, seq_len):
+        """x (n_seq*seq_len, D), ego (n_seq, K, D): attention of every token over K IMU keys (JointEncoder)."""
+        d = x.shape[1]
+        pq = _lin(pos_bf, self.query_pos)
+        q = _lin(x, self.query_content, residual=pq, res_row_mod=seq_len)
+        k = _lin(_rows(ego), self.key).view(n_seq, -1, d)
+        v = _lin(_rows(ego), self.value).view(n_seq, -1, d)
+        qkv_free = A.PlainAttnFn.apply(q.view(n_seq, seq_len, d), k, v, self.heads, (d // self.heads) ** -0.5)
+        o = _lin(qkv_free.view(-1, d), self.fun.out_proj)
+        return self._post(o)
+
+
+class TransformerEncoderLayer(nn.Module):
+    """transformer.py:422-487."""
+
+    def __init__(self, D, Nhead, Dff, dropout=0.1, use_egodeep=False):
+        super().__init__()
+        self.self_attn = EncoderAttention(D, Nhead, Dff, dropout)
+        self.use_egodeep = use_egodeep
+        if use_egodeep:
+            self.egodeep_attend = EgodeepAttention(D, Nhead, Dff, dropout)
+            self.norm_eda = nn.LayerNorm(D)
+
+    def forward(self, x, pos_bf, ego, n_seq, seq_len):
+        x = self.self_attn(x, pos_bf, n_seq, seq_len)
+        if self.use_egodeep and ego is not None:
+            if ego.dim() == 2:
+                o = self.egodeep_attend.forward_single_key(ego)
+                x = A.add_ln(x, self.norm_eda.weight, self.norm_eda.bias, bcast=o, rows_per_group=seq_len,
+                             eps=self.norm_eda.eps)
+            else:
+                o = self.egodeep_attend.forward_multi_key(x, pos_bf, ego, n_seq, seq_len)
+                x = A.add_ln(x + o, self.norm_eda.weight, self.norm_eda.bias, eps=self.norm_eda.eps)
+        return x
+
+
+class TransformerEncoder(nn.Module):
+    """transformer.py:490-512."""
+
+    def __init__(self, layers):
+        super().__init__()
+        self.layers = layers
+        _xavier_(self)
+
+    def forward(self, x, pos_bf, ego, n_seq, seq_len):
+        for layer in self.layers:
+            x = layer(x, pos_bf, ego, n_seq, seq_len)
+        return x

@@ -1,0 +1,300 @@
+"""Raw operator layer: torch CUDA tensors -> C-ABI calls (include/fod_b200.h).  No autograd here (see autograd.py).
+
+Every function enqueues on torch's current stream, allocates its outputs with torch (device memory plumbing only)
+and raises `lib.FodError` on a non-zero status.  `LAUNCH_COUNTS` counts the kernels each call launches so
+bench.py can report `gpu_launches`.
+"""
+import collections
+import ctypes as C
+import math
+
+import torch
+
+from . import lib
+
+LAUNCH_COUNTS = collections.Counter()
+BF16 = torch.bfloat16
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _chk_bf16(t, name):
+    if t.dtype != BF16 or not t.is_cuda:
+        raise lib.FodError(f"{name}: expected a CUDA bf16 tensor, got {t.dtype} on {t.device}")
+
+
+def gemm(x, w, bias=None, residual=None, res_row_mod=0, relu=False, ln=None, out_f32=False, save_ln=False,
+         relu_mask=None, col_scale=None, a_mn=False, b_mn=False, split_k=1, accum_into=None, M=None, N=None, K=None):
+    """Y = epi(op(x) · op(w)ᵀ) on the tcgen05 GEMM.  x (M,K) [or (K,M) if a_mn], w (N,K) [or (K,N) if b_mn].
+
+    Returns y (bf16, or fp32 if out_f32); with ln=(gamma, beta, eps) and save_ln also (pre_ln, mean, rstd).
+    accum_into: fp32 (M,N) tensor that receives atomic adds (split-K weight gradients)."""
+    L = lib.load()
+    _chk_bf16(x, "gemm x")
+    _chk_bf16(w, "gemm w")
+    assert x.dim() == 2 and w.dim() == 2 and x.stride(1) == 1 and w.stride(1) == 1
+    if M is None:
+        M, K = (x.shape[1], x.shape[0]) if a_mn else (x.shape[0], x.shape[1])
+    if N is None:
+        N = w.shape[1] if b_mn else w.shape[0]
+    a = lib.LinearArgs()
+    a.x, a.w = _p(x), _p(w)
+    a.ldx, a.ldw = x.stride(0), w.stride(0)
+    a.M, a.N, a.K = M, N, K
+    a.a_mn, a.b_mn = int(a_mn), int(b_mn)
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.numel() == N
+        a.bias = _p(bias)
+    if residual is not None:
+        _chk_bf16(residual, "gemm residual")
+        assert residual.stride(-1) == 1
+        a.residual, a.ld_res, a.res_row_mod = _p(residual), residual.stride(0), res_row_mod
+    a.relu = int(relu)
+    if relu_mask is not None:
+        _chk_bf16(relu_mask, "gemm relu_mask")
+        assert relu_mask.is_contiguous() and relu_mask.shape == (M, N)
+        a.relu_mask = _p(relu_mask)
+    if col_scale is not None:
+        assert col_scale.dtype == torch.float32 and col_scale.is_contiguous()
+        a.col_scale = _p(col_scale)
+        a.res_row_mod = res_row_mod
+    outs = []
+    if accum_into is not None:
+        assert accum_into.dtype == torch.float32 and accum_into.is_contiguous() and accum_into.shape == (M, N)
+        a.out_f32, a.atomic_out, a.split_k = _p(accum_into), 1, max(1, split_k)
+        y = accum_into
+    elif out_f32:
+        y = torch.empty((M, N), dtype=torch.float32, device=x.device)
+        a.out_f32 = _p(y)
+    else:
+        y = torch.empty((M, N), dtype=BF16, device=x.device)
+        a.out_bf16 = _p(y)
+    a.ld_out = N
+    outs.append(y)
+    if ln is not None:
+        gamma, beta, eps = ln
+        a.ln_gamma, a.ln_beta, a.ln_eps = _p(gamma), _p(beta), eps
+        if save_ln:
+            pre = torch.empty((M, N), dtype=BF16, device=x.device)
+            mean = torch.empty((M,), dtype=torch.float32, device=x.device)
+            rstd = torch.empty((M,), dtype=torch.float32, device=x.device)
+            a.pre_ln_bf16, a.ln_mean, a.ln_rstd = _p(pre), _p(mean), _p(rstd)
+            outs += [pre, mean, rstd]
+    lib.check(L.fod_linear_fwd(C.byref(a), _stream()), "fod_linear_fwd")
+    LAUNCH_COUNTS["gemm_bf16_kernel"] += 1
+    return outs[0] if len(outs) == 1 else tuple(outs)
+
+
+def _seq(t, B):
+    """(ptr, row stride, batch stride) of a (B, L, C) or batch-invariant (L, C) bf16 tensor with unit channel stride."""
+    _chk_bf16(t, "attention operand")
+    assert t.stride(-1) == 1
+    if t.dim() == 2:
+        return _p(t), t.stride(0), 0
+    assert t.dim() == 3 and t.shape[0] in (1, B)
+    return _p(t), t.stride(1), (t.stride(0) if t.shape[0] == B and B > 1 else 0)
+
+
+def _fill_attn(a, q1, k1, v, q2, k2, out, lse, scale, heads):
+    B, Lq = out.shape[0], out.shape[1]
+    Lk = v.shape[-2]
+    a.q1, a.ldq1, a.bsq1 = _seq(q1, B)
+    a.k1, a.ldk1, a.bsk1 = _seq(k1, B)
+    a.v, a.ldv, a.bsv = _seq(v, B)
+    if q2 is not None:
+        a.q2, a.ldq2, a.bsq2 = _seq(q2, B)
+        a.k2, a.ldk2, a.bsk2 = _seq(k2, B)
+    a.out, a.ldo, a.bso = _p(out), out.stride(1), out.stride(0)
+    a.lse = _p(lse)
+    a.B, a.H, a.Lq, a.Lk, a.scale = B, heads, Lq, Lk, scale
+
+
+def attn_fwd(q1, k1, v, scale, heads=8, q2=None, k2=None, batch=None):
+    """Flash attention forward.  Operands (B, L, heads*32) bf16 (row-strided views allowed) or (L, heads*32) when
+    batch-invariant.  Returns out (B, Lq, heads*32) bf16 and lse (B, heads, Lq) fp32."""
+    L = lib.load()
+    B = batch if batch is not None else max(t.shape[0] for t in (q1, k1, v) if t.dim() == 3)
+    Lq = q1.shape[-2]
+    out = torch.empty((B, Lq, heads * 32), dtype=BF16, device=v.device)
+    lse = torch.empty((B, heads, Lq), dtype=torch.float32, device=v.device)
+    a = lib.AttnArgs()
+    _fill_attn(a, q1, k1, v, q2, k2, out, lse, scale, heads)
+    lib.check(L.fod_attn_fwd(C.byref(a), _stream()), "fod_attn_fwd")
+    LAUNCH_COUNTS["attn_fwd_kernel"] += 1
+    return out, lse
+
+
+def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=None):
+    """Flash attention backward -> (dq1, dk1, dv, dq2, dk2), (B, L, heads*32) bf16 (dq2/dk2 None if unused).
+
+    fused="qkv": dq1/dk1/dv are column slices of ONE (B, L, 3*heads*32) tensor (self-attention on a fused projection);
+    fused="kv": dk1/dv are slices of one (B, Lk, 2*heads*32) tensor.  The kernels write the slices in place."""
+    L = lib.load()
+    B, Lq = out.shape[0], out.shape[1]
+    Lk = v.shape[-2]
+    dev = out.device
+    g = lib.AttnBwdArgs()
+    _fill_attn(g.fwd, q1, k1, v, q2, k2, out, lse, scale, heads)
+    _chk_bf16(dout, "attn dout")
+    assert dout.shape == out.shape and dout.stride(-1) == 1
+    g.dout, g.lddo, g.bsdo = _p(dout), dout.stride(1), dout.stride(0)
+    delta = torch.empty((B, heads, Lq), dtype=torch.float32, device=dev)
+    Cw = heads * 32
+    if fused == "qkv":
+        assert Lq == Lk
+        whole = torch.empty((B, Lq, 3 * Cw), dtype=BF16, device=dev)
+        dq1, dk1, dv = whole[..., :Cw], whole[..., Cw:2 * Cw], whole[..., 2 * Cw:]
+        g.ld_dq = g.ld_dk = 3 * Cw
+    elif fused == "kv":
+        dq1 = torch.empty((B, Lq, Cw), dtype=BF16, device=dev)
+        whole = torch.empty((B, Lk, 2 * Cw), dtype=BF16, device=dev)
+        dk1, dv = whole[..., :Cw], whole[..., Cw:]
+        g.ld_dk = 2 * Cw
+    else:
+        dq1 = torch.empty((B, Lq, Cw), dtype=BF16, device=dev)
+        dk1 = torch.empty((B, Lk, Cw), dtype=BF16, device=dev)
+        dv = torch.empty((B, Lk, Cw), dtype=BF16, device=dev)
+    dq2 = dk2 = None
+    g.delta, g.dq1, g.dk1, g.dv = _p(delta), _p(dq1), _p(dk1), _p(dv)
+    if q2 is not None:
+        dq2 = torch.empty((B, Lq, Cw), dtype=BF16, device=dev)
+        dk2 = torch.empty((B, Lk, Cw), dtype=BF16, device=dev)
+        g.dq2, g.dk2 = _p(dq2), _p(dk2)
+    lib.check(L.fod_attn_bwd(C.byref(g), _stream()), "fod_attn_bwd")
+    LAUNCH_COUNTS["attn_delta_kernel"] += 1
+    LAUNCH_COUNTS["attn_bwd_dq_kernel"] += 1
+    LAUNCH_COUNTS["attn_bwd_dkdv_kernel"] += 1
+    return dq1, dk1, dv, dq2, dk2
+
+
+def add_ln_fwd(x, gamma, beta, eps=1e-5, bcast=None, rows_per_group=0, save=False):
+    """y = LayerNorm(x + bcast[row // rows_per_group]); x (M,256) bf16.  save -> also (mean, rstd)."""
+    L = lib.load()
+    _chk_bf16(x, "add_ln x")
+    assert x.is_contiguous() and x.shape[-1] == 256
+    M = x.numel() // 256
+    y = torch.empty_like(x)
+    mean = rstd = None
+    if save:
+        mean = torch.empty((M,), dtype=torch.float32, device=x.device)
+        rstd = torch.empty((M,), dtype=torch.float32, device=x.device)
+    if bcast is not None:
+        _chk_bf16(bcast, "add_ln bcast")
+        assert bcast.is_contiguous() and bcast.numel() * rows_per_group == x.numel()
+    lib.check(L.fod_add_ln_fwd(_p(x), _p(bcast), rows_per_group, _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), M,
+                               eps, _stream()), "fod_add_ln_fwd")
+    LAUNCH_COUNTS["add_ln_fwd_kernel"] += 1
+    return (y, mean, rstd) if save else y
+
+
+def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows_per_group=0):
+    """LayerNorm backward: returns dz (bf16); accumulates into fp32 dgamma / dbeta (256,)."""
+    L = lib.load()
+    _chk_bf16(dy, "ln_bwd dy")
+    _chk_bf16(pre, "ln_bwd pre")
+    assert dy.is_contiguous() and pre.is_contiguous() and pre.shape[-1] == 256
+    M = pre.numel() // 256
+    dz = torch.empty_like(pre)
+    lib.check(L.fod_ln_bwd(_p(dy), _p(dy2), _p(pre), _p(bcast), rows_per_group, _p(mean), _p(rstd), _p(gamma), _p(dz),
+                           _p(dgamma), _p(dbeta), M, _stream()), "fod_ln_bwd")
+    LAUNCH_COUNTS["ln_bwd_kernel"] += 1
+    return dz
+
+
+def colsum(x, rows_per_group=0, out=None):
+    """out[g, c] (+)= sum over rows of group g of x[row, c]; x (M,N) bf16, unit column stride."""
+    L = lib.load()
+    _chk_bf16(x, "colsum x")
+    assert x.dim() == 2 and x.stride(1) == 1
+    M, N = x.shape
+    rpg = rows_per_group or M
+    if out is None:
+        out = torch.zeros((M // rpg, N), dtype=torch.float32, device=x.device)
+    lib.check(L.fod_colsum(_p(x), x.stride(0), _p(out), M, N, rpg, _stream()), "fod_colsum")
+    LAUNCH_COUNTS["colsum_kernel"] += 1
+    return out
+
+
+def targets_compact(boxes_xyxy, classes, active, height, width):
+    """st_detr.py:237-263 on the device: returns (tgt_boxes (B,slots,4) cxcywh, tgt_labels int32, tgt_count int32,
+    total_count fp32 scalar tensor)."""
+    L = lib.load()
+    B, slots = active.shape
+    dev = boxes_xyxy.device
+    boxes_xyxy = boxes_xyxy.contiguous().float()
+    classes = classes.contiguous().long()
+    active = active.contiguous().long()
+    ob = torch.zeros((B, slots, 4), dtype=torch.float32, device=dev)
+    ol = torch.zeros((B, slots), dtype=torch.int32, device=dev)
+    oc = torch.empty((B,), dtype=torch.int32, device=dev)
+    tot = torch.zeros((1,), dtype=torch.float32, device=dev)
+    inv_w = float(torch.tensor(1 / width, dtype=torch.float32))
+    inv_h = float(torch.tensor(1 / height, dtype=torch.float32))
+    lib.check(L.fod_targets_compact(_p(boxes_xyxy), _p(classes), _p(active), _p(ob), _p(ol), _p(oc), _p(tot), B, slots,
+                                    inv_w, inv_h, _stream()), "fod_targets_compact")
+    LAUNCH_COUNTS["targets_compact_kernel"] += 1
+    return ob, ol, oc, tot
+
+
+def match(logits, boxes, tgt_boxes, tgt_labels, tgt_count, w_class=2.0, w_bbox=5.0, w_giou=2.0, alpha=0.25,
+          want_lists=True, want_cost=False, status=None):
+    """All-level Hungarian matching (matcher.py:40-87).  logits (L,B,M,C) fp32, boxes (L,B,M,4) fp32.
+
+    Returns dict(match_tgt (L,B,M) int32, pred_idx/tgt_idx (L,B,KMAX) int64 padded with -1, status (1,) int32, cost)."""
+    Lb = lib.load()
+    logits = logits.contiguous().float()
+    boxes = boxes.contiguous().float()
+    Lv, B, M, Cn = logits.shape
+    NT = tgt_boxes.shape[1]
+    dev = logits.device
+    kmax = min(M, NT)
+    out = {"match_tgt": torch.empty((Lv, B, M), dtype=torch.int32, device=dev),
+           "status": status if status is not None else torch.zeros((1,), dtype=torch.int32, device=dev)}
+    a = lib.MatchArgs()
+    a.logits, a.boxes, a.tgt_boxes, a.tgt_labels, a.tgt_count = _p(logits), _p(boxes), _p(tgt_boxes), _p(tgt_labels), _p(tgt_count)
+    a.match_tgt, a.status = _p(out["match_tgt"]), _p(out["status"])
+    if want_lists:
+        out["pred_idx"] = torch.empty((Lv, B, kmax), dtype=torch.int64, device=dev)
+        out["tgt_idx"] = torch.empty((Lv, B, kmax), dtype=torch.int64, device=dev)
+        a.pred_idx, a.tgt_idx = _p(out["pred_idx"]), _p(out["tgt_idx"])
+    if want_cost:
+        out["cost"] = torch.zeros((Lv, B, M, NT), dtype=torch.float32, device=dev)
+        a.cost_out = _p(out["cost"])
+    if M * NT * 4 + 24 * (M + NT) + M * Cn * 4 + 64 > 200 * 1024:
+        out["_ws"] = torch.empty((Lv, B, M, NT), dtype=torch.float32, device=dev)
+        a.cost_ws = _p(out["_ws"])
+    a.L, a.B, a.M, a.C, a.NT = Lv, B, M, Cn, NT
+    a.w_class, a.w_bbox, a.w_giou, a.alpha = w_class, w_bbox, w_giou, alpha
+    lib.check(Lb.fod_match(C.byref(a), _stream()), "fod_match")
+    LAUNCH_COUNTS["match_kernel"] += 1
+    return out
+
+
+def set_loss(logits, boxes, match_tgt, tgt_boxes, tgt_labels, tgt_count, num_boxes, w_ce=2.0, w_bbox=5.0, w_giou=2.0,
+             alpha=0.25, want_grads=True):
+    """Losses + their gradients (set_criterion.py:36-115).  Returns (out (8+3L,) fp32, dlogits, dboxes)."""
+    Lb = lib.load()
+    logits = logits.contiguous().float()
+    boxes = boxes.contiguous().float()
+    Lv, B, M, Cn = logits.shape
+    dev = logits.device
+    out = torch.zeros((8 + 3 * Lv,), dtype=torch.float32, device=dev)
+    partial = torch.empty((Lv, B, 8), dtype=torch.float32, device=dev)
+    dl = torch.empty_like(logits) if want_grads else None
+    db = torch.empty_like(boxes) if want_grads else None
+    a = lib.SetLossArgs()
+    a.logits, a.boxes, a.match_tgt = _p(logits), _p(boxes), _p(match_tgt)
+    a.tgt_boxes, a.tgt_labels, a.tgt_count, a.num_boxes = _p(tgt_boxes), _p(tgt_labels), _p(tgt_count), _p(num_boxes)
+    a.dlogits, a.dboxes, a.partial, a.out = _p(dl), _p(db), _p(partial), _p(out)
+    a.L, a.B, a.M, a.C, a.NT, a.main_level = Lv, B, M, Cn, tgt_boxes.shape[1], Lv - 1
+    a.w_ce, a.w_bbox, a.w_giou, a.alpha = w_ce, w_bbox, w_giou, alpha
+    lib.check(Lb.fod_set_loss(C.byref(a), _stream()), "fod_set_loss")
+    LAUNCH_COUNTS["set_loss_kernel"] += 1
+    LAUNCH_COUNTS["set_loss_finalize_kernel"] += 1
+    return out, dl, db

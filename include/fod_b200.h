@@ -53,8 +53,16 @@ typedef struct fod_linear_args {
     int32_t res_row_mod;    /* 0: residual row = row; >0: row % res_row_mod (batch-invariant positional term) */
     int32_t relu;
     float ln_eps;
+    /* --- backward / general-GEMM extensions (zero = forward defaults) --- */
+    const void* relu_mask;  /* bf16 (M,N), ld_out: output zeroed where mask <= 0 (ReLU backward, transformer.py:408) */
+    const float* col_scale; /* fp32 (res_row_mod or M, N): y = (acc + bias) * col_scale  (query_scale ⊙ sine, :366) */
+    int64_t ldw;            /* row stride of w; 0 = contiguous */
+    int32_t a_mn;           /* 1: x is stored (K, M) row-major (contraction outermost) — dW = dYᵀ·X */
+    int32_t b_mn;           /* 1: w is stored (K, N) row-major — dX = dY·W with W in its nn.Linear layout */
+    int32_t split_k;        /* >1: split the contraction over grid.z; needs atomic_out */
+    int32_t atomic_out;     /* 1: out_f32 += result (atomic adds into a caller-initialised buffer) */
 } fod_linear_args;
-int fod_linear_fwd(const fod_linear_args* a, void* stream);
+int fod_linear_fwd(const fod_linear_args* a, void* stream);  /* also the backward GEMMs via a_mn / b_mn */
 
 /* ------------------------------------------------------------------------------------------------
  * Flash attention forward (TMA + tcgen05/TMEM, online softmax), multi-head, no mask:
@@ -81,6 +89,99 @@ typedef struct fod_attn_args {
     float scale;
 } fod_attn_args;
 int fod_attn_fwd(const fod_attn_args* a, void* stream);
+
+
+/* Flash attention backward (same layouts as fod_attn_fwd; recomputes S and dP on the tensor cores):
+ *   delta = rowsum(dO ⊙ O) (written to `delta`, (B,H,Lq) fp32 workspace), then
+ *   dQ_p = scale·(P ⊙ (dP − delta))·K_p,  dK_p = scale·(P ⊙ (dP − delta))ᵀ·Q_p,  dV = Pᵀ·dO.
+ * Gradients are dense bf16: dq1/dq2 (B,Lq,H*32), dk1/dk2/dv (B,Lk,H*32) — a batch-broadcast K part (bsk2 == 0)
+ * still gets a per-batch dk2 that the caller sums.  Backward of ConditionalDETR/models/attention.py:350-372 and of
+ * torch.nn.MultiheadAttention's core (future_od/models/transformer.py:404,417).
+ */
+typedef struct fod_attn_bwd_args {
+    fod_attn_args fwd;   /* the forward call's arguments: q/k/v, out (= O), lse, strides, scale */
+    const void* dout;    /* (B,Lq,H*32) bf16 */
+    int64_t lddo, bsdo;
+    float* delta;        /* (B,H,Lq) fp32 workspace/output */
+    void *dq1, *dq2, *dk1, *dk2, *dv;
+    int64_t ld_dq;       /* row stride of dq1 (0 = H*32); batch stride = Lq*ld_dq.  dq2 is always dense */
+    int64_t ld_dk;       /* row stride of dk1 and dv (0 = H*32); batch stride = Lk*ld_dk.  dk2 is always dense */
+} fod_attn_bwd_args;
+int fod_attn_bwd(const fod_attn_bwd_args* a, void* stream);
+
+/* Row kernels over 256-channel rows (HBM-bound):
+ *   fod_add_ln_fwd: y = LayerNorm(x + bcast[row / rows_per_group]) — norm_eda over the broadcast egodeep vector
+ *     (future_od/models/transformer.py:479-486) and the decoder's per-level norm (:386-387; bcast = NULL).
+ *   fod_ln_bwd: dz, dgamma += , dbeta += for z = pre (+ bcast[row / rows_per_group]); dy2 is an optional second
+ *     addend of the incoming gradient.  Backward of every nn.LayerNorm on the path.
+ *   fod_colsum: out[g][c] += sum_{rows of group g} x[row][c] (bias and broadcast-operand gradients).
+ */
+int fod_add_ln_fwd(const void* x, const void* bcast, int32_t rows_per_group, const float* gamma, const float* beta,
+                   void* y, float* mean_out, float* rstd_out, int64_t M, float eps, void* stream);
+int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bcast, int32_t rows_per_group,
+               const float* mean, const float* rstd, const float* gamma, void* dz, float* dgamma, float* dbeta,
+               int64_t M, void* stream);
+int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int32_t rows_per_group, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Set-prediction loss path (north-star piece 4).  Levels are the decoder levels (main output = level L-1).
+ *
+ * fod_targets_compact — replaces to_detr_targets (future_od/models/st_detr.py:237-263): dense 256-slot xyxy-pixel
+ *   annotations -> per-sample compacted cxcywh boxes normalised by (W,H), labels and counts; no host sync.
+ *   inv_w / inv_h are float32(1/W), float32(1/H) as the reference builds them.  total_count (optional, device
+ *   float, must be zeroed by the caller) accumulates sum(Nt) for num_boxes (set_criterion.py:185-193).
+ */
+int fod_targets_compact(const float* boxes_xyxy /*(B,slots,4)*/, const int64_t* classes /*(B,slots)*/,
+                        const int64_t* active /*(B,slots)*/, float* out_boxes /*(B,slots,4)*/,
+                        int32_t* out_labels /*(B,slots)*/, int32_t* out_count /*(B)*/, float* total_count,
+                        int32_t B, int32_t slots, float inv_w, float inv_h, void* stream);
+
+/* fod_match — replaces HungarianMatcher.forward (ConditionalDETR/models/matcher.py:40-87), generalized_box_iou /
+ *   box_cxcywh_to_xyxy (ConditionalDETR/util/box_ops.py:17-69) and scipy.optimize.linear_sum_assignment
+ *   (matcher.py:86) for all L levels and B samples in one launch.  Only the per-sample diagonal blocks are built.
+ *   match_tgt[l,b,q] = matched target index or -1.  pred_idx/tgt_idx (optional) are the reference's index lists
+ *   (prediction indices ascending), padded with -1 to KMAX = min(M,NT).  *status is OR'd with
+ *   1 (NaN/-inf cost: scipy's ValueError), 2 (degenerate box: the assert at box_ops.py:59-60), 4 (infeasible).
+ */
+typedef struct fod_match_args {
+    const float* logits;       /* (L,B,M,C) */
+    const float* boxes;        /* (L,B,M,4) cxcywh in [0,1] */
+    const float* tgt_boxes;    /* (B,NT,4) compacted */
+    const int32_t* tgt_labels; /* (B,NT) */
+    const int32_t* tgt_count;  /* (B) */
+    int32_t* match_tgt;        /* (L,B,M) out */
+    int64_t* pred_idx;         /* (L,B,KMAX) out or NULL */
+    int64_t* tgt_idx;          /* (L,B,KMAX) out or NULL */
+    int32_t* status;           /* (1) device flag word, caller zeroes */
+    float* cost_out;           /* (L,B,M,NT) optional copy of the fp32 cost blocks (tests) */
+    float* cost_ws;            /* (L,B,M,NT) workspace, needed only when M*NT*4 + bookkeeping > 200 KB */
+    int32_t L, B, M, C, NT;
+    float w_class, w_bbox, w_giou, alpha;
+} fod_match_args;
+int fod_match(const fod_match_args* a, void* stream);
+
+/* fod_set_loss — replaces SetCriterion.loss_labels/loss_boxes/loss_cardinality (future_od/models/set_criterion.py:
+ *   36-115), sigmoid_focal_loss (ConditionalDETR/models/segmentation.py:198-223), accuracy (util/misc.py:439-455) and
+ *   the weighting of st_detr.py:169-188, forward AND backward: dlogits/dboxes are d(total)/d(input).
+ *   out[0] total; out[1..5] = labels, box_l1, box_giou, cardinality, class_error; out[8+3l..] per-level
+ *   unweighted loss_ce, loss_bbox, loss_giou.  out needs 8+3L floats, partial L*B*8 floats.
+ */
+typedef struct fod_set_loss_args {
+    const float* logits;
+    const float* boxes;
+    const int32_t* match_tgt;
+    const float* tgt_boxes;
+    const int32_t* tgt_labels;
+    const int32_t* tgt_count;
+    const float* num_boxes;    /* device scalar: clamp(sum Nt over ranks / world, 1) */
+    float* dlogits;            /* (L,B,M,C) or NULL */
+    float* dboxes;             /* (L,B,M,4) or NULL */
+    float* partial;            /* (L,B,8) workspace */
+    float* out;                /* (8+3L) */
+    int32_t L, B, M, C, NT, main_level;
+    float w_ce, w_bbox, w_giou, alpha;
+} fod_set_loss_args;
+int fod_set_loss(const fod_set_loss_args* a, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,146 @@
+"""GPU parity of the set-prediction loss path (north-star piece 4) against the CPU oracle:
+matcher assignments BIT-EXACT (identical fp32 inputs), costs within 1e-5, losses/gradients within 1e-4."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import fod_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _case(seed, bsz, m=128, c=8, nts=None, levels=1, dup=False):
+    g = torch.Generator().manual_seed(seed)
+    logits = torch.randn(levels, bsz, m, c, generator=g) * 2 - 2
+    boxes = torch.cat((torch.rand(levels, bsz, m, 2, generator=g), torch.rand(levels, bsz, m, 2, generator=g) * 0.5 + 0.01), -1)
+    nts = nts if nts is not None else [int(torch.randint(0, 40, (1,), generator=g)) for _ in range(bsz)]
+    targets = []
+    for n in nts:
+        tb = torch.cat((torch.rand(n, 2, generator=g), torch.rand(n, 2, generator=g) * 0.4 + 0.01), -1)
+        tl = torch.randint(0, c, (n,), generator=g)
+        if dup and n >= 4:
+            tb[1], tl[1] = tb[0], tl[0]
+            tb[3], tl[3] = tb[2], tl[2]
+        targets.append({"boxes": tb, "labels": tl})
+    if dup:
+        boxes[:, :, 5], logits[:, :, 5] = boxes[:, :, 4], logits[:, :, 4]
+    return logits, boxes, targets
+
+
+def _pack(targets, nt_cap):
+    bsz = len(targets)
+    tb = torch.zeros(bsz, nt_cap, 4)
+    tl = torch.zeros(bsz, nt_cap, dtype=torch.int32)
+    for i, t in enumerate(targets):
+        n = len(t["labels"])
+        tb[i, :n], tl[i, :n] = t["boxes"], t["labels"].int()
+    cnt = torch.tensor([len(t["labels"]) for t in targets], dtype=torch.int32)
+    return tb.to(DEV), tl.to(DEV), cnt.to(DEV)
+
+
+def _check_match(logits, boxes, targets, nt_cap):
+    from fod_b200 import ops
+    tb, tl, cnt = _pack(targets, nt_cap)
+    r = ops.match(logits.to(DEV), boxes.to(DEV), tb, tl, cnt, want_cost=True)
+    assert int(r["status"].item()) == 0
+    pi, ti, cost = r["pred_idx"].cpu(), r["tgt_idx"].cpu(), r["cost"].cpu()
+    for lv in range(logits.shape[0]):
+        ref = O.hungarian_match(logits[lv], boxes[lv], targets)
+        for b, (ri, rj) in enumerate(ref):
+            n = len(targets[b]["labels"])
+            got_i, got_j = pi[lv, b][pi[lv, b] >= 0], ti[lv, b][ti[lv, b] >= 0]
+            if n:
+                c_ref = O.matcher_cost(logits[lv, b], boxes[lv, b], targets[b]["labels"], targets[b]["boxes"])
+                assert float((cost[lv, b, :, :n] - c_ref).abs().max()) < 1e-5
+            assert torch.equal(got_i, ri) and torch.equal(got_j, rj), (lv, b, n)
+            mt = r["match_tgt"][lv, b].cpu()
+            assert int((mt >= 0).sum()) == len(ri) and torch.equal(mt[ri].long(), rj)
+
+
+def test_matcher_bit_exact_random():
+    for seed in range(40):
+        logits, boxes, targets = _case(seed, bsz=4, levels=2)
+        _check_match(logits, boxes, targets, 40)
+
+
+@pytest.mark.parametrize("nts", [[0, 1, 2], [128, 127], [129, 256], [200, 0, 64]])
+def test_matcher_edge_sizes(nts):
+    logits, boxes, targets = _case(100 + sum(nts), bsz=len(nts), nts=nts)
+    _check_match(logits, boxes, targets, 256)
+
+
+def test_matcher_ties_follow_scipy_scan_order():
+    for seed in range(10):
+        logits, boxes, targets = _case(200 + seed, bsz=3, nts=[6, 12, 30], dup=True)
+        _check_match(logits, boxes, targets, 32)
+
+
+def test_matcher_in_kernel_solver_on_exact_cost_matrices():
+    """Feed integer-valued / constant costs through a crafted input so ties dominate: all-equal boxes and logits."""
+    bsz, m, c = 2, 128, 8
+    logits = torch.zeros(1, bsz, m, c)
+    boxes = torch.full((1, bsz, m, 4), 0.25)
+    targets = [{"boxes": torch.full((7, 4), 0.25), "labels": torch.zeros(7, dtype=torch.int64)},
+               {"boxes": torch.full((3, 4), 0.25), "labels": torch.ones(3, dtype=torch.int64)}]
+    _check_match(logits, boxes, targets, 8)
+
+
+def test_matcher_status_flags():
+    from fod_b200 import ops
+    from fod_b200.st_detr import check_match_status
+    logits, boxes, targets = _case(7, bsz=2, nts=[5, 5])
+    logits[0, 1, 3, 2] = float("nan")
+    tb, tl, cnt = _pack(targets, 8)
+    r = ops.match(logits.to(DEV), boxes.to(DEV), tb, tl, cnt)
+    assert int(r["status"].item()) & 1
+    with pytest.raises(ValueError):
+        check_match_status(r["status"])
+    logits, boxes, targets = _case(8, bsz=2, nts=[5, 5])
+    targets[0]["boxes"][2, 2] = -0.1  # negative width -> x1 < x0
+    tb, tl, cnt = _pack(targets, 8)
+    r = ops.match(logits.to(DEV), boxes.to(DEV), tb, tl, cnt)
+    with pytest.raises(AssertionError):
+        check_match_status(r["status"])
+
+
+def test_targets_compact_matches_reference_layout():
+    from fod_b200 import ops
+    from fod_b200.synthetic import make_clip
+    data = make_clip(5, 3, 448, 800, seed=11)
+    data["active"][1, 3] = 0  # a hole: compaction must preserve order
+    ref = O.to_detr_targets(448, 800, data["active"], data["boxes"], data["classes"])
+    tb, tl, tc, tot = ops.targets_compact(data["boxes"].to(DEV), data["classes"].to(DEV), data["active"].to(DEV), 448, 800)
+    assert int(tot.item()) == sum(len(t["labels"]) for t in ref)
+    for b, t in enumerate(ref):
+        n = len(t["labels"])
+        assert int(tc[b]) == n
+        assert torch.equal(tb[b, :n].cpu(), t["boxes"]) and torch.equal(tl[b, :n].cpu().long(), t["labels"])
+
+
+@pytest.mark.parametrize("seed,nts", [(1, None), (2, [0, 0, 0]), (3, [1, 130, 17])])
+def test_set_loss_and_gradients_match_oracle(seed, nts):
+    from fod_b200 import autograd as A
+    levels, bsz = 6, 3
+    logits, boxes, targets = _case(seed, bsz=bsz, nts=nts, levels=levels)
+    cap = 256 if nts and max(nts) > 40 else 40
+    tb, tl, cnt = _pack(targets, cap)
+    # oracle: criterion() expects main output + aux list; main level is the LAST one
+    lo = logits.clone().requires_grad_(True)
+    bo = boxes.clone().requires_grad_(True)
+    out = {"pred_logits": lo[-1], "pred_boxes": bo[-1],
+           "aux_outputs": [{"pred_logits": lo[i], "pred_boxes": bo[i]} for i in range(levels - 1)]}
+    loss_ref, stats_ref, _ = O.criterion(out, targets)
+    loss_ref.backward()
+    lg = logits.to(DEV).requires_grad_(True)
+    bg = boxes.to(DEV).requires_grad_(True)
+    nb = torch.tensor([max(1.0, float(sum(len(t["labels"]) for t in targets)))], device=DEV)
+    status = torch.zeros(1, dtype=torch.int32, device=DEV)
+    res, _ = A.SetLossFn.apply(lg, bg, tb, tl, cnt, nb, (2.0, 5.0, 2.0, 2.0, 5.0, 2.0, 0.25), status)
+    res[0].backward()
+    rel = lambda a, b: float((a.cpu() - b).abs().max() / max(1.0, float(b.abs().max())))
+    assert rel(res[0].detach(), loss_ref.detach()) < 1e-4
+    for i, k in enumerate(["labels", "box_l1", "box_giou", "cardinality", "class_error"]):
+        assert rel(res[1 + i].detach(), stats_ref[k].detach()) < 1e-4, k
+    assert rel(lg.grad, lo.grad) < 1e-4 and float((lg.grad.cpu() - lo.grad).abs().max()) < 1e-5
+    assert rel(bg.grad, bo.grad) < 1e-4 and float((bg.grad.cpu() - bo.grad).abs().max()) < 1e-4

@@ -1,0 +1,171 @@
+"""GPU parity of the individual C-ABI kernels (through fod_b200.ops -> ctypes -> libfod_b200.so) against plain
+torch fp32 references on the same bf16-rounded inputs.  Tolerances: bf16 outputs 2e-2 relative to max|ref|
+(north star), fp32 statistics 1e-3."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+BF = torch.bfloat16
+
+
+def _dev():
+    return torch.device("cuda:0")
+
+
+def _rnd(*shape, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed + sum(shape))
+    return (torch.randn(*shape, generator=g) * scale).to(BF).to(_dev())
+
+
+def _close(a, b, tol=2e-2, what=""):
+    a, b = a.float(), b.float()
+    err = float((a - b).abs().max() / max(1e-6, float(b.abs().max())))
+    assert err < tol, f"{what}: rel err {err:.4g} >= {tol}"
+    return err
+
+
+@pytest.mark.parametrize("M,N,K", [(5600, 768, 256), (300, 256, 2048), (1024, 64, 256), (77, 2048, 256), (16, 256, 256)])
+def test_gemm_forward_epilogues(M, N, K):
+    from fod_b200 import ops
+    x, w = _rnd(M, K), _rnd(N, K, scale=0.06)
+    b = torch.randn(N, device=_dev())
+    ref = x.float() @ w.float().t() + b
+    _close(ops.gemm(x, w, bias=b), ref, what="bias")
+    _close(ops.gemm(x, w, bias=b, relu=True), ref.relu(), what="relu")
+    _close(ops.gemm(x, w, bias=b, out_f32=True), ref, tol=5e-3, what="f32 out")
+    mod = 50 if M % 50 == 0 else 0
+    res = _rnd(mod or M, N, seed=3)
+    rr = res.float().repeat(M // mod, 1) if mod else res.float()
+    _close(ops.gemm(x, w, bias=b, residual=res, res_row_mod=mod), ref + rr, what="residual")
+    if N == 256:
+        gam, bet = torch.rand(N, device=_dev()) + 0.5, torch.randn(N, device=_dev())
+        y, pre, mean, rstd = ops.gemm(x, w, bias=b, residual=res, res_row_mod=mod, ln=(gam, bet, 1e-5), save_ln=True)
+        z = ref + rr
+        _close(y, torch.nn.functional.layer_norm(z, (N,), gam, bet, 1e-5), what="ln")
+        _close(pre, z, what="pre_ln")
+        _close(mean, z.mean(1), tol=1e-2, what="mean")
+        _close(rstd, (z.var(1, unbiased=False) + 1e-5).rsqrt(), tol=1e-2, what="rstd")
+
+
+@pytest.mark.parametrize("M,N,K", [(5600, 2048, 256), (5600, 256, 2048), (1000, 768, 256), (130, 64, 256), (16, 256, 256)])
+def test_gemm_backward_forms(M, N, K):
+    """dX = dY·W (B operand MN-major) with ReLU-mask / residual epilogues; dW = dYᵀ·X (both MN-major, split-K atomics)."""
+    from fod_b200 import autograd as A
+    from fod_b200 import ops
+    dy, w, x = _rnd(M, N, seed=1), _rnd(N, K, scale=0.06, seed=2), _rnd(M, K, seed=3)
+    ref_dx = dy.float() @ w.float()
+    _close(ops.gemm(dy, w, b_mn=True), ref_dx, what="dX")
+    mask, res = _rnd(M, K, seed=4), _rnd(M, K, seed=5)
+    _close(ops.gemm(dy, w, b_mn=True, relu_mask=mask), ref_dx * (mask.float() > 0), what="dX relu mask")
+    _close(ops.gemm(dy, w, b_mn=True, residual=res), ref_dx + res.float(), what="dX + residual")
+    dw = A.weight_grad(dy, x)
+    assert dw.dtype == torch.float32 and dw.shape == (N, K)
+    _close(dw, dy.float().t() @ x.float(), tol=5e-3, what="dW")
+
+
+@pytest.mark.parametrize("B,Lq,Lk,two,bcast", [(2, 350, 350, False, False), (3, 128, 350, True, True),
+                                                 (2, 128, 128, False, False), (1, 700, 700, False, False),
+                                                 (2, 100, 3, False, False), (2, 128, 1400, True, True)])
+def test_attention_forward_backward(B, Lq, Lk, two, bcast):
+    from fod_b200 import ops
+    H, C = 8, 256
+    q1, k1, v = _rnd(B, Lq, C, seed=1), _rnd(B, Lk, C, seed=2), _rnd(B, Lk, C, seed=3)
+    q2 = _rnd(B, Lq, C, seed=4) if two else None
+    k2 = (_rnd(Lk, C, seed=5) if bcast else _rnd(B, Lk, C, seed=5)) if two else None
+    scale = (64 if two else 32) ** -0.5
+    leaves = [t.float().requires_grad_(True) for t in (q1, k1, v)] + ([q2.float().requires_grad_(True), k2.float().requires_grad_(True)] if two else [])
+
+    def heads(t, L):
+        t = t.expand(B, L, C) if t.dim() == 2 else t
+        return t.reshape(B, L, H, 32).transpose(1, 2)
+
+    s = heads(leaves[0], Lq) @ heads(leaves[1], Lk).transpose(-1, -2)
+    if two:
+        s = s + heads(leaves[3], Lq) @ heads(leaves[4], Lk).transpose(-1, -2)
+    s = s * scale
+    ref = (s.softmax(-1) @ heads(leaves[2], Lk)).transpose(1, 2).reshape(B, Lq, C)
+    out, lse = ops.attn_fwd(q1, k1, v, scale, H, q2=q2, k2=k2, batch=B)
+    _close(out, ref, what="attn out")
+    _close(lse, torch.logsumexp(s, -1), tol=1e-3, what="lse")
+    dout = _rnd(B, Lq, C, seed=9)
+    ref.backward(dout.float())
+    dq1, dk1, dv, dq2, dk2 = ops.attn_bwd(q1, k1, v, out, lse, dout, scale, H, q2=q2, k2=k2)
+    _close(dq1, leaves[0].grad, what="dq1")
+    _close(dk1, leaves[1].grad, what="dk1")
+    _close(dv, leaves[2].grad, what="dv")
+    if two:
+        _close(dq2, leaves[3].grad, what="dq2")
+        _close(dk2.sum(0) if bcast else dk2, leaves[4].grad, what="dk2")
+
+
+def test_attention_fused_gradient_layouts():
+    from fod_b200 import ops
+    B, L, H, C = 2, 200, 8, 256
+    qkv = _rnd(B, L, 3 * C, seed=7)
+    q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
+    out, lse = ops.attn_fwd(q, k, v, 32 ** -0.5, H)
+    dout = _rnd(B, L, C, seed=8)
+    a = ops.attn_bwd(q.contiguous(), k.contiguous(), v.contiguous(), out, lse, dout, 32 ** -0.5, H)
+    b = ops.attn_bwd(q, k, v, out, lse, dout, 32 ** -0.5, H, fused="qkv")
+    assert b[0]._base is not None and b[0]._base.shape == (B, L, 3 * C)
+    for x, y in zip(a[:3], b[:3]):
+        assert torch.equal(x, y)
+
+
+@pytest.mark.parametrize("M,rpg", [(5600, 350), (1024, 0), (37, 0)])
+def test_row_kernels(M, rpg):
+    from fod_b200 import ops
+    x = _rnd(M, 256, seed=1)
+    gam, bet = torch.rand(256, device=_dev()) + 0.5, torch.randn(256, device=_dev())
+    bc = _rnd(M // rpg, 256, seed=2) if rpg else None
+    z = (x.float() + (bc.float().repeat_interleave(rpg, 0) if rpg else 0)).requires_grad_(True)
+    g32 = gam.clone().requires_grad_(True)
+    b32 = bet.clone().requires_grad_(True)
+    ref = torch.nn.functional.layer_norm(z, (256,), g32, b32, 1e-5)
+    y, mean, rstd = ops.add_ln_fwd(x, gam, bet, 1e-5, bc, rpg, save=True)
+    _close(y, ref, what="add_ln")
+    dy = _rnd(M, 256, seed=3)
+    ref.backward(dy.float())
+    dg, db = torch.zeros(256, device=_dev()), torch.zeros(256, device=_dev())
+    dz = ops.ln_bwd(dy, x, mean, rstd, gam, dg, db, bcast=bc, rows_per_group=rpg)
+    _close(dz, z.grad, what="ln_bwd dz")
+    _close(dg, g32.grad, tol=1e-2, what="dgamma")
+    _close(db, b32.grad, tol=1e-2, what="dbeta")
+    cs = ops.colsum(dy, rpg)
+    ref_cs = dy.float().view(-1, rpg or M, 256).sum(1)
+    _close(cs, ref_cs, tol=2e-3, what="colsum")
+
+
+def test_block_functions_match_torch_autograd():
+    """LinearFn / LinearLNFn / FFNLNFn / AddLNFn forward + parameter and input gradients vs torch fp32 autograd."""
+    from fod_b200 import autograd as A
+    dev = _dev()
+    M, D, Dff = 700, 256, 2048
+    x = _rnd(M, D, seed=1).requires_grad_(True)
+    res = _rnd(M, D, seed=2).requires_grad_(True)
+    mk = lambda *s, sc=0.05, sd=0: (torch.randn(*s, generator=torch.Generator().manual_seed(sd)) * sc).to(dev).requires_grad_(True)
+    w1, b1, w2, b2 = mk(Dff, D, sd=1), mk(Dff, sd=2), mk(D, Dff, sd=3), mk(D, sd=4)
+    wo, bo = mk(D, D, sd=5), mk(D, sd=6)
+    g1, be1 = (torch.rand(D, device=dev) + 0.5).requires_grad_(True), mk(D, sd=8)
+    g2, be2 = (torch.rand(D, device=dev) + 0.5).requires_grad_(True), mk(D, sd=9)
+    q = lambda w: w.detach().to(BF)
+    # fod path
+    y1 = A.linear_ln(x, res, wo, bo, q(wo), g1, be1)
+    y2 = A.ffn_ln(y1, w1, b1, q(w1), w2, b2, q(w2), g2, be2)
+    dy = _rnd(M, D, seed=11)
+    (y2.float() * dy.float()).sum().backward()
+    leaves = [x, res, wo, bo, g1, be1, w1, b1, w2, b2, g2, be2]
+    got = [t.grad.clone().float() for t in leaves]
+    out_fod = y2.detach().float()
+    for t in leaves:
+        t.grad = None
+    # torch fp32 reference with bf16-rounded weights (the kernels' inputs)
+    F = torch.nn.functional
+    r = lambda w: w.to(BF).float() + (w - w.detach())  # value rounded to bf16, gradient to the fp32 leaf
+    z1 = F.layer_norm(res.float() + F.linear(x.float(), r(wo), bo), (D,), g1, be1)
+    z2 = F.layer_norm(z1 + F.linear(F.linear(z1, r(w1), b1).relu(), r(w2), b2), (D,), g2, be2)
+    (z2 * dy.float()).sum().backward()
+    _close(out_fod, z2, what="block forward")
+    names = ["x", "res", "wo", "bo", "g1", "be1", "w1", "b1", "w2", "b2", "g2", "be2"]
+    for n, t, gg in zip(names, leaves, got):
+        _close(gg, t.grad.float(), tol=3e-2, what=f"grad {n}")

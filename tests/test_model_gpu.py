@@ -1,0 +1,161 @@
+"""Whole-path GPU parity: the drop-in model (bf16 kernels) against (a) the golden outputs of the UNMODIFIED
+reference (tests/golden/*.pt) and (b) the fp32 CPU oracle on the same synthetic clips and weights.
+
+Tolerance (north star): relative L2 error <= 2e-2 per tensor in bf16.  Matcher assignments are checked bit-exact by
+re-running the oracle's matcher on the model's own fp32 logits/boxes (identical inputs)."""
+from argparse import Namespace
+
+import pytest
+import torch
+
+from conftest import load_golden
+from oracle import fod_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+TOL = 2e-2
+
+
+def rel_l2(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return float((a - b).norm() / max(1e-12, float(b.norm())))
+
+
+@pytest.fixture(scope="module")
+def model(ref_state_dict):
+    from fod_b200 import SpatioTemporalDETRArgs, build_model
+    m = build_model(Namespace(device=DEV, distributed=False),
+                    SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4))
+    m.load_state_dict(ref_state_dict, strict=True)
+    return m.eval()
+
+
+def _to(data, dev):
+    return {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in data.items()}
+
+
+def _run(model, data):
+    out = {}
+    det = model._model.detector
+    h = det.register_forward_hook(lambda m, i, o: out.__setitem__("core", o))
+    res = model(_to(data, DEV))
+    h.remove()
+    return res, out["core"]
+
+
+@pytest.mark.parametrize("name", ["g1_b2_l3_128x160", "g2_b1_l4_224x320", "g3_b3_l3_96x128_nt0"])
+def test_forward_matches_reference_golden(model, name):
+    from fod_b200.synthetic import make_clip
+    gold = load_golden(name)
+    b, l, h, w, seed, nt = gold["case"]
+    data = make_clip(b, l, h, w, seed=seed, fixed_targets=nt)
+    with torch.no_grad():
+        (outputs, state, loss, stats, stuffs), core = _run(model, data)
+    assert state is None
+    enc = model._model.last_encoder_tokens.view(b, l - 1, -1, 256).float()
+    g_enc = gold["encoder_features"].flatten(3).permute(0, 1, 3, 2)
+    errs = {"encoder": rel_l2(enc, g_enc), "hs": rel_l2(core["hs"].float(), gold["hs"]),
+            "pred_logits": rel_l2(core["pred_logits"], gold["pred_logits"]),
+            "pred_boxes": rel_l2(core["pred_boxes"], gold["pred_boxes"]),
+            "aux_logits": rel_l2(core["all_logits"][:-1], gold["aux_logits"]),
+            "aux_boxes": rel_l2(core["all_boxes"][:-1], gold["aux_boxes"]),
+            "class_scores": rel_l2(outputs["class_scores"], gold["class_scores"]),
+            "boxes": rel_l2(outputs["boxes"], gold["boxes"])}
+    print(name, {k: round(v, 5) for k, v in errs.items()}, "loss", float(loss), float(gold["loss"]))
+    for k, v in errs.items():
+        assert v < TOL, (k, v)
+    assert outputs["class_scores"].shape == gold["class_scores"].shape and outputs["boxes"].shape == gold["boxes"].shape
+    assert set(stats) == {"labels", "box_l1", "box_giou", "cardinality", "class_error"}
+    # the loss depends on the (discrete) assignment; with identical assignments it must agree to bf16 accuracy
+    lv = model._criterion.last_match.cpu()  # (L, B, M), main level last
+    same = True
+    order = list(range(1, len(gold["indices"]))) + [0]  # golden list: main first, then aux 0..4
+    for li, gi in enumerate(order):
+        for bi, (pi, ti) in enumerate(gold["indices"][gi]):
+            mt = lv[li, bi]
+            same &= int((mt >= 0).sum()) == len(pi) and torch.equal(mt[pi].long(), ti)
+    if same:
+        assert abs(float(loss) - float(gold["loss"])) <= TOL * max(1.0, abs(float(gold["loss"])))
+        assert abs(float(stats["box_l1"]) - float(gold["stats"]["box_l1"])) <= TOL * max(1.0, abs(float(gold["stats"]["box_l1"])))
+    confs, is_pos, size_cat, num_annos = stuffs
+    assert confs.shape == gold["od_map"][0].shape and is_pos.shape == gold["od_map"][1].shape
+    assert torch.equal(num_annos.cpu(), gold["od_map"][3])
+
+
+def test_matcher_and_postproc_exact_on_model_outputs(model):
+    """Identical fp32 inputs -> bit-identical assignments (all 6 levels) and exact bool/int AP bookkeeping."""
+    from fod_b200.synthetic import make_clip
+    data = make_clip(3, 3, 128, 160, seed=21)
+    with torch.no_grad():
+        (outputs, _, loss, stats, stuffs), core = _run(model, data)
+    from fod_b200.st_detr import check_match_status
+    check_match_status(model._criterion.last_status)
+    targets = O.to_detr_targets(128, 160, data["active"], data["boxes"], data["classes"])
+    lv = model._criterion.last_match.cpu()
+    for li in range(lv.shape[0]):
+        ref = O.hungarian_match(core["all_logits"][li].float().cpu(), core["all_boxes"][li].float().cpu(), targets)
+        for bi, (pi, ti) in enumerate(ref):
+            mt = lv[li, bi]
+            assert int((mt >= 0).sum()) == len(pi) and torch.equal(mt[pi].long(), ti), (li, bi)
+    # criterion on identical inputs: loss and stats to fp32 accuracy
+    cpu_core = {"pred_logits": core["pred_logits"].float().cpu(), "pred_boxes": core["pred_boxes"].float().cpu(),
+                "aux_outputs": [{"pred_logits": a.float().cpu(), "pred_boxes": c.float().cpu()}
+                                for a, c in zip(core["all_logits"][:-1], core["all_boxes"][:-1])]}
+    l_ref, s_ref, _ = O.criterion(cpu_core, targets)
+    assert abs(float(loss) - float(l_ref)) < 1e-4 * max(1.0, abs(float(l_ref)))
+    for k in s_ref:
+        assert abs(float(stats[k]) - float(s_ref[k])) < 1e-4 * max(1.0, abs(float(s_ref[k]))), k
+    st_ref, post_ref = O.post_process(cpu_core["pred_logits"], cpu_core["pred_boxes"], data)
+    assert rel_l2(outputs["class_scores"], post_ref["class_scores"]) < 1e-5
+    assert rel_l2(outputs["boxes"], post_ref["boxes"]) < 1e-5
+    assert torch.equal(stuffs[1].cpu(), st_ref[1]) and torch.equal(stuffs[2].cpu().bool(), st_ref[2].bool())
+    assert torch.equal(stuffs[3].cpu(), st_ref[3]) and rel_l2(stuffs[0], st_ref[0]) < 1e-5
+
+
+def test_backward_matches_reference_gradients(model, ref_state_dict):
+    """loss.backward() parameter gradients against the reference's (golden g1), relative L2 per tensor."""
+    from fod_b200.synthetic import make_clip
+    gold = load_golden("g1_b2_l3_128x160")
+    b, l, h, w, seed, nt = gold["case"]
+    data = make_clip(b, l, h, w, seed=seed, fixed_targets=nt)
+    model.train()
+    model.zero_grad(set_to_none=True)
+    _, _, loss, _, _ = model(_to(data, DEV))
+    loss.backward()
+    model.eval()
+    missing = [k for k, p in model.named_parameters() if p.requires_grad and p.grad is None]
+    assert not missing, missing[:5]
+    worst, report = 0.0, []
+    params = dict(model.named_parameters())
+    for k, g in gold["grads_small"].items():
+        if float(g.norm()) < 1e-7:
+            assert float(params[k].grad.float().norm()) < 1e-5, k  # dead egodeep parameters: exact zeros
+            continue
+        e = rel_l2(params[k].grad.float(), g)
+        report.append((round(e, 4), k))
+        worst = max(worst, e)
+    report.sort(reverse=True)
+    print("worst gradient errors:", report[:8])
+    norm_bad = []
+    for k, n in gold["grad_norms"].items():
+        if k not in params or params[k].grad is None or float(n) < 1e-6:
+            continue
+        r = float(params[k].grad.float().norm()) / float(n)
+        if not (0.9 < r < 1.1):
+            norm_bad.append((k, round(r, 3)))
+    print("gradient-norm ratios outside 10%:", norm_bad[:10], len(norm_bad))
+    assert worst < 5e-2, report[:5]
+    assert len(norm_bad) <= 0.02 * len(gold["grad_norms"]), norm_bad[:10]
+
+
+def test_state_dict_round_trip_and_attention_store(model, ref_state_dict):
+    from fod_b200.synthetic import make_clip
+    sd = model.state_dict()
+    assert set(sd) == set(ref_state_dict)
+    ia = model._model.detector.decoder.layers[5].image_attend[0]
+    ia.store_attention = True
+    with torch.no_grad():
+        model(_to(make_clip(1, 3, 128, 160, seed=5), DEV))
+    ia.store_attention = False
+    w = ia.stored_attention
+    assert w.shape == (1, 128, 20) and torch.allclose(w.sum(-1), torch.ones_like(w.sum(-1)), atol=1e-3)
