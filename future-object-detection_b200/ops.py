@@ -11,6 +11,7 @@ import math
 import torch
 
 from . import lib
+from . import profile as prof
 
 LAUNCH_COUNTS = collections.Counter()
 BF16 = torch.bfloat16
@@ -86,7 +87,10 @@ def gemm(x, w, bias=None, residual=None, res_row_mod=0, relu=False, ln=None, out
             rstd = torch.empty((M,), dtype=torch.float32, device=x.device)
             a.pre_ln_bf16, a.ln_mean, a.ln_rstd = _p(pre), _p(mean), _p(rstd)
             outs += [pre, mean, rstd]
+    _t = prof.begin()
     lib.check(L.fod_linear_fwd(C.byref(a), _stream()), "fod_linear_fwd")
+    prof.end(_t, "gemm_dw" if a_mn else ("gemm_dx" if b_mn else "gemm_fwd"), 2.0 * M * N * K,
+             2.0 * (M * K + N * K) + M * N * (4 if (out_f32 or accum_into is not None) else 2))
     LAUNCH_COUNTS["gemm_bf16_kernel"] += 1
     return outs[0] if len(outs) == 1 else tuple(outs)
 
@@ -125,7 +129,12 @@ def attn_fwd(q1, k1, v, scale, heads=8, q2=None, k2=None, batch=None):
     lse = torch.empty((B, heads, Lq), dtype=torch.float32, device=v.device)
     a = lib.AttnArgs()
     _fill_attn(a, q1, k1, v, q2, k2, out, lse, scale, heads)
+    _t = prof.begin()
     lib.check(L.fod_attn_fwd(C.byref(a), _stream()), "fod_attn_fwd")
+    Lk, parts, D = v.shape[-2], (2 if q2 is not None else 1), heads * 32
+    kb = B if (k2 is not None and k2.dim() == 3) else 1
+    prof.end(_t, "attn_fwd_p%d_%dx%d" % (parts, Lq, Lk), (2.0 + 2.0 * parts) * B * Lq * Lk * D,
+             2.0 * D * (B * Lq * (parts + 1) + B * Lk * 2 + (parts - 1) * kb * Lk))
     LAUNCH_COUNTS["attn_fwd_kernel"] += 1
     return out, lse
 
@@ -166,7 +175,11 @@ def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=
         dq2 = torch.empty((B, Lq, Cw), dtype=BF16, device=dev)
         dk2 = torch.empty((B, Lk, Cw), dtype=BF16, device=dev)
         g.dq2, g.dk2 = _p(dq2), _p(dk2)
+    _t = prof.begin()
     lib.check(L.fod_attn_bwd(C.byref(g), _stream()), "fod_attn_bwd")
+    parts = 2 if q2 is not None else 1
+    prof.end(_t, "attn_bwd_p%d_%dx%d" % (parts, Lq, Lk), (4.0 + 6.0 * parts) * B * Lq * Lk * Cw,
+             2.0 * Cw * (B * Lq * (2 * parts + 2) + B * Lk * (2 * parts + 2)))
     LAUNCH_COUNTS["attn_delta_kernel"] += 1
     LAUNCH_COUNTS["attn_bwd_dq_kernel"] += 1
     LAUNCH_COUNTS["attn_bwd_dkdv_kernel"] += 1
@@ -187,8 +200,10 @@ def add_ln_fwd(x, gamma, beta, eps=1e-5, bcast=None, rows_per_group=0, save=Fals
     if bcast is not None:
         _chk_bf16(bcast, "add_ln bcast")
         assert bcast.is_contiguous() and bcast.numel() * rows_per_group == x.numel()
+    _t = prof.begin()
     lib.check(L.fod_add_ln_fwd(_p(x), _p(bcast), rows_per_group, _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), M,
                                eps, _stream()), "fod_add_ln_fwd")
+    prof.end(_t, "add_ln_fwd", 0.0, 1024.0 * M)
     LAUNCH_COUNTS["add_ln_fwd_kernel"] += 1
     return (y, mean, rstd) if save else y
 
@@ -201,8 +216,10 @@ def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows
     assert dy.is_contiguous() and pre.is_contiguous() and pre.shape[-1] == 256
     M = pre.numel() // 256
     dz = torch.empty_like(pre)
+    _t = prof.begin()
     lib.check(L.fod_ln_bwd(_p(dy), _p(dy2), _p(pre), _p(bcast), rows_per_group, _p(mean), _p(rstd), _p(gamma), _p(dz),
                            _p(dgamma), _p(dbeta), M, _stream()), "fod_ln_bwd")
+    prof.end(_t, "ln_bwd", 0.0, 1536.0 * M)
     LAUNCH_COUNTS["ln_bwd_kernel"] += 1
     return dz
 
@@ -216,7 +233,9 @@ def colsum(x, rows_per_group=0, out=None):
     rpg = rows_per_group or M
     if out is None:
         out = torch.zeros((M // rpg, N), dtype=torch.float32, device=x.device)
+    _t = prof.begin()
     lib.check(L.fod_colsum(_p(x), x.stride(0), _p(out), M, N, rpg, _stream()), "fod_colsum")
+    prof.end(_t, "colsum", 0.0, 2.0 * M * N)
     LAUNCH_COUNTS["colsum_kernel"] += 1
     return out
 
@@ -271,7 +290,9 @@ def match(logits, boxes, tgt_boxes, tgt_labels, tgt_count, w_class=2.0, w_bbox=5
         a.cost_ws = _p(out["_ws"])
     a.L, a.B, a.M, a.C, a.NT = Lv, B, M, Cn, NT
     a.w_class, a.w_bbox, a.w_giou, a.alpha = w_class, w_bbox, w_giou, alpha
+    _t = prof.begin()
     lib.check(Lb.fod_match(C.byref(a), _stream()), "fod_match")
+    prof.end(_t, "match", 0.0, 4.0 * Lv * B * M * (Cn + 4 + 1))
     LAUNCH_COUNTS["match_kernel"] += 1
     return out
 
@@ -294,7 +315,9 @@ def set_loss(logits, boxes, match_tgt, tgt_boxes, tgt_labels, tgt_count, num_box
     a.dlogits, a.dboxes, a.partial, a.out = _p(dl), _p(db), _p(partial), _p(out)
     a.L, a.B, a.M, a.C, a.NT, a.main_level = Lv, B, M, Cn, tgt_boxes.shape[1], Lv - 1
     a.w_ce, a.w_bbox, a.w_giou, a.alpha = w_ce, w_bbox, w_giou, alpha
+    _t = prof.begin()
     lib.check(Lb.fod_set_loss(C.byref(a), _stream()), "fod_set_loss")
+    prof.end(_t, "set_loss", 0.0, 8.0 * Lv * B * M * (Cn + 4))
     LAUNCH_COUNTS["set_loss_kernel"] += 1
     LAUNCH_COUNTS["set_loss_finalize_kernel"] += 1
     return out, dl, db

@@ -52,7 +52,8 @@ def _check_match(logits, boxes, targets, nt_cap):
             got_i, got_j = pi[lv, b][pi[lv, b] >= 0], ti[lv, b][ti[lv, b] >= 0]
             if n:
                 c_ref = O.matcher_cost(logits[lv, b], boxes[lv, b], targets[b]["labels"], targets[b]["boxes"])
-                assert float((cost[lv, b, :, :n] - c_ref).abs().max()) < 1e-5
+                # CUDA expf/logf vs the CPU's vectorised libm differ by ULPs: costs ~10 agree to ~1e-5; assignments are exact
+                assert float((cost[lv, b, :, :n] - c_ref).abs().max()) < 5e-5
             assert torch.equal(got_i, ri) and torch.equal(got_j, rj), (lv, b, n)
             mt = r["match_tgt"][lv, b].cpu()
             assert int((mt >= 0).sum()) == len(ri) and torch.equal(mt[ri].long(), rj)

@@ -159,13 +159,21 @@ def test_block_functions_match_torch_autograd():
     out_fod = y2.detach().float()
     for t in leaves:
         t.grad = None
-    # torch fp32 reference with bf16-rounded weights (the kernels' inputs)
+    # torch fp32 reference with bf16-rounded weights (the kernels' inputs).  The kernels hand activations from one
+    # block to the next in bf16; rounding y1 alone moves grad x by ~2.5e-2 relative L2 against a pure-fp32 chain (the
+    # ReLU/LayerNorm Jacobians are evaluated at the rounded point), so the reference rounds at the same hand-over
+    # points with a straight-through estimator and the kernels are then held to 1e-2.
     F = torch.nn.functional
-    r = lambda w: w.to(BF).float() + (w - w.detach())  # value rounded to bf16, gradient to the fp32 leaf
-    z1 = F.layer_norm(res.float() + F.linear(x.float(), r(wo), bo), (D,), g1, be1)
-    z2 = F.layer_norm(z1 + F.linear(F.linear(z1, r(w1), b1).relu(), r(w2), b2), (D,), g2, be2)
+    r = lambda w: w + (w.to(BF).float() - w).detach()  # value rounded to bf16, identity gradient (straight-through)
+    z1 = r(F.layer_norm(res.float() + F.linear(x.float(), r(wo), bo), (D,), g1, be1))
+    hid = r(F.linear(z1, r(w1), b1).relu())
+    z2 = F.layer_norm(z1 + F.linear(hid, r(w2), b2), (D,), g2, be2)
     (z2 * dy.float()).sum().backward()
     _close(out_fod, z2, what="block forward")
     names = ["x", "res", "wo", "bo", "g1", "be1", "w1", "b1", "w2", "b2", "g2", "be2"]
+    errs = {}
     for n, t, gg in zip(names, leaves, got):
-        _close(gg, t.grad.float(), tol=3e-2, what=f"grad {n}")
+        ref = t.grad.float()
+        errs[n] = float((gg - ref).norm() / ref.norm())
+    print("block gradient rel-L2 errors:", {k: round(v, 5) for k, v in errs.items()})
+    assert max(errs.values()) < 1e-2, errs
