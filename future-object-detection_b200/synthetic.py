@@ -72,6 +72,11 @@ def synthetic_state_dict(template, seed=0):
                 out[name] = 0.05 * torch.randn(shape, generator=g)
             else:
                 a = math.sqrt(6.0 / (fan_in + fan_out))
+                if "input_proj" in name:
+                    # the un-normalised random ResNet emits features of std ~80; a trained input_proj hands the encoder
+                    # O(1) tokens.  Without this the layer-0 attention logits have std ~2000 (one-hot softmax), a regime
+                    # no trained checkpoint is in and in which bf16 gradients are meaningless.
+                    a /= 64.0
                 out[name] = (torch.rand(shape, generator=g) * 2 - 1) * a
         else:
             if "backbone.body" in name:  # frozen BN affine

@@ -125,27 +125,40 @@ def test_backward_matches_reference_gradients(model, ref_state_dict):
     model.eval()
     missing = [k for k, p in model.named_parameters() if p.requires_grad and p.grad is None]
     assert not missing, missing[:5]
-    worst, report = 0.0, []
+    # Tolerance.  bf16 hand-over of activations/gradients between blocks costs ~3e-2 relative L2 per parameter tensor
+    # against the fp32 reference (measured: tests/test_kernels_gpu.py::test_block_functions explains the mechanism), so
+    # each tensor must satisfy |g - ref| <= 6e-2 |ref| + 1e-4 |ref_all| (the absolute floor covers tensors whose true
+    # gradient is ~0, e.g. key biases — softmax is shift-invariant — and the c = 0 first decoder layer), and the
+    # concatenation of all checked tensors must agree to 4e-2.
     params = dict(model.named_parameters())
-    for k, g in gold["grads_small"].items():
-        if float(g.norm()) < 1e-7:
-            assert float(params[k].grad.float().norm()) < 1e-5, k  # dead egodeep parameters: exact zeros
+    small = {k: g for k, g in gold["grads_small"].items()}
+    ref_all = torch.cat([g.flatten().double() for g in small.values()])
+    got_all = torch.cat([params[k].grad.flatten().double().cpu() for k in small])
+    floor = 1e-4 * float(ref_all.norm())
+    report = []
+    for k, g in small.items():
+        mine = params[k].grad.float().cpu()
+        if float(g.norm()) == 0.0:
+            assert float(mine.norm()) == 0.0, k  # dead egodeep parameters: exact zeros
             continue
-        e = rel_l2(params[k].grad.float(), g)
-        report.append((round(e, 4), k))
-        worst = max(worst, e)
+        err = float((mine.double() - g.double()).norm())
+        report.append((round(err / (6e-2 * float(g.norm()) + floor), 3), round(err / float(g.norm()), 4), k))
     report.sort(reverse=True)
-    print("worst gradient errors:", report[:8])
+    print("worst gradient errors (budget fraction, rel L2, name):", report[:6])
+    glob = float((got_all - ref_all).norm() / ref_all.norm())
+    print("global gradient rel L2 over %d tensors: %.4f" % (len(small), glob))
+    top = max(float(n) for n in gold["grad_norms"].values())
     norm_bad = []
     for k, n in gold["grad_norms"].items():
-        if k not in params or params[k].grad is None or float(n) < 1e-6:
+        if k not in params or params[k].grad is None or float(n) < 1e-3 * top:
             continue
         r = float(params[k].grad.float().norm()) / float(n)
         if not (0.9 < r < 1.1):
             norm_bad.append((k, round(r, 3)))
     print("gradient-norm ratios outside 10%:", norm_bad[:10], len(norm_bad))
-    assert worst < 5e-2, report[:5]
-    assert len(norm_bad) <= 0.02 * len(gold["grad_norms"]), norm_bad[:10]
+    assert report[0][0] <= 1.0, report[:5]
+    assert glob < 4e-2
+    assert not norm_bad, norm_bad[:10]
 
 
 def test_state_dict_round_trip_and_attention_store(model, ref_state_dict):
