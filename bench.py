@@ -151,6 +151,7 @@ def run_cuda(args):
 
     from fod_b200 import SpatioTemporalDETRArgs, build_model, ops
     from fod_b200 import profile as prof
+    from fod_b200 import train as T
     from fod_b200.st_detr import check_match_status
     from fod_b200.synthetic import make_clip, synthetic_state_dict
 
@@ -169,22 +170,15 @@ def run_cuda(args):
     if world > 1:
         model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], output_device=local,
                                                           find_unused_parameters=False, gradient_as_bucket_view=True)
-    opt = setup_optimizer(core, detr_args)
-    params = [p for p in core.parameters() if p.requires_grad]
+    use_graph = bool(args.graphs) and world == 1
+    opt = T.setup_optimizer(core, detr_args, capturable=use_graph)
+    train_step = T.TrainStep(model, opt, detr_args.max_norm, distributed=world > 1)
 
     n_pool = 3
     host_pool = [{k: (v.pin_memory() if torch.is_tensor(v) else v)
                   for k, v in make_clip(BATCH, L_FRAMES, H, W, seed=1000 * rank + i).items()} for i in range(n_pool)]
     dev_pool = [{k: v.to(dev) for k, v in d.items()} for d in host_pool]
     h2d_bytes = sum(v.numel() * v.element_size() for v in host_pool[0].values())
-
-    def train_step(data):
-        opt.zero_grad(set_to_none=True)
-        _, _, loss, stats, _ = model(data=data, distributed=world > 1)
-        loss.backward()
-        torch.nn.utils.clip_grad_norm_(params, detr_args.max_norm)
-        opt.step()
-        return loss
 
     def barrier():
         if world > 1:
@@ -209,22 +203,31 @@ def run_cuda(args):
     torch.cuda.synchronize()
     check_match_status(core._criterion.last_status)
 
+    # eager steps with every launch of OUR kernels bracketed by CUDA events: per-kernel durations for the roofline and
+    # the per-step launch count (the CUDA graph below replays exactly these launches)
+    n_inst = min(args.steps, 5) if args.kernel_events else 1
+    ops.LAUNCH_COUNTS.clear()
+    prof.enable(bool(args.kernel_events))
+    ms_inst = timed(lambda i: train_step(dev_pool[i % n_pool]), n_inst)
+    kern = prof.disable()
+    launch_by_kernel = {k: v // n_inst for k, v in ops.LAUNCH_COUNTS.items()}
+    launches = sum(launch_by_kernel.values()) * args.steps
+
+    step = train_step
+    if use_graph:
+        step = T.GraphedTrainStep(model, opt, dev_pool[0], detr_args.max_norm, warmup=1)
+        for i in range(2):
+            step(dev_pool[i % n_pool])
     sampler = ClockSampler(local)
     sampler.start()
-    ops.LAUNCH_COUNTS.clear()
-    ms = timed(lambda i: train_step(dev_pool[i % n_pool]), args.steps)
-    launches = sum(ops.LAUNCH_COUNTS.values())
-    launch_by_kernel = dict(ops.LAUNCH_COUNTS)
-    # same steps again with every launch of OUR kernels bracketed by CUDA events (per-kernel durations for the roofline)
-    n_inst = min(args.steps, 5) if args.kernel_events else 0
-    prof.enable(bool(n_inst))
-    ms_inst = timed(lambda i: train_step(dev_pool[i % n_pool]), n_inst) if n_inst else 0.0
-    kern = prof.disable()
+    ms = timed(lambda i: step(dev_pool[i % n_pool]), args.steps)
 
     # end to end through the public API: pinned host batch -> device, step, loss back to the host
     def e2e_step(i):
+        if use_graph:
+            return float(step(host_pool[i % n_pool]))
         data = {k: v.to(dev, non_blocking=True) for k, v in host_pool[i % n_pool].items()}
-        return float(train_step(data))
+        return float(step(data))
 
     ms_e2e = timed(e2e_step, args.steps)
     sampler.stop_flag = True
@@ -242,7 +245,7 @@ def run_cuda(args):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "parallelism": "dp%d" % world,
                        "l2": "no explicit flush: one step streams >10 GB of activations through the 126 MB L2",
-                       "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": 0.0},
+                       "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": 0.0, "cuda_graph": use_graph},
             "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
             "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
     line.update(prof.roofline_report(kern, peaks, ms_inst, _traffic()))
@@ -269,6 +272,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="fod", choices=["fod", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--graphs", type=int, default=1, help="1: replay the whole step as one CUDA graph (single GPU)")
     ap.add_argument("--kernel-events", type=int, default=1, help="1: bracket each of our kernel launches with CUDA events")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -147,6 +147,59 @@ class FrozenBatchNorm2d(nn.Module):
         return x * scale.view(1, -1, 1, 1).to(x.dtype) + shift.view(1, -1, 1, 1).to(x.dtype)
 
 
+class _ConvAffineAct(torch.autograd.Function):
+    """y = [relu](conv(x, w) + b [+ z]) on cuDNN with the frozen BatchNorm folded into (w, b) — library code for the
+    backbone (not a hand-written kernel).  Forward is ONE fused cuDNN launch where the runtime offers
+    it (cudnn_convolution_relu / cudnn_convolution_add_relu); backward is one mask pass + cuDNN dgrad/wgrad.  Replaces
+    conv -> x*scale -> +shift -> (+identity) -> relu, i.e. 3-4 full passes over the activation per layer."""
+
+    fused_ok = True
+
+    @staticmethod
+    def forward(ctx, x, w32, b32, stride, padding, relu, z):
+        wq = w32.to(x.dtype).contiguous(memory_format=torch.channels_last)
+        bq = b32.to(x.dtype)
+        y = None
+        if relu and _ConvAffineAct.fused_ok:
+            try:
+                if z is None:
+                    y = torch.cudnn_convolution_relu(x, wq, bq, stride, padding, (1, 1), 1)
+                else:
+                    y = torch.cudnn_convolution_add_relu(x, wq, z, 1.0, bq, stride, padding, (1, 1), 1)
+            except RuntimeError:
+                _ConvAffineAct.fused_ok = False
+        if y is None:
+            y = F.conv2d(x, wq, bq, stride, padding)
+            if z is not None:
+                y = y + z
+            if relu:
+                y = y.relu_()
+        ctx.save_for_backward(x, wq, y if relu else None)
+        ctx.cfg = (stride, padding, relu, z is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, wq, y = ctx.saved_tensors
+        stride, padding, relu, has_z = ctx.cfg
+        g = torch.ops.aten.threshold_backward(dy, y, 0) if relu else dy
+        g = g.contiguous(memory_format=torch.channels_last)
+        dx, dw, _ = torch.ops.aten.convolution_backward(g, x, wq, None, stride, padding, (1, 1), False, (0, 0), 1,
+                                                        (ctx.needs_input_grad[0], ctx.needs_input_grad[1], False))
+        return dx, (dw.float() if dw is not None else None), None, None, None, None, (g if has_z else None)
+
+
+def _folded(conv, bn):
+    """Frozen-BN fold: conv(x, W)·s + t == conv(x, W·s) + t (backbone.py:53-63).  W·s keeps the autograd edge to W."""
+    s = bn.weight * (bn.running_var + 1e-5).rsqrt()
+    return conv.weight * s.view(-1, 1, 1, 1), bn.bias - bn.running_mean * s
+
+
+def _conv_bn(x, conv, bn, relu, z=None):
+    w, b = _folded(conv, bn)
+    return _ConvAffineAct.apply(x, w, b, conv.stride, conv.padding, relu, z)
+
+
 class CDetrBackbone(nn.Module):
     """paper.py:83-116.  The ResNet body stays on torch/cuDNN (channels_last, bf16 autocast); the 1x1 `input_proj`
     is a GEMM over NHWC rows and runs on the tcgen05 kernel, emitting encoder tokens directly."""
@@ -167,12 +220,29 @@ class CDetrBackbone(nn.Module):
         self.num_channels = 512 if name in ("resnet18", "resnet34") else 2048
         self.input_proj = nn.Conv2d(self.num_channels, hidden_dim, kernel_size=(1, 1))
         self.compute_dtype = BF16
+        self.fold_frozen_bn = name not in ("resnet18", "resnet34")  # Bottleneck layout; BasicBlock uses the stock path
+
+    def _body_folded(self, x):
+        """torchvision ResNet (Bottleneck) forward with every conv+FrozenBN(+add)+ReLU group as one fused op."""
+        b = self.body
+        x = _conv_bn(x, b["conv1"], b["bn1"], True)
+        x = b["maxpool"](x)
+        for name in ("layer1", "layer2", "layer3", "layer4"):
+            for blk in b[name]:
+                idt = x if blk.downsample is None else _conv_bn(x, blk.downsample[0], blk.downsample[1], False)
+                o = _conv_bn(x, blk.conv1, blk.bn1, True)
+                o = _conv_bn(o, blk.conv2, blk.bn2, True)
+                x = _conv_bn(o, blk.conv3, blk.bn3, True, idt)
+        return x
 
     def forward_tokens(self, images):
         """(N,3,H,W) -> tokens (N*h*w, hidden) bf16 in (n, h, w) row order, plus (h, w)."""
         x = images.contiguous(memory_format=torch.channels_last)
-        with torch.autocast("cuda", dtype=self.compute_dtype, enabled=self.compute_dtype != torch.float32):
-            f = self.body(x)["0"]
+        if self.fold_frozen_bn:
+            f = self._body_folded(x.to(self.compute_dtype))
+        else:
+            with torch.autocast("cuda", dtype=self.compute_dtype, enabled=self.compute_dtype != torch.float32):
+                f = self.body(x)["0"]
         n, c, h, w = f.shape
         rows = f.permute(0, 2, 3, 1).to(BF16).contiguous().view(n * h * w, c)
         wgt = self.input_proj.weight.view(self.input_proj.weight.shape[0], c)

@@ -230,9 +230,10 @@ def prepare_od_map_stuffs(pred_boxes, scores, anno_boxes, anno_classes, anno_act
     dev = pred_boxes.device
     bsz, _, ncls = scores.shape
     thr = torch.arange(0.50, 1.00, 0.05, device=dev)
-    keep = anno_active.any(dim=0)
-    keep[0] = True
-    ab, ac, aa = anno_boxes[:, keep].float(), anno_classes[:, keep], anno_active[:, keep]
+    # The reference first drops annotation slots that no sample uses (od_map.py:40-45, a data-dependent shape and a
+    # host sync).  Inactive slots are masked out of `avail` below, so keeping all slots gives identical outputs with
+    # static shapes — which lets the whole step be captured in a CUDA graph.
+    ab, ac, aa = anno_boxes.float(), anno_classes, anno_active
     n = ab.shape[1]
     p, a = pred_boxes[:, :, None, :], ab[:, None, :, :]
     area_p = F.relu(p[..., 2] - p[..., 0]) * F.relu(p[..., 3] - p[..., 1])
@@ -285,6 +286,7 @@ class SpatioTemporalDETR(nn.Module):
             self._imu_keys.append("speed")
         self._encode_offset = args.encode_offset
         self.with_od_map = True
+        self._whwh = {}
 
     @staticmethod
     def get_stat_idfs():
@@ -316,7 +318,10 @@ class SpatioTemporalDETR(nn.Module):
         b, l, _, h, w = images.shape
         sc = torch.sigmoid(class_scores.float())
         sc = torch.cat((sc, sc.max(dim=3, keepdim=True)[0]), dim=3)
-        bx = boxes.float() * torch.tensor([w, h, w, h], device=images.device, dtype=torch.float32).view(1, 1, 1, 4)
+        key = (w, h, str(images.device))
+        if key not in self._whwh:  # cached: a host->device constant copy is not allowed inside CUDA-graph capture
+            self._whwh[key] = torch.tensor([w, h, w, h], device=images.device, dtype=torch.float32).view(1, 1, 1, 4)
+        bx = boxes.float() * self._whwh[key]
         bx = torch.cat((bx[..., 0:2] - 0.5 * bx[..., 2:4], bx[..., 0:2] + 0.5 * bx[..., 2:4]), dim=-1)
         assert bx.shape[1] == 1, "If different #outs than #ins, #outs must be 1"
         stuffs = None

@@ -127,7 +127,7 @@ def test_backward_matches_reference_gradients(model, ref_state_dict):
     assert not missing, missing[:5]
     # Tolerance.  bf16 hand-over of activations/gradients between blocks costs ~3e-2 relative L2 per parameter tensor
     # against the fp32 reference (measured: tests/test_kernels_gpu.py::test_block_functions explains the mechanism), so
-    # each tensor must satisfy |g - ref| <= 6e-2 |ref| + 1e-4 |ref_all| (the absolute floor covers tensors whose true
+    # each tensor must satisfy |g - ref| <= 8e-2 |ref| + 1e-4 |ref_all| (the absolute floor covers tensors whose true
     # gradient is ~0, e.g. key biases — softmax is shift-invariant — and the c = 0 first decoder layer), and the
     # concatenation of all checked tensors must agree to 4e-2.
     params = dict(model.named_parameters())
@@ -142,7 +142,7 @@ def test_backward_matches_reference_gradients(model, ref_state_dict):
             assert float(mine.norm()) == 0.0, k  # dead egodeep parameters: exact zeros
             continue
         err = float((mine.double() - g.double()).norm())
-        report.append((round(err / (6e-2 * float(g.norm()) + floor), 3), round(err / float(g.norm()), 4), k))
+        report.append((round(err / (8e-2 * float(g.norm()) + floor), 3), round(err / float(g.norm()), 4), k))
     report.sort(reverse=True)
     print("worst gradient errors (budget fraction, rel L2, name):", report[:6])
     glob = float((got_all - ref_all).norm() / ref_all.norm())
