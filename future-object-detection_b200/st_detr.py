@@ -113,7 +113,7 @@ class FuturePredCore(nn.Module):
         s, d = h * w, x.shape[1]
         if self.joint_encoder is not None:
             x = self.joint_encoder(x, pos_bf, ego, b, t, s)
-        self.last_encoder_tokens = x
+        self.last_encoder_tokens = x.detach()  # detached: a live graph would pin last step's AccumulateGrad nodes
         # (b, t, s) rows -> one contiguous (B*S, D) token matrix per frame for the decoder's K/V GEMMs
         per_frame = x.view(b, t, s, d).transpose(0, 1).contiguous()
         frames = [per_frame[l].reshape(b * s, d) for l in range(t)]
