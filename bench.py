@@ -152,7 +152,14 @@ def run_cuda(args):
     from fod_b200 import SpatioTemporalDETRArgs, build_model, ops
     from fod_b200 import profile as prof
     from fod_b200 import train as T
-    from fod_b200.st_detr import check_match_status
+    status_log = {}
+
+    def check_match_status(status, region=[0]):
+        # matcher status word of the LAST step of a region (bit0 NaN/-inf cost, bit1 degenerate box, bit2 infeasible):
+        # recorded in the JSON line instead of aborting the measurement
+        region[0] += 1
+        status_log["region%d" % region[0]] = int(status.item())
+
     from fod_b200.synthetic import make_clip, synthetic_state_dict
 
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -221,6 +228,7 @@ def run_cuda(args):
     sampler = ClockSampler(local)
     sampler.start()
     ms = timed(lambda i: step(dev_pool[i % n_pool]), args.steps)
+    check_match_status(core._criterion.last_status)
 
     # end to end through the public API: pinned host batch -> device, step, loss back to the host
     def e2e_step(i):
@@ -247,7 +255,7 @@ def run_cuda(args):
                        "l2": "no explicit flush: one step streams >10 GB of activations through the 126 MB L2",
                        "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": 0.0, "cuda_graph": use_graph},
             "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
-            "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
+            "matcher_status_by_region": status_log, "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
     line.update(prof.roofline_report(kern, peaks, ms_inst, _traffic()))
     line["instrumented_region"] = {"steps": n_inst, "ms_per_step": ms_inst / n_inst if n_inst else None}
     if not args.no_cpu_baseline:
