@@ -13,6 +13,7 @@ from . import autograd as A
 from . import lib, ops
 from . import model as M
 from . import detector as D
+from .dist import global_num_boxes
 
 BF16 = torch.bfloat16
 
@@ -195,11 +196,7 @@ class SetCriterion(nn.Module):
 
     def forward(self, all_logits, all_boxes, tgt_boxes, tgt_labels, tgt_count, total_count, distributed=False):
         """all_logits (L,B,M,C), all_boxes (L,B,M,4) fp32 with the main output last.  Returns (loss, stats)."""
-        num_boxes = total_count.clone()
-        if distributed and torch.distributed.is_available() and torch.distributed.is_initialized():
-            torch.distributed.all_reduce(num_boxes)  # set_criterion.py:190 — consumed on the device, no .item()
-            num_boxes = num_boxes / torch.distributed.get_world_size()
-        num_boxes = num_boxes.clamp(min=1.0)
+        num_boxes = global_num_boxes(total_count, distributed)  # set_criterion.py:185-193, stays on the device
         wd, mt = self.weight_dict, self.matcher
         weights = (wd["loss_ce"], wd["loss_bbox"], wd["loss_giou"], mt.cost_class, mt.cost_bbox, mt.cost_giou,
                    self.focal_alpha)
