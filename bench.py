@@ -174,12 +174,15 @@ def run_cuda(args):
     model.load_state_dict(synthetic_state_dict(_template(), seed=0))
     model.train()
     core = model
-    if world > 1:
-        model = torch.nn.parallel.DistributedDataParallel(model, device_ids=[local], output_device=local,
-                                                          find_unused_parameters=False, gradient_as_bucket_view=True)
-    use_graph = bool(args.graphs) and world == 1
+    use_graph = bool(args.graphs)
     opt = T.setup_optimizer(core, detr_args, capturable=use_graph)
-    train_step = T.TrainStep(model, opt, detr_args.max_norm, distributed=world > 1)
+    # N > 1: gradients are averaged by the graph-capturable bucketed reducer (fod_b200/ddp.py: flat fp32 buckets,
+    # NCCL AVG on a side stream overlapping backward) instead of torch's host-driven DDP wrapper
+    reducer = None
+    if world > 1 or args.flat_grads:
+        from fod_b200.ddp import BucketedGradReducer
+        reducer = BucketedGradReducer(core.parameters(), bucket_mb=args.bucket_mb)
+    train_step = T.TrainStep(model, opt, detr_args.max_norm, distributed=world > 1, reducer=reducer)
 
     n_pool = 3
     host_pool = [{k: (v.pin_memory() if torch.is_tensor(v) else v)
@@ -222,12 +225,17 @@ def run_cuda(args):
 
     step = train_step
     if use_graph:
-        step = T.GraphedTrainStep(model, opt, dev_pool[0], detr_args.max_norm, warmup=1)
+        step = T.GraphedTrainStep(model, opt, dev_pool[0], detr_args.max_norm, warmup=1, distributed=world > 1,
+                                  reducer=reducer)
         for i in range(2):
             step(dev_pool[i % n_pool])
     sampler = ClockSampler(local)
     sampler.start()
+    if args.profiler_range:  # ncu --profile-from-start off: only the timed steps are captured
+        torch.cuda.profiler.start()
     ms = timed(lambda i: step(dev_pool[i % n_pool]), args.steps)
+    if args.profiler_range:
+        torch.cuda.profiler.stop()
     check_match_status(core._criterion.last_status)
 
     # end to end through the public API: pinned host batch -> device, step, loss back to the host
@@ -253,7 +261,8 @@ def run_cuda(args):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "parallelism": "dp%d" % world,
                        "l2": "no explicit flush: one step streams >10 GB of activations through the 126 MB L2",
-                       "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": 0.0, "cuda_graph": use_graph},
+                       "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": 0.0, "cuda_graph": use_graph,
+                       "grad_allreduce": ("bucketed NCCL AVG, %g MB fp32 buckets, side stream inside the graph" % args.bucket_mb) if world > 1 else None},
             "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
             "matcher_status_by_region": status_log, "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
     line.update(prof.roofline_report(kern, peaks, ms_inst, _traffic()))
@@ -282,6 +291,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--graphs", type=int, default=1, help="1: replay the whole step as one CUDA graph (single GPU)")
     ap.add_argument("--kernel-events", type=int, default=1, help="1: bracket each of our kernel launches with CUDA events")
+    ap.add_argument("--flat-grads", type=int, default=0, help="1: use the flat-bucket gradient path at N=1 too")
+    ap.add_argument("--bucket-mb", type=float, default=32.0)
+    ap.add_argument("--profiler-range", type=int, default=0, help="1: cudaProfilerStart/Stop around the timed steps (for ncu)")
     args = ap.parse_args()
     if args.impl == "reference":
         args.steps = min(args.steps, 8)

@@ -17,30 +17,44 @@ def setup_optimizer(model, detr_args, capturable=False):
 
 
 class TrainStep:
-    """Eager step.  `model` may be DDP-wrapped; `params` are the trainable parameters that get clipped."""
+    """Eager step.  `model` may be DDP-wrapped; `params` are the trainable parameters that get clipped.
 
-    def __init__(self, model, optimizer, max_norm=0.1, distributed=False):
+    With `reducer` (fod_b200.ddp.BucketedGradReducer over the UNWRAPPED model's parameters) the gradients live in flat
+    fp32 buckets that are averaged over ranks during backward and clipped bucket-wise; this form has static structure
+    and is what GraphedTrainStep captures for N > 1 GPUs."""
+
+    def __init__(self, model, optimizer, max_norm=0.1, distributed=False, reducer=None):
         self.model, self.opt, self.max_norm, self.distributed = model, optimizer, max_norm, distributed
         self.params = [p for p in model.parameters() if p.requires_grad]
+        self.reducer = reducer
 
     def __call__(self, data):
-        self.opt.zero_grad(set_to_none=True)
+        if self.reducer is not None:
+            self.reducer.zero_grad()
+        else:
+            self.opt.zero_grad(set_to_none=True)
         _, _, loss, stats, _ = self.model(data=data, distributed=self.distributed)
         loss.backward()
-        torch.nn.utils.clip_grad_norm_(self.params, self.max_norm)
+        if self.reducer is not None:
+            self.reducer.finish()
+            self.reducer.clip_grad_norm_(self.max_norm)
+        else:
+            torch.nn.utils.clip_grad_norm_(self.params, self.max_norm)
         self.opt.step()
         return loss
 
 
 class GraphedTrainStep:
-    """The same step captured into one CUDA graph (single process / single GPU).  Inputs are copied into static
-    device buffers, the graph is replayed, and the static loss tensor is returned (read it with .item() if needed).
+    """The same step captured into one CUDA graph.  Inputs are copied into static device buffers, the graph is
+    replayed, and the static loss tensor is returned (read it with .item() if needed).  With N > 1 ranks pass a
+    `reducer`: the bucketed NCCL all-reduces and the num_boxes exchange become nodes of the graph (side-stream
+    branches that overlap backward), so a multi-GPU step is still ONE cudaGraphLaunch per rank.
 
     The optimizer must have been built with capturable=True.  `warmup` eager steps run first on a side stream, as
     CUDA-graph capture requires (allocator warm-up, cuDNN autotuning, lazily created kernel attributes)."""
 
-    def __init__(self, model, optimizer, example, max_norm=0.1, warmup=3):
-        self.eager = TrainStep(model, optimizer, max_norm)
+    def __init__(self, model, optimizer, example, max_norm=0.1, warmup=3, distributed=False, reducer=None):
+        self.eager = TrainStep(model, optimizer, max_norm, distributed=distributed, reducer=reducer)
         self.static = {k: (v.clone() if torch.is_tensor(v) else v) for k, v in example.items()}
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
@@ -50,8 +64,10 @@ class GraphedTrainStep:
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        optimizer.zero_grad(set_to_none=True)
-        with torch.cuda.graph(self.graph):
+        if reducer is None:
+            optimizer.zero_grad(set_to_none=True)
+        # thread_local: the NCCL watchdog thread may query events while this thread captures
+        with torch.cuda.graph(self.graph, capture_error_mode="thread_local" if distributed else "global"):
             self.loss = self.eager(self.static)
         torch.cuda.synchronize()
 

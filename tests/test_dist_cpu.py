@@ -54,3 +54,58 @@ def test_two_rank_gloo_plumbing():
     xs = [torch.arange(8, dtype=torch.float32).view(2, 4) + 10 * r for r in range(2)]
     expect = sum(x.sum(0, keepdim=True) for x in xs) / 2
     assert torch.allclose(r0["grad"], expect) and torch.allclose(r1["grad"], expect)
+
+
+def _reducer_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from fod_b200.ddp import BucketedGradReducer
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.ReLU(), torch.nn.Linear(5, 3), torch.nn.Linear(3, 1))
+    net[2].bias.requires_grad_(False)  # frozen parameters take no slot
+    red = BucketedGradReducer(net.parameters(), bucket_mb=64 / (1 << 20))  # 16-float buckets -> several buckets
+    res = {"n_buckets": len(red.buckets)}
+    for it in range(2):  # second iteration: views survive zero_grad, counters re-arm
+        red.zero_grad()
+        x = torch.arange(12, dtype=torch.float32).view(2, 6) * 0.1 + rank + it
+        net(x).sum().backward()
+        red.finish()
+        res["grads%d" % it] = [p.grad.clone() for p in net.parameters() if p.requires_grad]
+    res["norm"] = float(red.clip_grad_norm_(0.1))
+    res["clipped_norm"] = float(torch.cat([p.grad.flatten() for p in net.parameters() if p.requires_grad]).norm())
+    try:  # replacing a view must be caught, not silently drop the parameter out of the all-reduce
+        net[0].weight.grad = None
+        red.zero_grad()
+        net(torch.ones(1, 6)).sum().backward()
+        res["caught"] = False
+    except (RuntimeError, AttributeError):
+        res["caught"] = True
+    out[rank] = res
+    dist.destroy_process_group()
+
+
+def test_bucketed_grad_reducer_two_ranks():
+    """fod_b200.ddp.BucketedGradReducer == DDP semantics (mean of per-rank gradients), multi-bucket, re-armed per step,
+    flat clipping == torch.nn.utils.clip_grad_norm_."""
+    world = 2
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_reducer_worker, args=(world, _free_port(), out), nprocs=world, join=True)
+    assert out[0]["n_buckets"] >= 3
+    for it in range(2):
+        torch.manual_seed(0)
+        net = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.ReLU(), torch.nn.Linear(5, 3), torch.nn.Linear(3, 1))
+        net[2].bias.requires_grad_(False)
+        tot = 0
+        for r in range(world):
+            x = torch.arange(12, dtype=torch.float32).view(2, 6) * 0.1 + r + it
+            tot = tot + net(x).sum() / world
+        tot.backward()
+        expect = [p.grad for p in net.parameters() if p.requires_grad]
+        for r in range(world):
+            for g, e in zip(out[r]["grads%d" % it], expect):
+                assert torch.allclose(g, e, rtol=1e-5, atol=1e-6)
+    ref_norm = float(torch.nn.utils.clip_grad_norm_([p for p in net.parameters() if p.requires_grad], 0.1))
+    assert abs(out[0]["norm"] - ref_norm) < 1e-4 * ref_norm
+    assert abs(out[0]["clipped_norm"] - min(0.1, ref_norm)) < 1e-5
+    assert out[0]["caught"] and out[1]["caught"]
