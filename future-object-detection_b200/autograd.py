@@ -18,19 +18,11 @@ def _bf(t):
     return t.to(BF16).contiguous() if t.dtype != BF16 else t.contiguous()
 
 
-def _split_k(m_out, n_out, k):
-    bn = 256 if n_out > 128 else (128 if n_out > 64 else 64)
-    tiles = ((m_out + 127) // 128) * ((n_out + bn - 1) // bn)
-    kb = (k + 63) // 64
-    return max(1, min(kb // 2 if kb >= 2 else 1, (_NUM_SMS + tiles - 1) // tiles))
-
-
 def weight_grad(dy, x):
-    """dW (N, K) fp32 = dyᵀ (N, rows) · x (rows, K), contraction over rows on the MN-major tcgen05 GEMM."""
+    """dW (N, K) fp32 = dyᵀ (N, rows) · x (rows, K), contraction over rows on the MN-major tcgen05 GEMM; the library
+    picks the split-K factor (plain stores when it does not split, zero-fill + vector reductions when it does)."""
     n, k = dy.shape[1], x.shape[1]
-    dw = torch.zeros((n, k), dtype=torch.float32, device=dy.device)
-    ops.gemm(dy, x, a_mn=True, b_mn=True, accum_into=dw, split_k=_split_k(n, k, dy.shape[0]))
-    return dw
+    return ops.gemm(dy, x, a_mn=True, b_mn=True, out_f32=True, split_k=-1)
 
 
 def input_grad(dy, wq, **kw):
@@ -83,13 +75,11 @@ class LinearLNFn(Function):
     @staticmethod
     def backward(ctx, dy):
         x, wq, pre, mean, rstd, gamma = ctx.saved_tensors
-        dgamma = torch.zeros_like(gamma)
-        dbeta = torch.zeros_like(gamma)
-        dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, dgamma, dbeta)
+        acc = torch.zeros((3, gamma.numel()), dtype=torch.float32, device=gamma.device)  # dgamma, dbeta, db
+        dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, acc[0], acc[1], dzsum=acc[2])
         dx = input_grad(dz, wq)
         dw = weight_grad(dz, x)
-        db = ops.colsum(dz).view(-1)
-        return dx, dz, dw, db, None, dgamma, dbeta, None, None
+        return dx, dz, dw, acc[2], None, acc[0], acc[1], None, None
 
 
 def linear_ln(x, res, w, b, wq, gamma, beta, eps=1e-5):
@@ -113,15 +103,14 @@ class FFNLNFn(Function):
     @staticmethod
     def backward(ctx, dy):
         x, h, w1q, w2q, pre, mean, rstd, gamma = ctx.saved_tensors
-        dgamma = torch.zeros_like(gamma)
-        dbeta = torch.zeros_like(gamma)
-        dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, dgamma, dbeta)
-        dh = input_grad(dz, w2q, relu_mask=h)
+        d = gamma.numel()
+        acc = torch.zeros((3 * d + h.shape[1],), dtype=torch.float32, device=gamma.device)  # dgamma, dbeta, db2, db1
+        dgamma, dbeta, db2, db1 = acc[:d], acc[d:2 * d], acc[2 * d:3 * d], acc[3 * d:]
+        dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, dgamma, dbeta, dzsum=db2)
+        dh = input_grad(dz, w2q, relu_mask=h, colsum_out=db1)  # ReLU mask and the bias-1 gradient ride in the epilogue
         dw2 = weight_grad(dz, h)
-        db2 = ops.colsum(dz).view(-1)
         dx = input_grad(dh, w1q, residual=dz)
         dw1 = weight_grad(dh, x)
-        db1 = ops.colsum(dh).view(-1)
         return dx, dw1, db1, None, dw2, db2, None, dgamma, dbeta, None, None
 
 

@@ -12,11 +12,8 @@ namespace fod {
 
 struct GemmEpi {
     const float* bias;
-    const __nv_bfloat16* residual;
-    const __nv_bfloat16* relu_mask;  // (M,N), ld_out: output is zeroed where mask <= 0 (ReLU backward)
-    const float* col_scale;          // optional (res_row_mod or M, N) fp32 multiplier applied after bias: y = (acc+b)*s
-    int atomic_out;                  // 1: red.add into out_f32 (split-K / gradient accumulation)
-    int kb_per_split;
+    const __nv_bfloat16* aux;        // residual (aux_mode 1) or ReLU mask (aux_mode 2) tile source, prefetched via cp.async
+    const float* col_scale;          // optional (aux_row_mod or M, N) fp32 multiplier applied after bias: y = (acc+b)*s
     const float* ln_gamma;
     const float* ln_beta;
     __nv_bfloat16* out_bf16;
@@ -24,25 +21,37 @@ struct GemmEpi {
     __nv_bfloat16* pre_ln;
     float* ln_mean;
     float* ln_rstd;
-    long long ld_res, ld_out;
+    float* colsum_out;               // optional (N) fp32: += column sums of the stored bf16 output (bias gradients)
+    long long ld_aux, ld_out;
     int M, N, K;
-    int res_row_mod;
+    int aux_mode;                    // 0 none, 1 add residual, 2 zero where mask <= 0
+    int aux_row_mod;                 // residual row = row % aux_row_mod when > 0
     int relu;
+    int atomic_out;                  // 1: red.add into out_f32 (split-K / gradient accumulation)
+    int kb_per_split;
+    int num_stages;
+    int vec_ok;                      // 1: 16-byte vector paths are legal for out / aux (alignment + N % 8 == 0)
     float ln_eps;
 };
 
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
 constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_MAX_STAGES = 8;
 
 template <int BN>
 struct GemmCfg {
     static constexpr int kABytes = GEMM_BM * GEMM_BK * 2;
     static constexpr int kBBytes = BN * GEMM_BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
-    static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
-    static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+    // epilogue staging rows carry 16 bytes of padding: a lane's 16-byte accesses to ITS row and a warp's accesses
+    // along ONE row are both bank-conflict free (row stride = 4 banks mod 32)
+    static constexpr int kRowBf16 = BN * 2 + 16;
+    static constexpr int kRowF32 = BN * 4 + 16;
+    static constexpr int kAuxBytes = GEMM_BM * kRowBf16;
     static constexpr int kTmemCols = BN < 32 ? 32 : BN;
+    static constexpr int kBarBytes = 256;
+    static int smem_bytes(int stages, bool aux) { return 1024 + stages * kStageBytes + (aux ? kAuxBytes : 0) + kBarBytes; }
 };
 
 __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t (&v)[32]) {
@@ -58,67 +67,174 @@ __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_
 }
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-// add bias and residual to 32 accumulator columns [col0, col0+32) of one row
-__device__ __forceinline__ void epi_bias_res(float (&z)[32], const GemmEpi& p, long long res_row, int col0) {
+__device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, uint32_t src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+__device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float2 t = __bfloat1622float2(h[j]);
+        f[2 * j] = t.x;
+        f[2 * j + 1] = t.y;
+    }
+}
+
+// bias, col_scale, staged residual, ReLU, staged mask on 32 accumulator columns [col0, col0+32) of one row
+template <int BN>
+__device__ __forceinline__ void epi_chunk(float (&z)[32], const GemmEpi& p, const uint8_t* aux_row, long long row,
+                                          long long mod_row, int col0, int c) {
     if (p.bias) {
 #pragma unroll
         for (int i = 0; i < 32; ++i)
             if (col0 + i < p.N) z[i] += __ldg(p.bias + col0 + i);
     }
     if (p.col_scale) {
-        const float* sc = p.col_scale + res_row * (long long)p.N + col0;
+        const float* sc = p.col_scale + mod_row * (long long)p.N + col0;
 #pragma unroll
         for (int i = 0; i < 32; ++i)
             if (col0 + i < p.N) z[i] *= __ldg(sc + i);
     }
-    if (p.residual) {
-        const __nv_bfloat16* r = p.residual + res_row * p.ld_res + col0;
-        if (col0 + 32 <= p.N && ((reinterpret_cast<uintptr_t>(r) & 15) == 0)) {
+    if (p.aux_mode == 1) {
+        if (p.vec_ok) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                uint4 u = __ldg(reinterpret_cast<const uint4*>(r) + q);
-                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+                float f[8];
+                unpack8(*reinterpret_cast<const uint4*>(aux_row + c * 64 + q * 16), f);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    float2 f = __bfloat1622float2(h[j]);
-                    z[q * 8 + 2 * j] += f.x;
-                    z[q * 8 + 2 * j + 1] += f.y;
-                }
+                for (int j = 0; j < 8; ++j) z[q * 8 + j] += f[j];
             }
         } else {
+            const __nv_bfloat16* r = p.aux + mod_row * p.ld_aux + col0;
 #pragma unroll
             for (int i = 0; i < 32; ++i)
                 if (col0 + i < p.N) z[i] += __bfloat162float(r[i]);
         }
     }
-}
-
-__device__ __forceinline__ void epi_store_bf16(__nv_bfloat16* dst, const float (&z)[32], int ncols_valid) {
-    if (ncols_valid >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+    if (p.relu) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            uint4 u;
-            u.x = pack_bf16x2(z[q * 8 + 0], z[q * 8 + 1]);
-            u.y = pack_bf16x2(z[q * 8 + 2], z[q * 8 + 3]);
-            u.z = pack_bf16x2(z[q * 8 + 4], z[q * 8 + 5]);
-            u.w = pack_bf16x2(z[q * 8 + 6], z[q * 8 + 7]);
-            reinterpret_cast<uint4*>(dst)[q] = u;
+        for (int i = 0; i < 32; ++i) z[i] = fmaxf(z[i], 0.f);
+    }
+    if (p.aux_mode == 2) {
+        if (p.vec_ok) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                float f[8];
+                unpack8(*reinterpret_cast<const uint4*>(aux_row + c * 64 + q * 16), f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (!(f[j] > 0.f)) z[q * 8 + j] = 0.f;
+            }
+        } else {
+            const __nv_bfloat16* mk = p.aux + row * p.ld_aux + col0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                if (col0 + i < p.N && !(__bfloat162float(mk[i]) > 0.f)) z[i] = 0.f;
         }
-    } else {
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-            if (i < ncols_valid) dst[i] = __float2bfloat16(z[i]);
     }
 }
-__device__ __forceinline__ void epi_store_f32(float* dst, const float (&z)[32], int ncols_valid) {
-    if (ncols_valid >= 32 && ((reinterpret_cast<uintptr_t>(dst) & 15) == 0)) {
+
+__device__ __forceinline__ void stage_bf16(uint8_t* dst, const float (&z)[32]) {
 #pragma unroll
-        for (int q = 0; q < 8; ++q)
-            reinterpret_cast<float4*>(dst)[q] = make_float4(z[q * 4], z[q * 4 + 1], z[q * 4 + 2], z[q * 4 + 3]);
+    for (int q = 0; q < 4; ++q) {
+        uint4 u;
+        u.x = pack_bf16x2(z[q * 8 + 0], z[q * 8 + 1]);
+        u.y = pack_bf16x2(z[q * 8 + 2], z[q * 8 + 3]);
+        u.z = pack_bf16x2(z[q * 8 + 4], z[q * 8 + 5]);
+        u.w = pack_bf16x2(z[q * 8 + 6], z[q * 8 + 7]);
+        reinterpret_cast<uint4*>(dst)[q] = u;
+    }
+}
+__device__ __forceinline__ void stage_f32(uint8_t* dst, const float (&z)[32]) {
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+        reinterpret_cast<float4*>(dst)[q] = make_float4(z[q * 4], z[q * 4 + 1], z[q * 4 + 2], z[q * 4 + 3]);
+}
+
+// One warp drains ITS 32 staged rows (bf16) to global memory with lane-contiguous 16-byte stores: a full 128-byte
+// line per 8 lanes instead of 32 scattered row segments.  Optionally accumulates column sums of what it stored.
+template <int BN>
+__device__ __forceinline__ void drain_bf16(const uint8_t* stage_warp, __nv_bfloat16* out, long long ld_out, int M, int N,
+                                           long long row0, int n0, int lane, bool vec_ok, float* colsum_out) {
+    constexpr int ROWB = GemmCfg<BN>::kRowBf16;
+    if (vec_ok) {
+        constexpr int CH = BN / 8;    // 16-byte chunks per row: 32 / 16 / 8
+        constexpr int RPI = 32 / CH;  // rows per warp-wide instruction
+        const int ch = lane % CH, rsub = lane / CH;
+        const int col = n0 + ch * 8;
+        float cs[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) cs[j] = 0.f;
+        if (col < N) {
+#pragma unroll 4
+            for (int r = rsub; r < 32; r += RPI) {
+                if (row0 + r >= M) break;
+                const uint4 u = *reinterpret_cast<const uint4*>(stage_warp + r * ROWB + ch * 16);
+                *reinterpret_cast<uint4*>(out + (row0 + r) * ld_out + col) = u;
+                if (colsum_out) {
+                    float f[8];
+                    unpack8(u, f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) cs[j] += f[j];
+                }
+            }
+        }
+        if (colsum_out) {
+#pragma unroll
+            for (int o = CH; o < 32; o <<= 1) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) cs[j] += __shfl_xor_sync(0xffffffffu, cs[j], o);
+            }
+            if (rsub == 0 && col < N) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) atomicAdd(colsum_out + col + j, cs[j]);
+            }
+        }
     } else {
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-            if (i < ncols_valid) dst[i] = z[i];
+        for (int r = 0; r < 32; ++r) {
+            if (row0 + r >= M) break;
+            const __nv_bfloat16* s = reinterpret_cast<const __nv_bfloat16*>(stage_warp + r * ROWB);
+            for (int cc = lane; cc < BN; cc += 32) {
+                if (n0 + cc < N) {
+                    out[(row0 + r) * ld_out + n0 + cc] = s[cc];
+                    if (colsum_out) atomicAdd(colsum_out + n0 + cc, __bfloat162float(s[cc]));
+                }
+            }
+        }
+    }
+}
+
+template <int BN>
+__device__ __forceinline__ void drain_f32(const uint8_t* stage_warp, float* out, long long ld_out, int M, int N,
+                                          long long row0, int n0, int lane, bool vec_ok, bool atomic) {
+    constexpr int ROWB = GemmCfg<BN>::kRowF32;
+    if (vec_ok) {
+        constexpr int CH = BN / 4;  // float4 chunks per row: 64 / 32 / 16
+#pragma unroll 4
+        for (int i = lane; i < 32 * CH; i += 32) {
+            const int r = i / CH, ch = i % CH;
+            if (row0 + r >= M) break;
+            const int col = n0 + ch * 4;
+            if (col >= N) continue;
+            const float4 v = *reinterpret_cast<const float4*>(stage_warp + r * ROWB + ch * 16);
+            float4* dst = reinterpret_cast<float4*>(out + (row0 + r) * ld_out + col);
+            if (atomic) atomicAdd(dst, v);  // sm_90+: one 16-byte vector reduction
+            else *dst = v;
+        }
+    } else {
+        for (int r = 0; r < 32; ++r) {
+            if (row0 + r >= M) break;
+            const float* s = reinterpret_cast<const float*>(stage_warp + r * ROWB);
+            for (int cc = lane; cc < BN; cc += 32) {
+                if (n0 + cc < N) {
+                    if (atomic) atomicAdd(out + (row0 + r) * ld_out + n0 + cc, s[cc]);
+                    else out[(row0 + r) * ld_out + n0 + cc] = s[cc];
+                }
+            }
+        }
     }
 }
 
@@ -128,9 +244,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     using Cfg = GemmCfg<BN>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + Cfg::kStages * Cfg::kStageBytes);
-    uint64_t* empty_bar = full_bar + Cfg::kStages;
-    uint64_t* accum_bar = empty_bar + Cfg::kStages;
+    uint8_t* aux_stage = smem + p.num_stages * Cfg::kStageBytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(aux_stage + (p.aux_mode ? Cfg::kAuxBytes : 0));
+    uint64_t* empty_bar = full_bar + GEMM_MAX_STAGES;
+    uint64_t* accum_bar = empty_bar + GEMM_MAX_STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
 
     const int warp = threadIdx.x >> 5;
@@ -141,11 +258,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int kb_begin = blockIdx.z * p.kb_per_split;
     const int kb_end = min(total_kb, kb_begin + p.kb_per_split);
     const int num_kb = kb_end - kb_begin;  // >= 1 by construction of the grid
+    const int num_stages = p.num_stages;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
-        for (int s = 0; s < Cfg::kStages; ++s) {
+        for (int s = 0; s < num_stages; ++s) {
             mbar_init(full_bar + s, 1);
             mbar_init(empty_bar + s, 1);
         }
@@ -160,9 +278,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
     if (warp == 0) {
         if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
             for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % Cfg::kStages;
-                const uint32_t ph = (kb / Cfg::kStages) & 1;
                 mbar_wait(empty_bar + s, ph ^ 1);
                 uint8_t* sa = smem + s * Cfg::kStageBytes;
                 uint8_t* sb = sa + Cfg::kABytes;
@@ -180,14 +298,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 } else {
                     tma_load_2d(sb, &tmB, full_bar + s, k0, n0);
                 }
+                if (++s == num_stages) {
+                    s = 0;
+                    ph ^= 1;
+                }
             }
         }
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+            int s = 0;
+            uint32_t ph = 0;
             for (int kb = 0; kb < num_kb; ++kb) {
-                const int s = kb % Cfg::kStages;
-                const uint32_t ph = (kb / Cfg::kStages) & 1;
                 mbar_wait(full_bar + s, ph);
                 tc_fence_after();
                 const uint32_t a_addr = smem_u32(smem + s * Cfg::kStageBytes);
@@ -203,22 +325,48 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                     umma_bf16_ss(tmem_base, da, db, idesc, (kb | k) ? 1u : 0u);
                 }
                 umma_commit(empty_bar + s);  // frees the smem stage when these MMAs retire
+                if (++s == num_stages) {
+                    s = 0;
+                    ph ^= 1;
+                }
             }
             umma_commit(accum_bar);
         }
     } else {
-        // ---------------- epilogue: warps 2..5, lane quarter = warp % 4
+        // ---------------- epilogue: warps 2..5, TMEM lane quarter = warp % 4, one accumulator row per thread
         const int quarter = warp & 3;
         const int row_in_tile = quarter * 32 + lane;
         const long long row = (long long)m0 + row_in_tile;
         const bool row_ok = row < p.M;
-        const long long res_row = p.res_row_mod > 0 ? (row % p.res_row_mod) : row;
+        const long long mod_row = p.aux_row_mod > 0 ? (row % p.aux_row_mod) : row;
         const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16);
+        const uint8_t* aux_row = aux_stage + row_in_tile * Cfg::kRowBf16;
+
+        // phase 0 (overlaps the main loop): this thread's residual / mask row -> shared memory, 16 bytes at a time
+        if (p.aux_mode && p.vec_ok) {
+            const __nv_bfloat16* src = p.aux + (p.aux_mode == 1 ? mod_row : row) * p.ld_aux + n0;
+            const uint32_t dst = smem_u32(aux_row);
+#pragma unroll 8
+            for (int j = 0; j < BN / 8; ++j) {
+                const bool ok = row_ok && (n0 + j * 8 + 8 <= p.N);
+                cp_async_16(dst + j * 16, ok ? static_cast<const void*>(src + j * 8) : static_cast<const void*>(p.aux),
+                            ok ? 16u : 0u);
+            }
+            cp_async_commit();
+        }
+
         mbar_wait(accum_bar, 0);
         tc_fence_after();
+        if (p.aux_mode && p.vec_ok) cp_async_wait_all();
+        // The pipeline stages are dead now (every TMA write landed and every MMA retired before accum_bar fired):
+        // they become the output staging area.
+        uint8_t* stage_a = smem;
         uint32_t v[32];
         float z[32];
         if (p.ln_gamma == nullptr) {
+            const bool f32out = p.out_f32 != nullptr;
+            const int rowb = f32out ? Cfg::kRowF32 : Cfg::kRowBf16;
+            uint8_t* my_row = stage_a + row_in_tile * rowb;
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
                 const int col0 = n0 + c * 32;
@@ -227,44 +375,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tmem_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 32; ++i) z[i] = __uint_as_float(v[i]);
-                if (row_ok) {
-                    epi_bias_res(z, p, res_row, col0);
-                    if (p.relu) {
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) z[i] = fmaxf(z[i], 0.f);
-                    }
-                    const int nv = p.N - col0;
-                    if (p.relu_mask) {
-                        const __nv_bfloat16* mk = p.relu_mask + row * p.ld_out + col0;
-                        if (nv >= 32 && ((reinterpret_cast<uintptr_t>(mk) & 15) == 0)) {
-#pragma unroll
-                            for (int q = 0; q < 4; ++q) {
-                                uint4 u = __ldg(reinterpret_cast<const uint4*>(mk) + q);
-                                const __nv_bfloat16* hm = reinterpret_cast<const __nv_bfloat16*>(&u);
-#pragma unroll
-                                for (int j = 0; j < 8; ++j)
-                                    if (!(__bfloat162float(hm[j]) > 0.f)) z[q * 8 + j] = 0.f;
-                            }
-                        } else {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (i < nv && !(__bfloat162float(mk[i]) > 0.f)) z[i] = 0.f;
-                        }
-                    }
-                    if (p.out_bf16) epi_store_bf16(p.out_bf16 + row * p.ld_out + col0, z, nv);
-                    if (p.out_f32) {
-                        if (p.atomic_out) {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                if (i < nv) atomicAdd(p.out_f32 + row * p.ld_out + col0 + i, z[i]);
-                        } else {
-                            epi_store_f32(p.out_f32 + row * p.ld_out + col0, z, nv);
-                        }
-                    }
-                }
+                if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, col0, c);
+                if (f32out) stage_f32(my_row + c * 128, z);
+                else stage_bf16(my_row + c * 64, z);
             }
+            __syncwarp();
+            const uint8_t* stage_warp = stage_a + quarter * 32 * rowb;
+            if (f32out)
+                drain_f32<BN>(stage_warp, p.out_f32, p.ld_out, p.M, p.N, (long long)m0 + quarter * 32, n0, lane,
+                              p.vec_ok != 0, p.atomic_out != 0);
+            else
+                drain_bf16<BN>(stage_warp, p.out_bf16, p.ld_out, p.M, p.N, (long long)m0 + quarter * 32, n0, lane,
+                               p.vec_ok != 0, p.colsum_out);
         } else {
             // LayerNorm over the whole row (N == BN == 256, n0 == 0). Three TMEM passes; z parked in TMEM.
+            uint8_t* stage_b = stage_a + GEMM_BM * Cfg::kRowBf16;  // pre-LN copy
+            uint8_t* my_a = stage_a + row_in_tile * Cfg::kRowBf16;
+            uint8_t* my_b = stage_b + row_in_tile * Cfg::kRowBf16;
             float sum = 0.f;
 #pragma unroll 1
             for (int c = 0; c < BN / 32; ++c) {
@@ -272,14 +399,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tmem_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 32; ++i) z[i] = __uint_as_float(v[i]);
-                if (row_ok) epi_bias_res(z, p, res_row, c * 32);
+                if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, c * 32, c);
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
                     sum += z[i];
                     v[i] = __float_as_uint(z[i]);
                 }
                 tmem_st_32x32b_x32(taddr + c * 32, v);
-                if (row_ok && p.pre_ln) epi_store_bf16(p.pre_ln + row * p.ld_out + c * 32, z, 32);
+                if (p.pre_ln) stage_bf16(my_b + c * 64, z);
             }
             tmem_st_wait();
             const float mean = sum * (1.f / BN);
@@ -307,11 +434,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 for (int i = 0; i < 32; ++i)
                     z[i] = (__uint_as_float(v[i]) - mean) * rstd * __ldg(p.ln_gamma + c * 32 + i) +
                            __ldg(p.ln_beta + c * 32 + i);
-                if (row_ok) {
-                    if (p.out_bf16) epi_store_bf16(p.out_bf16 + row * p.ld_out + c * 32, z, 32);
-                    if (p.out_f32) epi_store_f32(p.out_f32 + row * p.ld_out + c * 32, z, 32);
-                }
+                stage_bf16(my_a + c * 64, z);
             }
+            __syncwarp();
+            const long long row0 = (long long)m0 + quarter * 32;
+            drain_bf16<BN>(stage_a + quarter * 32 * Cfg::kRowBf16, p.out_bf16, p.ld_out, p.M, p.N, row0, 0, lane,
+                           p.vec_ok != 0, nullptr);
+            if (p.pre_ln)
+                drain_bf16<BN>(stage_b + quarter * 32 * Cfg::kRowBf16, p.pre_ln, p.ld_out, p.M, p.N, row0, 0, lane,
+                               p.vec_ok != 0, nullptr);
         }
         tc_fence_before();
     }
@@ -349,19 +480,39 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
         uint32_t box[2] = {GEMM_BK, (uint32_t)BN};
         if (make_tmap_bf16(&tmB, a->w, 2, dims, str, box, 128)) return fod_fail(FOD_E_TMAP, "gemm: tmap B");
     }
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             Cfg::kSmemBytes);
-        attr_set = true;
-    }
+    const bool aux = epi.aux_mode != 0;
+    // stage count: the pipeline stages double as output staging, so they must hold the staged tile
+    int stages = BN == 256 ? (aux ? 3 : 4) : (BN == 128 ? 4 : 3);
     const int total_kb = (a->K + GEMM_BK - 1) / GEMM_BK;
-    int splits = a->split_k > 1 ? a->split_k : 1;
+    const int mt = (a->M + GEMM_BM - 1) / GEMM_BM, nt = (a->N + BN - 1) / BN;
+    int splits = 1;
+    if (a->split_k > 1) splits = a->split_k;
+    else if (a->split_k < 0) {  // auto: fill the 148 SMs, at least two k-blocks per split
+        splits = (148 + mt * nt - 1) / (mt * nt);
+        if (splits > total_kb / 2) splits = total_kb / 2;
+        if (splits < 1) splits = 1;
+    }
     if (splits > total_kb) splits = total_kb;
     epi.kb_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + epi.kb_per_split - 1) / epi.kb_per_split;  // no empty split
-    dim3 grid((a->N + BN - 1) / BN, (a->M + GEMM_BM - 1) / GEMM_BM, splits);
-    gemm_bf16_kernel<BN, A_MN, B_MN><<<grid, GEMM_THREADS, Cfg::kSmemBytes, st>>>(tmA, tmB, epi);
+    if (a->split_k < 0 && !a->atomic_out) {  // overwrite semantics: plain stores, or zero-fill + reductions
+        if (splits > 1) {
+            if (a->ld_out != a->N) return fod_fail(FOD_E_ARG, "gemm: auto split-K needs a dense fp32 output");
+            cudaMemsetAsync(a->out_f32, 0, sizeof(float) * (size_t)a->M * a->N, st);
+            epi.atomic_out = 1;
+        }
+    }
+    epi.num_stages = stages;
+    const int smem_bytes = Cfg::smem_bytes(stages, aux);
+    static bool attr_set = false;
+    if (!attr_set) {
+        const int a1 = Cfg::smem_bytes(BN == 256 ? 3 : stages, true), a2 = Cfg::smem_bytes(stages, false);
+        cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             a1 > a2 ? a1 : a2);
+        attr_set = true;
+    }
+    dim3 grid(nt, mt, splits);
+    gemm_bf16_kernel<BN, A_MN, B_MN><<<grid, GEMM_THREADS, smem_bytes, st>>>(tmA, tmB, epi);
     return fod_check_launch("gemm_bf16_kernel");
 }
 
@@ -371,6 +522,21 @@ static int launch_gemm_major(const fod_linear_args* a, const GemmEpi& e, cudaStr
     if (a->b_mn) return launch_gemm<BN, false, true>(a, e, st);
     if (a->a_mn) return fod_fail(FOD_E_ARG, "gemm: A MN-major with B K-major is not instantiated");
     return launch_gemm<BN, false, false>(a, e, st);
+}
+
+// Largest N tile that still yields >= half a wave of CTAs; small problems take the narrowest tile (more CTAs, a
+// 4x shorter epilogue per CTA).  LayerNorm needs the whole 256-wide row in one CTA.
+static int pick_bn(const fod_linear_args* a) {
+    if (a->ln_gamma) return 256;
+    if (a->N <= 64) return 64;
+    const int mt = (a->M + GEMM_BM - 1) / GEMM_BM;
+    const int cands[3] = {256, 128, 64};
+    for (int i = 0; i < 3; ++i) {
+        const int bn = cands[i];
+        if (bn == 256 && a->N <= 128) continue;
+        if (mt * ((a->N + bn - 1) / bn) >= 74) return bn;
+    }
+    return 64;
 }
 
 }  // namespace fod
@@ -384,18 +550,22 @@ extern "C" int fod_linear_fwd(const fod_linear_args* a, void* stream) {
     if (a->b_mn ? (a->N % 8) : (a->K % 8)) return fod_fail(FOD_E_ARG, "linear: W inner extent must be a multiple of 8");
     if ((reinterpret_cast<uintptr_t>(a->x) | reinterpret_cast<uintptr_t>(a->w)) & 15)
         return fod_fail(FOD_E_ARG, "linear: x/w must be 16-byte aligned");
-    if (a->ln_gamma && (a->N != 256 || !a->ln_beta || a->relu || a->split_k > 1 || a->relu_mask))
-        return fod_fail(FOD_E_ARG, "linear: LayerNorm epilogue needs N == 256, beta, no relu/mask/split");
+    if (a->ln_gamma && (a->N != 256 || !a->ln_beta || a->relu || a->split_k > 1 || a->relu_mask || a->out_f32 || !a->out_bf16))
+        return fod_fail(FOD_E_ARG, "linear: LayerNorm epilogue needs N == 256, beta, bf16 output, no relu/mask/split");
     if (!a->out_bf16 && !a->out_f32) return fod_fail(FOD_E_ARG, "linear: no output");
-    if (a->split_k > 1 && (!a->atomic_out || !a->out_f32 || a->out_bf16 || a->relu || a->bias || a->residual))
-        return fod_fail(FOD_E_ARG, "linear: split_k needs atomic fp32 output and a plain epilogue");
+    if (a->out_bf16 && a->out_f32) return fod_fail(FOD_E_ARG, "linear: one output (bf16 or fp32)");
+    if (a->residual && a->relu_mask) return fod_fail(FOD_E_ARG, "linear: residual and relu_mask are exclusive");
+    if ((a->split_k > 1 || a->split_k < 0) && (!a->out_f32 || a->relu || a->bias || a->residual || a->relu_mask))
+        return fod_fail(FOD_E_ARG, "linear: split_k needs fp32 output and a plain epilogue");
+    if (a->split_k > 1 && !a->atomic_out) return fod_fail(FOD_E_ARG, "linear: explicit split_k needs atomic_out");
+    if (a->atomic_out && !a->out_f32) return fod_fail(FOD_E_ARG, "linear: atomic_out needs out_f32");
+    if (a->colsum_out && (!a->out_bf16 || a->ln_gamma)) return fod_fail(FOD_E_ARG, "linear: colsum_out needs a plain bf16 output");
     GemmEpi e;
     e.bias = a->bias;
-    e.residual = reinterpret_cast<const __nv_bfloat16*>(a->residual);
-    e.relu_mask = reinterpret_cast<const __nv_bfloat16*>(a->relu_mask);
     e.col_scale = a->col_scale;
     e.atomic_out = a->atomic_out;
     e.kb_per_split = 0;
+    e.num_stages = 0;
     e.ln_gamma = a->ln_gamma;
     e.ln_beta = a->ln_beta;
     e.out_bf16 = reinterpret_cast<__nv_bfloat16*>(a->out_bf16);
@@ -403,16 +573,37 @@ extern "C" int fod_linear_fwd(const fod_linear_args* a, void* stream) {
     e.pre_ln = reinterpret_cast<__nv_bfloat16*>(a->pre_ln_bf16);
     e.ln_mean = a->ln_mean;
     e.ln_rstd = a->ln_rstd;
-    e.ld_res = a->ld_res;
+    e.colsum_out = a->colsum_out;
     e.ld_out = a->ld_out;
     e.M = a->M;
     e.N = a->N;
     e.K = a->K;
-    e.res_row_mod = a->res_row_mod;
     e.relu = a->relu;
     e.ln_eps = a->ln_eps;
+    e.aux = nullptr;
+    e.ld_aux = 0;
+    e.aux_mode = 0;
+    e.aux_row_mod = a->res_row_mod;  // also indexes col_scale
+    if (a->residual) {
+        e.aux = reinterpret_cast<const __nv_bfloat16*>(a->residual);
+        e.ld_aux = a->ld_res;
+        e.aux_mode = 1;
+    } else if (a->relu_mask) {
+        e.aux = reinterpret_cast<const __nv_bfloat16*>(a->relu_mask);
+        e.ld_aux = a->ld_out;
+        e.aux_mode = 2;
+    }
+    // 16-byte vector paths: every row start and every 8-column (bf16) / 4-column (fp32) chunk must be aligned
+    bool vec = (a->N % 8 == 0);
+    if (a->out_bf16) vec = vec && (a->ld_out % 8 == 0) && !(reinterpret_cast<uintptr_t>(a->out_bf16) & 15);
+    if (a->out_f32) vec = vec && (a->ld_out % 4 == 0) && !(reinterpret_cast<uintptr_t>(a->out_f32) & 15);
+    if (a->pre_ln_bf16) vec = vec && !(reinterpret_cast<uintptr_t>(a->pre_ln_bf16) & 15);
+    if (e.aux) vec = vec && (e.ld_aux % 8 == 0) && !(reinterpret_cast<uintptr_t>(e.aux) & 15);
+    e.vec_ok = vec ? 1 : 0;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-    if (a->ln_gamma || a->N > 128) return launch_gemm_major<256>(a, e, st);
-    if (a->N > 64) return launch_gemm_major<128>(a, e, st);
-    return launch_gemm_major<64>(a, e, st);
+    switch (pick_bn(a)) {
+        case 256: return launch_gemm_major<256>(a, e, st);
+        case 128: return launch_gemm_major<128>(a, e, st);
+        default: return launch_gemm_major<64>(a, e, st);
+    }
 }

@@ -86,16 +86,18 @@ __global__ void __launch_bounds__(RO_WARPS * 32)
 ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ dy2,
               const __nv_bfloat16* __restrict__ pre, const __nv_bfloat16* __restrict__ bcast, int rows_per_group,
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
-              __nv_bfloat16* __restrict__ dz, float* __restrict__ dgamma, float* __restrict__ dbeta, long long M) {
-    __shared__ float red[2][RO_WARPS][RO_D];
+              __nv_bfloat16* __restrict__ dz, float* __restrict__ dgamma, float* __restrict__ dbeta,
+              float* __restrict__ dzsum, long long M) {
+    __shared__ float red[3][RO_WARPS][RO_D];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c0 = lane * 8;
-    float g[8], ag[8], ab[8];
+    float g[8], ag[8], ab[8], az[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         g[j] = __ldg(gamma + c0 + j);
         ag[j] = 0.f;
         ab[j] = 0.f;
+        az[j] = 0.f;
     }
     const long long stride = (long long)gridDim.x * RO_WARPS;
     for (long long row = (long long)blockIdx.x * RO_WARPS + warp; row < M; row += stride) {
@@ -129,40 +131,82 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
         s2 = warp_sum(s2) * (1.f / RO_D);
         float o[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) o[j] = rstd * (d[j] * g[j] - s1 - xh[j] * s2);
+        for (int j = 0; j < 8; ++j) {
+            o[j] = rstd * (d[j] * g[j] - s1 - xh[j] * s2);
+            az[j] += o[j];
+        }
         store8(dz + row * RO_D + c0, o);
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         red[0][warp][c0 + j] = ag[j];
         red[1][warp][c0 + j] = ab[j];
+        red[2][warp][c0 + j] = az[j];
     }
     __syncthreads();
     for (int c = threadIdx.x; c < RO_D; c += RO_WARPS * 32) {
-        float sg = 0.f, sb = 0.f;
+        float sg = 0.f, sb = 0.f, sz = 0.f;
 #pragma unroll
         for (int w = 0; w < RO_WARPS; ++w) {
             sg += red[0][w][c];
             sb += red[1][w][c];
+            sz += red[2][w][c];
         }
         if (dgamma) atomicAdd(dgamma + c, sg);
         if (dbeta) atomicAdd(dbeta + c, sb);
+        if (dzsum) atomicAdd(dzsum + c, sz);  // bias gradient of the linear layer feeding this LayerNorm
     }
 }
 
-// out[g][c] += sum over the rows of group g of x[row][c];  one CTA handles a strip of rows of one group.
+// out[g][c] += sum over the rows of group g of x[row][c].  A CTA owns a strip of rows of one group and a 256-column
+// slab: 32 lanes x 8 columns (one 16-byte load) per row, 8 warps on 8 different rows, 4 independent loads in flight
+// per thread; the 8 warps are combined through shared memory and one atomic per column leaves the CTA.
 __global__ void __launch_bounds__(256)
 colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, float* __restrict__ out, int N, int rows_per_group,
-              int strips_per_group, int rows_per_strip) {
+              int strips_per_group, int rows_per_strip, int vec_ok) {
+    __shared__ float red[8][256];
     const int g = blockIdx.x / strips_per_group;
     const int strip = blockIdx.x % strips_per_group;
     const int r0 = strip * rows_per_strip;
     const int r1 = min(rows_per_group, r0 + rows_per_strip);
-    for (int c = blockIdx.y * 256 + threadIdx.x; c < N; c += gridDim.y * 256) {
-        float s = 0.f;
-        const __nv_bfloat16* px = x + ((long long)g * rows_per_group + r0) * ldx + c;
-        for (int r = r0; r < r1; ++r, px += ldx) s += __bfloat162float(*px);
-        atomicAdd(out + (long long)g * N + c, s);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c0 = blockIdx.y * 256 + lane * 8;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    const __nv_bfloat16* base = x + (long long)g * rows_per_group * ldx + c0;
+    if (vec_ok && c0 + 8 <= N) {
+        int r = r0 + warp;
+        for (; r + 24 < r1; r += 32) {
+            float f[4][8];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) load8(base + (long long)(r + 8 * u) * ldx, f[u]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += f[u][j];
+        }
+        for (; r < r1; r += 8) {
+            float f[8];
+            load8(base + (long long)r * ldx, f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += f[j];
+        }
+    } else {
+        for (int r = r0 + warp; r < r1; r += 8)
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (c0 + j < N) acc[j] += __bfloat162float(base[(long long)r * ldx + j]);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) red[warp][lane * 8 + j] = acc[j];
+    __syncthreads();
+    const int c = blockIdx.y * 256 + threadIdx.x;
+    if (c < N) {
+        float s2 = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s2 += red[w][threadIdx.x];
+        atomicAdd(out + (long long)g * N + c, s2);
     }
 }
 
@@ -189,13 +233,13 @@ extern "C" int fod_add_ln_fwd(const void* x, const void* bcast, int32_t rows_per
 
 extern "C" int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bcast, int32_t rows_per_group,
                           const float* mean, const float* rstd, const float* gamma, void* dz, float* dgamma,
-                          float* dbeta, int64_t M, void* stream) {
+                          float* dbeta, float* dzsum, int64_t M, void* stream) {
     if (!dy || !pre || !mean || !rstd || !gamma || !dz || M <= 0) return fod_fail(FOD_E_ARG, "ln_bwd: null/empty");
     if (bcast && rows_per_group <= 0) return fod_fail(FOD_E_ARG, "ln_bwd: rows_per_group");
     ln_bwd_kernel<<<ro_grid(M), RO_WARPS * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
         reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(dy2),
         reinterpret_cast<const __nv_bfloat16*>(pre), reinterpret_cast<const __nv_bfloat16*>(bcast), rows_per_group, mean,
-        rstd, gamma, reinterpret_cast<__nv_bfloat16*>(dz), dgamma, dbeta, M);
+        rstd, gamma, reinterpret_cast<__nv_bfloat16*>(dz), dgamma, dbeta, dzsum, M);
     return fod_check_launch("ln_bwd_kernel");
 }
 
@@ -205,14 +249,16 @@ extern "C" int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int
     if (rows_per_group <= 0) rows_per_group = (int32_t)M;
     if (M % rows_per_group) return fod_fail(FOD_E_ARG, "colsum: M must be a multiple of rows_per_group");
     const int groups = (int)(M / rows_per_group);
-    int strips = (148 * 4 + groups - 1) / groups;
-    const int max_strips = (rows_per_group + 31) / 32;
+    const int col_slabs = (N + 255) / 256;
+    int strips = (148 * 2 + groups * col_slabs - 1) / (groups * col_slabs);
+    const int max_strips = (rows_per_group + 63) / 64;
     if (strips > max_strips) strips = max_strips;
     if (strips < 1) strips = 1;
     const int rows_per_strip = (rows_per_group + strips - 1) / strips;
     strips = (rows_per_group + rows_per_strip - 1) / rows_per_strip;
-    dim3 grid(groups * strips, (N + 255) / 256);
+    dim3 grid(groups * strips, col_slabs);
+    const int vec_ok = (ldx % 8 == 0) && !(reinterpret_cast<uintptr_t>(x) & 15);
     colsum_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        reinterpret_cast<const __nv_bfloat16*>(x), ldx, out, N, rows_per_group, strips, rows_per_strip);
+        reinterpret_cast<const __nv_bfloat16*>(x), ldx, out, N, rows_per_group, strips, rows_per_strip, vec_ok);
     return fod_check_launch("colsum_kernel");
 }

@@ -9,7 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfod_b200.so")
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 FOD_OK, FOD_E_ARG, FOD_E_TMAP, FOD_E_LAUNCH, FOD_E_NUMERIC = 0, 1, 2, 3, 4
 
@@ -28,6 +28,7 @@ class LinearArgs(C.Structure):
         ("ln_eps", C.c_float),
         ("relu_mask", C.c_void_p), ("col_scale", C.c_void_p), ("ldw", C.c_int64),
         ("a_mn", C.c_int32), ("b_mn", C.c_int32), ("split_k", C.c_int32), ("atomic_out", C.c_int32),
+        ("colsum_out", C.c_void_p),
     ]
 
 
@@ -81,7 +82,7 @@ SYMBOLS = {
     "fod_attn_fwd": (C.c_int, [C.POINTER(AttnArgs), _VP]),
     "fod_attn_bwd": (C.c_int, [C.POINTER(AttnBwdArgs), _VP]),
     "fod_add_ln_fwd": (C.c_int, [_VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _I64, _F, _VP]),
-    "fod_ln_bwd": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _VP]),
+    "fod_ln_bwd": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_colsum": (C.c_int, [_VP, _I64, _VP, _I64, _I32, _I32, _VP]),
     "fod_targets_compact": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _F, _F, _VP]),
     "fod_match": (C.c_int, [C.POINTER(MatchArgs), _VP]),

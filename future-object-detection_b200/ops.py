@@ -31,11 +31,14 @@ def _chk_bf16(t, name):
 
 
 def gemm(x, w, bias=None, residual=None, res_row_mod=0, relu=False, ln=None, out_f32=False, save_ln=False,
-         relu_mask=None, col_scale=None, a_mn=False, b_mn=False, split_k=1, accum_into=None, M=None, N=None, K=None):
+         relu_mask=None, col_scale=None, a_mn=False, b_mn=False, split_k=1, accum_into=None, M=None, N=None, K=None,
+         colsum_out=None, out=None):
     """Y = epi(op(x) · op(w)ᵀ) on the tcgen05 GEMM.  x (M,K) [or (K,M) if a_mn], w (N,K) [or (K,N) if b_mn].
 
     Returns y (bf16, or fp32 if out_f32); with ln=(gamma, beta, eps) and save_ln also (pre_ln, mean, rstd).
-    accum_into: fp32 (M,N) tensor that receives atomic adds (split-K weight gradients)."""
+    accum_into: fp32 (M,N) tensor that receives vector reductions (weight gradients accumulated in place; the library
+    picks the split-K factor).  split_k=-1 with out_f32: library-chosen split-K with overwrite semantics.
+    colsum_out: fp32 (N,) that receives += column sums of the bf16 output (a fused bias gradient)."""
     L = lib.load()
     _chk_bf16(x, "gemm x")
     _chk_bf16(w, "gemm w")
@@ -68,15 +71,20 @@ def gemm(x, w, bias=None, residual=None, res_row_mod=0, relu=False, ln=None, out
     outs = []
     if accum_into is not None:
         assert accum_into.dtype == torch.float32 and accum_into.is_contiguous() and accum_into.shape == (M, N)
-        a.out_f32, a.atomic_out, a.split_k = _p(accum_into), 1, max(1, split_k)
+        a.out_f32, a.atomic_out, a.split_k = _p(accum_into), 1, (split_k if split_k > 1 else -1)
         y = accum_into
     elif out_f32:
-        y = torch.empty((M, N), dtype=torch.float32, device=x.device)
+        y = out if out is not None else torch.empty((M, N), dtype=torch.float32, device=x.device)
         a.out_f32 = _p(y)
+        if split_k < 0:
+            a.split_k = -1
     else:
         y = torch.empty((M, N), dtype=BF16, device=x.device)
         a.out_bf16 = _p(y)
     a.ld_out = N
+    if colsum_out is not None:
+        assert colsum_out.dtype == torch.float32 and colsum_out.numel() == N and accum_into is None and not out_f32
+        a.colsum_out = _p(colsum_out)
     outs.append(y)
     if ln is not None:
         gamma, beta, eps = ln
@@ -208,8 +216,9 @@ def add_ln_fwd(x, gamma, beta, eps=1e-5, bcast=None, rows_per_group=0, save=Fals
     return (y, mean, rstd) if save else y
 
 
-def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows_per_group=0):
-    """LayerNorm backward: returns dz (bf16); accumulates into fp32 dgamma / dbeta (256,)."""
+def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows_per_group=0, dzsum=None):
+    """LayerNorm backward: returns dz (bf16); accumulates into fp32 dgamma / dbeta (256,) and, if given, the column
+    sums of dz into dzsum (256,) — the bias gradient of the linear layer that feeds the norm."""
     L = lib.load()
     _chk_bf16(dy, "ln_bwd dy")
     _chk_bf16(pre, "ln_bwd pre")
@@ -218,7 +227,7 @@ def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows
     dz = torch.empty_like(pre)
     _t = prof.begin()
     lib.check(L.fod_ln_bwd(_p(dy), _p(dy2), _p(pre), _p(bcast), rows_per_group, _p(mean), _p(rstd), _p(gamma), _p(dz),
-                           _p(dgamma), _p(dbeta), M, _stream()), "fod_ln_bwd")
+                           _p(dgamma), _p(dbeta), _p(dzsum), M, _stream()), "fod_ln_bwd")
     prof.end(_t, "ln_bwd", 0.0, 1536.0 * M)
     LAUNCH_COUNTS["ln_bwd_kernel"] += 1
     return dz

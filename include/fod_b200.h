@@ -59,8 +59,11 @@ typedef struct fod_linear_args {
     int64_t ldw;            /* row stride of w; 0 = contiguous */
     int32_t a_mn;           /* 1: x is stored (K, M) row-major (contraction outermost) — dW = dYᵀ·X */
     int32_t b_mn;           /* 1: w is stored (K, N) row-major — dX = dY·W with W in its nn.Linear layout */
-    int32_t split_k;        /* >1: split the contraction over grid.z; needs atomic_out */
-    int32_t atomic_out;     /* 1: out_f32 += result (atomic adds into a caller-initialised buffer) */
+    int32_t split_k;        /* >1: split the contraction over grid.z (needs atomic_out); <0: the library picks the
+                               split and, without atomic_out, zero-fills out_f32 itself when it splits */
+    int32_t atomic_out;     /* 1: out_f32 += result (vector reductions into a caller-initialised buffer) */
+    float* colsum_out;      /* (N) fp32 or NULL: += column sums of the stored bf16 output — the bias gradient of the
+                               layer that produced the GEMM's input gradient (transformer.py:407-410 backward) */
 } fod_linear_args;
 int fod_linear_fwd(const fod_linear_args* a, void* stream);  /* also the backward GEMMs via a_mn / b_mn */
 
@@ -120,6 +123,7 @@ int fod_add_ln_fwd(const void* x, const void* bcast, int32_t rows_per_group, con
                    void* y, float* mean_out, float* rstd_out, int64_t M, float eps, void* stream);
 int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bcast, int32_t rows_per_group,
                const float* mean, const float* rstd, const float* gamma, void* dz, float* dgamma, float* dbeta,
+               float* dzsum /* (256) or NULL: += column sums of dz = bias gradient of the linear feeding the norm */,
                int64_t M, void* stream);
 int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int32_t rows_per_group, void* stream);
 

@@ -63,6 +63,45 @@ def test_gemm_backward_forms(M, N, K):
     _close(dw, dy.float().t() @ x.float(), tol=5e-3, what="dW")
 
 
+@pytest.mark.parametrize("M,N,K", [(1024, 256, 256), (5600, 2048, 256), (1024, 2048, 256), (200, 128, 64), (130, 64, 512),
+                                   (5600, 512, 256), (127, 768, 264)])
+def test_gemm_tile_shapes_fused_colsum_and_accumulate(M, N, K):
+    """Every N-tile width (64/128/256 chosen by the library from the grid size), ragged M/N/K edges, the fused
+    column-sum (bias-gradient) epilogue, in-place gradient accumulation and library-chosen split-K."""
+    from fod_b200 import ops
+    dy, w = _rnd(M, N, seed=11), _rnd(N, K, scale=0.06, seed=12)
+    mask = _rnd(M, K, seed=13)
+    cs = torch.zeros(K, device=_dev())
+    dx = ops.gemm(dy, w, b_mn=True, relu_mask=mask, colsum_out=cs)
+    ref = (dy.float() @ w.float()) * (mask.float() > 0)
+    _close(dx, ref, what="dX mask")
+    _close(cs, dx.float().sum(0), tol=3e-3, what="fused colsum == colsum of the stored bf16 output")
+    _close(cs, ref.sum(0), tol=2e-2, what="fused colsum vs fp32")
+    x = _rnd(M, K, seed=14)
+    ref_dw = dy.float().t() @ x.float()
+    acc = torch.full((N, K), 0.5, device=_dev())
+    ops.gemm(dy, x, a_mn=True, b_mn=True, accum_into=acc)
+    _close(acc, ref_dw + 0.5, tol=5e-3, what="dW accumulated in place")
+    out = torch.full((N, K), 7.0, device=_dev())  # overwrite semantics: stale contents must not leak through
+    ops.gemm(dy, x, a_mn=True, b_mn=True, out_f32=True, split_k=-1, out=out)
+    _close(out, ref_dw, tol=5e-3, what="dW auto split-K overwrite")
+    xin, wf = _rnd(M, K, seed=15), _rnd(N, K, scale=0.06, seed=16)
+    b = torch.randn(N, device=_dev())
+    res = _rnd(M, N, seed=17)
+    _close(ops.gemm(xin, wf, bias=b, residual=res, relu=True), (xin.float() @ wf.float().t() + b + res.float()).relu(),
+           what="fwd bias+residual+relu")
+
+
+def test_gemm_unaligned_output_falls_back_to_scalar_stores():
+    from fod_b200 import ops
+    M, N, K = 300, 256, 256
+    x, w = _rnd(M, K, seed=21), _rnd(N, K, scale=0.06, seed=22)
+    res_full = _rnd(M, N + 8, seed=23)
+    res = res_full[:, 4:4 + N]  # 8-byte-aligned rows only: the residual cannot use the 16-byte cp.async path
+    assert res.data_ptr() % 16 != 0
+    _close(ops.gemm(x, w, residual=res), x.float() @ w.float().t() + res.float(), what="unaligned residual")
+
+
 @pytest.mark.parametrize("B,Lq,Lk,two,bcast", [(2, 350, 350, False, False), (3, 128, 350, True, True),
                                                  (2, 128, 128, False, False), (1, 700, 700, False, False),
                                                  (2, 100, 3, False, False), (2, 128, 1400, True, True)])
@@ -127,8 +166,10 @@ def test_row_kernels(M, rpg):
     dy = _rnd(M, 256, seed=3)
     ref.backward(dy.float())
     dg, db = torch.zeros(256, device=_dev()), torch.zeros(256, device=_dev())
-    dz = ops.ln_bwd(dy, x, mean, rstd, gam, dg, db, bcast=bc, rows_per_group=rpg)
+    dzs = torch.zeros(256, device=_dev())
+    dz = ops.ln_bwd(dy, x, mean, rstd, gam, dg, db, bcast=bc, rows_per_group=rpg, dzsum=dzs)
     _close(dz, z.grad, what="ln_bwd dz")
+    _close(dzs, z.grad.sum(0), tol=1e-2, what="ln_bwd fused column sum of dz")
     _close(dg, g32.grad, tol=1e-2, what="dgamma")
     _close(db, b32.grad, tol=1e-2, what="dbeta")
     cs = ops.colsum(dy, rpg)
