@@ -50,7 +50,8 @@ struct GemmCfg {
     static constexpr int kRowF32 = BN * 4 + 16;
     static constexpr int kAuxBytes = GEMM_BM * kRowBf16;
     static constexpr int kTmemCols = BN < 32 ? 32 : BN;
-    static constexpr int kBarBytes = 256;
+    static constexpr int kParamBytes = 3 * BN * 4;  // bias / gamma / beta slices of this N tile, fp32
+    static constexpr int kBarBytes = 256 + kParamBytes;
     static int smem_bytes(int stages, bool aux) { return 1024 + stages * kStageBytes + (aux ? kAuxBytes : 0) + kBarBytes; }
 };
 
@@ -86,11 +87,16 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
 // bias, col_scale, staged residual, ReLU, staged mask on 32 accumulator columns [col0, col0+32) of one row
 template <int BN>
 __device__ __forceinline__ void epi_chunk(float (&z)[32], const GemmEpi& p, const uint8_t* aux_row, long long row,
-                                          long long mod_row, int col0, int c) {
+                                          long long mod_row, int col0, int c, const float* s_bias) {
     if (p.bias) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-            if (col0 + i < p.N) z[i] += __ldg(p.bias + col0 + i);
+        for (int q = 0; q < 8; ++q) {
+            const float4 b4 = *reinterpret_cast<const float4*>(s_bias + c * 32 + q * 4);  // smem broadcast
+            z[q * 4] += b4.x;
+            z[q * 4 + 1] += b4.y;
+            z[q * 4 + 2] += b4.z;
+            z[q * 4 + 3] += b4.w;
+        }
     }
     if (p.col_scale) {
         const float* sc = p.col_scale + mod_row * (long long)p.N + col0;
@@ -239,7 +245,7 @@ __device__ __forceinline__ void drain_f32(const uint8_t* stage_warp, float* out,
 }
 
 template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 2)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmEpi p) {
     using Cfg = GemmCfg<BN>;
     extern __shared__ uint8_t smem_raw[];
@@ -249,6 +255,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint64_t* empty_bar = full_bar + GEMM_MAX_STAGES;
     uint64_t* accum_bar = empty_bar + GEMM_MAX_STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+    float* s_bias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full_bar) + 256);
+    float* s_gamma = s_bias + BN;
+    float* s_beta = s_gamma + BN;
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -342,7 +351,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16);
         const uint8_t* aux_row = aux_stage + row_in_tile * Cfg::kRowBf16;
 
-        // phase 0 (overlaps the main loop): this thread's residual / mask row -> shared memory, 16 bytes at a time
+        // phase 0 (overlaps the main loop): per-column parameters of this N tile -> shared memory (coalesced, once),
+        const int et = threadIdx.x - 64;  // 0..127 over the four epilogue warps
+        for (int i = et; i < BN; i += 128) {
+            const bool ok = n0 + i < p.N;
+            s_bias[i] = (p.bias && ok) ? __ldg(p.bias + n0 + i) : 0.f;
+            if (p.ln_gamma) {
+                s_gamma[i] = ok ? __ldg(p.ln_gamma + n0 + i) : 0.f;
+                s_beta[i] = ok ? __ldg(p.ln_beta + n0 + i) : 0.f;
+            }
+        }
+        // ... and this thread's residual / mask row -> shared memory, 16 bytes at a time
         if (p.aux_mode && p.vec_ok) {
             const __nv_bfloat16* src = p.aux + (p.aux_mode == 1 ? mod_row : row) * p.ld_aux + n0;
             const uint32_t dst = smem_u32(aux_row);
@@ -355,6 +374,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             cp_async_commit();
         }
 
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // parameter slices visible to the four epilogue warps
         mbar_wait(accum_bar, 0);
         tc_fence_after();
         if (p.aux_mode && p.vec_ok) cp_async_wait_all();
@@ -375,7 +395,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tmem_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 32; ++i) z[i] = __uint_as_float(v[i]);
-                if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, col0, c);
+                if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, col0, c, s_bias);
                 if (f32out) stage_f32(my_row + c * 128, z);
                 else stage_bf16(my_row + c * 64, z);
             }
@@ -399,7 +419,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tmem_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 32; ++i) z[i] = __uint_as_float(v[i]);
-                if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, c * 32, c);
+                if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, c * 32, c, s_bias);
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
                     sum += z[i];
@@ -432,8 +452,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tmem_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 32; ++i)
-                    z[i] = (__uint_as_float(v[i]) - mean) * rstd * __ldg(p.ln_gamma + c * 32 + i) +
-                           __ldg(p.ln_beta + c * 32 + i);
+                    z[i] = (__uint_as_float(v[i]) - mean) * rstd * s_gamma[c * 32 + i] + s_beta[c * 32 + i];
                 stage_bf16(my_a + c * 64, z);
             }
             __syncwarp();
@@ -495,6 +514,16 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     if (splits > total_kb) splits = total_kb;
     epi.kb_per_split = (total_kb + splits - 1) / splits;
     splits = (total_kb + epi.kb_per_split - 1) / epi.kb_per_split;  // no empty split
+    // Short contractions (K <= 256: every projection of the 256-wide model) need no deep pipeline: with 2 stages two
+    // CTAs fit one SM (smem and the 512 TMEM columns), so one CTA's epilogue overlaps the other's main loop.  The
+    // stages must still hold the staged output tile (and the pre-LN copy for the LayerNorm epilogue).
+    {
+        const int need = a->out_f32 ? GEMM_BM * Cfg::kRowF32 : GEMM_BM * Cfg::kRowBf16 * (a->pre_ln_bf16 ? 2 : 1);
+        int min_stages = (need + Cfg::kStageBytes - 1) / Cfg::kStageBytes;
+        if (min_stages < 2) min_stages = 2;
+        const int want = epi.kb_per_split < min_stages ? min_stages : epi.kb_per_split;
+        if (want < stages) stages = want;
+    }
     if (a->split_k < 0 && !a->atomic_out) {  // overwrite semantics: plain stores, or zero-fill + reductions
         if (splits > 1) {
             if (a->ld_out != a->N) return fod_fail(FOD_E_ARG, "gemm: auto split-K needs a dense fp32 output");
@@ -506,7 +535,7 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     const int smem_bytes = Cfg::smem_bytes(stages, aux);
     static bool attr_set = false;
     if (!attr_set) {
-        const int a1 = Cfg::smem_bytes(BN == 256 ? 3 : stages, true), a2 = Cfg::smem_bytes(stages, false);
+        const int a1 = Cfg::smem_bytes(BN == 256 ? 3 : (BN == 128 ? 4 : 3), true), a2 = Cfg::smem_bytes(BN == 64 ? 3 : 4, false);
         cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              a1 > a2 ? a1 : a2);
         attr_set = true;
