@@ -175,11 +175,18 @@ def run_cuda(args):
     model.train()
     core = model
     use_graph = bool(args.graphs)
-    opt = T.setup_optimizer(core, detr_args, capturable=use_graph)
+    flat = None
+    if args.flat:
+        # flat arenas: parameters / gradients / moments / bf16 operand copies share one layout; the gradient average is
+        # an all-reduce over arena slices and clip + AdamW + casts + zero_grad are one fused call (fod_b200/optim.py)
+        from fod_b200.optim import FlatTrainState
+        flat = FlatTrainState(core, lr=detr_args.lr, lr_backbone=detr_args.lr_backbone,
+                              weight_decay=detr_args.weight_decay, bucket_mb=args.bucket_mb)
+    opt = flat if flat is not None else T.setup_optimizer(core, detr_args, capturable=use_graph)
     # N > 1: gradients are averaged by the graph-capturable bucketed reducer (fod_b200/ddp.py: flat fp32 buckets,
     # NCCL AVG on a side stream overlapping backward) instead of torch's host-driven DDP wrapper
     reducer = None
-    if world > 1 or args.flat_grads:
+    if flat is None and (world > 1 or args.flat_grads):
         from fod_b200.ddp import BucketedGradReducer
         reducer = BucketedGradReducer(core.parameters(), bucket_mb=args.bucket_mb)
     train_step = T.TrainStep(model, opt, detr_args.max_norm, distributed=world > 1, reducer=reducer)
@@ -262,6 +269,7 @@ def run_cuda(args):
             "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "parallelism": "dp%d" % world,
                        "l2": "no explicit flush: one step streams >10 GB of activations through the 126 MB L2",
                        "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": 0.0, "cuda_graph": use_graph,
+                       "optimizer": "fused flat clip+AdamW (fod_flat_adamw_step)" if flat is not None else "torch fused AdamW",
                        "grad_allreduce": ("bucketed NCCL AVG, %g MB fp32 buckets, side stream inside the graph" % args.bucket_mb) if world > 1 else None},
             "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
             "matcher_status_by_region": status_log, "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
@@ -291,6 +299,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--graphs", type=int, default=1, help="1: replay the whole step as one CUDA graph (single GPU)")
     ap.add_argument("--kernel-events", type=int, default=1, help="1: bracket each of our kernel launches with CUDA events")
+    ap.add_argument("--flat", type=int, default=1, help="1: flat parameter/gradient arenas with the fused clip+AdamW kernel")
     ap.add_argument("--flat-grads", type=int, default=0, help="1: use the flat-bucket gradient path at N=1 too")
     ap.add_argument("--bucket-mb", type=float, default=32.0)
     ap.add_argument("--profiler-range", type=int, default=0, help="1: cudaProfilerStart/Stop around the timed steps (for ncu)")

@@ -21,36 +21,42 @@ import torch.distributed as dist
 
 
 class BucketedGradReducer:
-    def __init__(self, params, bucket_mb=32.0, group=None, overlap=True):
+    def __init__(self, params, bucket_mb=32.0, group=None, overlap=True, order=None):
+        """params: iterable of parameters (trainable ones are taken).  order: optional explicit layout order of the
+        trainable parameters (default: reverse registration order)."""
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.params = [p for p in params if p.requires_grad]
-        order = list(reversed(self.params))
+        order = list(order) if order is not None else list(reversed(self.params))
+        assert len(order) == len(self.params)
         cap = int(bucket_mb * (1 << 20)) // 4
-        self.buckets, cur, cur_n = [], [], 0
+        # ONE arena holds every bucket back to back (the flat optimizer walks it in a single launch); a bucket is a
+        # slice of it.  16-byte slots keep every gradient view vector-load friendly.
+        self.offset, self.buckets, bounds = {}, [], []
+        n, b0, cur = 0, 0, []
         for p in order:
-            if cur and cur_n + p.numel() > cap:
+            assert p.dtype == torch.float32, "gradient buckets are fp32 (checkpoint contract: fp32 parameters)"
+            if cur and n - b0 + p.numel() > cap:
                 self.buckets.append(cur)
-                cur, cur_n = [], 0
+                bounds.append((b0, n))
+                cur, b0 = [], n
+            self.offset[p] = n
             cur.append(p)
-            cur_n += p.numel()
+            n += (p.numel() + 3) // 4 * 4
         if cur:
             self.buckets.append(cur)
-        self.flat, self._bucket_of, self._offs, self._pending, self._launched, self._handles = [], {}, {}, [], [], []
+            bounds.append((b0, n))
+        dev = order[0].device if order else "cpu"
+        self.order, self.numel = order, n
+        self.arena = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.flat = [self.arena[a:b] for a, b in bounds]
+        self._bucket_of, self._pending, self._launched, self._handles = {}, [], [], []
         for bi, plist in enumerate(self.buckets):
-            dev = plist[0].device
-            # 16-byte aligned slots keep every gradient view vector-load friendly for the fused optimizer
-            offs, n = [], 0
             for p in plist:
-                offs.append(n)
-                n += (p.numel() + 3) // 4 * 4
-            flat = torch.zeros(n, dtype=torch.float32, device=dev)
-            for p, o in zip(plist, offs):
-                assert p.dtype == torch.float32, "gradient buckets are fp32 (checkpoint contract: fp32 parameters)"
-                p.grad = flat[o:o + p.numel()].view_as(p)
-                self._bucket_of[p], self._offs[p] = bi, o
+                o = self.offset[p]
+                p.grad = self.arena[o:o + p.numel()].view_as(p)
+                self._bucket_of[p] = bi
                 self._handles.append(p.register_post_accumulate_grad_hook(self._hook))
-            self.flat.append(flat)
             self._pending.append(len(plist))
             self._launched.append(False)
         self.cuda = self.params[0].is_cuda if self.params else False
@@ -61,8 +67,11 @@ class BucketedGradReducer:
     # ------------------------------------------------------------------ per step
     def zero_grad(self):
         """Replaces optimizer.zero_grad(set_to_none=True): the views must survive, so the buckets are memset."""
-        for f in self.flat:
-            f.zero_()
+        self.arena.zero_()
+        self.rearm()
+
+    def rearm(self):
+        """Re-arm the per-bucket countdowns (the gradients themselves are zeroed by zero_grad or the fused optimizer)."""
         for bi, plist in enumerate(self.buckets):
             self._pending[bi] = len(plist)
             self._launched[bi] = False
@@ -88,12 +97,17 @@ class BucketedGradReducer:
 
     def _hook(self, p):
         bi = self._bucket_of[p]
-        if p.grad.data_ptr() != self.flat[bi].data_ptr() + 4 * self._offs[p]:
+        if p.grad.data_ptr() != self.arena.data_ptr() + 4 * self.offset[p]:
             raise RuntimeError("a gradient view was replaced (optimizer.zero_grad(set_to_none=True) or p.grad = ...); "
                                "use BucketedGradReducer.zero_grad()")
         self._pending[bi] -= 1
         if self._pending[bi] == 0:
             self._reduce(bi)
+
+    def mark_ready(self, p):
+        """For gradients written into the arena by a kernel instead of autograd's AccumulateGrad (fused weight-gradient
+        accumulation): counts the parameter's bucket down exactly as the post-accumulate hook would."""
+        self._hook(p)
 
     def finish(self):
         """Call after backward: reduces buckets whose countdown never reached zero (parameters that got no gradient
@@ -108,10 +122,9 @@ class BucketedGradReducer:
     def clip_grad_norm_(self, max_norm, eps=1e-6):
         """torch.nn.utils.clip_grad_norm_ (trainer.py:186) over the flat buckets: one norm kernel per bucket instead
         of one per parameter; padding slots are zero and do not change the norm.  No host sync."""
-        norms = torch._foreach_norm(self.flat)
-        total = torch.linalg.vector_norm(torch.stack(norms))
+        total = torch.linalg.vector_norm(self.arena)
         coef = torch.clamp(max_norm / (total + eps), max=1.0)
-        torch._foreach_mul_(self.flat, coef)
+        self.arena.mul_(coef)
         return total
 
     def remove(self):

@@ -35,7 +35,8 @@ class SlotToSlotAttention(nn.Module):
         res = torch.cat((pq, pk, pq.new_zeros(m, d)), dim=1)
         w = torch.cat((self.query_content.weight, self.key_content.weight, self.value.weight), dim=0)
         b = torch.cat((self.query_content.bias, self.key_content.bias, self.value.bias), dim=0)
-        qkv = A.linear(c, w, b, _q(w), residual=res, res_row_mod=m)
+        wq = torch.cat((_q(self.query_content.weight), _q(self.key_content.weight), _q(self.value.weight)), dim=0)
+        qkv = A.linear(c, w, b, wq, residual=res, res_row_mod=m)
         a = A.self_attention(qkv.view(batch, m, 3 * d), self.heads, (d // self.heads) ** -0.5)
         return a.view(-1, d)
 
@@ -63,11 +64,12 @@ class SlotToImageAttention(nn.Module):
         kp = _lin(img_pos_bf, self.key_pos)  # (S, D) batch-invariant key positional part
         wkv = torch.cat((self.key_content.weight, self.value.weight), dim=0)
         bkv = torch.cat((self.key_content.bias, self.value.bias), dim=0)
+        wkvq = torch.cat((_q(self.key_content.weight), _q(self.value.weight)), dim=0)
         if is_first:
-            kv = A.linear(img, wkv, bkv, _q(wkv), residual=torch.cat((kp, kp.new_zeros(s, d)), dim=1), res_row_mod=s)
+            kv = A.linear(img, wkv, bkv, wkvq, residual=torch.cat((kp, kp.new_zeros(s, d)), dim=1), res_row_mod=s)
             qc = _lin(c, self.query_content, residual=_lin(qpos_bf, self.query_pos), res_row_mod=m)
         else:
-            kv = A.linear(img, wkv, bkv, _q(wkv))
+            kv = A.linear(img, wkv, bkv, wkvq)
             qc = _lin(c, self.query_content)
         qs = _lin(qsine, self.query_sine)
         qs = qs.view(batch, m, d) if qs.shape[0] == batch * m else qs

@@ -9,7 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfod_b200.so")
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 FOD_OK, FOD_E_ARG, FOD_E_TMAP, FOD_E_LAUNCH, FOD_E_NUMERIC = 0, 1, 2, 3, 4
 
@@ -73,6 +73,16 @@ class SetLossArgs(C.Structure):
     ]
 
 
+class AdamWArgs(C.Structure):
+    _fields_ = [
+        ("params", C.c_void_p), ("grads", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+        ("shadow_bf16", C.c_void_p), ("state", C.c_void_p), ("partial", C.c_void_p),
+        ("n", C.c_int64), ("group_begin", C.c_int64 * 4), ("group_lr", C.c_float * 4), ("group_wd", C.c_float * 4),
+        ("num_groups", C.c_int32), ("zero_grad", C.c_int32),
+        ("beta1", C.c_float), ("beta2", C.c_float), ("eps", C.c_float), ("max_norm", C.c_float),
+    ]
+
+
 # every symbol include/fod_b200.h declares: name -> (restype, argtypes)
 _VP, _I32, _I64, _F = C.c_void_p, C.c_int32, C.c_int64, C.c_float
 SYMBOLS = {
@@ -87,6 +97,9 @@ SYMBOLS = {
     "fod_targets_compact": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _F, _F, _VP]),
     "fod_match": (C.c_int, [C.POINTER(MatchArgs), _VP]),
     "fod_set_loss": (C.c_int, [C.POINTER(SetLossArgs), _VP]),
+    "fod_flat_adamw_step": (C.c_int, [C.POINTER(AdamWArgs), _VP]),
+    "fod_optim_workspace_floats": (C.c_int, []),
+    "fod_cast_bf16": (C.c_int, [_VP, _VP, _I64, _VP]),
 }
 
 _lib = None

@@ -25,7 +25,12 @@ BF16 = torch.bfloat16
 
 
 def _q(w):
-    """bf16 copy of an fp32 weight for the kernels (no autograd edge; the Function routes the gradient)."""
+    """bf16 copy of an fp32 weight for the kernels (no autograd edge; the Function routes the gradient).  Under a
+    FlatTrainState (optim.py) parameters carry `_fod_shadow`, a view of the bf16 arena the fused optimizer keeps
+    current, and no cast is launched."""
+    s = getattr(w, "_fod_shadow", None)
+    if s is not None:
+        return s
     return w.detach().to(BF16).contiguous()
 
 
@@ -50,7 +55,7 @@ def _lin_padded(x, layer, n_pad=64):
     n = layer.weight.shape[0]
     w = F.pad(layer.weight, (0, 0, 0, n_pad - n))
     b = F.pad(layer.bias, (0, n_pad - n))
-    return A.linear(x, w, b, _q(w), None, 0, False, True)[:, :n]
+    return A.linear(x, w, b, F.pad(_q(layer.weight), (0, 0, 0, n_pad - n)), None, 0, False, True)[:, :n]
 
 
 class MLP(nn.Module):
@@ -246,7 +251,8 @@ class CDetrBackbone(nn.Module):
         n, c, h, w = f.shape
         rows = f.permute(0, 2, 3, 1).to(BF16).contiguous().view(n * h * w, c)
         wgt = self.input_proj.weight.view(self.input_proj.weight.shape[0], c)
-        return A.linear(rows, wgt, self.input_proj.bias, _q(wgt)), h, w
+        wq = _q(self.input_proj.weight).view(wgt.shape)
+        return A.linear(rows, wgt, self.input_proj.bias, wq), h, w
 
     def forward(self, images):
         t, h, w = self.forward_tokens(images)

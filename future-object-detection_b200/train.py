@@ -24,11 +24,21 @@ class TrainStep:
     and is what GraphedTrainStep captures for N > 1 GPUs."""
 
     def __init__(self, model, optimizer, max_norm=0.1, distributed=False, reducer=None):
+        """optimizer: a torch optimizer, or a fod_b200.optim.FlatTrainState (flat arenas: gradient average, clipping,
+        AdamW, bf16 operand refresh and zero_grad fused; `reducer` is then its own)."""
         self.model, self.opt, self.max_norm, self.distributed = model, optimizer, max_norm, distributed
         self.params = [p for p in model.parameters() if p.requires_grad]
         self.reducer = reducer
+        self.flat = optimizer if hasattr(optimizer, "finish_backward") else None
 
     def __call__(self, data):
+        if self.flat is not None:
+            self.flat.begin_step()
+            _, _, loss, stats, _ = self.model(data=data, distributed=self.distributed)
+            loss.backward()
+            self.flat.finish_backward()
+            self.flat.step(self.max_norm)
+            return loss
         if self.reducer is not None:
             self.reducer.zero_grad()
         else:
@@ -64,7 +74,7 @@ class GraphedTrainStep:
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        if reducer is None:
+        if reducer is None and hasattr(optimizer, "zero_grad"):
             optimizer.zero_grad(set_to_none=True)
         # thread_local: the NCCL watchdog thread may query events while this thread captures
         with torch.cuda.graph(self.graph, capture_error_mode="thread_local" if distributed else "global"):

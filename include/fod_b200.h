@@ -128,6 +128,39 @@ int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bca
 int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int32_t rows_per_group, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Flat optimizer step.  One contiguous arena of n fp32 elements holds every trainable parameter
+ * (n % 4 == 0, 16-byte slots); grads / exp_avg / exp_avg_sq / the bf16 shadow mirror its layout.  One call =
+ *   total = ||grads||_2; coef = min(1, max_norm / (total + 1e-6))      torch.nn.utils.clip_grad_norm_, trainer.py:186
+ *   t += 1; AdamW(lr, betas, eps, weight_decay) on coef * grads          torch.optim.AdamW.step, trainer.py:188 with the
+ *                                                                         parameter groups of runs/_helper.py:84-107
+ *   shadow_bf16 = bf16(params)                                           the operand copies the GEMM kernels read
+ *   grads = 0 (zero_grad != 0) or coef * grads                           optimizer.zero_grad, trainer.py:171
+ * in three launches (sum of squares -> scalars -> update), no host synchronisation.
+ * state: 8 device floats {grad norm, clip coef, step t, 1 - beta1^t, 1 - beta2^t, ...}; state[2] must start at 0.
+ * partial: fod_optim_workspace_floats() device floats.  Groups: elements [group_begin[i], group_begin[i+1]) use
+ * group_lr[i] / group_wd[i].
+ */
+typedef struct fod_adamw_args {
+    float* params;
+    float* grads;
+    float* exp_avg;
+    float* exp_avg_sq;
+    void* shadow_bf16;   /* (n) bf16 or NULL */
+    float* state;
+    float* partial;
+    int64_t n;
+    int64_t group_begin[4];
+    float group_lr[4];
+    float group_wd[4];
+    int32_t num_groups;
+    int32_t zero_grad;
+    float beta1, beta2, eps, max_norm;
+} fod_adamw_args;
+int fod_flat_adamw_step(const fod_adamw_args* a, void* stream);
+int fod_optim_workspace_floats(void);
+int fod_cast_bf16(const float* src, void* dst, int64_t n, void* stream);  /* dst = bf16(src), n % 4 == 0 */
+
+/* ------------------------------------------------------------------------------------------------
  * Set-prediction loss path (north-star piece 4).  Levels are the decoder levels (main output = level L-1).
  *
  * fod_targets_compact — replaces to_detr_targets (future_od/models/st_detr.py:237-263): dense 256-slot xyxy-pixel

@@ -109,3 +109,24 @@ def test_bucketed_grad_reducer_two_ranks():
     assert abs(out[0]["norm"] - ref_norm) < 1e-4 * ref_norm
     assert abs(out[0]["clipped_norm"] - min(0.1, ref_norm)) < 1e-5
     assert out[0]["caught"] and out[1]["caught"]
+
+
+def test_flat_train_state_layout_cpu():
+    """fod_b200.optim.FlatTrainState on CPU (no kernel call): parameters / gradients become views of the arenas with
+    16-byte slots, the backbone group sits last (lower LR, runs/_helper.py:93-100), names and values are unchanged."""
+    from fod_b200.optim import FlatTrainState
+    torch.manual_seed(0)
+    net = torch.nn.ModuleDict({"backbone": torch.nn.Linear(5, 3), "head": torch.nn.Linear(3, 7)})
+    before = {k: v.clone() for k, v in net.state_dict().items()}
+    flat = FlatTrainState(net, lr=1e-4, lr_backbone=1e-5, bucket_mb=1e-5)
+    assert list(net.state_dict()) == list(before) and all(torch.equal(net.state_dict()[k], before[k]) for k in before)
+    offs = sorted(flat.reducer.offset.values())
+    assert all(o % 4 == 0 for o in offs) and flat.n % 4 == 0
+    back = [flat.reducer.offset[p] for n, p in net.named_parameters() if "backbone" in n]
+    head = [flat.reducer.offset[p] for n, p in net.named_parameters() if "backbone" not in n]
+    assert max(head) < min(back) == flat.group_begin[1] and flat.group_lr == [1e-4, 1e-5]
+    net["head"](net["backbone"](torch.ones(2, 5))).sum().backward()
+    w = net["head"].weight
+    o = flat.reducer.offset[w]
+    assert torch.equal(flat.grads[o:o + w.numel()].view_as(w), w.grad) and float(w.grad.abs().sum()) > 0
+    assert torch.equal(flat.params[o:o + w.numel()].view_as(w), w.data)
