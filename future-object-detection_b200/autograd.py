@@ -25,6 +25,57 @@ def weight_grad(dy, x):
     return ops.gemm(dy, x, a_mn=True, b_mn=True, out_f32=True, split_k=-1)
 
 
+# ---- gradients written straight into the flat gradient arena (optim.FlatTrainState) -------------------------------
+# A Parameter that owns an arena slot carries `_fod_reducer`.  Its gradient kernels (split-K dW GEMM, column sums,
+# LayerNorm backward) accumulate into `p.grad` in place and the Function returns None for it: no temporary, no zero
+# fill, no AccumulateGrad add kernel.  `_fod_uses` counts the forward uses of the step so that the reducer's bucket
+# countdown fires after the LAST contribution, as autograd's own accumulation would.
+def _arena(p):
+    return p is not None and getattr(p, "_fod_reducer", None) is not None and p.requires_grad
+
+
+def _direct(p):
+    """For module code (outside Function.forward, where grad mode is the caller's)."""
+    return _arena(p) and torch.is_grad_enabled()
+
+
+def _use(*ps):
+    """Inside Function.forward of a call that will be differentiated: per-tensor flags; a use is counted for every
+    arena-backed parameter."""
+    flags = [_arena(p) for p in ps]
+    for p, d in zip(ps, flags):
+        if d:
+            p._fod_uses = getattr(p, "_fod_uses", 0) + 1
+    return flags
+
+
+def _use_all(*ps):
+    """All-or-nothing (block functions): direct mode only if EVERY parameter of the block owns an arena slot."""
+    if all(_arena(p) for p in ps):
+        _use(*ps)
+        return True
+    return False
+
+
+def _done(p):
+    p._fod_uses -= 1
+    if p._fod_uses == 0:
+        p._fod_reducer.mark_ready(p)
+
+
+def weight_grad_into(p, dy, x, rows=None):
+    g = p.grad.view(-1, x.shape[1])  # (N, K) view of the slot (a 1x1 conv weight is stored (N, K, 1, 1))
+    if rows is not None:
+        g = g[rows[0]:rows[1]]
+    ops.gemm(dy, x, a_mn=True, b_mn=True, accum_into=g)
+    _done(p)
+
+
+def bias_grad_into(p, dy):
+    ops.colsum(dy, out=p.grad.view(1, -1))
+    _done(p)
+
+
 def input_grad(dy, wq, **kw):
     """dX (rows, K) bf16 = dy (rows, N) · W (N, K), W read in its nn.Linear layout (MN-major B operand)."""
     return ops.gemm(dy, wq, b_mn=True, **kw)
@@ -34,10 +85,15 @@ class LinearFn(Function):
     """y = [relu](x·Wᵀ + b + residual[row % mod]) — nn.Linear (+ReLU) call sites of transformer.py / paper.py."""
 
     @staticmethod
-    def forward(ctx, x, w, b, wq, residual, res_row_mod, relu, out_f32):
+    def forward(ctx, x, w, b, wq, residual, res_row_mod, relu, out_f32, w_rows=None):
+        """w_rows=(r0, r1): `wq` is rows [r0, r1) of the arena-backed parameter `w`; its gradient accumulates into the
+        same rows of w.grad (direct mode only — otherwise pass the slice itself and let autograd route it)."""
         y = ops.gemm(x, wq, bias=b, residual=residual, res_row_mod=res_row_mod, relu=relu, out_f32=out_f32)
+        ctx.w_rows = w_rows
         ctx.save_for_backward(x, wq, y if relu else None)
         ctx.cfg = (res_row_mod, relu, b is not None, residual is not None)
+        ctx.direct = _use(w, b) if any(ctx.needs_input_grad) else [False, False]
+        ctx.params = (w, b)
         return y
 
     @staticmethod
@@ -48,16 +104,26 @@ class LinearFn(Function):
         if relu:
             dy = dy * (y > 0)
         dx = input_grad(dy, wq) if ctx.needs_input_grad[0] else None
-        dw = weight_grad(dy, x) if ctx.needs_input_grad[1] else None
-        db = ops.colsum(dy).view(-1) if has_b and ctx.needs_input_grad[2] else None
+        (w_direct, b_direct), (w, b) = ctx.direct, ctx.params
+        dw = db = None
+        if w_direct:
+            weight_grad_into(w, dy, x, ctx.w_rows)
+        elif ctx.w_rows is not None:
+            raise RuntimeError("w_rows needs an arena-backed parameter")
+        elif ctx.needs_input_grad[1]:
+            dw = weight_grad(dy, x)
+        if b_direct:
+            bias_grad_into(b, dy)
+        elif has_b and ctx.needs_input_grad[2]:
+            db = ops.colsum(dy).view(-1)
         dres = None
         if has_res and ctx.needs_input_grad[4]:
             dres = dy if mod == 0 else dy.view(-1, mod, dy.shape[1]).sum(0)
-        return dx, dw, db, None, dres, None, None, None
+        return dx, dw, db, None, dres, None, None, None, None
 
 
-def linear(x, w, b, wq, residual=None, res_row_mod=0, relu=False, out_f32=False):
-    return LinearFn.apply(x, w, b, wq, residual, res_row_mod, relu, out_f32)
+def linear(x, w, b, wq, residual=None, res_row_mod=0, relu=False, out_f32=False, w_rows=None):
+    return LinearFn.apply(x, w, b, wq, residual, res_row_mod, relu, out_f32, w_rows)
 
 
 class LinearLNFn(Function):
@@ -68,6 +134,8 @@ class LinearLNFn(Function):
         if need_grad:
             y, pre, mean, rstd = ops.gemm(x, wq, bias=b, residual=res, ln=(gamma, beta, eps), save_ln=True)
             ctx.save_for_backward(x, wq, pre, mean, rstd, gamma)
+            ctx.direct = _use_all(w, b, gamma, beta)
+            ctx.params = (w, b, gamma, beta)
         else:
             y = ops.gemm(x, wq, bias=b, residual=res, ln=(gamma, beta, eps))
         return y
@@ -75,6 +143,14 @@ class LinearLNFn(Function):
     @staticmethod
     def backward(ctx, dy):
         x, wq, pre, mean, rstd, gamma = ctx.saved_tensors
+        if ctx.direct:  # all four parameters own arena slots: every gradient kernel accumulates in place
+            w, b, g, bt = ctx.params
+            dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, g.grad, bt.grad, dzsum=b.grad)
+            dx = input_grad(dz, wq)
+            weight_grad_into(w, dz, x)
+            for q in (b, g, bt):
+                _done(q)
+            return dx, dz, None, None, None, None, None, None, None
         acc = torch.zeros((3, gamma.numel()), dtype=torch.float32, device=gamma.device)  # dgamma, dbeta, db
         dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, acc[0], acc[1], dzsum=acc[2])
         dx = input_grad(dz, wq)
@@ -96,6 +172,8 @@ class FFNLNFn(Function):
         if need_grad:
             y, pre, mean, rstd = ops.gemm(h, w2q, bias=b2, residual=x, ln=(gamma, beta, eps), save_ln=True)
             ctx.save_for_backward(x, h, w1q, w2q, pre, mean, rstd, gamma)
+            ctx.direct = _use_all(w1, b1, w2, b2, gamma, beta)
+            ctx.params = (w1, b1, w2, b2, gamma, beta)
         else:
             y = ops.gemm(h, w2q, bias=b2, residual=x, ln=(gamma, beta, eps))
         return y
@@ -103,6 +181,16 @@ class FFNLNFn(Function):
     @staticmethod
     def backward(ctx, dy):
         x, h, w1q, w2q, pre, mean, rstd, gamma = ctx.saved_tensors
+        if ctx.direct:
+            w1, b1, w2, b2, g, bt = ctx.params
+            dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, g.grad, bt.grad, dzsum=b2.grad)
+            dh = input_grad(dz, w2q, relu_mask=h, colsum_out=b1.grad)
+            weight_grad_into(w2, dz, h)
+            dx = input_grad(dh, w1q, residual=dz)
+            weight_grad_into(w1, dh, x)
+            for q in (b1, b2, g, bt):
+                _done(q)
+            return dx, None, None, None, None, None, None, None, None, None, None
         d = gamma.numel()
         acc = torch.zeros((3 * d + h.shape[1],), dtype=torch.float32, device=gamma.device)  # dgamma, dbeta, db2, db1
         dgamma, dbeta, db2, db1 = acc[:d], acc[d:2 * d], acc[2 * d:3 * d], acc[3 * d:]
@@ -127,6 +215,8 @@ class AddLNFn(Function):
             y, mean, rstd = ops.add_ln_fwd(x, gamma, beta, eps, bcast, rows_per_group, save=True)
             ctx.save_for_backward(x, bcast, mean, rstd, gamma)
             ctx.rpg = rows_per_group
+            ctx.direct = _use_all(gamma, beta)
+            ctx.params = (gamma, beta)
         else:
             y = ops.add_ln_fwd(x, gamma, beta, eps, bcast, rows_per_group)
         return y
@@ -134,10 +224,18 @@ class AddLNFn(Function):
     @staticmethod
     def backward(ctx, dy):
         x, bcast, mean, rstd, gamma = ctx.saved_tensors
-        dgamma = torch.zeros_like(gamma)
-        dbeta = torch.zeros_like(gamma)
+        if ctx.direct:
+            g, bt = ctx.params
+            dgamma, dbeta = g.grad, bt.grad
+        else:
+            dgamma = torch.zeros_like(gamma)
+            dbeta = torch.zeros_like(gamma)
         dz = ops.ln_bwd(_bf(dy), x, mean, rstd, gamma, dgamma, dbeta, bcast=bcast, rows_per_group=ctx.rpg)
         db = ops.colsum(dz, ctx.rpg).to(BF16) if bcast is not None else None
+        if ctx.direct:
+            _done(g)
+            _done(bt)
+            return dz, db, None, None, None, None, None
         return dz, db, None, dgamma, dbeta, None, None
 
 

@@ -42,7 +42,7 @@ class BucketedGradReducer:
                 cur, b0 = [], n
             self.offset[p] = n
             cur.append(p)
-            n += (p.numel() + 3) // 4 * 4
+            n += (p.numel() + 7) // 8 * 8  # 8-element slots: 16-byte aligned in the bf16 shadow arena too (TMA operands)
         if cur:
             self.buckets.append(cur)
             bounds.append((b0, n))
@@ -63,6 +63,7 @@ class BucketedGradReducer:
         self.overlap = overlap and self.cuda
         self.side = torch.cuda.Stream() if self.overlap else None
         self.enabled = True
+        self._ready = set()
 
     # ------------------------------------------------------------------ per step
     def zero_grad(self):
@@ -75,6 +76,7 @@ class BucketedGradReducer:
         for bi, plist in enumerate(self.buckets):
             self._pending[bi] = len(plist)
             self._launched[bi] = False
+        self._ready.clear()
 
     def _reduce(self, bi):
         self._launched[bi] = True
@@ -96,6 +98,12 @@ class BucketedGradReducer:
             flat.div_(self.world)
 
     def _hook(self, p):
+        if p in self._ready:
+            # Second signal for the same parameter in one step: a gradient kernel wrote the slot directly
+            # (mark_ready) AND autograd ran the parameter's AccumulateGrad node with an undefined gradient (it does,
+            # once every producer has finished).  Either signal means "all contributions are enqueued".
+            return
+        self._ready.add(p)
         bi = self._bucket_of[p]
         if p.grad.data_ptr() != self.arena.data_ptr() + 4 * self.offset[p]:
             raise RuntimeError("a gradient view was replaced (optimizer.zero_grad(set_to_none=True) or p.grad = ...); "

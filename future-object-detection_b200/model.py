@@ -252,7 +252,8 @@ class CDetrBackbone(nn.Module):
         rows = f.permute(0, 2, 3, 1).to(BF16).contiguous().view(n * h * w, c)
         wgt = self.input_proj.weight.view(self.input_proj.weight.shape[0], c)
         wq = _q(self.input_proj.weight).view(wgt.shape)
-        return A.linear(rows, wgt, self.input_proj.bias, wq), h, w
+        wsrc = self.input_proj.weight if A._direct(self.input_proj.weight) else wgt
+        return A.linear(rows, wsrc, self.input_proj.bias, wq), h, w
 
     def forward(self, images):
         t, h, w = self.forward_tokens(images)
@@ -290,7 +291,10 @@ class EncoderAttention(nn.Module):
         wq = _q(w)
         d = w.shape[1]
         # (x + pos)·Wᵀ = x·Wᵀ + pos·Wᵀ: the positional half is batch-invariant -> a (seq_len, 3D) row-modular residual
-        pqk = A.linear(pos_bf, w[:2 * d], None, wq[:2 * d])
+        if A._direct(w):  # gradient of the positional half accumulates into rows [0, 2d) of in_proj_weight.grad
+            pqk = A.linear(pos_bf, w, None, wq[:2 * d], w_rows=(0, 2 * d))
+        else:
+            pqk = A.linear(pos_bf, w[:2 * d], None, wq[:2 * d])
         res = torch.cat((pqk, pqk.new_zeros(seq_len, d)), dim=1)
         qkv = A.linear(x, w, b, wq, residual=res, res_row_mod=seq_len)
         a = A.self_attention(qkv.view(n_seq, seq_len, 3 * d), self.heads, (d // self.heads) ** -0.5)

@@ -51,6 +51,8 @@ class FlatTrainState:
             view.copy_(p.data)
             p.data = view
             p._fod_shadow = self.shadow[o:o + p.numel()].view_as(p)
+            p._fod_reducer = r   # autograd.py: gradient kernels accumulate straight into the arena slot
+            p._fod_uses = 0
         self._args = None
         self._partial = None
         if dev.type == "cuda":
@@ -75,6 +77,8 @@ class FlatTrainState:
         """Start of a training step.  Gradients were zeroed by the previous fused update (or are the initial zeros),
         so only the per-bucket countdowns of the reducer are re-armed."""
         self.reducer.rearm()
+        for p in self.reducer.order:
+            p._fod_uses = 0
 
     def finish_backward(self):
         self.reducer.finish()
@@ -133,5 +137,6 @@ class FlatTrainState:
         self._hook.remove()
         self.reducer.remove()
         for p in self.reducer.order:
-            if hasattr(p, "_fod_shadow"):
-                del p._fod_shadow
+            for attr in ("_fod_shadow", "_fod_reducer", "_fod_uses"):
+                if hasattr(p, attr):
+                    delattr(p, attr)
