@@ -257,10 +257,18 @@ def run_cuda(args):
     sampler.join(timeout=2)
     check_match_status(core._criterion.last_status)
 
-    if rank != 0:
+    def finish():
+        # Captured NCCL kernels keep the communicator busy: tearing the process group down with the graph alive can
+        # block forever.  All ranks meet at a barrier, flush, and leave without the NCCL teardown.
         if world > 1:
-            dist.destroy_process_group()
-        return
+            sys.stdout.flush()
+            sys.stderr.flush()
+            dist.barrier()
+            torch.cuda.synchronize()
+            os._exit(0)
+
+    if rank != 0:
+        return finish()
     peaks = _peaks()
     clips = BATCH * world * args.steps
     line = {"metric": METRIC, "value": clips / (ms / 1e3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -275,7 +283,7 @@ def run_cuda(args):
             "matcher_status_by_region": status_log, "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
     line.update(prof.roofline_report(kern, peaks, ms_inst, _traffic()))
     line["instrumented_region"] = {"steps": n_inst, "ms_per_step": ms_inst / n_inst if n_inst else None}
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:
         step = cpu_reference_step_fn(1)
         step()
         t0 = time.perf_counter()
@@ -286,8 +294,7 @@ def run_cuda(args):
         line["cpu_baseline"] = {"value": n / dt, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
                                 "sample": "%d steps x 1 clip (fwd+bwd+clip+AdamW) of the same workload, fp32 oracle, %d threads" % (n, os.cpu_count())}
     print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    finish()
 
 
 def main():

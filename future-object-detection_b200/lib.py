@@ -9,7 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfod_b200.so")
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 FOD_OK, FOD_E_ARG, FOD_E_TMAP, FOD_E_LAUNCH, FOD_E_NUMERIC = 0, 1, 2, 3, 4
 
@@ -73,6 +73,16 @@ class SetLossArgs(C.Structure):
     ]
 
 
+class ApArgs(C.Structure):
+    _fields_ = [
+        ("pred_boxes", C.c_void_p), ("scores", C.c_void_p), ("anno_boxes", C.c_void_p), ("anno_classes", C.c_void_p),
+        ("anno_active", C.c_void_p), ("thresholds", C.c_void_p), ("confs", C.c_void_p), ("is_positive", C.c_void_p),
+        ("size_cat", C.c_void_p), ("num_annos", C.c_void_p),
+        ("B", C.c_int32), ("M", C.c_int32), ("C", C.c_int32), ("N", C.c_int32), ("K", C.c_int32), ("T", C.c_int32),
+        ("size_lo", C.c_float), ("size_hi", C.c_float),
+    ]
+
+
 class AdamWArgs(C.Structure):
     _fields_ = [
         ("params", C.c_void_p), ("grads", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
@@ -97,6 +107,7 @@ SYMBOLS = {
     "fod_targets_compact": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _F, _F, _VP]),
     "fod_match": (C.c_int, [C.POINTER(MatchArgs), _VP]),
     "fod_set_loss": (C.c_int, [C.POINTER(SetLossArgs), _VP]),
+    "fod_ap_match": (C.c_int, [C.POINTER(ApArgs), _VP]),
     "fod_flat_adamw_step": (C.c_int, [C.POINTER(AdamWArgs), _VP]),
     "fod_optim_workspace_floats": (C.c_int, []),
     "fod_cast_bf16": (C.c_int, [_VP, _VP, _I64, _VP]),

@@ -330,3 +330,43 @@ def set_loss(logits, boxes, match_tgt, tgt_boxes, tgt_labels, tgt_count, num_box
     LAUNCH_COUNTS["set_loss_kernel"] += 1
     LAUNCH_COUNTS["set_loss_finalize_kernel"] += 1
     return out, dl, db
+
+
+_AP_THR = {}
+
+
+def ap_match(pred_boxes, scores, anno_boxes, anno_classes, anno_active, imsize, topk=50):
+    """utils/od_map.py:214-287 in one launch.  pred_boxes (B,M,4) xyxy px fp32, scores (B,M,C) with the generic class
+    last, annotation slots (B,N,...).  Returns (confs (10,C,B*K) fp32, is_positive bool, size_categories (C,4,B*K)
+    bool, num_annos (C,4) int64)."""
+    L = lib.load()
+    dev = pred_boxes.device
+    B, M, Cn = scores.shape
+    N = anno_boxes.shape[1]
+    K = min(topk, M)
+    key = str(dev)
+    if key not in _AP_THR:  # od_map.py:24: the ten IoU thresholds, torch.arange's own fp32 values
+        _AP_THR[key] = torch.arange(0.50, 1.00, 0.05).to(dev)
+    thr = _AP_THR[key]
+    T = thr.numel()
+    pb = pred_boxes.contiguous().float()
+    sc = scores.contiguous().float()
+    ab = anno_boxes.contiguous().float()
+    ac = anno_classes.contiguous().long()
+    aa = anno_active.contiguous().long()
+    confs = torch.empty((T, Cn, B * K), dtype=torch.float32, device=dev)
+    is_pos = torch.empty((T, Cn, B * K), dtype=torch.bool, device=dev)
+    size_cat = torch.empty((Cn, 4, B * K), dtype=torch.bool, device=dev)
+    num_annos = torch.zeros((Cn, 4), dtype=torch.int64, device=dev)
+    h, w = imsize
+    a = lib.ApArgs()
+    a.pred_boxes, a.scores, a.anno_boxes, a.anno_classes, a.anno_active = _p(pb), _p(sc), _p(ab), _p(ac), _p(aa)
+    a.thresholds, a.confs, a.is_positive, a.size_cat, a.num_annos = _p(thr), _p(confs), _p(is_pos), _p(size_cat), _p(num_annos)
+    a.B, a.M, a.C, a.N, a.K, a.T = B, M, Cn, N, K, T
+    # od_map.py:20-23 delimiters times H*W, evaluated as the reference does (python floats -> fp32 at the comparison)
+    a.size_lo, a.size_hi = (1 / 24) * (1 / 64) * h * w, (1 / 4) * (1 / 12) * h * w
+    _t = prof.begin()
+    lib.check(L.fod_ap_match(C.byref(a), _stream()), "fod_ap_match")
+    prof.end(_t, "ap_match", 0.0, 4.0 * B * (M * (Cn + 4) + N * 6))
+    LAUNCH_COUNTS["ap_match_kernel"] += 1
+    return confs, is_pos, size_cat, num_annos

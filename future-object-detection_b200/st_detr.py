@@ -222,8 +222,19 @@ def _size_onehot(boxes, imsize):
 
 @torch.no_grad()
 def prepare_od_map_stuffs(pred_boxes, scores, anno_boxes, anno_classes, anno_active, imsize, topk=50):
-    """utils/od_map.py:214-287 on the device with torch ops (next-row f1 of SURVEY.md §8: a one-launch greedy-claim
-    kernel replaces the 50-step loop later).  Same outputs: confs (10,C+1,50B), is_positive, size_categories, num_annos."""
+    """utils/od_map.py:214-287 as ONE kernel launch (fod_ap_match): top-50 per class, smoothed
+    IoU, the 50-step greedy claim loop at 10 thresholds, size buckets.  Same outputs as the reference: confs
+    (10,C+1,50B), is_positive, size_categories, num_annos.  Shapes outside the kernel's limits (more than 256
+    detections or annotation slots) take the torch formulation below."""
+    if pred_boxes.is_cuda and pred_boxes.shape[1] <= 256 and anno_boxes.shape[1] <= 256:
+        return ops.ap_match(pred_boxes, scores, anno_boxes, anno_classes, anno_active, imsize, topk)
+    return prepare_od_map_stuffs_torch(pred_boxes, scores, anno_boxes, anno_classes, anno_active, imsize, topk)
+
+
+@torch.no_grad()
+def prepare_od_map_stuffs_torch(pred_boxes, scores, anno_boxes, anno_classes, anno_active, imsize, topk=50):
+    """The same bookkeeping with torch ops on the device (static shapes, no host sync): used beyond the kernel's size
+    limits and as the kernel's on-device cross-check in tests/test_criterion_gpu.py."""
     dev = pred_boxes.device
     bsz, _, ncls = scores.shape
     thr = torch.arange(0.50, 1.00, 0.05, device=dev)

@@ -128,6 +128,33 @@ int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bca
 int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int32_t rows_per_group, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * AP bookkeeping of one forward pass: future_od/utils/od_map.py:214-287 prepare_od_map_stuffs,
+ * called from future_od/models/st_detr.py:222-229 inside every forward.  One launch, grid (B, C):
+ *   top-K detections per class by score; IoU+1e-7 smoothing against the N annotation slots (od_map.py:48-71); the
+ *   K-step greedy claim loop at T IoU thresholds (od_map.py:267-277); size buckets (od_map.py:163-181,199-211).
+ * scores carry the generic "any class" column last (st_detr.py:200-205); class c < C-1 only claims annotations of
+ * class c, the generic column claims any active annotation.  Slots with active != 1 never match, so the caller need
+ * not drop unused slots (od_map.py:40-45) — outputs are identical.
+ * Outputs: confs (T, C, B*K) fp32; is_positive (T, C, B*K) and size_cat (C, 4, B*K) as 1-byte bools;
+ * num_annos (C, 4) int64, += (zero it first).  Limits: M, N <= 256, K <= min(64, M), T <= 10.
+ */
+typedef struct fod_ap_args {
+    const float* pred_boxes;
+    const float* scores;
+    const float* anno_boxes;
+    const void* anno_classes;   /* int64 (B, N) */
+    const void* anno_active;    /* int64 (B, N) */
+    const float* thresholds;    /* (T) */
+    float* confs;
+    void* is_positive;
+    void* size_cat;
+    void* num_annos;
+    int32_t B, M, C, N, K, T;
+    float size_lo, size_hi;     /* bucket delimiters in pixel^2: (1/24)(1/64)·H·W and (1/4)(1/12)·H·W */
+} fod_ap_args;
+int fod_ap_match(const fod_ap_args* a, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Flat optimizer step.  One contiguous arena of n fp32 elements holds every trainable parameter
  * (n % 4 == 0, 16-byte slots); grads / exp_avg / exp_avg_sq / the bf16 shadow mirror its layout.  One call =
  *   total = ||grads||_2; coef = min(1, max_norm / (total + 1e-6))      torch.nn.utils.clip_grad_norm_, trainer.py:186

@@ -145,3 +145,41 @@ def test_set_loss_and_gradients_match_oracle(seed, nts):
         assert rel(res[1 + i].detach(), stats_ref[k].detach()) < 1e-4, k
     assert rel(lg.grad, lo.grad) < 1e-4 and float((lg.grad.cpu() - lo.grad).abs().max()) < 1e-5
     assert rel(bg.grad, bo.grad) < 1e-4 and float((bg.grad.cpu() - bo.grad).abs().max()) < 1e-4
+
+
+@pytest.mark.parametrize("seed,nts", [(0, (5, 0, 17)), (1, (256, 1, 40)), (2, (0, 0)), (3, (100, 100, 100, 3))])
+def test_ap_bookkeeping_kernel_matches_oracle(seed, nts):
+    """fod_ap_match (one launch) against the oracle's restatement of od_map.py:214-287 on identical fp32 inputs:
+    booleans and counts exact, confidences exact; also against the on-device torch formulation.  Cases: empty
+    samples, all 256 slots active, duplicated annotation boxes (claim ties) and detections that coincide with
+    annotations (IoU ~ 1, every threshold hit)."""
+    from fod_b200 import ops
+    from fod_b200.st_detr import prepare_od_map_stuffs_torch
+    from oracle import fod_oracle as O
+    g = torch.Generator().manual_seed(seed)
+    B, M, C, N, H, W = len(nts), 128, 9, 256, 448, 800
+    xy = torch.rand(B, N, 2, generator=g) * torch.tensor([W * 0.6, H * 0.6])
+    wh = 4 + torch.rand(B, N, 2, generator=g) * torch.tensor([W * 0.3, H * 0.3])
+    anno = torch.cat((xy, xy + wh), dim=2)
+    anno[:, 1::7] = anno[:, 0:1]                      # duplicated boxes -> equal IoUs, lowest slot must win
+    classes = torch.randint(0, C - 1, (B, N), generator=g)
+    active = torch.zeros(B, N, dtype=torch.int64)
+    for b, nt in enumerate(nts):
+        active[b, torch.randperm(N, generator=g)[:nt]] = 1
+    pxy = torch.rand(B, M, 2, generator=g) * torch.tensor([W * 0.6, H * 0.6])
+    pwh = 4 + torch.rand(B, M, 2, generator=g) * torch.tensor([W * 0.3, H * 0.3])
+    pred = torch.cat((pxy, pxy + pwh), dim=2)
+    pred[:, :40] = anno[:, :40] + torch.randn(B, 40, 4, generator=g) * 2.0   # near-hits at various IoUs
+    pred[:, 40:44] = anno[:, 3:7]                                            # exact hits
+    scores = torch.rand(B, M, C - 1, generator=g)
+    scores = torch.cat((scores, scores.max(dim=2, keepdim=True)[0]), dim=2)
+    ref = O.od_map_stuffs(pred, scores, anno, classes, active, (H, W))
+    dev = "cuda:0"
+    args = [t.to(dev) for t in (pred, scores, anno, classes, active)]
+    got = ops.ap_match(*args, (H, W))
+    tor = prepare_od_map_stuffs_torch(*args, (H, W))
+    for name, a, r, t in zip(("confs", "is_positive", "size_categories", "num_annos"), got, ref, tor):
+        assert a.shape == r.shape and a.dtype == t.dtype, name
+        assert torch.equal(a.cpu(), r.to(a.dtype)), name
+        assert torch.equal(a, t), name + " (device torch formulation)"
+    assert got[1].any() or sum(nts) == 0
