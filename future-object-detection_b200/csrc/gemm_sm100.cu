@@ -36,7 +36,10 @@ struct GemmEpi {
 
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS_MAX = 320;
+// Epilogue warps: 4 (one per TMEM lane quarter) for the 64/128-wide tiles; 8 for the 256-wide tile, where two warps
+// share a lane quarter and split the columns — the one-row-per-thread epilogue is the longest phase of that tile.
+template <int BN> struct GemmThreads { static constexpr int kEpiWarps = BN == 256 ? 8 : 4; static constexpr int kThreads = 64 + 32 * kEpiWarps; };
 constexpr int GEMM_MAX_STAGES = 8;
 
 template <int BN>
@@ -51,7 +54,8 @@ struct GemmCfg {
     static constexpr int kAuxBytes = GEMM_BM * kRowBf16;
     static constexpr int kTmemCols = BN < 32 ? 32 : BN;
     static constexpr int kParamBytes = 3 * BN * 4;  // bias / gamma / beta slices of this N tile, fp32
-    static constexpr int kBarBytes = 256 + kParamBytes;
+    static constexpr int kStatBytes = 2 * 2 * GEMM_BM * 4;  // LayerNorm partial sums of the two column halves
+    static constexpr int kBarBytes = 256 + kParamBytes + kStatBytes;
     static int smem_bytes(int stages, bool aux) { return 1024 + stages * kStageBytes + (aux ? kAuxBytes : 0) + kBarBytes; }
 };
 
@@ -162,12 +166,13 @@ __device__ __forceinline__ void stage_f32(uint8_t* dst, const float (&z)[32]) {
 
 // One warp drains ITS 32 staged rows (bf16) to global memory with lane-contiguous 16-byte stores: a full 128-byte
 // line per 8 lanes instead of 32 scattered row segments.  Optionally accumulates column sums of what it stored.
-template <int BN>
+template <int BN, int W>
 __device__ __forceinline__ void drain_bf16(const uint8_t* stage_warp, __nv_bfloat16* out, long long ld_out, int M, int N,
                                            long long row0, int n0, int lane, bool vec_ok, float* colsum_out) {
+    // stage_warp points at this warp's first row AND first column; n0 is the global column of that first column
     constexpr int ROWB = GemmCfg<BN>::kRowBf16;
     if (vec_ok) {
-        constexpr int CH = BN / 8;    // 16-byte chunks per row: 32 / 16 / 8
+        constexpr int CH = W / 8;     // 16-byte chunks per row: 32 / 16 / 8
         constexpr int RPI = 32 / CH;  // rows per warp-wide instruction
         const int ch = lane % CH, rsub = lane / CH;
         const int col = n0 + ch * 8;
@@ -203,7 +208,7 @@ __device__ __forceinline__ void drain_bf16(const uint8_t* stage_warp, __nv_bfloa
         for (int r = 0; r < 32; ++r) {
             if (row0 + r >= M) break;
             const __nv_bfloat16* s = reinterpret_cast<const __nv_bfloat16*>(stage_warp + r * ROWB);
-            for (int cc = lane; cc < BN; cc += 32) {
+            for (int cc = lane; cc < W; cc += 32) {
                 if (n0 + cc < N) {
                     out[(row0 + r) * ld_out + n0 + cc] = s[cc];
                     if (colsum_out) atomicAdd(colsum_out + n0 + cc, __bfloat162float(s[cc]));
@@ -213,12 +218,12 @@ __device__ __forceinline__ void drain_bf16(const uint8_t* stage_warp, __nv_bfloa
     }
 }
 
-template <int BN>
+template <int BN, int W>
 __device__ __forceinline__ void drain_f32(const uint8_t* stage_warp, float* out, long long ld_out, int M, int N,
                                           long long row0, int n0, int lane, bool vec_ok, bool atomic) {
     constexpr int ROWB = GemmCfg<BN>::kRowF32;
     if (vec_ok) {
-        constexpr int CH = BN / 4;  // float4 chunks per row: 64 / 32 / 16
+        constexpr int CH = W / 4;  // float4 chunks per row
 #pragma unroll 4
         for (int i = lane; i < 32 * CH; i += 32) {
             const int r = i / CH, ch = i % CH;
@@ -234,7 +239,7 @@ __device__ __forceinline__ void drain_f32(const uint8_t* stage_warp, float* out,
         for (int r = 0; r < 32; ++r) {
             if (row0 + r >= M) break;
             const float* s = reinterpret_cast<const float*>(stage_warp + r * ROWB);
-            for (int cc = lane; cc < BN; cc += 32) {
+            for (int cc = lane; cc < W; cc += 32) {
                 if (n0 + cc < N) {
                     if (atomic) atomicAdd(out + (row0 + r) * ld_out + n0 + cc, s[cc]);
                     else out[(row0 + r) * ld_out + n0 + cc] = s[cc];
@@ -245,7 +250,7 @@ __device__ __forceinline__ void drain_f32(const uint8_t* stage_warp, float* out,
 }
 
 template <int BN, bool A_MN, bool B_MN>
-__global__ void __launch_bounds__(GEMM_THREADS, 2)
+__global__ void __launch_bounds__(GemmThreads<BN>::kThreads, BN == 256 ? 1 : 2)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmEpi p) {
     using Cfg = GemmCfg<BN>;
     extern __shared__ uint8_t smem_raw[];
@@ -258,6 +263,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     float* s_bias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full_bar) + 256);
     float* s_gamma = s_bias + BN;
     float* s_beta = s_gamma + BN;
+    float* s_stat = s_beta + BN;  // [2 passes][2 halves][128 rows]
+    constexpr int EW = GemmThreads<BN>::kEpiWarps;
+    constexpr int CPW = (BN / 32) / (EW / 4);  // 32-column chunks per epilogue warp
+    constexpr int WCOLS = CPW * 32;            // columns per epilogue warp
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -342,8 +351,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             umma_commit(accum_bar);
         }
     } else {
-        // ---------------- epilogue: warps 2..5, TMEM lane quarter = warp % 4, one accumulator row per thread
+        // ---------------- epilogue warps: TMEM lane quarter = warp % 4, one accumulator row per thread; with 8 warps
+        // the two warps of a quarter split the tile's columns in halves
         const int quarter = warp & 3;
+        const int half = (warp - 2) >> 2;      // 0 for the 4-warp configurations
+        const int c_begin = half * CPW;
         const int row_in_tile = quarter * 32 + lane;
         const long long row = (long long)m0 + row_in_tile;
         const bool row_ok = row < p.M;
@@ -353,7 +365,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
         // phase 0 (overlaps the main loop): per-column parameters of this N tile -> shared memory (coalesced, once),
         const int et = threadIdx.x - 64;  // 0..127 over the four epilogue warps
-        for (int i = et; i < BN; i += 128) {
+        for (int i = et; i < BN; i += EW * 32) {
             const bool ok = n0 + i < p.N;
             s_bias[i] = (p.bias && ok) ? __ldg(p.bias + n0 + i) : 0.f;
             if (p.ln_gamma) {
@@ -366,7 +378,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const __nv_bfloat16* src = p.aux + (p.aux_mode == 1 ? mod_row : row) * p.ld_aux + n0;
             const uint32_t dst = smem_u32(aux_row);
 #pragma unroll 8
-            for (int j = 0; j < BN / 8; ++j) {
+            for (int j = c_begin * 4; j < (c_begin + CPW) * 4; ++j) {
                 const bool ok = row_ok && (n0 + j * 8 + 8 <= p.N);
                 cp_async_16(dst + j * 16, ok ? static_cast<const void*>(src + j * 8) : static_cast<const void*>(p.aux),
                             ok ? 16u : 0u);
@@ -374,7 +386,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             cp_async_commit();
         }
 
-        asm volatile("bar.sync 1, 128;" ::: "memory");  // parameter slices visible to the four epilogue warps
+        asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");  // parameter slices visible to all epilogue warps
         mbar_wait(accum_bar, 0);
         tc_fence_after();
         if (p.aux_mode && p.vec_ok) cp_async_wait_all();
@@ -388,7 +400,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const int rowb = f32out ? Cfg::kRowF32 : Cfg::kRowBf16;
             uint8_t* my_row = stage_a + row_in_tile * rowb;
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
+            for (int c = c_begin; c < c_begin + CPW; ++c) {
                 const int col0 = n0 + c * 32;
                 if (col0 >= p.N) break;  // warp-uniform
                 tmem_ld_32x32b_x32(taddr + c * 32, v);
@@ -400,68 +412,71 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 else stage_bf16(my_row + c * 64, z);
             }
             __syncwarp();
-            const uint8_t* stage_warp = stage_a + quarter * 32 * rowb;
+            const uint8_t* stage_warp = stage_a + quarter * 32 * rowb + c_begin * 32 * (f32out ? 4 : 2);
             if (f32out)
-                drain_f32<BN>(stage_warp, p.out_f32, p.ld_out, p.M, p.N, (long long)m0 + quarter * 32, n0, lane,
-                              p.vec_ok != 0, p.atomic_out != 0);
+                drain_f32<BN, WCOLS>(stage_warp, p.out_f32, p.ld_out, p.M, p.N, (long long)m0 + quarter * 32,
+                                     n0 + c_begin * 32, lane, p.vec_ok != 0, p.atomic_out != 0);
             else
-                drain_bf16<BN>(stage_warp, p.out_bf16, p.ld_out, p.M, p.N, (long long)m0 + quarter * 32, n0, lane,
-                               p.vec_ok != 0, p.colsum_out);
+                drain_bf16<BN, WCOLS>(stage_warp, p.out_bf16, p.ld_out, p.M, p.N, (long long)m0 + quarter * 32,
+                                      n0 + c_begin * 32, lane, p.vec_ok != 0, p.colsum_out);
         } else {
-            // LayerNorm over the whole row (N == BN == 256, n0 == 0). Three TMEM passes; z parked in TMEM.
-            uint8_t* stage_b = stage_a + GEMM_BM * Cfg::kRowBf16;  // pre-LN copy
-            uint8_t* my_a = stage_a + row_in_tile * Cfg::kRowBf16;
-            uint8_t* my_b = stage_b + row_in_tile * Cfg::kRowBf16;
-            float sum = 0.f;
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                tmem_ld_32x32b_x32(taddr + c * 32, v);
-                tmem_ld_wait();
+            // LayerNorm over the whole row (N == BN == 256, n0 == 0).  Each of the two warps of a lane quarter keeps
+            // its 128 columns of the row in registers (one TMEM pass); row statistics are combined through smem.
+            if constexpr (BN == 256) {
+                uint8_t* stage_b = stage_a + GEMM_BM * Cfg::kRowBf16;  // pre-LN copy
+                uint8_t* my_a = stage_a + row_in_tile * Cfg::kRowBf16;
+                uint8_t* my_b = stage_b + row_in_tile * Cfg::kRowBf16;
+                float zr[CPW * 32];
+                float sum = 0.f;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) z[i] = __uint_as_float(v[i]);
-                if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, c * 32, c, s_bias);
+                for (int cc = 0; cc < CPW; ++cc) {
+                    const int c = c_begin + cc;
+                    tmem_ld_32x32b_x32(taddr + c * 32, v);
+                    tmem_ld_wait();
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    sum += z[i];
-                    v[i] = __float_as_uint(z[i]);
+                    for (int i = 0; i < 32; ++i) z[i] = __uint_as_float(v[i]);
+                    if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, c * 32, c, s_bias);
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        sum += z[i];
+                        zr[cc * 32 + i] = z[i];
+                    }
+                    if (p.pre_ln) stage_bf16(my_b + c * 64, z);
                 }
-                tmem_st_32x32b_x32(taddr + c * 32, v);
-                if (p.pre_ln) stage_bf16(my_b + c * 64, z);
-            }
-            tmem_st_wait();
-            const float mean = sum * (1.f / BN);
-            float var = 0.f;
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                tmem_ld_32x32b_x32(taddr + c * 32, v);
-                tmem_ld_wait();
+                s_stat[half * GEMM_BM + row_in_tile] = sum;
+                asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
+                const float mean = (s_stat[row_in_tile] + s_stat[GEMM_BM + row_in_tile]) * (1.f / BN);
+                float var = 0.f;
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const float d = __uint_as_float(v[i]) - mean;
+                for (int i = 0; i < CPW * 32; ++i) {
+                    const float d = zr[i] - mean;
                     var += d * d;
                 }
-            }
-            const float rstd = rsqrtf(var * (1.f / BN) + p.ln_eps);
-            if (row_ok) {
-                if (p.ln_mean) p.ln_mean[row] = mean;
-                if (p.ln_rstd) p.ln_rstd[row] = rstd;
-            }
-#pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                tmem_ld_32x32b_x32(taddr + c * 32, v);
-                tmem_ld_wait();
+                s_stat[(2 + half) * GEMM_BM + row_in_tile] = var;
+                asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
+                var = s_stat[2 * GEMM_BM + row_in_tile] + s_stat[3 * GEMM_BM + row_in_tile];
+                const float rstd = rsqrtf(var * (1.f / BN) + p.ln_eps);
+                if (row_ok && half == 0) {
+                    if (p.ln_mean) p.ln_mean[row] = mean;
+                    if (p.ln_rstd) p.ln_rstd[row] = rstd;
+                }
 #pragma unroll
-                for (int i = 0; i < 32; ++i)
-                    z[i] = (__uint_as_float(v[i]) - mean) * rstd * s_gamma[c * 32 + i] + s_beta[c * 32 + i];
-                stage_bf16(my_a + c * 64, z);
+                for (int cc = 0; cc < CPW; ++cc) {
+                    const int c = c_begin + cc;
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        z[i] = (zr[cc * 32 + i] - mean) * rstd * s_gamma[c * 32 + i] + s_beta[c * 32 + i];
+                    stage_bf16(my_a + c * 64, z);
+                }
+                __syncwarp();
+                const long long row0 = (long long)m0 + quarter * 32;
+                const int off = c_begin * 64;  // byte offset of this warp's column half inside a staged bf16 row
+                drain_bf16<BN, WCOLS>(stage_a + quarter * 32 * Cfg::kRowBf16 + off, p.out_bf16, p.ld_out, p.M, p.N, row0,
+                                      c_begin * 32, lane, p.vec_ok != 0, nullptr);
+                if (p.pre_ln)
+                    drain_bf16<BN, WCOLS>(stage_b + quarter * 32 * Cfg::kRowBf16 + off, p.pre_ln, p.ld_out, p.M, p.N, row0,
+                                          c_begin * 32, lane, p.vec_ok != 0, nullptr);
             }
-            __syncwarp();
-            const long long row0 = (long long)m0 + quarter * 32;
-            drain_bf16<BN>(stage_a + quarter * 32 * Cfg::kRowBf16, p.out_bf16, p.ld_out, p.M, p.N, row0, 0, lane,
-                           p.vec_ok != 0, nullptr);
-            if (p.pre_ln)
-                drain_bf16<BN>(stage_b + quarter * 32 * Cfg::kRowBf16, p.pre_ln, p.ld_out, p.M, p.N, row0, 0, lane,
-                               p.vec_ok != 0, nullptr);
         }
         tc_fence_before();
     }
@@ -541,7 +556,7 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
         attr_set = true;
     }
     dim3 grid(nt, mt, splits);
-    gemm_bf16_kernel<BN, A_MN, B_MN><<<grid, GEMM_THREADS, smem_bytes, st>>>(tmA, tmB, epi);
+    gemm_bf16_kernel<BN, A_MN, B_MN><<<grid, GemmThreads<BN>::kThreads, smem_bytes, st>>>(tmA, tmB, epi);
     return fod_check_launch("gemm_bf16_kernel");
 }
 
