@@ -181,7 +181,8 @@ def run_cuda(args):
         # an all-reduce over arena slices and clip + AdamW + casts + zero_grad are one fused call (fod_b200/optim.py)
         from fod_b200.optim import FlatTrainState
         flat = FlatTrainState(core, lr=detr_args.lr, lr_backbone=detr_args.lr_backbone,
-                              weight_decay=detr_args.weight_decay, bucket_mb=args.bucket_mb)
+                              weight_decay=detr_args.weight_decay, bucket_mb=args.bucket_mb,
+                              wgrad_stream=bool(args.wgrad_stream))
     opt = flat if flat is not None else T.setup_optimizer(core, detr_args, capturable=use_graph)
     # N > 1: gradients are averaged by the graph-capturable bucketed reducer (fod_b200/ddp.py: flat fp32 buckets,
     # NCCL AVG on a side stream overlapping backward) instead of torch's host-driven DDP wrapper
@@ -307,6 +308,7 @@ def main():
     ap.add_argument("--graphs", type=int, default=1, help="1: replay the whole step as one CUDA graph (single GPU)")
     ap.add_argument("--kernel-events", type=int, default=1, help="1: bracket each of our kernel launches with CUDA events")
     ap.add_argument("--flat", type=int, default=1, help="1: flat parameter/gradient arenas with the fused clip+AdamW kernel")
+    ap.add_argument("--wgrad-stream", type=int, default=1, help="1: weight/bias gradient kernels on a second stream")
     ap.add_argument("--flat-grads", type=int, default=0, help="1: use the flat-bucket gradient path at N=1 too")
     ap.add_argument("--bucket-mb", type=float, default=32.0)
     ap.add_argument("--profiler-range", type=int, default=0, help="1: cudaProfilerStart/Stop around the timed steps (for ncu)")

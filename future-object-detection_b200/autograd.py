@@ -63,16 +63,41 @@ def _done(p):
         p._fod_reducer.mark_ready(p)
 
 
+class _OffCriticalPath:
+    """Weight / bias gradients are leaves of the backward graph: nothing downstream of backward waits for them except
+    the gradient all-reduce and the optimizer.  They are enqueued on the reducer's weight-gradient stream, forked from
+    the backward stream at the point where their operands exist, so that these small grids (a few CTAs each) fill SMs
+    the activation-gradient chain leaves idle.  Under CUDA-graph capture the fork becomes a parallel branch."""
+
+    def __init__(self, reducer, *operands):
+        self.ws = getattr(reducer, "wgrad_stream", None)
+        self.operands = operands
+
+    def __enter__(self):
+        if self.ws is not None:
+            self.ws.wait_stream(torch.cuda.current_stream())
+            self.ctx = torch.cuda.stream(self.ws)
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ws is not None:
+            self.ctx.__exit__(*exc)
+            for t in self.operands:  # the caching allocator must not recycle operands the side stream still reads
+                t.record_stream(self.ws)
+
+
 def weight_grad_into(p, dy, x, rows=None):
     g = p.grad.view(-1, x.shape[1])  # (N, K) view of the slot (a 1x1 conv weight is stored (N, K, 1, 1))
     if rows is not None:
         g = g[rows[0]:rows[1]]
-    ops.gemm(dy, x, a_mn=True, b_mn=True, accum_into=g)
+    with _OffCriticalPath(p._fod_reducer, dy, x):
+        ops.gemm(dy, x, a_mn=True, b_mn=True, accum_into=g)
     _done(p)
 
 
 def bias_grad_into(p, dy):
-    ops.colsum(dy, out=p.grad.view(1, -1))
+    with _OffCriticalPath(p._fod_reducer, dy):
+        ops.colsum(dy, out=p.grad.view(1, -1))
     _done(p)
 
 

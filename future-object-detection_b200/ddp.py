@@ -21,7 +21,7 @@ import torch.distributed as dist
 
 
 class BucketedGradReducer:
-    def __init__(self, params, bucket_mb=32.0, group=None, overlap=True, order=None):
+    def __init__(self, params, bucket_mb=32.0, group=None, overlap=True, order=None, wgrad_stream=True):
         """params: iterable of parameters (trainable ones are taken).  order: optional explicit layout order of the
         trainable parameters (default: reverse registration order)."""
         self.group = group
@@ -64,6 +64,9 @@ class BucketedGradReducer:
         self.side = torch.cuda.Stream() if self.overlap else None
         self.enabled = True
         self._ready = set()
+        # second stream for gradient kernels that are off backward's critical path (autograd._OffCriticalPath); the
+        # all-reduce of a bucket and the optimizer wait for it
+        self.wgrad_stream = torch.cuda.Stream() if (self.cuda and wgrad_stream) else None
 
     # ------------------------------------------------------------------ per step
     def zero_grad(self):
@@ -85,9 +88,13 @@ class BucketedGradReducer:
         flat = self.flat[bi]
         if self.overlap:
             self.side.wait_stream(torch.cuda.current_stream())
+            if self.wgrad_stream is not None:
+                self.side.wait_stream(self.wgrad_stream)
             with torch.cuda.stream(self.side):
                 self._all_reduce_avg(flat)
         else:
+            if self.wgrad_stream is not None:
+                torch.cuda.current_stream().wait_stream(self.wgrad_stream)
             self._all_reduce_avg(flat)
 
     def _all_reduce_avg(self, flat):
@@ -123,6 +130,8 @@ class BucketedGradReducer:
         for bi in range(len(self.buckets)):
             if not self._launched[bi]:
                 self._reduce(bi)
+        if self.wgrad_stream is not None:
+            torch.cuda.current_stream().wait_stream(self.wgrad_stream)
         if self.overlap and self.world > 1 and self.enabled:
             torch.cuda.current_stream().wait_stream(self.side)
 

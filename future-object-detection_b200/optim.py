@@ -22,7 +22,7 @@ BF16 = torch.bfloat16
 
 class FlatTrainState:
     def __init__(self, model, lr=1e-4, lr_backbone=1e-5, weight_decay=1e-4, betas=(0.9, 0.999), eps=1e-8,
-                 bucket_mb=32.0, group=None, overlap=True):
+                 bucket_mb=32.0, group=None, overlap=True, wgrad_stream=True):
         """Parameter groups as runs/_helper.py:84-107: names containing "backbone" train at lr_backbone."""
         self.model = model
         named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
@@ -31,7 +31,7 @@ class FlatTrainState:
         # layout = the order in which backward produces gradients: heads/decoder, encoder, ..., backbone last
         order = list(reversed(rest)) + list(reversed(back))
         self.reducer = BucketedGradReducer([p for _, p in named], bucket_mb=bucket_mb, group=group, overlap=overlap,
-                                           order=order)
+                                           order=order, wgrad_stream=wgrad_stream)
         r = self.reducer
         dev = r.arena.device
         self.n = r.numel
