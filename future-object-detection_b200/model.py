@@ -151,19 +151,51 @@ class FrozenBatchNorm2d(nn.Module):
         shift = self.bias - self.running_mean * scale
         return x * scale.view(1, -1, 1, 1).to(x.dtype) + shift.view(1, -1, 1, 1).to(x.dtype)
 
+    def fold(self):
+        """(scale, shift) of the frozen affine map, cached: the four buffers only change through load_state_dict / .to,
+        which bump their version counters.  Refreshed IN PLACE so a captured CUDA graph keeps reading valid memory."""
+        bufs = (self.weight, self.bias, self.running_mean, self.running_var)
+        key = tuple(b._version for b in bufs) + (self.weight.device, self.weight.data_ptr())
+        if getattr(self, "_fold_key", None) != key:
+            with torch.no_grad():
+                s = self.weight * (self.running_var + 1e-5).rsqrt()
+                t = self.bias - self.running_mean * s
+                old = getattr(self, "_fold_st", None)
+                if old is not None and old[0].device == s.device and old[0].shape == s.shape:
+                    old[0].copy_(s)
+                    old[1].copy_(t)
+                else:
+                    self._fold_st = (s, t)
+            self._fold_key = key
+            if not getattr(self, "_fold_hooked", False):
+                self.register_load_state_dict_post_hook(lambda m, keys: m.fold())
+                self._fold_hooked = True
+        return self._fold_st
+
 
 class _ConvAffineAct(torch.autograd.Function):
-    """y = [relu](conv(x, w) + b [+ z]) on cuDNN with the frozen BatchNorm folded into (w, b) — library code for the
-    backbone (not a hand-written kernel).  Forward is ONE fused cuDNN launch where the runtime offers
-    it (cudnn_convolution_relu / cudnn_convolution_add_relu); backward is one mask pass + cuDNN dgrad/wgrad.  Replaces
-    conv -> x*scale -> +shift -> (+identity) -> relu, i.e. 3-4 full passes over the activation per layer."""
+    """y = [relu](conv(x, W·s) + t [+ z]) on cuDNN with the frozen BatchNorm (scale s, shift t) folded into the conv —
+    library code for the backbone (not a hand-written kernel).  Forward is ONE fused cuDNN launch where
+    the runtime offers it (cudnn_convolution_relu / cudnn_convolution_add_relu); backward is one mask pass + cuDNN
+    dgrad / wgrad.  Replaces conv -> x*scale -> +shift -> (+identity) -> relu, i.e. 3-4 full passes per layer.
+    The fold is done here (dW = dW_folded · s), so an arena-backed weight gets its gradient written in place on the
+    weight-gradient stream (autograd._OffCriticalPath) instead of through MulBackward + AccumulateGrad."""
 
     fused_ok = True
 
     @staticmethod
-    def forward(ctx, x, w32, b32, stride, padding, relu, z):
-        wq = w32.to(x.dtype).contiguous(memory_format=torch.channels_last)
-        bq = b32.to(x.dtype)
+    def forward(ctx, x, w, scale, shift, stride, padding, relu, z):
+        s4 = scale.view(-1, 1, 1, 1)
+        if w.requires_grad:
+            wq = (w.detach() * s4).to(x.dtype).contiguous(memory_format=torch.channels_last)
+            bq = shift.to(x.dtype)
+        else:  # frozen stem / layer1 (paper.py:102-109): folded operands cached on the version counters
+            key = (w._version, scale._version, shift._version, x.dtype, w.device, w.data_ptr(), scale.data_ptr())
+            c = getattr(w, "_fod_folded", None)
+            if c is None or c[0] != key:
+                c = (key, (w.detach() * s4).to(x.dtype).contiguous(memory_format=torch.channels_last), shift.to(x.dtype))
+                w._fod_folded = c
+            wq, bq = c[1], c[2]
         y = None
         if relu and _ConvAffineAct.fused_ok:
             try:
@@ -179,30 +211,40 @@ class _ConvAffineAct(torch.autograd.Function):
                 y = y + z
             if relu:
                 y = y.relu_()
-        ctx.save_for_backward(x, wq, y if relu else None)
+        ctx.save_for_backward(x, wq, y if relu else None, s4)
         ctx.cfg = (stride, padding, relu, z is not None)
+        ctx.direct = A._use(w)[0] if ctx.needs_input_grad[1] else False
+        ctx.w = w
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, wq, y = ctx.saved_tensors
+        x, wq, y, s4 = ctx.saved_tensors
         stride, padding, relu, has_z = ctx.cfg
         g = torch.ops.aten.threshold_backward(dy, y, 0) if relu else dy
         g = g.contiguous(memory_format=torch.channels_last)
-        dx, dw, _ = torch.ops.aten.convolution_backward(g, x, wq, None, stride, padding, (1, 1), False, (0, 0), 1,
-                                                        (ctx.needs_input_grad[0], ctx.needs_input_grad[1], False))
-        return dx, (dw.float() if dw is not None else None), None, None, None, None, (g if has_z else None)
-
-
-def _folded(conv, bn):
-    """Frozen-BN fold: conv(x, W)·s + t == conv(x, W·s) + t (backbone.py:53-63).  W·s keeps the autograd edge to W."""
-    s = bn.weight * (bn.running_var + 1e-5).rsqrt()
-    return conv.weight * s.view(-1, 1, 1, 1), bn.bias - bn.running_mean * s
+        cb = torch.ops.aten.convolution_backward
+        dw = None
+        if ctx.direct:
+            w = ctx.w
+            dx = cb(g, x, wq, None, stride, padding, (1, 1), False, (0, 0), 1, (True, False, False))[0] \
+                if ctx.needs_input_grad[0] else None
+            with A._OffCriticalPath(w._fod_reducer, g, x):
+                dwq = cb(g, x, wq, None, stride, padding, (1, 1), False, (0, 0), 1, (False, True, False))[1]
+                w.grad.addcmul_(dwq.float(), s4)
+            A._done(w)
+        else:
+            dx, dwq, _ = cb(g, x, wq, None, stride, padding, (1, 1), False, (0, 0), 1,
+                            (ctx.needs_input_grad[0], ctx.needs_input_grad[1], False))
+            if dwq is not None:
+                dw = dwq.float() * s4
+        return dx, dw, None, None, None, None, None, (g if has_z else None)
 
 
 def _conv_bn(x, conv, bn, relu, z=None):
-    w, b = _folded(conv, bn)
-    return _ConvAffineAct.apply(x, w, b, conv.stride, conv.padding, relu, z)
+    """Frozen-BN fold: conv(x, W)·s + t == conv(x, W·s) + t (backbone.py:53-63)."""
+    s, t = bn.fold()
+    return _ConvAffineAct.apply(x, conv.weight, s, t, conv.stride, conv.padding, relu, z)
 
 
 class CDetrBackbone(nn.Module):

@@ -88,3 +88,20 @@ def test_product_package_never_imports_the_oracle():
                 src = f.read()
             assert not re.search(r"^\s*(from|import)\s+[\w.]*oracle", src, flags=re.M), fn
             assert "import_module(" not in src and "__import__(" not in src, fn
+
+
+def test_frozen_bn_fold_cache_refreshes_in_place():
+    """FrozenBatchNorm2d.fold() caches (scale, shift); load_state_dict must refresh the SAME tensors (a captured CUDA
+    graph keeps reading them), and the values must equal backbone.py:53-63."""
+    from fod_b200.model import FrozenBatchNorm2d
+    bn = FrozenBatchNorm2d(6)
+    s0, t0 = bn.fold()
+    assert torch.equal(s0, torch.ones(6) * (1 + 1e-5) ** -0.5) and bn.fold()[0] is s0
+    sd = {"weight": torch.rand(6) + 0.5, "bias": torch.randn(6), "running_mean": torch.randn(6), "running_var": torch.rand(6) + 0.1}
+    bn.load_state_dict(sd)
+    s1, t1 = bn._fold_st  # refreshed by the post hook, without another fold() call
+    assert s1 is s0 and t1 is t0
+    scale = sd["weight"] * (sd["running_var"] + 1e-5).rsqrt()
+    assert torch.allclose(s1, scale) and torch.allclose(t1, sd["bias"] - sd["running_mean"] * scale)
+    x = torch.randn(2, 6, 3, 3)
+    assert torch.allclose(bn(x), x * s1.view(1, -1, 1, 1) + t1.view(1, -1, 1, 1), atol=1e-6)
