@@ -168,7 +168,7 @@ class FrozenBatchNorm2d(nn.Module):
                     self._fold_st = (s, t)
             self._fold_key = key
             if not getattr(self, "_fold_hooked", False):
-                self.register_load_state_dict_post_hook(lambda m, keys: m.fold())
+                self.register_load_state_dict_post_hook(lambda m, keys: (m.fold(), None)[1])
                 self._fold_hooked = True
         return self._fold_st
 
