@@ -262,3 +262,58 @@ extern "C" int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int
         reinterpret_cast<const __nv_bfloat16*>(x), ldx, out, N, rows_per_group, strips, rows_per_strip, vec_ok);
     return fod_check_launch("colsum_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// 3x3 / stride 2 / pad 1 max pooling over NHWC bf16 (the ResNet stem pool, torchvision resnet.py `maxpool`, reached
+// through ConditionalDETR/models/backbone.py:88-96): one thread = 8 channels (16 bytes) of one output pixel, nine
+// 16-byte loads.  HBM-bound: reads the input once (window overlap is served by L1/L2), writes a quarter of it.
+namespace fod {
+__global__ void __launch_bounds__(256)
+maxpool3x3s2_nhwc_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int H, int W, int C8,
+                         int OH, int OW) {
+    const long long total = (long long)N * OH * OW * C8;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+        const int c8 = (int)(i % C8);
+        long long t = i / C8;
+        const int ow = (int)(t % OW);
+        t /= OW;
+        const int oh = (int)(t % OH);
+        const int n = (int)(t / OH);
+        __nv_bfloat162 m[4];
+        const __nv_bfloat162 ninf = __floats2bfloat162_rn(-INFINITY, -INFINITY);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) m[j] = ninf;
+#pragma unroll
+        for (int dh = 0; dh < 3; ++dh) {
+            const int ih = oh * 2 - 1 + dh;
+            if (ih < 0 || ih >= H) continue;
+#pragma unroll
+            for (int dw = 0; dw < 3; ++dw) {
+                const int iw = ow * 2 - 1 + dw;
+                if (iw < 0 || iw >= W) continue;
+                const uint4 u = __ldg(reinterpret_cast<const uint4*>(x + (((long long)n * H + ih) * W + iw) * C8 * 8) + c8);
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) m[j] = __hmax2(m[j], h[j]);
+            }
+        }
+        uint4 o;
+        __nv_bfloat162* oh2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) oh2[j] = m[j];
+        reinterpret_cast<uint4*>(y)[i] = o;
+    }
+}
+}  // namespace fod
+
+extern "C" int fod_maxpool3x3s2_nhwc(const void* x, void* y, int32_t N, int32_t H, int32_t W, int32_t C, void* stream) {
+    if (!x || !y || N <= 0 || H <= 0 || W <= 0 || C <= 0 || C % 8) return fod_fail(FOD_E_ARG, "maxpool: null/empty or C % 8 != 0");
+    if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) return fod_fail(FOD_E_ARG, "maxpool: alignment");
+    const int OH = (H + 2 - 3) / 2 + 1, OW = (W + 2 - 3) / 2 + 1;
+    const long long total = (long long)N * OH * OW * (C / 8);
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148LL * 32) blocks = 148LL * 32;
+    fod::maxpool3x3s2_nhwc_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), N, H, W, C / 8, OH, OW);
+    return fod::fod_check_launch("maxpool3x3s2_nhwc_kernel");
+}

@@ -9,7 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfod_b200.so")
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 FOD_OK, FOD_E_ARG, FOD_E_TMAP, FOD_E_LAUNCH, FOD_E_NUMERIC = 0, 1, 2, 3, 4
 
@@ -104,6 +104,7 @@ SYMBOLS = {
     "fod_add_ln_fwd": (C.c_int, [_VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _I64, _F, _VP]),
     "fod_ln_bwd": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_colsum": (C.c_int, [_VP, _I64, _VP, _I64, _I32, _I32, _VP]),
+    "fod_maxpool3x3s2_nhwc": (C.c_int, [_VP, _VP, _I32, _I32, _I32, _I32, _VP]),
     "fod_targets_compact": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _F, _F, _VP]),
     "fod_match": (C.c_int, [C.POINTER(MatchArgs), _VP]),
     "fod_set_loss": (C.c_int, [C.POINTER(SetLossArgs), _VP]),

@@ -273,7 +273,12 @@ class CDetrBackbone(nn.Module):
         """torchvision ResNet (Bottleneck) forward with every conv+FrozenBN(+add)+ReLU group as one fused op."""
         b = self.body
         x = _conv_bn(x, b["conv1"], b["bn1"], True)
-        x = b["maxpool"](x)
+        mp = b["maxpool"]
+        if (not x.requires_grad and x.is_cuda and x.dtype == BF16 and (mp.kernel_size, mp.stride, mp.padding) == (3, 2, 1)
+                and x.is_contiguous(memory_format=torch.channels_last)):
+            x = ops.maxpool3x3s2_nhwc(x)  # frozen stem (paper.py:102-109): forward only, one HBM-bound kernel
+        else:
+            x = mp(x)
         for name in ("layer1", "layer2", "layer3", "layer4"):
             for blk in b[name]:
                 idt = x if blk.downsample is None else _conv_bn(x, blk.downsample[0], blk.downsample[1], False)

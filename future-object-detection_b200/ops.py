@@ -249,6 +249,21 @@ def colsum(x, rows_per_group=0, out=None):
     return out
 
 
+def maxpool3x3s2_nhwc(x):
+    """nn.MaxPool2d(3, 2, 1) on a channels_last bf16 (N,C,H,W) tensor -> channels_last (N,C,OH,OW); forward only."""
+    L = lib.load()
+    _chk_bf16(x, "maxpool x")
+    n, c, h, w = x.shape
+    assert x.is_contiguous(memory_format=torch.channels_last) and c % 8 == 0
+    oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    y = torch.empty((n, c, oh, ow), dtype=BF16, device=x.device, memory_format=torch.channels_last)
+    _t = prof.begin()
+    lib.check(L.fod_maxpool3x3s2_nhwc(_p(x), _p(y), n, h, w, c, _stream()), "fod_maxpool3x3s2_nhwc")
+    prof.end(_t, "maxpool", 0.0, 2.0 * (x.numel() + y.numel()))
+    LAUNCH_COUNTS["maxpool3x3s2_nhwc_kernel"] += 1
+    return y
+
+
 def targets_compact(boxes_xyxy, classes, active, height, width):
     """st_detr.py:237-263 on the device: returns (tgt_boxes (B,slots,4) cxcywh, tgt_labels int32, tgt_count int32,
     total_count fp32 scalar tensor)."""

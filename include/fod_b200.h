@@ -126,6 +126,10 @@ int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bca
                float* dzsum /* (256) or NULL: += column sums of dz = bias gradient of the linear feeding the norm */,
                int64_t M, void* stream);
 int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int32_t rows_per_group, void* stream);
+/* 3x3 / stride 2 / pad 1 max pooling, NHWC bf16, C % 8 == 0: the ResNet stem pool in front of the frozen layer1
+ * (ConditionalDETR/models/backbone.py:88-96 -> torchvision resnet `maxpool`); forward only (paper.py:102-109 freezes
+ * everything before layer2).  y is (N, (H-1)/2+1, (W-1)/2+1, C). */
+int fod_maxpool3x3s2_nhwc(const void* x, void* y, int32_t N, int32_t H, int32_t W, int32_t C, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * AP bookkeeping of one forward pass: future_od/utils/od_map.py:214-287 prepare_od_map_stuffs,

@@ -218,3 +218,12 @@ def test_block_functions_match_torch_autograd():
         errs[n] = float((gg - ref).norm() / ref.norm())
     print("block gradient rel-L2 errors:", {k: round(v, 5) for k, v in errs.items()})
     assert max(errs.values()) < 1e-2, errs
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 224, 400), (1, 8, 7, 9), (3, 64, 64, 80)])
+def test_maxpool_nhwc_exact(shape):
+    from fod_b200 import ops
+    x = _rnd(*shape, seed=5).contiguous(memory_format=torch.channels_last)
+    ref = torch.nn.functional.max_pool2d(x, 3, 2, 1)
+    got = ops.maxpool3x3s2_nhwc(x)
+    assert got.shape == ref.shape and torch.equal(got, ref)
