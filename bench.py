@@ -247,9 +247,16 @@ def run_cuda(args):
     check_match_status(core._criterion.last_status)
 
     # end to end through the public API: pinned host batch -> device, step, loss back to the host
+    # With the graph, the next batch's H2D copy is queued on a copy stream while the current step runs
+    # (GraphedTrainStep.prefetch); every step still moves its own 103 MB inside the timed region.
+    if use_graph:
+        step.prefetch(host_pool[0])
+
     def e2e_step(i):
         if use_graph:
-            return float(step(host_pool[i % n_pool]))
+            loss = step()                               # consumes the batch queued one step earlier
+            step.prefetch(host_pool[(i + 1) % n_pool])  # overlaps the step just launched
+            return float(loss.detach())
         data = {k: v.to(dev, non_blocking=True) for k, v in host_pool[i % n_pool].items()}
         return float(step(data))
 

@@ -81,9 +81,39 @@ class GraphedTrainStep:
             self.loss = self.eager(self.static)
         torch.cuda.synchronize()
 
-    def __call__(self, data):
-        for k, v in data.items():
-            if torch.is_tensor(v):
+    def __call__(self, data=None):
+        """data: a batch (host or device tensors) copied into the static inputs now, or None to consume the oldest
+        batch queued with prefetch()."""
+        cur = torch.cuda.current_stream()
+        if data is None:
+            j, ready = self._ready.pop(0)
+            cur.wait_event(ready)
+            for k, v in self._staging[j].items():
                 self.static[k].copy_(v, non_blocking=True)
+            self._consumed[j] = torch.cuda.Event()
+            self._consumed[j].record(cur)
+        else:
+            for k, v in data.items():
+                if torch.is_tensor(v):
+                    self.static[k].copy_(v, non_blocking=True)
         self.graph.replay()
         return self.loss
+
+    def prefetch(self, host_data):
+        """Queue the NEXT batch: pinned host -> device staging buffer on a copy stream, overlapping the step that is
+        running.  Two staging slots; a slot is rewritten only after the step that consumed it has copied it out."""
+        if not hasattr(self, "_staging"):
+            self._copy_stream = torch.cuda.Stream()
+            self._staging = [{k: torch.empty_like(v) for k, v in self.static.items() if torch.is_tensor(v)} for _ in range(2)]
+            self._consumed, self._ready, self._slot = [None, None], [], 0
+        assert len(self._ready) < 2, "at most two batches in flight"
+        j = self._slot
+        self._slot ^= 1
+        with torch.cuda.stream(self._copy_stream):
+            if self._consumed[j] is not None:
+                self._copy_stream.wait_event(self._consumed[j])
+            for k, v in self._staging[j].items():
+                v.copy_(host_data[k], non_blocking=True)
+            ready = torch.cuda.Event()
+            ready.record(self._copy_stream)
+        self._ready.append((j, ready))
