@@ -241,7 +241,14 @@ def run_cuda(args):
     sampler.start()
     if args.profiler_range:  # ncu --profile-from-start off: only the timed steps are captured
         torch.cuda.profiler.start()
-    ms = timed(lambda i: step(dev_pool[i % n_pool]), args.steps)
+    losses = []
+
+    def value_step(i):
+        out = step(dev_pool[i % n_pool])
+        if i in (0, args.steps - 1):
+            losses.append(out.detach().clone())  # device-side copy, read after the timed region
+
+    ms = timed(value_step, args.steps)
     if args.profiler_range:
         torch.cuda.profiler.stop()
     check_match_status(core._criterion.last_status)
@@ -278,6 +285,13 @@ def run_cuda(args):
     if rank != 0:
         return finish()
     peaks = _peaks()
+    loss_vals = [float(x) for x in losses]
+    finite = all(v == v and abs(v) != float("inf") for v in loss_vals) and \
+        all(bool(torch.isfinite(p).all()) for p in core.parameters())
+    if not finite:
+        sys.stderr.write("bench: non-finite loss or parameters after the timed steps (%s): the measurement is void\n" % loss_vals)
+        sys.stderr.flush()
+        os._exit(2)
     clips = BATCH * world * args.steps
     line = {"metric": METRIC, "value": clips / (ms / 1e3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -288,8 +302,11 @@ def run_cuda(args):
                        "optimizer": "fused flat clip+AdamW (fod_flat_adamw_step)" if flat is not None else "torch fused AdamW",
                        "grad_allreduce": ("bucketed NCCL AVG, %g MB fp32 buckets, side stream inside the graph" % args.bucket_mb) if world > 1 else None},
             "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
-            "matcher_status_by_region": status_log, "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
-    line.update(prof.roofline_report(kern, peaks, ms_inst, _traffic()))
+            "loss_first_last_timed_step": loss_vals, "matcher_status_by_region": status_log, "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
+    # warm, GPU-bound per-launch times of the heaviest (kernel, shape) pairs: each re-issued back to back in a small graph
+    cand = sorted((k for k in kern if k.startswith(("gemm", "attn"))), key=lambda k: -kern[k]["flops"] - 1e3 * kern[k]["bytes"])[:14]
+    isolated = prof.isolated_us(cand) if args.kernel_events else {}
+    line.update(prof.roofline_report(kern, peaks, ms_inst, _traffic(), isolated, n_inst))
     line["instrumented_region"] = {"steps": n_inst, "ms_per_step": ms_inst / n_inst if n_inst else None}
     if not args.no_cpu_baseline and world == 1:
         step = cpu_reference_step_fn(1)

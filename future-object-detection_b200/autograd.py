@@ -67,10 +67,16 @@ class _OffCriticalPath:
     """Weight / bias gradients are leaves of the backward graph: nothing downstream of backward waits for them except
     the gradient all-reduce and the optimizer.  They are enqueued on the reducer's weight-gradient stream, forked from
     the backward stream at the point where their operands exist, so that these small grids (a few CTAs each) fill SMs
-    the activation-gradient chain leaves idle.  Under CUDA-graph capture the fork becomes a parallel branch."""
+    the activation-gradient chain leaves idle.  Under CUDA-graph capture the fork becomes a parallel branch.
+
+    The operands the side stream reads are kept referenced until the backward stream has joined it again
+    (reducer.finish): (1) the caching allocator cannot recycle them early, and (2) autograd's InputBuffer cannot
+    accumulate another gradient INTO them in place (it only does so when it holds the last reference) — several of
+    these operands are also returned as activation gradients (LayerNorm / ReLU-mask outputs)."""
 
     def __init__(self, reducer, *operands):
         self.ws = getattr(reducer, "wgrad_stream", None)
+        self.reducer = reducer
         self.operands = operands
 
     def __enter__(self):
@@ -82,8 +88,7 @@ class _OffCriticalPath:
     def __exit__(self, *exc):
         if self.ws is not None:
             self.ctx.__exit__(*exc)
-            for t in self.operands:  # the caching allocator must not recycle operands the side stream still reads
-                t.record_stream(self.ws)
+            self.reducer.keepalive.append(self.operands)
 
 
 def weight_grad_into(p, dy, x, rows=None):

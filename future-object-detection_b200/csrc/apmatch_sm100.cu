@@ -51,13 +51,18 @@ ap_match_kernel(const ApArgs a) {
     for (int m = tid; m < M; m += AP_THREADS) s_score[m] = a.scores[((long long)b * M + m) * C + c];
     __syncthreads();
 
-    // ---- top-K by descending score (rank by counting; equal scores keep ascending index order)
+    // ---- top-K by descending score (rank by counting; equal scores keep ascending index order).  NaN sorts as the
+    // largest value, as torch.sort does, so the ranks stay a permutation and every s_order slot is written.
     for (int m = tid; m < M; m += AP_THREADS) {
         const float s = s_score[m];
+        const bool s_nan = s != s;
         int rank = 0;
         for (int j = 0; j < M; ++j) {
             const float t = s_score[j];
-            rank += (t > s) || (t == s && j < m);
+            const bool t_nan = t != t;
+            const bool greater = (t_nan && !s_nan) || (!t_nan && !s_nan && t > s);
+            const bool equal = (t_nan && s_nan) || (!t_nan && !s_nan && t == s);
+            rank += greater || (equal && j < m);
         }
         if (rank < K) {
             s_order[rank] = m;

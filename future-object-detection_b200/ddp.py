@@ -67,6 +67,7 @@ class BucketedGradReducer:
         # second stream for gradient kernels that are off backward's critical path (autograd._OffCriticalPath); the
         # all-reduce of a bucket and the optimizer wait for it
         self.wgrad_stream = torch.cuda.Stream() if (self.cuda and wgrad_stream) else None
+        self.keepalive = []  # operands of kernels in flight on wgrad_stream (see autograd._OffCriticalPath)
 
     # ------------------------------------------------------------------ per step
     def zero_grad(self):
@@ -80,6 +81,7 @@ class BucketedGradReducer:
             self._pending[bi] = len(plist)
             self._launched[bi] = False
         self._ready.clear()
+        self.keepalive.clear()
 
     def _reduce(self, bi):
         self._launched[bi] = True
@@ -132,6 +134,7 @@ class BucketedGradReducer:
                 self._reduce(bi)
         if self.wgrad_stream is not None:
             torch.cuda.current_stream().wait_stream(self.wgrad_stream)
+            self.keepalive.clear()  # the backward stream is ordered after every side-stream reader now
         if self.overlap and self.world > 1 and self.enabled:
             torch.cuda.current_stream().wait_stream(self.side)
 

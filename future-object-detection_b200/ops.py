@@ -97,8 +97,11 @@ def gemm(x, w, bias=None, residual=None, res_row_mod=0, relu=False, ln=None, out
             outs += [pre, mean, rstd]
     _t = prof.begin()
     lib.check(L.fod_linear_fwd(C.byref(a), _stream()), "fod_linear_fwd")
-    prof.end(_t, "gemm_dw" if a_mn else ("gemm_dx" if b_mn else "gemm_fwd"), 2.0 * M * N * K,
-             2.0 * (M * K + N * K) + M * N * (4 if (out_f32 or accum_into is not None) else 2))
+    prof.end(_t, "%s%s_%dx%dx%d" % ("gemm_dw" if a_mn else ("gemm_dx" if b_mn else "gemm_fwd"), "_ln" if ln is not None else "",
+                                    M, N, K), 2.0 * M * N * K,
+             2.0 * (M * K + N * K) + M * N * (4 if (out_f32 or accum_into is not None) else 2),
+             replay=(lambda: L.fod_linear_fwd(C.byref(a), _stream())) if _t is not None else None,
+             keep=(x, w, bias, residual, relu_mask, col_scale, accum_into, colsum_out, ln, outs))
     LAUNCH_COUNTS["gemm_bf16_kernel"] += 1
     return outs[0] if len(outs) == 1 else tuple(outs)
 
@@ -142,7 +145,9 @@ def attn_fwd(q1, k1, v, scale, heads=8, q2=None, k2=None, batch=None):
     Lk, parts, D = v.shape[-2], (2 if q2 is not None else 1), heads * 32
     kb = B if (k2 is not None and k2.dim() == 3) else 1
     prof.end(_t, "attn_fwd_p%d_%dx%d" % (parts, Lq, Lk), (2.0 + 2.0 * parts) * B * Lq * Lk * D,
-             2.0 * D * (B * Lq * (parts + 1) + B * Lk * 2 + (parts - 1) * kb * Lk))
+             2.0 * D * (B * Lq * (parts + 1) + B * Lk * 2 + (parts - 1) * kb * Lk),
+             replay=(lambda: L.fod_attn_fwd(C.byref(a), _stream())) if _t is not None else None,
+             keep=(q1, k1, v, q2, k2, out, lse))
     LAUNCH_COUNTS["attn_fwd_kernel"] += 1
     return out, lse
 
@@ -187,7 +192,9 @@ def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=
     lib.check(L.fod_attn_bwd(C.byref(g), _stream()), "fod_attn_bwd")
     parts = 2 if q2 is not None else 1
     prof.end(_t, "attn_bwd_p%d_%dx%d" % (parts, Lq, Lk), (4.0 + 6.0 * parts) * B * Lq * Lk * Cw,
-             2.0 * Cw * (B * Lq * (2 * parts + 2) + B * Lk * (2 * parts + 2)))
+             2.0 * Cw * (B * Lq * (2 * parts + 2) + B * Lk * (2 * parts + 2)),
+             replay=(lambda: L.fod_attn_bwd(C.byref(g), _stream())) if _t is not None else None,
+             keep=(q1, k1, v, q2, k2, out, lse, dout, delta, dq1, dk1, dv, dq2, dk2))
     LAUNCH_COUNTS["attn_delta_kernel"] += 1
     LAUNCH_COUNTS["attn_bwd_dq_kernel"] += 1
     LAUNCH_COUNTS["attn_bwd_dkdv_kernel"] += 1

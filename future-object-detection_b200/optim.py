@@ -15,6 +15,7 @@ import ctypes as C
 import torch
 
 from . import lib, ops
+from . import profile as prof
 from .ddp import BucketedGradReducer
 
 BF16 = torch.bfloat16
@@ -101,8 +102,11 @@ class FlatTrainState:
             self._args = a
         a = self._args
         a.max_norm, a.zero_grad = float(max_norm if max_norm else 0.0), int(zero_grad)
+        _t = prof.begin()
         lib.check(L.fod_flat_adamw_step(C.byref(a), C.c_void_p(torch.cuda.current_stream().cuda_stream)),
                   "fod_flat_adamw_step")
+        # algorithmic bytes: sumsq reads g (4 B); update reads p,g,m,v (16 B) and writes p,m,v,g (16 B) + bf16 shadow (2 B)
+        prof.end(_t, "adamw_flat_step", 0.0, 38.0 * self.n)
         ops.LAUNCH_COUNTS["sumsq_partial_kernel"] += 1
         ops.LAUNCH_COUNTS["optim_prepare_kernel"] += 1
         ops.LAUNCH_COUNTS["adamw_flat_kernel"] += 1

@@ -10,6 +10,7 @@ import torch
 
 _on = False
 _pending = []
+_replay = {}  # kernel name -> (callable re-issuing the LAST launch of that name, objects it needs alive)
 
 
 def enable(flag=True):
@@ -26,12 +27,64 @@ def begin():
     return e
 
 
-def end(start, name, flops=0.0, nbytes=0.0):
+def end(start, name, flops=0.0, nbytes=0.0, replay=None, keep=None):
     if start is None:
         return
     e = torch.cuda.Event(enable_timing=True)
     e.record()
     _pending.append((name, start, e, flops, nbytes))
+    if replay is not None:
+        _replay[name] = (replay, _storage_refs(keep))
+
+
+def _storage_refs(obj):
+    """Keep the MEMORY of the replayed launch alive without keeping its autograd graph alive (a stale AccumulateGrad
+    node from an eager step would drag the default stream into a later CUDA-graph capture)."""
+    if torch.is_tensor(obj):
+        return obj.detach()
+    if isinstance(obj, (tuple, list)):
+        return [_storage_refs(o) for o in obj]
+    return None
+
+
+def isolated_us(names, per_graph=16, reps=8):
+    """Device time per launch of the named kernels, each re-issued back to back inside a small CUDA graph (the launch
+    the eager, CPU-launch-bound instrumented step brackets with events is dominated by launch gaps for kernels of a
+    few microseconds; this is the warm, GPU-bound figure).  Returns {name: microseconds per launch}."""
+    out = {}
+    for name in names:
+        if name not in _replay:
+            continue
+        fn, _keep = _replay[name]
+        try:
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                for _ in range(2):
+                    fn()
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for _ in range(per_graph):
+                    fn()
+            g.replay()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(reps):
+                g.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            out[name] = 1e3 * e0.elapsed_time(e1) / (reps * per_graph)
+        except Exception as ex:  # measurement aid only: report instead of failing the bench
+            out[name] = None
+            print("isolated_us(%s) failed: %s" % (name, str(ex)[:200]))
+    return out
+
+
+def clear_replays():
+    _replay.clear()
 
 
 def disable():
@@ -50,7 +103,7 @@ def disable():
 
 
 # which roofline bounds each kernel family
-_BOUND = {"gemm": "tensor", "attn_fwd": "tensor", "attn_bwd": "tensor", "rows": "hbm", "loss": "hbm"}
+_BOUND = {"gemm": "tensor", "attn_fwd": "tensor", "attn_bwd": "tensor", "rows": "hbm", "loss": "hbm", "optim": "hbm"}
 
 
 def _family(name):
@@ -60,12 +113,14 @@ def _family(name):
         return "attn_fwd"
     if name.startswith("attn_bwd"):
         return "attn_bwd"
-    if name in ("match", "set_loss", "targets_compact"):
+    if name in ("match", "set_loss", "targets_compact", "ap_match"):
         return "loss"
+    if name.startswith("adamw") or name.startswith("optim"):
+        return "optim"
     return "rows"
 
 
-def roofline_report(kern, peaks, total_ms_timed_region=None, traffic=None):
+def roofline_report(kern, peaks, total_ms_timed_region=None, traffic=None, isolated=None, steps=1):
     """-> {"roofline": {...dominant kernel family...}, "kernels": {per-kernel table}}.  Fractions are of the MEASURED
     peaks (MEASURED_PEAKS.json) unless peaks["source"] == "fallback"; kernels timed inside a long step use the
     sustained bf16 figure."""
@@ -83,17 +138,43 @@ def roofline_report(kern, peaks, total_ms_timed_region=None, traffic=None):
                        "tflops": round(r["flops"] / sec / 1e12, 2) if sec > 0 else None,
                        "gbs": round(r["bytes"] / sec / 1e9, 1) if sec > 0 else None}
     ours_ms = sum(f["ms"] for f in fam.values())
-    top = max(fam, key=lambda k: fam[k]["ms"])
-    f = fam[top]
+    # The dominant kernel = the (kernel, shape) with the largest time per step.  Where an isolated (graph-replayed,
+    # GPU-bound) per-launch time is available it replaces the eager event bracket, which for kernels of a few
+    # microseconds mostly measures the CPU launch gap.
+    isolated = {k: v for k, v in (isolated or {}).items() if v}
+    for name, us in isolated.items():
+        table[name]["us_per_launch_isolated"] = round(us, 2)
+        r = kern[name]
+        sec_iso = us * 1e-6 * r["launches"]
+        table[name]["tflops_isolated"] = round(r["flops"] / sec_iso / 1e12, 2)
+        table[name]["gbs_isolated"] = round(r["bytes"] / sec_iso / 1e9, 1)
+
+    def per_step_ms(k):
+        r = kern[k]
+        return (isolated[k] * 1e-3 * r["launches"] if k in isolated else r["ms"]) / max(1, steps)
+
+    pool = [k for k in kern if k in isolated] or list(kern)
+    top_name = max(pool, key=per_step_ms)
+    top = _family(top_name)
+    f = dict(kern[top_name])
+    if top_name in isolated:
+        f["ms"] = isolated[top_name] * 1e-3 * f["launches"]
     sec = f["ms"] / 1e3
-    if _BOUND[top] == "tensor":
+    # the bounding roofline of THIS shape: whichever of (algorithmic flops / tensor peak) and (algorithmic bytes / HBM
+    # peak) takes longer; pure row / optimizer / loss kernels have no tensor work
+    t_tensor = f["flops"] / (peaks["bf16_sustained"] * 1e12)
+    t_hbm = f["bytes"] / (peaks["hbm_gbs"] * 1e9)
+    bound = "tensor" if (_BOUND[top] == "tensor" and t_tensor >= t_hbm) else "hbm"
+    if bound == "tensor":
         achieved, peak, unit = f["flops"] / sec / 1e12, peaks["bf16_sustained"], "TFLOP/s"
     else:
         achieved, peak, unit = f["bytes"] / sec / 1e9, peaks["hbm_gbs"], "GB/s"
-    roof = {"kernel": top, "bound": "tensor" if _BOUND[top] == "tensor" else "hbm", "achieved": achieved, "peak": peak,
-            "unit": unit, "frac": achieved / peak, "traffic": (traffic or {}).get(top), "peak_source": peaks["source"],
-            "launches": f["launches"], "avg_launch_us": 1e3 * f["ms"] / max(1, f["launches"]),
-            "share_of_our_kernel_time": f["ms"] / ours_ms if ours_ms else None}
+    roof = {"kernel": top_name, "family": top, "bound": bound, "achieved": achieved, "peak": peak,
+            "unit": unit, "frac": achieved / peak, "traffic": (traffic or {}).get(top_name, (traffic or {}).get(top)), "peak_source": peaks["source"],
+            "launches_per_step": f["launches"] / max(1, steps), "avg_launch_us": 1e3 * f["ms"] / max(1, f["launches"]),
+            "ms_per_step": per_step_ms(top_name),
+            "timing": "CUDA events around back-to-back graph replays of this launch" if top_name in isolated
+            else "CUDA events around each launch of the eager instrumented steps"}
     fams = {k: {"ms_total": round(v["ms"], 3), "launches": v["launches"],
                 "tflops": round(v["flops"] / (v["ms"] / 1e3) / 1e12, 2) if v["ms"] > 0 else None,
                 "gbs": round(v["bytes"] / (v["ms"] / 1e3) / 1e9, 1) if v["ms"] > 0 else None} for k, v in fam.items()}
