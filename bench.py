@@ -140,7 +140,7 @@ def run_reference(args):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
                              "sample": "%d steps x 1 clip, fwd+bwd+clip+AdamW, fp32, all %d host threads" % (args.steps, os.cpu_count())},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ---------------------------------------------------------------------------------------------- CUDA arm
@@ -318,11 +318,33 @@ def run_cuda(args):
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = {"value": n / dt, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
                                 "sample": "%d steps x 1 clip (fwd+bwd+clip+AdamW) of the same workload, fp32 oracle, %d threads" % (n, os.cpu_count())}
-    print(json.dumps(line))
+    emit(line)
     finish()
 
 
+_REAL_STDOUT = None
+
+
+def _claim_stdout():
+    """stdout carries exactly ONE JSON line.  Libraries write there too (NCCL prints its version banner on fd 1 when
+    NCCL_DEBUG=VERSION): everything else is sent to stderr and the line goes out through a private dup of fd 1."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
