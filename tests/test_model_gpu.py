@@ -172,3 +172,26 @@ def test_state_dict_round_trip_and_attention_store(model, ref_state_dict):
     ia.store_attention = False
     w = ia.stored_attention
     assert w.shape == (1, 128, 20) and torch.allclose(w.sum(-1), torch.ones_like(w.sum(-1)), atol=1e-3)
+
+
+def test_joint_encoder_matches_reference_golden(model):
+    """Optional JointEncoder mode (paper.py:180-203): all T*h*w tokens of a clip attend jointly, token
+    order (h w l), T IMU keys per clip (general egodeep attention).  Golden from the unmodified reference modules
+    (tests/golden/make_golden_joint.py); 2e-2 relative L2 in bf16."""
+    import os
+
+    from conftest import GOLDEN
+    from fod_b200.st_detr import JointEncoder
+    gold = torch.load(os.path.join(GOLDEN, "joint_b2_l3_5x7.pt"))
+    b, l, h, w = gold["shape"]
+    s, d = h * w, 256
+    se = model._model.separate_encoder
+    x = gold["features"].permute(0, 1, 3, 4, 2).reshape(b * l * s, d).to(DEV).to(torch.bfloat16)  # (b, t, h, w) rows
+    pos_bf = model._model.pos_encoder.spatial_tokens(h, w, d, torch.device(DEV)).to(torch.bfloat16)
+    ego = gold["egodeep"].reshape(b * l, d).to(DEV).to(torch.bfloat16)
+    with torch.no_grad():
+        y = JointEncoder(se.transformer)(x, pos_bf, ego, b, l, s)
+    got = y.view(b, l, h, w, d).permute(0, 1, 4, 2, 3).float()
+    err = rel_l2(got, gold["out"])
+    print("joint encoder rel L2", err)
+    assert err < TOL
