@@ -2,12 +2,19 @@
 // online softmax in registers.  Head dim is 32 per "part"; NPARTS = 2 realises the ConditionalDETR
 // concatenated query/key ([content ‖ sine], head dim 64) as two accumulating MMAs into the same S tile.
 //
-//   warps 0..3 : softmax (one query row per thread; TMEM lane = row), O accumulator (32 fp32) in registers
+//   warps 0..3 : softmax (one query row per thread; TMEM lane = row).  The whole 128-wide S row is pulled into
+//                registers with four back-to-back tcgen05.ld (one wait), so S is read from TMEM once per tile.
 //   warp 4     : TMA producer  (Q once, K/V double-buffered)
-//   warp 5     : TMEM alloc + tcgen05.mma issuer:  S = Q·Kᵀ (M128 N128 K32·NPARTS),  PV = P·V (M128 N32 K128)
+//   warp 5     : TMEM alloc + tcgen05.mma issuer:  S = Q·Kᵀ (M128 N128 K32·NPARTS),  O += P·V (M128 N32 K128) and
+//                L += P·1 (same shape against a constant tile of ones): the row sums come from the tensor core, from
+//                exactly the bf16 P that multiplies V.
 //
-// Per (batch, head, 128-query tile) CTA; 2 CTAs/SM overlap one CTA's softmax with the other's MMAs.
-// Bound: MUFU ex2 (one exp per 128 flop at head dim 32) and HBM at S=350; see DESIGN.md.
+// O and L ACCUMULATE IN TMEM across key tiles.  The exponent offset m_used is only raised when the running row
+// maximum exceeds it by more than 2^8 (lazy rescaling): then the softmax warp multiplies its O/L row in TMEM by
+// exp2(m_used - m_new).  In the steady state a softmax warp never waits for a P·V product; it reads O and L once.
+//
+// Per (batch, head, 128-query tile) CTA; TMEM (256 columns) admits 2 CTAs/SM, which overlap each other's phases.
+// Bound: MUFU ex2 (one exp per 128 flop at head dim 32) and HBM/latency at S=350; see DESIGN.md.
 #include "fod_internal.h"
 #include "sm100_ptx.cuh"
 #include "tmap.h"
@@ -28,7 +35,8 @@ struct AttnSmem {
     static constexpr int kK = kQ + NPARTS * AT_TILE_BYTES;
     static constexpr int kV = kK + AT_KV_STAGES * NPARTS * AT_TILE_BYTES;
     static constexpr int kP = kV + AT_KV_STAGES * AT_TILE_BYTES;
-    static constexpr int kBars = kP + AT_P_BYTES;
+    static constexpr int kOnes = kP + AT_P_BYTES;            // [128 keys][32] bf16 ones: B operand of the row-sum MMA
+    static constexpr int kBars = kOnes + AT_TILE_BYTES;
     static constexpr int kTotal = kBars + 128 + 1024;
 };
 
@@ -57,7 +65,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
     uint64_t* s_full = bars + 5;
     uint64_t* p_full = bars + 6;
     uint64_t* pv_full = bars + 7;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+    uint64_t* s_free = bars + 8;    // softmax warps have copied S(j) into registers: S(j+1) may overwrite it
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -82,15 +91,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
         mbar_init(s_full, 1);
         mbar_init(p_full, 128);
         mbar_init(pv_full, 1);
+        mbar_init(s_free, 128);
         fence_barrier_init();
     }
     if (warp == 5) tmem_alloc<256>(tmem_slot);
+    if (warp < 4) {  // constant tile of ones (every element equal, so the swizzle pattern is irrelevant)
+        uint4* ones = reinterpret_cast<uint4*>(smem + L::kOnes);
+        const uint32_t one2 = 0x3F803F80u;  // bf16x2 (1.0, 1.0)
+        for (int i = threadIdx.x; i < AT_TILE_BYTES / 16; i += 128) ones[i] = make_uint4(one2, one2, one2, one2);
+        fence_proxy_async_smem();
+    }
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     const uint32_t tmem_S = tmem_base;
-    const uint32_t tmem_PV = tmem_base + 128;
+    const uint32_t tmem_O = tmem_base + 128;  // 32 columns: O accumulator
+    const uint32_t tmem_L = tmem_base + 160;  // 32 columns, all equal: row sums of P
 
     if (warp == 4) {
         if (lane == 0) {
@@ -134,18 +151,28 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
             issue_S(0);
             for (int j = 0; j < nkt; ++j) {
                 const int s = j % AT_KV_STAGES;
+                // S(j) lives in the softmax warps' registers as soon as they have loaded it: the next score tile is
+                // computed while they exponentiate this one
+                if (j + 1 < nkt) {
+                    mbar_wait(s_free, j & 1);
+                    tc_fence_after();
+                    issue_S(j + 1);
+                }
                 mbar_wait(p_full, j & 1);
                 tc_fence_after();
                 const uint32_t v_addr = smem_u32(smem + L::kV + s * AT_TILE_BYTES);
+                const uint32_t ones_addr = smem_u32(smem + L::kOnes);
 #pragma unroll
                 for (int kk = 0; kk < AT_BN / 16; ++kk) {
                     const uint64_t da = umma_smem_desc(p_addr + (kk >> 2) * (AT_BM * 128) + (kk & 3) * 32, 16, 1024, 2);
                     const uint64_t db = umma_smem_desc(v_addr + kk * 1024, 4096, 512, 4);
-                    umma_bf16_ss(tmem_PV, da, db, idesc_pv, kk ? 1u : 0u);
+                    const uint64_t d1 = umma_smem_desc(ones_addr + kk * 1024, 4096, 512, 4);
+                    const uint32_t acc = (j | kk) ? 1u : 0u;  // O and L accumulate across key tiles
+                    umma_bf16_ss(tmem_O, da, db, idesc_pv, acc);
+                    umma_bf16_ss(tmem_L, da, d1, idesc_pv, acc);
                 }
                 umma_commit(pv_full);
                 umma_commit(kv_empty + s);
-                if (j + 1 < nkt) issue_S(j + 1);
             }
         }
     } else {
@@ -153,77 +180,103 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
         const int row = warp * 32 + lane;  // warp == TMEM lane quarter
         const uint32_t lane_off = uint32_t(warp * 32) << 16;
         uint8_t* sP = smem + L::kP;
-        float m_run = -INFINITY, l_run = 0.f;
-        float o[AT_D];
-#pragma unroll
-        for (int i = 0; i < AT_D; ++i) o[i] = 0.f;
-        uint32_t v[32];
+        float m_used = -INFINITY;  // exponent offset in use for this row (raw score units)
+        uint32_t v[4][32];
         for (int j = 0; j < nkt; ++j) {
             mbar_wait(s_full, j & 1);
             tc_fence_after();
+#pragma unroll
+            for (int c = 0; c < 4; ++c) tmem_ld_32x32b_x32(tmem_S + lane_off + c * 32, v[c]);
+            tmem_ld_wait();
+            tc_fence_before();
+            mbar_arrive(s_free);
             const int kvalid = p.Lk - j * AT_BN;  // >= 1
-            float mx = -INFINITY;
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                tmem_ld_32x32b_x32(tmem_S + lane_off + c * 32, v);
-                tmem_ld_wait();
+            if (kvalid < AT_BN) {                 // ragged last tile (warp-uniform): masked keys score -inf
 #pragma unroll
-                for (int i = 0; i < 32; ++i)
-                    if (c * 32 + i < kvalid) mx = fmaxf(mx, __uint_as_float(v[i]));
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        if (c * 32 + i >= kvalid) v[c][i] = 0xff800000u;
             }
-            const float m_new = fmaxf(m_run, mx);
-            const float alpha = fast_exp2((m_run - m_new) * p.scale_log2);
-            const float moff = m_new * p.scale_log2;
-            float rs = 0.f;
-#pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
-                tmem_ld_32x32b_x32(tmem_S + lane_off + c * 32, v);
-                tmem_ld_wait();
-                float pr[32];
+            float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;  // four independent chains
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const float e = fast_exp2(fmaf(__uint_as_float(v[i]), p.scale_log2, -moff));
-                    pr[i] = (c * 32 + i < kvalid) ? e : 0.f;
-                    rs += pr[i];
+            for (int i = 0; i < 32; ++i) {
+                mx0 = fmaxf(mx0, __uint_as_float(v[0][i]));
+                mx1 = fmaxf(mx1, __uint_as_float(v[1][i]));
+                mx2 = fmaxf(mx2, __uint_as_float(v[2][i]));
+                mx3 = fmaxf(mx3, __uint_as_float(v[3][i]));
+            }
+            const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+            // lazy rescaling: keep the offset unless the row maximum outgrew it by more than 2^8
+            const bool grow = (mx - m_used) * p.scale_log2 > 8.f;  // true on the first tile (m_used = -inf)
+            if (__any_sync(0xffffffffu, grow)) {
+                if (j > 0) {
+                    // O / L of this row hold sums taken with the old offset: bring them to the new one.  Every P·V
+                    // issued so far must have landed (the next one is only issued after this warp's p_full arrive).
+                    mbar_wait(pv_full, (j - 1) & 1);
+                    tc_fence_after();
+                    const float alpha = grow ? fast_exp2((m_used - mx) * p.scale_log2) : 1.f;
+                    uint32_t o[32];
+                    uint32_t l1[1];
+                    tmem_ld_32x32b_x32(tmem_O + lane_off, o);
+                    tmem_ld_32x32b_x1(tmem_L + lane_off, l1);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+                    l1[0] = __float_as_uint(__uint_as_float(l1[0]) * alpha);
+                    tmem_st_32x32b_x32(tmem_O + lane_off, o);
+                    tmem_st_32x32b_x1(tmem_L + lane_off, l1);
+                    tmem_st_wait();
                 }
+                if (grow) m_used = mx;
+            }
+            const float moff = m_used * p.scale_log2;
+            // the P buffer is single: P·V(j-1) must have consumed it (it was issued a whole max-pass ago)
+            if (j > 0) mbar_wait(pv_full, (j - 1) & 1);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
                 // 32 bf16 = four 16-byte chunks: logical chunk index within the 64-wide slab
                 uint8_t* slab = sP + (c >> 1) * (AT_BM * 128);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
+                    float e[8];
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) e[t] = fast_exp2(fmaf(__uint_as_float(v[c][q * 8 + t]), p.scale_log2, -moff));
                     uint4 u;
-                    u.x = pack_bf16x2(pr[q * 8 + 0], pr[q * 8 + 1]);
-                    u.y = pack_bf16x2(pr[q * 8 + 2], pr[q * 8 + 3]);
-                    u.z = pack_bf16x2(pr[q * 8 + 4], pr[q * 8 + 5]);
-                    u.w = pack_bf16x2(pr[q * 8 + 6], pr[q * 8 + 7]);
+                    u.x = pack_bf16x2(e[0], e[1]);
+                    u.y = pack_bf16x2(e[2], e[3]);
+                    u.z = pack_bf16x2(e[4], e[5]);
+                    u.w = pack_bf16x2(e[6], e[7]);
                     *reinterpret_cast<uint4*>(slab + swz_off<128>(row, (c & 1) * 4 + q)) = u;
                 }
             }
-            l_run = l_run * alpha + rs;
-            m_run = m_new;
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(p_full);
-            mbar_wait(pv_full, j & 1);
-            tc_fence_after();
-            tmem_ld_32x32b_x32(tmem_PV + lane_off, v);
-            tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < AT_D; ++i) o[i] = fmaf(o[i], alpha, __uint_as_float(v[i]));
         }
+        // every P·V and P·1 has been accumulated: read the row once
+        mbar_wait(pv_full, (nkt - 1) & 1);
+        tc_fence_after();
+        uint32_t o[32];
+        uint32_t l1[1];
+        tmem_ld_32x32b_x32(tmem_O + lane_off, o);
+        tmem_ld_32x32b_x1(tmem_L + lane_off, l1);
+        tmem_ld_wait();
         const int q = q0 + row;
         if (q < p.Lq) {
+            const float l_run = __uint_as_float(l1[0]);
             const float inv = 1.f / l_run;
             __nv_bfloat16* dst = p.out + (long long)b * p.bso + (long long)q * p.ldo + h * AT_D;
 #pragma unroll
             for (int qq = 0; qq < 4; ++qq) {
                 uint4 u;
-                u.x = pack_bf16x2(o[qq * 8 + 0] * inv, o[qq * 8 + 1] * inv);
-                u.y = pack_bf16x2(o[qq * 8 + 2] * inv, o[qq * 8 + 3] * inv);
-                u.z = pack_bf16x2(o[qq * 8 + 4] * inv, o[qq * 8 + 5] * inv);
-                u.w = pack_bf16x2(o[qq * 8 + 6] * inv, o[qq * 8 + 7] * inv);
+                u.x = pack_bf16x2(__uint_as_float(o[qq * 8 + 0]) * inv, __uint_as_float(o[qq * 8 + 1]) * inv);
+                u.y = pack_bf16x2(__uint_as_float(o[qq * 8 + 2]) * inv, __uint_as_float(o[qq * 8 + 3]) * inv);
+                u.z = pack_bf16x2(__uint_as_float(o[qq * 8 + 4]) * inv, __uint_as_float(o[qq * 8 + 5]) * inv);
+                u.w = pack_bf16x2(__uint_as_float(o[qq * 8 + 6]) * inv, __uint_as_float(o[qq * 8 + 7]) * inv);
                 reinterpret_cast<uint4*>(dst)[qq] = u;
             }
-            if (p.lse) p.lse[((long long)b * p.H + h) * p.Lq + q] = m_run * p.scale + logf(l_run);
+            if (p.lse) p.lse[((long long)b * p.H + h) * p.Lq + q] = m_used * p.scale + logf(l_run);
         }
         tc_fence_before();
     }
