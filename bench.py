@@ -99,7 +99,7 @@ def cpu_reference_step_fn(batch):
     from oracle import fod_oracle as O
 
     torch.set_num_threads(os.cpu_count())
-    sd = synthetic_state_dict(_template(), seed=0)
+    sd = synthetic_state_dict(_template(), seed=0, residual_gain=0.5)
     frozen = ("backbone.body.conv1", "backbone.body.bn1", "backbone.body.layer1")
     for k, v in sd.items():
         if v.is_floating_point() and not any(f in k for f in frozen) and "running_" not in k and \
@@ -171,7 +171,7 @@ def run_cuda(args):
         dist.init_process_group("nccl", device_id=dev)
     detr_args = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
     model = build_model(Namespace(device=dev, distributed=False), detr_args)
-    model.load_state_dict(synthetic_state_dict(_template(), seed=0))
+    model.load_state_dict(synthetic_state_dict(_template(), seed=0, residual_gain=0.5))
     model.train()
     core = model
     use_graph = bool(args.graphs)

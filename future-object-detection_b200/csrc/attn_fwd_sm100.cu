@@ -28,6 +28,25 @@ constexpr int AT_THREADS = 192;
 constexpr int AT_TILE_BYTES = AT_BN * AT_D * 2;  // 8 KB, rows of 64 B, SWIZZLE_64B
 constexpr int AT_P_BYTES = AT_BM * AT_BN * 2;    // 32 KB, two SWIZZLE_128B slabs of [128][64]
 constexpr int AT_KV_STAGES = 2;
+#ifndef FOD_ATTN_EARLY_S
+#define FOD_ATTN_EARLY_S 1
+#endif
+#ifndef FOD_ATTN_DEBUG
+#define FOD_ATTN_DEBUG 0
+#endif
+#if FOD_ATTN_DEBUG
+// first few anomalies seen by the softmax warps: 16 floats per record
+__device__ float g_attn_dbg[16 * 8];
+__device__ int g_attn_dbg_n;
+__device__ __noinline__ void attn_dbg_record(float kind, float b, float h, float q, float j, float nkt, float m_used,
+                                             float mx, float l, float o0, float o1, float s0, float s1, float extra) {
+    const int slot = atomicAdd(&g_attn_dbg_n, 1);
+    if (slot >= 8) return;
+    float* r = g_attn_dbg + slot * 16;
+    r[0] = kind; r[1] = b; r[2] = h; r[3] = q; r[4] = j; r[5] = nkt; r[6] = m_used; r[7] = mx; r[8] = l; r[9] = o0;
+    r[10] = o1; r[11] = s0; r[12] = s1; r[13] = extra; r[14] = (float)blockIdx.x; r[15] = (float)threadIdx.x;
+}
+#endif
 
 template <int NPARTS>
 struct AttnSmem {
@@ -153,11 +172,13 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                 const int s = j % AT_KV_STAGES;
                 // S(j) lives in the softmax warps' registers as soon as they have loaded it: the next score tile is
                 // computed while they exponentiate this one
+#if FOD_ATTN_EARLY_S
                 if (j + 1 < nkt) {
                     mbar_wait(s_free, j & 1);
                     tc_fence_after();
                     issue_S(j + 1);
                 }
+#endif
                 mbar_wait(p_full, j & 1);
                 tc_fence_after();
                 const uint32_t v_addr = smem_u32(smem + L::kV + s * AT_TILE_BYTES);
@@ -173,6 +194,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                 }
                 umma_commit(pv_full);
                 umma_commit(kv_empty + s);
+#if !FOD_ATTN_EARLY_S
+                if (j + 1 < nkt) issue_S(j + 1);
+#endif
             }
         }
     } else {
@@ -207,6 +231,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                 mx3 = fmaxf(mx3, __uint_as_float(v[3][i]));
             }
             const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+#if FOD_ATTN_DEBUG
+            {
+                bool anynan = false;
+#pragma unroll
+                for (int c = 0; c < 4; ++c)
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) anynan |= (__uint_as_float(v[c][i]) != __uint_as_float(v[c][i]));
+                if (anynan || !(fabsf(mx) < 3.0e38f))
+                    attn_dbg_record(1.f, b, h, q0 + row, j, nkt, m_used, mx, 0.f, 0.f, 0.f, __uint_as_float(v[0][0]),
+                                    __uint_as_float(v[3][31]), anynan ? 1.f : 0.f);
+            }
+#endif
             // lazy rescaling: keep the offset unless the row maximum outgrew it by more than 2^8
             const bool grow = (mx - m_used) * p.scale_log2 > 8.f;  // true on the first tile (m_used = -inf)
             if (__any_sync(0xffffffffu, grow)) {
@@ -266,6 +302,16 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
         if (q < p.Lq) {
             const float l_run = __uint_as_float(l1[0]);
             const float inv = 1.f / l_run;
+#if FOD_ATTN_DEBUG
+            {
+                bool bad = !(l_run >= 0.5f) || !(l_run < 3.0e38f) || !(fabsf(m_used) < 3.0e38f);
+#pragma unroll
+                for (int i = 0; i < 32; ++i) bad |= !(fabsf(__uint_as_float(o[i])) < 3.0e38f);
+                if (bad)
+                    attn_dbg_record(2.f, b, h, q, nkt, nkt, m_used, (float)p.Lk, l_run, __uint_as_float(o[0]), __uint_as_float(o[1]),
+                                    __uint_as_float(o[30]), __uint_as_float(o[31]), (float)p.Lq);
+            }
+#endif
             __nv_bfloat16* dst = p.out + (long long)b * p.bso + (long long)q * p.ldo + h * AT_D;
 #pragma unroll
             for (int qq = 0; qq < 4; ++qq) {
@@ -296,6 +342,15 @@ static int make_seq_tmap(CUtensorMap* tm, const void* base, int rowlen, int L, i
 }
 
 }  // namespace fod
+
+#if FOD_ATTN_DEBUG
+extern "C" int fod_attn_debug_read(float* host_records, int* host_count) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(host_records, fod::g_attn_dbg, sizeof(float) * 16 * 8);
+    cudaMemcpyFromSymbol(host_count, fod::g_attn_dbg_n, sizeof(int));
+    return 0;
+}
+#endif
 
 extern "C" int fod_attn_fwd(const fod_attn_args* a, void* stream) {
     using namespace fod;

@@ -170,10 +170,24 @@ static void test_linear(int M, int N, int K, int bias, int res, int res_mod, int
     cudaFree(yf32); cudaFree(mean); cudaFree(rstd);
 }
 
-static void test_attn(int B, int H, int Lq, int Lk, int two, int k2_bcast) {
+// keys scaled by a ramp over the key index: row maxima keep growing from one key tile to the next, which drives the
+// forward kernel through its accumulator-rescaling path on (almost) every tile
+__global__ void ramp_keys(__nv_bfloat16* k, int Lk, int C, float ramp, size_t n) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int key = int((i / C) % Lk);
+    k[i] = __float2bfloat16(__bfloat162float(k[i]) * (1.f + ramp * key / Lk));
+}
+
+static void test_attn(int B, int H, int Lq, int Lk, int two, int k2_bcast, float ramp = 0.f) {
     const int C = H * 32;
     __nv_bfloat16* q1 = dev_bf16((size_t)B * Lq * C, 1.5f);
     __nv_bfloat16* k1 = dev_bf16((size_t)B * Lk * C, 1.5f);
+    if (ramp != 0.f) {
+        const size_t n = (size_t)B * Lk * C;
+        ramp_keys<<<(unsigned)((n + 255) / 256), 256>>>(k1, Lk, C, ramp, n);
+        CK(cudaDeviceSynchronize());
+    }
     __nv_bfloat16* q2 = two ? dev_bf16((size_t)B * Lq * C, 1.5f) : nullptr;
     __nv_bfloat16* k2 = two ? dev_bf16((size_t)(k2_bcast ? 1 : B) * Lk * C, 1.5f) : nullptr;
     __nv_bfloat16* v = dev_bf16((size_t)B * Lk * C, 1.f);
@@ -218,7 +232,7 @@ static void test_attn(int B, int H, int Lq, int Lk, int two, int k2_bcast) {
     }
     for (size_t i = 0; i < hl.size(); ++i) lerr = fmax(lerr, fabs(hl[i] - hl2[i]));
     char name[128];
-    snprintf(name, sizeof name, "attn B%d H%d Lq%d Lk%d parts%d bc%d (lse err %.3g)", B, H, Lq, Lk, two + 1, k2_bcast, lerr);
+    snprintf(name, sizeof name, "attn B%d H%d Lq%d Lk%d parts%d bc%d ramp%g (lse err %.3g)", B, H, Lq, Lk, two + 1, k2_bcast, ramp, lerr);
     report(name, fmax(err, lerr), 2e-2, ms, (two ? 6.0 : 4.0) * B * H * (double)Lq * Lk * 32);
     cudaFree(q1); cudaFree(k1); cudaFree(q2); cudaFree(k2); cudaFree(v); cudaFree(oref); cudaFree(lref);
     cudaFree(lse); cudaFree(o);
@@ -246,6 +260,10 @@ int main(int argc, char** argv) {
         test_attn(16, 8, 350, 350, 0, 0);
         test_attn(16, 8, 1400, 1400, 0, 0);
         test_attn(2, 8, 2800, 2800, 0, 0);
+        test_attn(2, 8, 350, 350, 0, 0, 40.f);
+        test_attn(2, 8, 128, 350, 1, 1, 40.f);
+        test_attn(4, 8, 1400, 1400, 0, 0, 60.f);
+        test_attn(4, 8, 1400, 1400, 0, 0, -0.9f);
     }
     printf(g_fail ? "SELFTEST FAILED\n" : "SELFTEST OK\n");
     return g_fail;

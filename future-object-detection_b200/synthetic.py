@@ -48,8 +48,14 @@ def _gen_for(name, seed):
     return torch.Generator().manual_seed(int.from_bytes(h[:7], "little"))
 
 
-def synthetic_state_dict(template, seed=0):
-    """template: dict name -> shape (or tensor).  Values depend only on (seed, name, shape)."""
+def synthetic_state_dict(template, seed=0, residual_gain=1.0):
+    """template: dict name -> shape (or tensor).  Values depend only on (seed, name, shape).
+
+    residual_gain: factor on the affine weight of the LAST frozen BatchNorm of every backbone bottleneck (bn3).  With
+    1.0 (the fixtures under tests/golden were generated with it) the un-normalised He-initialised ResNet doubles its
+    activation variance per block (layer4 std ~60, end-to-end Jacobian gain ~1e4) and Adam's coherent first steps can
+    tip it into overflow within ~10-50 steps on a quarter of the runs.  0.5 keeps every stage at std 0.3-0.7, the
+    regime of a trained checkpoint; training workloads (bench.py, scripts/) use that."""
     out = {}
     for name, shp in template.items():
         shape = tuple(shp.shape) if hasattr(shp, "shape") else tuple(shp)
@@ -72,7 +78,7 @@ def synthetic_state_dict(template, seed=0):
                 out[name] = 0.05 * torch.randn(shape, generator=g)
             else:
                 a = math.sqrt(6.0 / (fan_in + fan_out))
-                if "input_proj" in name:
+                if "input_proj" in name and residual_gain == 1.0:
                     # the un-normalised random ResNet emits features of std ~80; a trained input_proj hands the encoder
                     # O(1) tokens.  Without this the layer-0 attention logits have std ~2000 (one-hot softmax), a regime
                     # no trained checkpoint is in and in which bf16 gradients are meaningless.
@@ -81,6 +87,8 @@ def synthetic_state_dict(template, seed=0):
         else:
             if "backbone.body" in name:  # frozen BN affine
                 out[name] = (0.9 + 0.2 * torch.rand(shape, generator=g)) if leaf == "weight" else 0.02 * torch.randn(shape, generator=g)
+                if leaf == "weight" and ".bn3." in name:
+                    out[name] = out[name] * residual_gain
             elif "norm" in name and leaf == "weight":
                 out[name] = 1.0 + 0.1 * torch.randn(shape, generator=g)
             elif "class_embed" in name:

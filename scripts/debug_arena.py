@@ -7,7 +7,7 @@ from fod_b200 import SpatioTemporalDETRArgs, build_model
 from fod_b200.optim import FlatTrainState
 from fod_b200.synthetic import make_clip, synthetic_state_dict
 dev = "cuda:0"
-sd = synthetic_state_dict(json.load(open(os.path.join(ROOT, "tests/golden/state_dict_template.json"))), seed=0)
+sd = synthetic_state_dict(json.load(open(os.path.join(ROOT, "tests/golden/state_dict_template.json"))), seed=0, residual_gain=0.5)
 dargs = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
 data = {k: v.to(dev) for k, v in make_clip(2, 3, 128, 160, seed=3).items()}
 model = build_model(Namespace(device=dev, distributed=False), dargs)

@@ -16,7 +16,7 @@ from oracle import fod_oracle as O  # noqa: E402
 
 dev = "cuda:0"
 with open(os.path.join(ROOT, "tests", "golden", "state_dict_template.json")) as f:
-    sd = synthetic_state_dict(json.load(f), seed=0)
+    sd = synthetic_state_dict(json.load(f), seed=0, residual_gain=0.5)
 model = build_model(Namespace(device=dev, distributed=False),
                     SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4))
 model.load_state_dict(sd)

@@ -20,7 +20,7 @@ from fod_b200.synthetic import make_clip, synthetic_state_dict  # noqa: E402
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 8
 dev = "cuda:0"
 with open(os.path.join(ROOT, "tests", "golden", "state_dict_template.json")) as f:
-    sd = synthetic_state_dict(json.load(f), seed=0)
+    sd = synthetic_state_dict(json.load(f), seed=0, residual_gain=0.5)
 args = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
 model = build_model(Namespace(device=dev, distributed=False), args)
 model.load_state_dict(sd)

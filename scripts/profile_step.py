@@ -18,7 +18,7 @@ H = int(sys.argv[2]) if len(sys.argv) > 2 else 448
 W = int(sys.argv[3]) if len(sys.argv) > 3 else 800
 dev = "cuda:0"
 with open(os.path.join(ROOT, "tests", "golden", "state_dict_template.json")) as f:
-    sd = synthetic_state_dict(json.load(f), seed=0)
+    sd = synthetic_state_dict(json.load(f), seed=0, residual_gain=0.5)
 args = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
 model = build_model(Namespace(device=dev, distributed=False), args)
 model.load_state_dict(sd)

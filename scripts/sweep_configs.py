@@ -20,7 +20,7 @@ from fod_b200.st_detr import JointEncoder  # noqa: E402
 from fod_b200.synthetic import make_clip, synthetic_state_dict  # noqa: E402
 
 dev = "cuda:0"
-sd = synthetic_state_dict(json.load(open(os.path.join(ROOT, "tests/golden/state_dict_template.json"))), seed=0)
+sd = synthetic_state_dict(json.load(open(os.path.join(ROOT, "tests/golden/state_dict_template.json"))), seed=0, residual_gain=0.5)
 dargs = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
 
 

@@ -12,7 +12,7 @@ from fod_b200.synthetic import make_clip, synthetic_state_dict
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 60
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 dev = "cuda:0"
-sd = synthetic_state_dict(json.load(open(os.path.join(ROOT, "tests/golden/state_dict_template.json"))), seed=0)
+sd = synthetic_state_dict(json.load(open(os.path.join(ROOT, "tests/golden/state_dict_template.json"))), seed=0, residual_gain=0.5)
 args = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
 model = build_model(Namespace(device=dev, distributed=False), args)
 model.load_state_dict(sd); model.train()
@@ -25,8 +25,36 @@ else:
     opt = T.setup_optimizer(model, args, capturable=bool(GRAPH))
 pool = [{k: v.to(dev) for k, v in make_clip(B, 3, 448, 800, seed=i).items()} for i in range(3)]
 step = T.GraphedTrainStep(model, opt, pool[0], args.max_norm, warmup=3) if GRAPH else T.TrainStep(model, opt, args.max_norm)
+def attn_debug():
+    import ctypes as C
+    from fod_b200 import lib
+    L = lib.load()
+    if not hasattr(L, "fod_attn_debug_read"):
+        return
+    rec, n = (C.c_float * 128)(), C.c_int(0)
+    L.fod_attn_debug_read(rec, C.byref(n))
+    print("attention anomaly records: %d" % n.value)
+    keys = "kind b h q j nkt m_used mx l o0 o1 s0 s1 extra block tid".split()
+    for r in range(min(n.value, 8)):
+        print("  ", {k: rec[r * 16 + i] for i, k in enumerate(keys)})
+
+
+STOP = int(os.environ.get("STOP_ON_NAN", "0"))
+hist = []
 for i in range(steps):
+    if STOP and FLAT:
+        # state BEFORE the step (what the forward of this step reads)
+        pa, sa = opt.params.abs(), opt.shadow.float().abs()
+        hist.append("before step %d: |p|max %.4g at %d  |shadow|max %.4g at %d  |p-shadow|max %.4g  |m|max %.4g |v|max %.4g  prev norm %.4g clip %.4g" % (
+            i, float(pa.max()), int(pa.argmax()), float(sa.max()), int(sa.argmax()),
+            float((opt.params - opt.shadow.float()).abs().max()), float(opt.exp_avg.abs().max()),
+            float(opt.exp_avg_sq.abs().max()), float(opt.state[0]), float(opt.state[1])))
     loss = step(pool[i % 3])
+    if STOP and not bool(torch.isfinite(loss.detach())):
+        print("step %d: non-finite loss" % i)
+        print("\n".join(hist[-4:]))
+        attn_debug()
+        break
     if i % EVERY == 0 or i == steps - 1:
         torch.cuda.synchronize()
         finite = all(bool(torch.isfinite(p).all()) for p in model.parameters())
