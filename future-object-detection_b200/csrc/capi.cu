@@ -19,5 +19,5 @@ int fod_check_launch(const char* kernel_name) {
 }
 }  // namespace fod
 
-extern "C" int fod_version(void) { return 6; }
+extern "C" int fod_version(void) { return 7; }
 extern "C" const char* fod_last_error(void) { return fod::g_err; }

@@ -9,7 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfod_b200.so")
-ABI_VERSION = 6
+ABI_VERSION = 7
 
 FOD_OK, FOD_E_ARG, FOD_E_TMAP, FOD_E_LAUNCH, FOD_E_NUMERIC = 0, 1, 2, 3, 4
 
@@ -73,6 +73,12 @@ class SetLossArgs(C.Structure):
     ]
 
 
+class FoldDesc(C.Structure):
+    """fod_fold_desc (include/fod_b200.h)."""
+    _fields_ = [("w", C.c_void_p), ("scale", C.c_void_p), ("out", C.c_void_p), ("O", C.c_int32), ("I", C.c_int32),
+                ("HW", C.c_int32), ("pad", C.c_int32)]
+
+
 class ApArgs(C.Structure):
     _fields_ = [
         ("pred_boxes", C.c_void_p), ("scores", C.c_void_p), ("anno_boxes", C.c_void_p), ("anno_classes", C.c_void_p),
@@ -105,6 +111,8 @@ SYMBOLS = {
     "fod_ln_bwd": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_colsum": (C.c_int, [_VP, _I64, _VP, _I64, _I32, _I32, _VP]),
     "fod_maxpool3x3s2_nhwc": (C.c_int, [_VP, _VP, _I32, _I32, _I32, _I32, _VP]),
+    "fod_fold_conv_weights": (C.c_int, [_VP, _I32, _I64, _VP]),
+    "fod_conv_wgrad_unfold": (C.c_int, [_VP, _VP, _VP, _I32, _I32, _I32, _VP]),
     "fod_targets_compact": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _F, _F, _VP]),
     "fod_match": (C.c_int, [C.POINTER(MatchArgs), _VP]),
     "fod_set_loss": (C.c_int, [C.POINTER(SetLossArgs), _VP]),

@@ -164,8 +164,10 @@ class FrozenBatchNorm2d(nn.Module):
                 if old is not None and old[0].device == s.device and old[0].shape == s.shape:
                     old[0].copy_(s)
                     old[1].copy_(t)
+                    self._fold_tq.copy_(t)
                 else:
                     self._fold_st = (s, t)
+                    self._fold_tq = t.to(BF16)  # the fused conv's bias operand, cast once instead of per step
             self._fold_key = key
             if not getattr(self, "_fold_hooked", False):
                 self.register_load_state_dict_post_hook(lambda m, keys: (m.fold(), None)[1])
@@ -184,18 +186,24 @@ class _ConvAffineAct(torch.autograd.Function):
     fused_ok = True
 
     @staticmethod
-    def forward(ctx, x, w, scale, shift, stride, padding, relu, z):
+    def forward(ctx, x, w, scale, shift, stride, padding, relu, z, wq_pre=None):
+        """shift None: bias-free (the downsample branch, whose shift rides on the consuming conv3).  wq_pre: W·s already
+        folded for this step by ops.ConvFoldTable (one launch for the whole backbone)."""
         s4 = scale.view(-1, 1, 1, 1)
-        if w.requires_grad:
+        if wq_pre is not None:
+            wq = wq_pre
+            bq = shift.to(x.dtype) if shift is not None else None
+        elif w.requires_grad:
             wq = (w.detach() * s4).to(x.dtype).contiguous(memory_format=torch.channels_last)
-            bq = shift.to(x.dtype)
+            bq = shift.to(x.dtype) if shift is not None else None
         else:  # frozen stem / layer1 (paper.py:102-109): folded operands cached on the version counters
-            key = (w._version, scale._version, shift._version, x.dtype, w.device, w.data_ptr(), scale.data_ptr())
+            key = (w._version, scale._version, x.dtype, w.device, w.data_ptr(), scale.data_ptr())
             c = getattr(w, "_fod_folded", None)
             if c is None or c[0] != key:
-                c = (key, (w.detach() * s4).to(x.dtype).contiguous(memory_format=torch.channels_last), shift.to(x.dtype))
+                c = (key, (w.detach() * s4).to(x.dtype).contiguous(memory_format=torch.channels_last))
                 w._fod_folded = c
-            wq, bq = c[1], c[2]
+            wq = c[1]
+            bq = shift.to(x.dtype) if shift is not None else None
         y = None
         if relu and _ConvAffineAct.fused_ok:
             try:
@@ -231,20 +239,30 @@ class _ConvAffineAct(torch.autograd.Function):
                 if ctx.needs_input_grad[0] else None
             with A._OffCriticalPath(w._fod_reducer, g, x):
                 dwq = cb(g, x, wq, None, stride, padding, (1, 1), False, (0, 0), 1, (False, True, False))[1]
-                w.grad.addcmul_(dwq.float(), s4)
+                if dwq.is_cuda and dwq.dtype == BF16 and dwq.permute(0, 2, 3, 1).is_contiguous() and w.grad.is_contiguous():
+                    ops.conv_wgrad_unfold(dwq, s4.view(-1), w.grad)   # dW += dW_folded · s, one launch
+                else:
+                    w.grad.addcmul_(dwq.float(), s4)
             A._done(w)
         else:
             dx, dwq, _ = cb(g, x, wq, None, stride, padding, (1, 1), False, (0, 0), 1,
                             (ctx.needs_input_grad[0], ctx.needs_input_grad[1], False))
             if dwq is not None:
                 dw = dwq.float() * s4
-        return dx, dw, None, None, None, None, None, (g if has_z else None)
+        return dx, dw, None, None, None, None, None, (g if has_z else None), None
 
 
-def _conv_bn(x, conv, bn, relu, z=None):
-    """Frozen-BN fold: conv(x, W)·s + t == conv(x, W·s) + t (backbone.py:53-63)."""
+def _conv_bn(x, conv, bn, relu, z=None, wq=None, shift=True, extra_shift=None):
+    """Frozen-BN fold: conv(x, W)·s + t == conv(x, W·s) + t (backbone.py:53-63).  shift=False leaves t out (the caller
+    adds it elsewhere); extra_shift is added to t."""
     s, t = bn.fold()
-    return _ConvAffineAct.apply(x, conv.weight, s, t, conv.stride, conv.padding, relu, z)
+    if x.dtype == BF16:
+        t = bn._fold_tq
+    if not shift:
+        t = None
+    elif extra_shift is not None:
+        t = t + extra_shift.to(t.dtype)
+    return _ConvAffineAct.apply(x, conv.weight, s, t, conv.stride, conv.padding, relu, z, wq)
 
 
 class CDetrBackbone(nn.Module):
@@ -272,6 +290,7 @@ class CDetrBackbone(nn.Module):
     def _body_folded(self, x):
         """torchvision ResNet (Bottleneck) forward with every conv+FrozenBN(+add)+ReLU group as one fused op."""
         b = self.body
+        pre = self._prefold(x)
         x = _conv_bn(x, b["conv1"], b["bn1"], True)
         mp = b["maxpool"]
         if (not x.requires_grad and x.is_cuda and x.dtype == BF16 and (mp.kernel_size, mp.stride, mp.padding) == (3, 2, 1)
@@ -281,11 +300,42 @@ class CDetrBackbone(nn.Module):
             x = mp(x)
         for name in ("layer1", "layer2", "layer3", "layer4"):
             for blk in b[name]:
-                idt = x if blk.downsample is None else _conv_bn(x, blk.downsample[0], blk.downsample[1], False)
-                o = _conv_bn(x, blk.conv1, blk.bn1, True)
-                o = _conv_bn(o, blk.conv2, blk.bn2, True)
-                x = _conv_bn(o, blk.conv3, blk.bn3, True, idt)
+                extra = None
+                if blk.downsample is None:
+                    idt = x
+                else:
+                    # relu(conv3(o)·s3 + t3 + convd(x)·sd + td): the downsample shift td rides on conv3's fused bias, so
+                    # the (bias-free) downsample conv needs no separate strided bias-add pass
+                    ds = blk.downsample
+                    idt = _conv_bn(x, ds[0], ds[1], False, wq=pre.get(ds[0].weight), shift=False)
+                    extra = ds[1]._fold_tq if x.dtype == BF16 else ds[1].fold()[1]
+                o = _conv_bn(x, blk.conv1, blk.bn1, True, wq=pre.get(blk.conv1.weight))
+                o = _conv_bn(o, blk.conv2, blk.bn2, True, wq=pre.get(blk.conv2.weight))
+                x = _conv_bn(o, blk.conv3, blk.bn3, True, idt, wq=pre.get(blk.conv3.weight), extra_shift=extra)
         return x
+
+    def _prefold(self, x):
+        """W·s (bf16, channels_last) of every TRAINABLE body conv for this step in one launch (ops.ConvFoldTable);
+        {} when not on the CUDA bf16 path.  Frozen convs keep their cached fold (_ConvAffineAct.forward)."""
+        if not (x.is_cuda and self.compute_dtype == BF16):
+            return {}
+        b = self.body
+        pairs = []
+        for name in ("layer1", "layer2", "layer3", "layer4"):
+            for blk in b[name]:
+                group = [(blk.conv1, blk.bn1), (blk.conv2, blk.bn2), (blk.conv3, blk.bn3)]
+                if blk.downsample is not None:
+                    group.append((blk.downsample[0], blk.downsample[1]))
+                pairs += [(c.weight, bn.fold()[0]) for c, bn in group if c.weight.requires_grad]
+        if not pairs:
+            return {}
+        ws, ss = [w for w, _ in pairs], [s_ for _, s_ in pairs]
+        tab = getattr(self, "_fold_table", None)
+        if tab is None or not tab.valid_for(ws, ss):
+            tab = ops.ConvFoldTable([w.detach() for w in ws], ss)
+            self._fold_table = tab
+        outs = tab.run()
+        return dict(zip(ws, outs))
 
     def forward_tokens(self, images):
         """(N,3,H,W) -> tokens (N*h*w, hidden) bf16 in (n, h, w) row order, plus (h, w)."""

@@ -271,6 +271,52 @@ def maxpool3x3s2_nhwc(x):
     return y
 
 
+class ConvFoldTable:
+    """Descriptor table (device memory) + persistent bf16 channels_last outputs for fod_fold_conv_weights: every
+    trainable backbone conv's W*s in ONE launch per step.  weights: fp32 (O,I,KH,KW) parameters; scales: fp32 (O)."""
+
+    def __init__(self, weights, scales):
+        dev = weights[0].device
+        self.weights, self.scales = list(weights), list(scales)
+        self.outs = [torch.empty(w.shape, dtype=BF16, device=dev).contiguous(memory_format=torch.channels_last) for w in weights]
+        arr = (lib.FoldDesc * len(weights))()
+        self.max_elems = 0
+        for d, w, s, o in zip(arr, self.weights, self.scales, self.outs):
+            assert w.dtype == torch.float32 and w.is_contiguous() and s.dtype == torch.float32 and s.numel() == w.shape[0]
+            O, I, KH, KW = w.shape
+            assert KH * KW > 1 or I % 4 == 0
+            assert o.permute(0, 2, 3, 1).is_contiguous()
+            d.w, d.scale, d.out, d.O, d.I, d.HW = w.data_ptr(), s.data_ptr(), o.data_ptr(), O, I, KH * KW
+            self.max_elems = max(self.max_elems, w.numel())
+        raw = bytes(arr)
+        self.table = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(dev)
+        self.key = tuple((w.data_ptr(), s.data_ptr()) for w, s in zip(self.weights, self.scales))
+        self.bytes = sum(6.0 * w.numel() for w in weights)
+
+    def valid_for(self, weights, scales):
+        return self.key == tuple((w.data_ptr(), s.data_ptr()) for w, s in zip(weights, scales))
+
+    def run(self):
+        L = lib.load()
+        _t = prof.begin()
+        lib.check(L.fod_fold_conv_weights(_p(self.table), len(self.outs), self.max_elems, _stream()), "fod_fold_conv_weights")
+        prof.end(_t, "fold_conv_weights", 0.0, self.bytes)
+        LAUNCH_COUNTS["fold_conv_weights_kernel"] += 1
+        return self.outs
+
+
+def conv_wgrad_unfold(dwq, scale, grad):
+    """grad (O,I,KH,KW) fp32 contiguous += float(dwq) * scale[o]; dwq bf16 (O,I,KH,KW) in channels_last storage."""
+    L = lib.load()
+    O, I, KH, KW = grad.shape
+    assert dwq.dtype == BF16 and dwq.shape == grad.shape and dwq.permute(0, 2, 3, 1).is_contiguous()
+    assert grad.dtype == torch.float32 and grad.is_contiguous() and scale.dtype == torch.float32
+    _t = prof.begin()
+    lib.check(L.fod_conv_wgrad_unfold(_p(dwq), _p(scale), _p(grad), O, I, KH * KW, _stream()), "fod_conv_wgrad_unfold")
+    prof.end(_t, "conv_wgrad_unfold", 0.0, 10.0 * grad.numel())
+    LAUNCH_COUNTS["conv_wgrad_unfold_kernel"] += 1
+
+
 def targets_compact(boxes_xyxy, classes, active, height, width):
     """st_detr.py:237-263 on the device: returns (tgt_boxes (B,slots,4) cxcywh, tgt_labels int32, tgt_count int32,
     total_count fp32 scalar tensor)."""

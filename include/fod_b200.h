@@ -131,6 +131,22 @@ int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int
  * everything before layer2).  y is (N, (H-1)/2+1, (W-1)/2+1, C). */
 int fod_maxpool3x3s2_nhwc(const void* x, void* y, int32_t N, int32_t H, int32_t W, int32_t C, void* stream);
 
+/* Frozen-BatchNorm folding of the trainable backbone convolutions (ConditionalDETR/models/backbone.py:53-63 applies
+ * y = conv(x, W)*s + t with frozen s, t; the cuDNN conv runs on W*s).  One descriptor per conv, the table lives in
+ * DEVICE memory: out[o][kh][kw][i] = bf16(w[o][i][kh][kw] * scale[o])  (torch channels_last storage). */
+typedef struct fod_fold_desc {
+    const float* w;      /* (O, I, KH, KW) fp32, contiguous */
+    const float* scale;  /* (O) */
+    void* out;           /* bf16, O*KH*KW*I elements */
+    int32_t O, I, HW, pad;
+} fod_fold_desc;
+/* ONE launch for `count` convs; max_elems = the largest O*I*HW in the table (grid sizing). */
+int fod_fold_conv_weights(const fod_fold_desc* descs_device, int32_t count, int64_t max_elems, void* stream);
+/* Backward of the fold: grad[o][i][hw] += float(dwq[o][hw][i]) * scale[o]; dwq is cuDNN's bf16 channels_last weight
+ * gradient of the folded conv, grad the fp32 (O, I, KH, KW) gradient slot of the unfolded weight. */
+int fod_conv_wgrad_unfold(const void* dwq, const float* scale, float* grad, int32_t O, int32_t I, int32_t HW,
+                          void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * AP bookkeeping of one forward pass: future_od/utils/od_map.py:214-287 prepare_od_map_stuffs,
  * called from future_od/models/st_detr.py:222-229 inside every forward.  One launch, grid (B, C):

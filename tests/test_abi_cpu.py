@@ -35,7 +35,8 @@ def test_library_exports_every_declared_symbol():
 
 @pytest.mark.parametrize("struct,cls", [("fod_linear_args", "LinearArgs"), ("fod_attn_args", "AttnArgs"),
                                         ("fod_attn_bwd_args", "AttnBwdArgs"), ("fod_match_args", "MatchArgs"),
-                                        ("fod_set_loss_args", "SetLossArgs"), ("fod_adamw_args", "AdamWArgs"), ("fod_ap_args", "ApArgs")])
+                                        ("fod_set_loss_args", "SetLossArgs"), ("fod_adamw_args", "AdamWArgs"), ("fod_ap_args", "ApArgs"),
+                                        ("fod_fold_desc", "FoldDesc")])
 def test_ctypes_structs_follow_the_header(struct, cls):
     from fod_b200 import lib
     body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (struct, struct), _header_text(), flags=re.S).group(1)

@@ -227,3 +227,55 @@ def test_maxpool_nhwc_exact(shape):
     ref = torch.nn.functional.max_pool2d(x, 3, 2, 1)
     got = ops.maxpool3x3s2_nhwc(x)
     assert got.shape == ref.shape and torch.equal(got, ref)
+
+
+def test_conv_weight_fold_table_matches_torch():
+    """fod_fold_conv_weights (one launch for many convs) == bf16(W * s) in channels_last storage, 1x1 and 3x3."""
+    from fod_b200 import ops
+    torch.manual_seed(11)
+    shapes = [(64, 256, 1, 1), (128, 128, 3, 3), (512, 1024, 1, 1), (40, 24, 3, 3), (8, 4, 1, 1)]
+    ws = [torch.randn(s, device="cuda") for s in shapes]
+    ss = [torch.rand(s[0], device="cuda") + 0.5 for s in shapes]
+    tab = ops.ConvFoldTable(ws, ss)
+    assert tab.valid_for(ws, ss)
+    outs = tab.run()
+    for w, s, o in zip(ws, ss, outs):
+        ref = (w * s.view(-1, 1, 1, 1)).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+        assert o.shape == ref.shape and o.permute(0, 2, 3, 1).is_contiguous()
+        assert torch.equal(o, ref)
+    ws[0].mul_(2.0)  # the table reads the live weights: a second run follows an in-place update
+    assert torch.equal(tab.run()[0], (ws[0] * ss[0].view(-1, 1, 1, 1)).to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("shape", [(64, 256, 1, 1), (128, 128, 3, 3), (40, 24, 3, 3)])
+def test_conv_wgrad_unfold_matches_addcmul(shape):
+    """grad += float(dW_folded) * s (fod_conv_wgrad_unfold) == torch addcmul_ on the same operands, bit-exact."""
+    from fod_b200 import ops
+    torch.manual_seed(12)
+    dwq = torch.randn(shape, device="cuda").to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    s = torch.rand(shape[0], device="cuda") + 0.5
+    grad = torch.randn(shape, device="cuda")
+    ref = grad.clone().addcmul_(dwq.float(), s.view(-1, 1, 1, 1))
+    ops.conv_wgrad_unfold(dwq, s, grad)
+    assert torch.allclose(grad, ref, rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("B,L,ramp", [(2, 350, 40.0), (2, 1400, 60.0), (1, 700, -0.9)])
+def test_attention_forward_growing_row_maxima(B, L, ramp):
+    """Keys scaled by a ramp over the key index: the row maximum keeps growing from key tile to key tile, which drives
+    the forward kernel through its lazy accumulator-rescaling path (attn_fwd_sm100.cu) on almost every tile."""
+    from fod_b200 import ops
+    H, C = 8, 256
+    q, k, v = _rnd(B, L, C, seed=31), _rnd(B, L, C, seed=32), _rnd(B, L, C, seed=33)
+    k = (k.float() * (1.0 + ramp * torch.arange(L, device=_dev()).view(1, L, 1) / L)).to(BF)
+    scale = 32 ** -0.5
+
+    def heads(t):
+        return t.float().reshape(B, L, H, 32).transpose(1, 2)
+
+    s = heads(q) @ heads(k).transpose(-1, -2) * scale
+    ref = (s.softmax(-1) @ heads(v)).transpose(1, 2).reshape(B, L, C)
+    out, lse = ops.attn_fwd(q, k, v, scale, H)
+    assert bool(torch.isfinite(out.float()).all()) and bool(torch.isfinite(lse).all())
+    _close(out, ref, what="attn out (peaked)")
+    _close(lse, torch.logsumexp(s, -1), tol=1e-3, what="lse (peaked)")
