@@ -111,6 +111,7 @@ SYMBOLS = {
     "fod_ln_bwd": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_colsum": (C.c_int, [_VP, _I64, _VP, _I64, _I32, _I32, _VP]),
     "fod_maxpool3x3s2_nhwc": (C.c_int, [_VP, _VP, _I32, _I32, _I32, _I32, _VP]),
+    "fod_stem_conv7x7s2": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),
     "fod_fold_conv_weights": (C.c_int, [_VP, _I32, _I64, _VP]),
     "fod_conv_wgrad_unfold": (C.c_int, [_VP, _VP, _VP, _I32, _I32, _I32, _VP]),
     "fod_targets_compact": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _F, _F, _VP]),

@@ -291,7 +291,21 @@ class CDetrBackbone(nn.Module):
         """torchvision ResNet (Bottleneck) forward with every conv+FrozenBN(+add)+ReLU group as one fused op."""
         b = self.body
         pre = self._prefold(x)
-        x = _conv_bn(x, b["conv1"], b["bn1"], True)
+        c1 = b["conv1"]
+        if (x.is_cuda and x.dtype == BF16 and not x.requires_grad and not c1.weight.requires_grad and c1.bias is None
+                and tuple(c1.weight.shape) == (64, 3, 7, 7) and (c1.stride, c1.padding) == ((2, 2), (3, 3))
+                and x.shape[3] % 8 == 0 and x.is_contiguous(memory_format=torch.channels_last)):
+            # frozen stem (paper.py:102-109): hand-written implicit-GEMM kernel, operands cached on the version counters
+            s1, t1 = b["bn1"].fold()
+            w1 = c1.weight
+            key = (w1._version, s1._version, t1._version, w1.data_ptr(), s1.data_ptr())
+            c = getattr(w1, "_fod_stem", None)
+            if c is None or c[0] != key:
+                c = (key, ops.stem_weights(w1, s1), t1.detach().float().contiguous())
+                w1._fod_stem = c
+            x = ops.stem_conv7x7s2(x, c[1], c[2])
+        else:
+            x = _conv_bn(x, c1, b["bn1"], True)
         mp = b["maxpool"]
         if (not x.requires_grad and x.is_cuda and x.dtype == BF16 and (mp.kernel_size, mp.stride, mp.padding) == (3, 2, 1)
                 and x.is_contiguous(memory_format=torch.channels_last)):

@@ -271,6 +271,35 @@ def maxpool3x3s2_nhwc(x):
     return y
 
 
+def stem_weights(w, scale):
+    """(64,3,7,7) fp32 conv weight and (64) fold scale -> the (64,192) bf16 operand of fod_stem_conv7x7s2:
+    [o][kh*24 + 1 + kw*3 + c] = w[o][c][kh][kw] * scale[o], zeros elsewhere."""
+    assert tuple(w.shape) == (64, 3, 7, 7)
+    wf = (w.detach().float() * scale.view(-1, 1, 1, 1)).permute(0, 2, 3, 1).reshape(64, 7, 21)  # [o][kh][kw*3+c]
+    wk = torch.zeros((64, 7, 24), dtype=torch.float32, device=w.device)
+    wk[:, :, 1:22] = wf
+    return torch.cat([wk.reshape(64, 168), torch.zeros((64, 24), device=w.device)], 1).to(BF16).contiguous()
+
+
+def stem_conv7x7s2(x, wk, bias):
+    """relu(conv7x7/s2/p3(x, W·s) + t) for a channels_last bf16 (N,3,H,W) image batch -> channels_last (N,64,OH,OW)."""
+    L = lib.load()
+    _chk_bf16(x, "stem x")
+    _chk_bf16(wk, "stem wk")
+    n, c, h, w = x.shape
+    assert c == 3 and x.is_contiguous(memory_format=torch.channels_last) and w % 8 == 0
+    assert tuple(wk.shape) == (64, 192) and wk.is_contiguous() and bias.dtype == torch.float32 and bias.numel() == 64
+    oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+    y = torch.empty((n, 64, oh, ow), dtype=BF16, device=x.device, memory_format=torch.channels_last)
+    _t = prof.begin()
+    lib.check(L.fod_stem_conv7x7s2(_p(x), _p(wk), _p(bias), _p(y), n, h, w, _stream()), "fod_stem_conv7x7s2")
+    prof.end(_t, "stem_conv7x7s2_%dx%d" % (h, w), 2.0 * n * oh * ow * 64 * 147, 2.0 * (x.numel() + y.numel()),
+             replay=(lambda: L.fod_stem_conv7x7s2(_p(x), _p(wk), _p(bias), _p(y), n, h, w, _stream())) if _t is not None else None,
+             keep=(x, wk, bias, y))
+    LAUNCH_COUNTS["stem_conv7x7s2_kernel"] += 1
+    return y
+
+
 class ConvFoldTable:
     """Descriptor table (device memory) + persistent bf16 channels_last outputs for fod_fold_conv_weights: every
     trainable backbone conv's W*s in ONE launch per step.  weights: fp32 (O,I,KH,KW) parameters; scales: fp32 (O)."""

@@ -131,6 +131,13 @@ int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int
  * everything before layer2).  y is (N, (H-1)/2+1, (W-1)/2+1, C). */
 int fod_maxpool3x3s2_nhwc(const void* x, void* y, int32_t N, int32_t H, int32_t W, int32_t C, void* stream);
 
+/* ResNet stem: conv 7x7 / stride 2 / pad 3, 3 -> 64 channels, frozen BatchNorm folded, ReLU
+ * (ConditionalDETR/models/backbone.py:88-96 -> torchvision resnet conv1+bn1+relu; frozen, forward only: paper.py:102-109).
+ * x (N,H,W,3) bf16 NHWC, W % 8 == 0; wk (64,192) bf16 with wk[o][kh*24 + 1 + kw*3 + c] = W[o][c][kh][kw]*scale[o] and
+ * zeros elsewhere; bias (64) fp32 = folded shift; y (N,(H-1)/2+1,(W-1)/2+1,64) bf16 NHWC.  Implicit GEMM on tcgen05. */
+int fod_stem_conv7x7s2(const void* x, const void* wk, const float* bias, void* y, int32_t N, int32_t H, int32_t W,
+                       void* stream);
+
 /* Frozen-BatchNorm folding of the trainable backbone convolutions (ConditionalDETR/models/backbone.py:53-63 applies
  * y = conv(x, W)*s + t with frozen s, t; the cuDNN conv runs on W*s).  One descriptor per conv, the table lives in
  * DEVICE memory: out[o][kh][kw][i] = bf16(w[o][i][kh][kw] * scale[o])  (torch channels_last storage). */

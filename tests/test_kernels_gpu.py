@@ -279,3 +279,27 @@ def test_attention_forward_growing_row_maxima(B, L, ramp):
     assert bool(torch.isfinite(out.float()).all()) and bool(torch.isfinite(lse).all())
     _close(out, ref, what="attn out (peaked)")
     _close(lse, torch.logsumexp(s, -1), tol=1e-3, what="lse (peaked)")
+
+
+@pytest.mark.parametrize("N,H,W", [(2, 64, 80), (1, 448, 800), (3, 70, 88), (1, 9, 8)])
+def test_stem_conv7x7s2_matches_torch(N, H, W):
+    """fod_stem_conv7x7s2 (implicit GEMM on tcgen05, operand rows assembled by the threads) == relu(conv2d(x, W*s) + t)
+    of torch fp32 on the same bf16-rounded image and weights, including ragged tiles and all four image borders."""
+    from fod_b200 import ops
+    torch.manual_seed(21)
+    x = torch.randn(N, 3, H, W, device="cuda").to(BF).contiguous(memory_format=torch.channels_last)
+    w = torch.randn(64, 3, 7, 7, device="cuda") * 0.1
+    s = torch.rand(64, device="cuda") + 0.5
+    t = torch.randn(64, device="cuda")
+    wk = ops.stem_weights(w, s)
+    assert wk.shape == (64, 192)
+    y = ops.stem_conv7x7s2(x, wk, t)
+    wq = (w * s.view(-1, 1, 1, 1)).to(BF).float()
+    ref = torch.nn.functional.conv2d(x.float(), wq, t, stride=2, padding=3).relu()
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=torch.channels_last)
+    _close(y, ref, what="stem conv")
+    # borders exactly: a constant image makes every interior output equal, so any mis-padded edge stands out
+    ones = torch.ones_like(x)
+    y1 = ops.stem_conv7x7s2(ones, wk, t)
+    ref1 = torch.nn.functional.conv2d(ones.float(), wq, t, stride=2, padding=3).relu()
+    _close(y1, ref1, tol=1e-2, what="stem conv borders")
