@@ -115,6 +115,8 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+    pdl_wait();
     const uint32_t tmem_S = tmem_base, tmem_dP = tmem_base + 128, tmem_dQ = tmem_base + 256;
 
     if (warp == 4) {
@@ -290,6 +292,8 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();
+    pdl_wait();
     const uint32_t tmem_S = tmem_base, tmem_dP = tmem_base + 128, tmem_dV = tmem_base + 256, tmem_dK = tmem_base + 288;
 
     if (warp == 4) {
@@ -427,6 +431,8 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
 __global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout,
                                   long long ldo, long long bso, long long lddo, long long bsdo,
                                   float* __restrict__ delta, int B, int H, int Lq) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     const long long total = (long long)B * Lq * H;
     if (idx >= total) return;
@@ -508,7 +514,7 @@ extern "C" int fod_attn_bwd(const fod_attn_bwd_args* g, void* stream) {
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     {
         const long long total = (long long)a->B * a->Lq * a->H;
-        attn_delta_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(
+        fod_launch(attn_delta_kernel, dim3((unsigned)((total + 255) / 256)), dim3(256), 0, st,
             reinterpret_cast<const __nv_bfloat16*>(a->out), reinterpret_cast<const __nv_bfloat16*>(g->dout), a->ldo,
             a->bso, g->lddo, g->bsdo, g->delta, a->B, a->H, a->Lq);
         int rc = fod_check_launch("attn_delta_kernel");
@@ -527,11 +533,11 @@ extern "C" int fod_attn_bwd(const fod_attn_bwd_args* g, void* stream) {
     }
     dim3 gq((a->Lq + AB_T - 1) / AB_T, a->H, a->B), gk((a->Lk + AB_T - 1) / AB_T, a->H, a->B);
     if (two) {
-        attn_bwd_dq_kernel<2><<<gq, AB_THREADS, DqSmem<2>::kTotal, st>>>(tq1, tk1, tq2, tk2, tv, tdo, p);
-        attn_bwd_dkdv_kernel<2><<<gk, AB_THREADS, DkvSmem<2>::kTotal, st>>>(tq1, tk1, tq2, tk2, tv, tdo, p);
+        fod_launch(attn_bwd_dq_kernel<2>, gq, dim3(AB_THREADS), DqSmem<2>::kTotal, st, tq1, tk1, tq2, tk2, tv, tdo, p);
+        fod_launch(attn_bwd_dkdv_kernel<2>, gk, dim3(AB_THREADS), DkvSmem<2>::kTotal, st, tq1, tk1, tq2, tk2, tv, tdo, p);
     } else {
-        attn_bwd_dq_kernel<1><<<gq, AB_THREADS, DqSmem<1>::kTotal, st>>>(tq1, tk1, tq2, tk2, tv, tdo, p);
-        attn_bwd_dkdv_kernel<1><<<gk, AB_THREADS, DkvSmem<1>::kTotal, st>>>(tq1, tk1, tq2, tk2, tv, tdo, p);
+        fod_launch(attn_bwd_dq_kernel<1>, gq, dim3(AB_THREADS), DqSmem<1>::kTotal, st, tq1, tk1, tq2, tk2, tv, tdo, p);
+        fod_launch(attn_bwd_dkdv_kernel<1>, gk, dim3(AB_THREADS), DkvSmem<1>::kTotal, st, tq1, tk1, tq2, tk2, tv, tdo, p);
     }
     return fod_check_launch("attn_bwd kernels");
 }

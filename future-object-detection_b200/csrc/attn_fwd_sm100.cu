@@ -124,6 +124,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_launch_dependents();  // the next kernel's prologue may overlap this grid (it still waits for our completion)
+    pdl_wait();               // ours overlapped the previous kernel up to here; global memory is touched below only
     const uint32_t tmem_S = tmem_base;
     const uint32_t tmem_O = tmem_base + 128;  // 32 columns: O accumulator
     const uint32_t tmem_L = tmem_base + 160;  // 32 columns, all equal: row sums of P
@@ -401,13 +403,13 @@ extern "C" int fod_attn_fwd(const fod_attn_args* a, void* stream) {
             cudaFuncSetAttribute(attn_fwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnSmem<2>::kTotal);
             attr2 = true;
         }
-        attn_fwd_kernel<2><<<grid, AT_THREADS, AttnSmem<2>::kTotal, st>>>(tq1, tk1, tq2, tk2, tv, p);
+        fod_launch(attn_fwd_kernel<2>, grid, dim3(AT_THREADS), AttnSmem<2>::kTotal, st, tq1, tk1, tq2, tk2, tv, p);
     } else {
         if (!attr1) {
             cudaFuncSetAttribute(attn_fwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnSmem<1>::kTotal);
             attr1 = true;
         }
-        attn_fwd_kernel<1><<<grid, AT_THREADS, AttnSmem<1>::kTotal, st>>>(tq1, tk1, tq2, tk2, tv, p);
+        fod_launch(attn_fwd_kernel<1>, grid, dim3(AT_THREADS), AttnSmem<1>::kTotal, st, tq1, tk1, tq2, tk2, tv, p);
     }
     return fod_check_launch("attn_fwd_kernel");
 }

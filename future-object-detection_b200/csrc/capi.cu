@@ -1,4 +1,5 @@
 // Error plumbing + version for the fod_b200 C ABI.
+#include <cstdlib>
 #include <stdio.h>
 #include <string.h>
 #include "fod_internal.h"
@@ -16,6 +17,13 @@ int fod_check_launch(const char* kernel_name) {
         return FOD_E_LAUNCH;
     }
     return FOD_OK;
+}
+bool fod_pdl_enabled() {
+    static const int on = [] {
+        const char* e = getenv("FOD_PDL");
+        return e ? atoi(e) : 1;
+    }();
+    return on != 0;
 }
 }  // namespace fod
 

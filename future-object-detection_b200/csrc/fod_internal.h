@@ -7,4 +7,23 @@
 namespace fod {
 int fod_fail(int code, const char* msg);          // records msg for fod_last_error(), returns code
 int fod_check_launch(const char* kernel_name);    // cudaGetLastError -> FOD_OK / FOD_E_LAUNCH
+bool fod_pdl_enabled();                           // env FOD_PDL (default on): programmatic dependent launch of the GEMMs
+
+// Kernel launch with the programmatic-stream-serialization attribute (when FOD_PDL is on): the kernel may start its
+// prologue while the previous kernel in the stream drains; it must execute griddepcontrol.wait (pdl_wait()) before its
+// first global-memory access.
+template <typename... KArgs, typename... Args>
+inline void fod_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = fod_pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 }  // namespace fod

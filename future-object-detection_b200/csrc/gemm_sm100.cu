@@ -280,6 +280,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    // Programmatic dependent launch: everything above (barrier init, TMEM allocation, descriptor prefetch) may overlap
+    // the tail of the previous kernel in the stream; nothing below reads or writes global memory before the previous
+    // kernel has completed.  The next kernel's prologue may start as soon as every CTA of this grid is resident.
+    pdl_wait();
+    pdl_launch_dependents();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -526,8 +531,10 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
         const int want = epi.kb_per_split < min_stages ? min_stages : epi.kb_per_split;
         if (want < stages) stages = want;
     }
+    bool memset_before = false;
     if (a->split_k < 0 && !a->atomic_out) {  // overwrite semantics: plain stores, or zero-fill + reductions
         if (splits > 1) {
+            memset_before = true;
             if (a->ld_out != a->N) return fod_fail(FOD_E_ARG, "gemm: auto split-K needs a dense fp32 output");
             cudaMemsetAsync(a->out_f32, 0, sizeof(float) * (size_t)a->M * a->N, st);
             epi.atomic_out = 1;
@@ -543,7 +550,17 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
         attr_set = true;
     }
     dim3 grid(nt, mt, splits);
-    gemm_bf16_kernel<BN, A_MN, B_MN><<<grid, GemmThreads<BN>::kThreads, smem_bytes, st>>>(tmA, tmB, epi);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(GemmThreads<BN>::kThreads);
+    cfg.dynamicSmemBytes = smem_bytes;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (fod_pdl_enabled() && !memset_before) ? 1 : 0;  // a memset node cannot be a programmatic predecessor
+    cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, A_MN, B_MN>, tmA, tmB, epi);
     return fod_check_launch("gemm_bf16_kernel");
 }
 

@@ -40,6 +40,8 @@ __global__ void __launch_bounds__(RO_WARPS * 32)
 add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ bcast, int rows_per_group,
                   const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
                   float* __restrict__ mean_out, float* __restrict__ rstd_out, long long M, float eps) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int lane = threadIdx.x & 31;
     const int c0 = lane * 8;
     float g[8], bt[8];
@@ -88,6 +90,8 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
               __nv_bfloat16* __restrict__ dz, float* __restrict__ dgamma, float* __restrict__ dbeta,
               float* __restrict__ dzsum, long long M) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float red[3][RO_WARPS][RO_D];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c0 = lane * 8;
@@ -164,6 +168,8 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
 __global__ void __launch_bounds__(256)
 colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ldx, float* __restrict__ out, int N, int rows_per_group,
               int strips_per_group, int rows_per_strip, int vec_ok) {
+    pdl_launch_dependents();
+    pdl_wait();
     __shared__ float red[8][256];
     const int g = blockIdx.x / strips_per_group;
     const int strip = blockIdx.x % strips_per_group;
@@ -225,7 +231,7 @@ extern "C" int fod_add_ln_fwd(const void* x, const void* bcast, int32_t rows_per
                               void* stream) {
     if (!x || !gamma || !beta || !y || M <= 0) return fod_fail(FOD_E_ARG, "add_ln_fwd: null/empty");
     if (bcast && rows_per_group <= 0) return fod_fail(FOD_E_ARG, "add_ln_fwd: rows_per_group");
-    add_ln_fwd_kernel<<<ro_grid(M), RO_WARPS * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+    fod_launch(add_ln_fwd_kernel, dim3(ro_grid(M)), dim3(RO_WARPS * 32), 0, reinterpret_cast<cudaStream_t>(stream),
         reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(bcast), rows_per_group,
         gamma, beta, reinterpret_cast<__nv_bfloat16*>(y), mean_out, rstd_out, M, eps);
     return fod_check_launch("add_ln_fwd_kernel");
@@ -236,7 +242,7 @@ extern "C" int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, cons
                           float* dbeta, float* dzsum, int64_t M, void* stream) {
     if (!dy || !pre || !mean || !rstd || !gamma || !dz || M <= 0) return fod_fail(FOD_E_ARG, "ln_bwd: null/empty");
     if (bcast && rows_per_group <= 0) return fod_fail(FOD_E_ARG, "ln_bwd: rows_per_group");
-    ln_bwd_kernel<<<ro_grid(M), RO_WARPS * 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+    fod_launch(ln_bwd_kernel, dim3(ro_grid(M)), dim3(RO_WARPS * 32), 0, reinterpret_cast<cudaStream_t>(stream),
         reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(dy2),
         reinterpret_cast<const __nv_bfloat16*>(pre), reinterpret_cast<const __nv_bfloat16*>(bcast), rows_per_group, mean,
         rstd, gamma, reinterpret_cast<__nv_bfloat16*>(dz), dgamma, dbeta, dzsum, M);
@@ -258,7 +264,7 @@ extern "C" int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int
     strips = (rows_per_group + rows_per_strip - 1) / rows_per_strip;
     dim3 grid(groups * strips, col_slabs);
     const int vec_ok = (ldx % 8 == 0) && !(reinterpret_cast<uintptr_t>(x) & 15);
-    colsum_kernel<<<grid, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+    fod_launch(colsum_kernel, grid, dim3(256), 0, reinterpret_cast<cudaStream_t>(stream),
         reinterpret_cast<const __nv_bfloat16*>(x), ldx, out, N, rows_per_group, strips, rows_per_strip, vec_ok);
     return fod_check_launch("colsum_kernel");
 }
