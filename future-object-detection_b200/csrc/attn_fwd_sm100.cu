@@ -54,9 +54,14 @@ struct AttnSmem {
     static constexpr int kK = kQ + NPARTS * AT_TILE_BYTES;
     static constexpr int kV = kK + AT_KV_STAGES * NPARTS * AT_TILE_BYTES;
     static constexpr int kP = kV + AT_KV_STAGES * AT_TILE_BYTES;
-    static constexpr int kOnes = kP + AT_P_BYTES;            // [128 keys][32] bf16 ones: B operand of the row-sum MMA
+    // one-part attention double-buffers P: the softmax warps of tile j only wait for P·V(j-2); with two parts the
+    // second buffer would cost the second resident CTA
+    static constexpr int kPBuf = NPARTS == 1 ? 2 : 1;
+    static constexpr int kOnes = kP + kPBuf * AT_P_BYTES;            // [128 keys][32] bf16 ones: B operand of the row-sum MMA
     static constexpr int kBars = kOnes + AT_TILE_BYTES;
-    static constexpr int kTotal = kBars + 128 + 1024;
+    // the dynamic window starts 1024-aligned (checked in the kernel): no alignment slack, which is what lets two
+    // 112 KB CTAs share an SM
+    static constexpr int kTotal = kBars + 128;
 };
 
 struct AttnParams {
@@ -76,16 +81,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                 const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
     using L = AttnSmem<NPARTS>;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = smem_raw;
+    if (smem_u32(smem_raw) & 1023u) __trap();  // the swizzled tiles need a 1024-byte aligned window (no static smem here)
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBars);
     uint64_t* q_full = bars + 0;
     uint64_t* kv_full = bars + 1;   // [2]
     uint64_t* kv_empty = bars + 3;  // [2]
     uint64_t* s_full = bars + 5;
     uint64_t* p_full = bars + 6;
-    uint64_t* pv_full = bars + 7;
+    // P·V(j) completion alternates between two barriers: a parity wait can only tell the latest phase from the one
+    // before, and with double-buffered P the softmax warps look two tiles back
+    auto pv_full = [&](int j) { return bars + ((j & 1) ? 9 : 7); };
     uint64_t* s_free = bars + 8;    // softmax warps have copied S(j) into registers: S(j+1) may overwrite it
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -109,7 +117,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
         }
         mbar_init(s_full, 1);
         mbar_init(p_full, 128);
-        mbar_init(pv_full, 1);
+        mbar_init(pv_full(0), 1);
+        mbar_init(pv_full(1), 1);
         mbar_init(s_free, 128);
         fence_barrier_init();
     }
@@ -187,14 +196,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                 const uint32_t ones_addr = smem_u32(smem + L::kOnes);
 #pragma unroll
                 for (int kk = 0; kk < AT_BN / 16; ++kk) {
-                    const uint64_t da = umma_smem_desc(p_addr + (kk >> 2) * (AT_BM * 128) + (kk & 3) * 32, 16, 1024, 2);
+                    const uint64_t da = umma_smem_desc(p_addr + (j % L::kPBuf) * AT_P_BYTES + (kk >> 2) * (AT_BM * 128) + (kk & 3) * 32, 16, 1024, 2);
                     const uint64_t db = umma_smem_desc(v_addr + kk * 1024, 4096, 512, 4);
                     const uint64_t d1 = umma_smem_desc(ones_addr + kk * 1024, 4096, 512, 4);
                     const uint32_t acc = (j | kk) ? 1u : 0u;  // O and L accumulate across key tiles
                     umma_bf16_ss(tmem_O, da, db, idesc_pv, acc);
                     umma_bf16_ss(tmem_L, da, d1, idesc_pv, acc);
                 }
-                umma_commit(pv_full);
+                umma_commit(pv_full(j));
                 umma_commit(kv_empty + s);
 #if !FOD_ATTN_EARLY_S
                 if (j + 1 < nkt) issue_S(j + 1);
@@ -251,7 +260,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                 if (j > 0) {
                     // O / L of this row hold sums taken with the old offset: bring them to the new one.  Every P·V
                     // issued so far must have landed (the next one is only issued after this warp's p_full arrive).
-                    mbar_wait(pv_full, (j - 1) & 1);
+                    mbar_wait(pv_full(j - 1), ((j - 1) >> 1) & 1);
                     tc_fence_after();
                     const float alpha = grow ? fast_exp2((m_used - mx) * p.scale_log2) : 1.f;
                     uint32_t o[32];
@@ -269,12 +278,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                 if (grow) m_used = mx;
             }
             const float moff = m_used * p.scale_log2;
-            // the P buffer is single: P·V(j-1) must have consumed it (it was issued a whole max-pass ago)
-            if (j > 0) mbar_wait(pv_full, (j - 1) & 1);
+            // the P buffer about to be overwritten must have been consumed by its P·V (two tiles ago when double-buffered)
+            if (j >= L::kPBuf) mbar_wait(pv_full(j - L::kPBuf), ((j - L::kPBuf) >> 1) & 1);
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 // 32 bf16 = four 16-byte chunks: logical chunk index within the 64-wide slab
-                uint8_t* slab = sP + (c >> 1) * (AT_BM * 128);
+                uint8_t* slab = sP + (j % L::kPBuf) * AT_P_BYTES + (c >> 1) * (AT_BM * 128);
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     float e[8];
@@ -293,7 +302,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
             mbar_arrive(p_full);
         }
         // every P·V and P·1 has been accumulated: read the row once
-        mbar_wait(pv_full, (nkt - 1) & 1);
+        mbar_wait(pv_full(nkt - 1), ((nkt - 1) >> 1) & 1);
         tc_fence_after();
         uint32_t o[32];
         uint32_t l1[1];

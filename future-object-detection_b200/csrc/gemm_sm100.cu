@@ -4,6 +4,7 @@
 //   warps 2..5: epilogue, one accumulator row per thread (tcgen05.ld 32x32b), bias / residual / ReLU /
 //               LayerNorm over the full 256-wide row without leaving the CTA.
 // Roofline: tensor-bound for the encoder FFN (K=256/2048, M>=5600); weight/launch bound for the decoder.
+#include <cstdlib>
 #include "fod_internal.h"
 #include "sm100_ptx.cuh"
 #include "tmap.h"
@@ -577,6 +578,8 @@ static int launch_gemm_major(const fod_linear_args* a, const GemmEpi& e, cudaStr
 static int pick_bn(const fod_linear_args* a) {
     if (a->ln_gamma) return 256;
     if (a->N <= 64) return 64;
+    static const int forced = [] { const char* e = getenv("FOD_GEMM_BN"); return e ? atoi(e) : 0; }();  // tuning probe
+    if (forced == 64 || forced == 128 || (forced == 256 && a->N > 128)) return forced;
     const int mt = (a->M + GEMM_BM - 1) / GEMM_BM;
     const int cands[3] = {256, 128, 64};
     for (int i = 0; i < 3; ++i) {
