@@ -14,7 +14,9 @@ namespace fod {
 
 constexpr int AB_T = 128;                       // tile edge (queries and keys)
 constexpr int AB_D = 32;                        // head dim per part
-constexpr int AB_THREADS = 192;
+constexpr int AB_THREADS = 320;  // 8 softmax warps (two per TMEM lane quarter, 64 of the 128 score columns each: one
+                                 // warp per scheduler cannot hide the ex2 / TMEM-load latencies), TMA warp, MMA warp
+constexpr int AB_PROD = 8, AB_MMA = 9;
 constexpr int AB_TILE = AB_T * AB_D * 2;        // 8 KB operand tile, 64-byte rows, SWIZZLE_64B
 constexpr int AB_PT = AB_T * AB_T * 2;          // 32 KB P / dS tile: two SWIZZLE_128B slabs [128][64]
 constexpr int AB_STAGES = 2;
@@ -95,7 +97,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
     const int q0 = blockIdx.x * AB_T, h = blockIdx.y, b = blockIdx.z;
     const int nkt = (p.Lk + AB_T - 1) / AB_T;
 
-    if (warp == 4 && lane == 0) {
+    if (warp == AB_PROD && lane == 0) {
         tma_prefetch_desc(&tmQ1);
         tma_prefetch_desc(&tmK1);
         tma_prefetch_desc(&tmV);
@@ -106,11 +108,11 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
             mbar_init(kv_empty + s, 1);
         }
         mbar_init(s_full, 1);
-        mbar_init(ds_full, 128);
+        mbar_init(ds_full, 256);
         mbar_init(dq_done, 1);
         fence_barrier_init();
     }
-    if (warp == 5) tmem_alloc<512>(tmem_slot);
+    if (warp == AB_MMA) tmem_alloc<512>(tmem_slot);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -119,7 +121,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
     pdl_wait();
     const uint32_t tmem_S = tmem_base, tmem_dP = tmem_base + 128, tmem_dQ = tmem_base + 256;
 
-    if (warp == 4) {
+    if (warp == AB_PROD) {
         if (lane == 0) {
             mbar_arrive_expect_tx(q_full, (NPARTS + 1) * AB_TILE);
             tma_load_3d(smem + L::kQ, &tmQ1, q_full, h * AB_D, q0, b * p.bm_q1);
@@ -135,7 +137,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
                 tma_load_3d(smem + L::kV + s * AB_TILE, &tmV, kv_full + s, h * AB_D, j * AB_T, b * p.bm_v);
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == AB_MMA) {
         if (lane == 0) {
             constexpr uint32_t idesc_s = umma_idesc_bf16(AB_T, AB_T, 0, 0);
             constexpr uint32_t idesc_g = umma_idesc_bf16(AB_T, AB_D, 0, 1);  // B operand MN-major
@@ -182,8 +184,9 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
             umma_commit(dq_done);
         }
     } else {
-        const int row = warp * 32 + lane;
-        const uint32_t lane_off = uint32_t(warp * 32) << 16;
+        const int half = warp >> 2;  // which 64 of the 128 score columns
+        const int row = (warp & 3) * 32 + lane;
+        const uint32_t lane_off = uint32_t((warp & 3) * 32) << 16;
         const int q = q0 + row;
         const bool q_ok = q < p.Lq;
         const long long st = ((long long)b * p.H + h) * p.Lq + q;
@@ -197,7 +200,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
             tc_fence_after();
             const int kvalid = p.Lk - j * AB_T;
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 2 * half; c < 2 * half + 2; ++c) {
                 tmem_ld_32x32b_x32(tmem_S + lane_off + c * 32, vs);
                 tmem_ld_32x32b_x32(tmem_dP + lane_off + c * 32, vp);
                 tmem_ld_wait();
@@ -218,6 +221,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
         tc_fence_after();
 #pragma unroll
         for (int part = 0; part < NPARTS; ++part) {
+            if (half != part) continue;  // warp-uniform: part 0 by the first four warps, part 1 by the others
             tmem_ld_32x32b_x32(tmem_dQ + lane_off + part * AB_D, vs);
             tmem_ld_wait();
             if (q_ok) {
@@ -229,7 +233,7 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
         tc_fence_before();
     }
     __syncthreads();
-    if (warp == 5) {
+    if (warp == AB_MMA) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
     }
@@ -272,7 +276,7 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
     const int k0 = blockIdx.x * AB_T, h = blockIdx.y, b = blockIdx.z;
     const int nqt = (p.Lq + AB_T - 1) / AB_T;
 
-    if (warp == 4 && lane == 0) {
+    if (warp == AB_PROD && lane == 0) {
         tma_prefetch_desc(&tmQ1);
         tma_prefetch_desc(&tmK1);
         tma_prefetch_desc(&tmV);
@@ -283,11 +287,11 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
             mbar_init(q_empty + s, 1);
         }
         mbar_init(s_full, 1);
-        mbar_init(pds_full, 128);
+        mbar_init(pds_full, 256);
         mbar_init(done, 1);
         fence_barrier_init();
     }
-    if (warp == 5) tmem_alloc<512>(tmem_slot);
+    if (warp == AB_MMA) tmem_alloc<512>(tmem_slot);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -296,7 +300,7 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
     pdl_wait();
     const uint32_t tmem_S = tmem_base, tmem_dP = tmem_base + 128, tmem_dV = tmem_base + 256, tmem_dK = tmem_base + 288;
 
-    if (warp == 4) {
+    if (warp == AB_PROD) {
         if (lane == 0) {
             mbar_arrive_expect_tx(kv_full, (NPARTS + 1) * AB_TILE);
             tma_load_3d(smem + L::kK, &tmK1, kv_full, h * AB_D, k0, b * p.bm_k1);
@@ -312,7 +316,7 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
                 tma_load_3d(smem + L::kDO + s * AB_TILE, &tmDO, q_full + s, h * AB_D, i * AB_T, b);
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == AB_MMA) {
         if (lane == 0) {
             constexpr uint32_t idesc_s = umma_idesc_bf16(AB_T, AB_T, 0, 0);
             constexpr uint32_t idesc_g = umma_idesc_bf16(AB_T, AB_D, 0, 1);
@@ -365,8 +369,9 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
             umma_commit(done);
         }
     } else {
-        const int row = warp * 32 + lane;  // key row
-        const uint32_t lane_off = uint32_t(warp * 32) << 16;
+        const int half = warp >> 2;        // which 64 of the 128 query columns of Sᵀ / dPᵀ
+        const int row = (warp & 3) * 32 + lane;  // key row
+        const uint32_t lane_off = uint32_t((warp & 3) * 32) << 16;
         const float sl2 = p.scale * AB_LOG2E;
         uint8_t* sPT = smem + L::kPT;
         uint8_t* sDST = smem + L::kDST;
@@ -375,17 +380,17 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
         for (int i = 0; i < nqt; ++i) {
             float* lse_s = stat + (i & 1) * 2 * AB_T;
             float* dl_s = lse_s + AB_T;
-            {
+            if (half == 0) {
                 const int q = i * AB_T + row;
                 const bool ok = q < p.Lq;
                 lse_s[row] = ok ? p.lse[st0 + q] * AB_LOG2E : INFINITY;  // padded query columns -> P = 0
                 dl_s[row] = ok ? p.delta[st0 + q] : 0.f;
             }
-            named_bar_sync(1, 128);
+            named_bar_sync(1, 256);
             mbar_wait(s_full, i & 1);  // also implies tile i-1's dV/dK MMAs (reading sPT/sDST) have retired
             tc_fence_after();
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 2 * half; c < 2 * half + 2; ++c) {
                 tmem_ld_32x32b_x32(tmem_S + lane_off + c * 32, vs);
                 tmem_ld_32x32b_x32(tmem_dP + lane_off + c * 32, vp);
                 tmem_ld_wait();
@@ -409,11 +414,14 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
         const bool k_ok = key < p.Lk;
         const long long orow = ((long long)b * p.Lk + key) * p.ld_dk + h * AB_D;
         const long long orow2 = ((long long)b * p.Lk + key) * (p.H * AB_D) + h * AB_D;
-        tmem_ld_32x32b_x32(tmem_dV + lane_off, vs);
-        tmem_ld_wait();
-        if (k_ok) store_row32_bf16(p.dv + orow, vs);
+        if (half == 0) {  // warp-uniform split of the read-out: dV (and dK part 1) by warps 0-3, dK part 0 by warps 4-7
+            tmem_ld_32x32b_x32(tmem_dV + lane_off, vs);
+            tmem_ld_wait();
+            if (k_ok) store_row32_bf16(p.dv + orow, vs);
+        }
 #pragma unroll
         for (int part = 0; part < NPARTS; ++part) {
+            if (half == part) continue;
             tmem_ld_32x32b_x32(tmem_dK + lane_off + part * AB_D, vs);
             tmem_ld_wait();
             if (k_ok) store_row32_bf16(part ? p.dk2 + orow2 : p.dk1 + orow, vs);
@@ -421,7 +429,7 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
         tc_fence_before();
     }
     __syncthreads();
-    if (warp == 5) {
+    if (warp == AB_MMA) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
     }

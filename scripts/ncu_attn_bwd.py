@@ -14,3 +14,20 @@ for _ in range(3):
     dout = torch.randn_like(out)
     ops.attn_bwd(q, k, v, out, lse, dout, scale, fused="qkv")
 torch.cuda.synchronize()
+if os.environ.get("TIME"):
+    for (b, l) in [(16, 350), (16, 1400), (8, 1050)]:
+        qkv = torch.randn(b, l, 3 * C, device="cuda").to(torch.bfloat16)
+        q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
+        out, lse = ops.attn_fwd(q, k, v, scale)
+        dout = torch.randn_like(out)
+        for _ in range(5):
+            ops.attn_bwd(q, k, v, out, lse, dout, scale, fused="qkv")
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(20):
+                ops.attn_bwd(q, k, v, out, lse, dout, scale, fused="qkv")
+        g.replay(); torch.cuda.synchronize()
+        e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
+        us = e0.elapsed_time(e1) * 1e3 / 20
+        print("attn_bwd B%d S%d: %.1f us per call, %.1f TFLOP/s (10*B*S^2*256 algorithmic)" % (b, l, us, 10.0 * b * l * l * 256 / us / 1e6))
