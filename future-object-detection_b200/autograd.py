@@ -63,6 +63,49 @@ def _done(p):
         p._fod_reducer.mark_ready(p)
 
 
+class FusedParams:
+    """Several arena-backed parameters that optim.FlatTrainState laid out back to back (a module announces them through
+    `fused_param_groups()`), seen as ONE parameter with the rows concatenated: `data`, `grad` and the bf16 operand copy are
+    strided views over the arenas.  A fused projection (decoder q/k/v content halves, transformer.py:122-181) then
+    needs no torch.cat of weights / biases per step, and its dW GEMM and bias column sum accumulate straight into the
+    members' gradient slots instead of into a temporary that autograd splits and adds slice by slice."""
+    requires_grad = True
+
+    def __init__(self, members):
+        p0 = members[0]
+        shape = (sum(p.shape[0] for p in members),) + tuple(p0.shape[1:])
+        stride = torch.empty(shape, device="meta").stride()
+        self._fod_members = tuple(members)
+        self._fod_reducer = p0._fod_reducer
+        self._fod_uses = 0
+        self.shape = shape
+        self.data = torch.as_strided(p0.data, shape, stride)
+        self.grad = torch.as_strided(p0.grad, shape, stride)
+        self._fod_shadow = torch.as_strided(p0._fod_shadow, shape, stride)
+        self.key = FusedParams.key_of(members)
+        reg = getattr(self._fod_reducer, "fused", None)
+        if reg is not None:
+            reg[self.key] = self
+
+    @staticmethod
+    def key_of(members):
+        return tuple((p.data_ptr(), p.grad.data_ptr() if p.grad is not None else 0) for p in members)
+
+    @staticmethod
+    def build(members, cached=None):
+        """FusedParams over `members` if every one owns an arena slot, gradients are being recorded and the slots are
+        adjacent in this order; else None (the caller falls back to torch.cat + autograd routing)."""
+        if not torch.is_grad_enabled() or not all(_arena(p) and p.grad is not None for p in members):
+            return None
+        if cached is not None and cached.key == FusedParams.key_of(members):
+            return cached
+        for a, b in zip(members, members[1:]):
+            if (b.data_ptr() != a.data_ptr() + 4 * a.numel() or b.grad.data_ptr() != a.grad.data_ptr() + 4 * a.numel()
+                    or b._fod_shadow.data_ptr() != a._fod_shadow.data_ptr() + 2 * a.numel() or b.shape[1:] != a.shape[1:]):
+                return None
+        return FusedParams(members)
+
+
 class _OffCriticalPath:
     """Weight / bias gradients are leaves of the backward graph: nothing downstream of backward waits for them except
     the gradient all-reduce and the optimizer.  They are enqueued on the reducer's weight-gradient stream, forked from
@@ -118,7 +161,8 @@ class LinearFn(Function):
     def forward(ctx, x, w, b, wq, residual, res_row_mod, relu, out_f32, w_rows=None):
         """w_rows=(r0, r1): `wq` is rows [r0, r1) of the arena-backed parameter `w`; its gradient accumulates into the
         same rows of w.grad (direct mode only — otherwise pass the slice itself and let autograd route it)."""
-        y = ops.gemm(x, wq, bias=b, residual=residual, res_row_mod=res_row_mod, relu=relu, out_f32=out_f32)
+        y = ops.gemm(x, wq, bias=b.data if isinstance(b, FusedParams) else b, residual=residual, res_row_mod=res_row_mod,
+                     relu=relu, out_f32=out_f32)
         ctx.w_rows = w_rows
         ctx.save_for_backward(x, wq, y if relu else None)
         ctx.cfg = (res_row_mod, relu, b is not None, residual is not None)

@@ -64,6 +64,7 @@ class BucketedGradReducer:
         self.side = torch.cuda.Stream() if self.overlap else None
         self.enabled = True
         self._ready = set()
+        self.fused = {}  # autograd.FusedParams views over adjacent slots (their use counters are reset with the step)
         # second stream for gradient kernels that are off backward's critical path (autograd._OffCriticalPath); the
         # all-reduce of a bucket and the optimizer wait for it
         self.wgrad_stream = torch.cuda.Stream() if (self.cuda and wgrad_stream) else None
@@ -82,6 +83,8 @@ class BucketedGradReducer:
             self._launched[bi] = False
         self._ready.clear()
         self.keepalive.clear()
+        for f in self.fused.values():
+            f._fod_uses = 0
 
     def _reduce(self, bi):
         self._launched[bi] = True
@@ -123,8 +126,10 @@ class BucketedGradReducer:
 
     def mark_ready(self, p):
         """For gradients written into the arena by a kernel instead of autograd's AccumulateGrad (fused weight-gradient
-        accumulation): counts the parameter's bucket down exactly as the post-accumulate hook would."""
-        self._hook(p)
+        accumulation): counts the parameter's bucket down exactly as the post-accumulate hook would.  A fused view
+        (autograd.FusedParams) signals every member."""
+        for m in getattr(p, "_fod_members", (p,)):
+            self._hook(m)
 
     def finish(self):
         """Call after backward: reduces buckets whose countdown never reached zero (parameters that got no gradient

@@ -27,16 +27,27 @@ class SlotToSlotAttention(nn.Module):
         self.fun = _OutProjOnly(D)
         self.heads = Nhead
 
+    def fused_param_groups(self):
+        """Parameters read as one concatenated operand (optim.FlatTrainState gives them adjacent arena slots)."""
+        return ([self.query_content.weight, self.key_content.weight, self.value.weight],
+                [self.query_content.bias, self.key_content.bias, self.value.bias])
+
     def forward(self, c, qpos_bf, batch, m):
         d = c.shape[1]
         # batch-invariant positional halves (their biases ride along); content halves as ONE fused (3D x D) GEMM
         pq = _lin(qpos_bf, self.query_pos)
         pk = _lin(qpos_bf, self.key_pos)
         res = torch.cat((pq, pk, pq.new_zeros(m, d)), dim=1)
-        w = torch.cat((self.query_content.weight, self.key_content.weight, self.value.weight), dim=0)
-        b = torch.cat((self.query_content.bias, self.key_content.bias, self.value.bias), dim=0)
-        wq = torch.cat((_q(self.query_content.weight), _q(self.key_content.weight), _q(self.value.weight)), dim=0)
-        qkv = A.linear(c, w, b, wq, residual=res, res_row_mod=m)
+        gw, gb = self.fused_param_groups()
+        self._fw = fw = A.FusedParams.build(gw, getattr(self, "_fw", None))
+        self._fb = fb = A.FusedParams.build(gb, getattr(self, "_fb", None))
+        if fw is not None and fb is not None:  # adjacent arena slots: no per-step cat, gradients written in place
+            qkv = A.linear(c, fw, fb, fw._fod_shadow, residual=res, res_row_mod=m)
+        else:
+            w = torch.cat((self.query_content.weight, self.key_content.weight, self.value.weight), dim=0)
+            b = torch.cat((self.query_content.bias, self.key_content.bias, self.value.bias), dim=0)
+            wq = torch.cat((_q(self.query_content.weight), _q(self.key_content.weight), _q(self.value.weight)), dim=0)
+            qkv = A.linear(c, w, b, wq, residual=res, res_row_mod=m)
         a = A.self_attention(qkv.view(batch, m, 3 * d), self.heads, (d // self.heads) ** -0.5)
         return a.view(-1, d)
 
@@ -58,13 +69,22 @@ class SlotToImageAttention(nn.Module):
         self.store_attention = False
         self.stored_attention = None
 
+    def fused_param_groups(self):
+        return ([self.key_content.weight, self.value.weight], [self.key_content.bias, self.value.bias])
+
     def forward(self, c, qpos_bf, qsine, img, img_pos_bf, is_first, batch, m, s):
         """c (B*M, D); qsine (B*M, D) or batch-invariant (M, D); img (B*S, D) tokens; img_pos_bf (S, D)."""
         d = c.shape[1]
         kp = _lin(img_pos_bf, self.key_pos)  # (S, D) batch-invariant key positional part
-        wkv = torch.cat((self.key_content.weight, self.value.weight), dim=0)
-        bkv = torch.cat((self.key_content.bias, self.value.bias), dim=0)
-        wkvq = torch.cat((_q(self.key_content.weight), _q(self.value.weight)), dim=0)
+        gw, gb = self.fused_param_groups()
+        self._fw = fw = A.FusedParams.build(gw, getattr(self, "_fw", None))
+        self._fb = fb = A.FusedParams.build(gb, getattr(self, "_fb", None))
+        if fw is not None and fb is not None:
+            wkv, bkv, wkvq = fw, fb, fw._fod_shadow
+        else:
+            wkv = torch.cat((self.key_content.weight, self.value.weight), dim=0)
+            bkv = torch.cat((self.key_content.bias, self.value.bias), dim=0)
+            wkvq = torch.cat((_q(self.key_content.weight), _q(self.value.weight)), dim=0)
         if is_first:
             kv = A.linear(img, wkv, bkv, wkvq, residual=torch.cat((kp, kp.new_zeros(s, d)), dim=1), res_row_mod=s)
             qc = _lin(c, self.query_content, residual=_lin(qpos_bf, self.query_pos), res_row_mod=m)

@@ -31,6 +31,19 @@ class FlatTrainState:
         back = [p for n, p in named if "backbone" in n]
         # layout = the order in which backward produces gradients: heads/decoder, encoder, ..., backbone last
         order = list(reversed(rest)) + list(reversed(back))
+        # parameters a module reads as one concatenated operand (fused_param_groups()) get adjacent slots in that order
+        groups = [list(g) for m in model.modules() if hasattr(m, "fused_param_groups") for g in m.fused_param_groups()]
+        groups = [g for g in groups if all(p.requires_grad for p in g)]
+        member_of = {p: g for g in groups for p in g}
+        assert len(member_of) == sum(len(g) for g in groups), "a parameter may belong to one fused group only"
+        placed, new_order = set(), []
+        for p in order:
+            if p in placed:
+                continue
+            for q in member_of.get(p, (p,)):
+                new_order.append(q)
+                placed.add(q)
+        order = new_order
         self.reducer = BucketedGradReducer([p for _, p in named], bucket_mb=bucket_mb, group=group, overlap=overlap,
                                            order=order, wgrad_stream=wgrad_stream)
         r = self.reducer

@@ -130,3 +130,39 @@ def test_flat_train_state_layout_cpu():
     o = flat.reducer.offset[w]
     assert torch.equal(flat.grads[o:o + w.numel()].view_as(w), w.grad) and float(w.grad.abs().sum()) > 0
     assert torch.equal(flat.params[o:o + w.numel()].view_as(w), w.data)
+
+
+def test_fused_param_groups_get_adjacent_slots_cpu():
+    """Modules that read several parameters as one concatenated operand announce them through fused_param_groups():
+    FlatTrainState gives them adjacent arena slots in that order, autograd.FusedParams exposes data / grad / bf16 copy as
+    one strided view each, and the reducer's ready signal of the view counts every member's bucket down."""
+    from fod_b200 import autograd as A
+    from fod_b200.optim import FlatTrainState
+
+    class Proj(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a, self.other, self.b, self.c = (torch.nn.Linear(8, 8) for _ in range(4))
+
+        def fused_param_groups(self):
+            return [self.c.weight, self.a.weight, self.b.weight], [self.c.bias, self.a.bias, self.b.bias]
+
+    torch.manual_seed(0)
+    net = Proj()
+    ref = torch.cat([net.c.weight, net.a.weight, net.b.weight]).detach().clone()
+    flat = FlatTrainState(net, bucket_mb=1e-4)   # several buckets: the group straddles bucket boundaries
+    assert len(flat.reducer.buckets) > 1
+    gw, gb = net.fused_param_groups()
+    fw, fb = A.FusedParams.build(gw), A.FusedParams.build(gb)
+    assert fw is not None and fb is not None and fw.shape == (24, 8) and fb.shape == (24,)
+    assert torch.equal(fw.data, ref) and torch.equal(fw._fod_shadow.float(), flat.shadow[flat.reducer.offset[net.c.weight]:][:192].view(24, 8).float())
+    fw.grad.fill_(2.0)
+    assert all(float(p.grad.min()) == 2.0 for p in gw) and float(net.other.weight.grad.abs().sum()) == 0.0
+    assert A.FusedParams.build([net.a.weight, net.c.weight]) is None      # not adjacent in this order
+    assert A.FusedParams.build(gw, fw) is fw                              # cached view is reused
+    with torch.no_grad():
+        assert A.FusedParams.build(gw) is None                           # no gradient recording: caller falls back
+    flat.begin_step()
+    fw._fod_uses = 1
+    A._done(fw)
+    assert all(p in flat.reducer._ready for p in gw)
