@@ -107,12 +107,17 @@ class PositionalEncoder(nn.Module):
             self._cache[key] = enc.reshape(h * w, c).contiguous()
         return self._cache[key]
 
-    def temporal_channels(self, offsets, c):
-        """paper.py:66-73 — (B, L, c) sine code of the frame offsets, added to every token of the frame."""
-        idx = torch.arange(c, dtype=torch.float32, device=offsets.device)
+    def temporal_channels(self, offsets, b, t, c, device):
+        """paper.py:66-73 — (B, T, c) fp32 sine code of the frame offsets (None: the frame counter 1..T), normalised
+        by the LAST frame's value; it is constant over a frame's tokens, so it is kept as one vector per frame."""
+        if offsets is not None:
+            te = offsets.to(device=device, dtype=torch.float32) + self.extra_temporal_offset
+        else:
+            te = torch.arange(1, t + 1, dtype=torch.float32, device=device).expand(b, t)
+        te = te / (te[:, -1:] + 1e-6) * (2 * math.pi)
+        idx = torch.arange(c, dtype=torch.float32, device=device)
         dim_t = self.temperature ** (2 * torch.div(idx, 2, rounding_mode="floor") / c)
-        ang = (offsets[..., None].float() + self.extra_temporal_offset) * (2 * math.pi) / dim_t
-        return _sincos(ang)
+        return _sincos(te[..., None] / dim_t)
 
 
 def gen_sineembed_for_position(ref_xy, d=256):
@@ -385,6 +390,11 @@ class _InProjMHA(nn.Module):
         nn.init.zeros_(self.out_proj.bias)
 
 
+def _pos_mod(pos_bf, seq_len):
+    """Row modulus of a positional residual: seq_len rows are shared by all sequences, otherwise one row per token."""
+    return seq_len if pos_bf.shape[0] == seq_len else 0
+
+
 class EncoderAttention(nn.Module):
     """transformer.py:401-419: x1 = LN(x + MHA(q=k=x+pos, v=x)); x2 = LN(x1 + W2 relu(W1 x1))."""
 
@@ -397,7 +407,8 @@ class EncoderAttention(nn.Module):
         self.heads = Nhead
 
     def forward(self, x, pos_bf, n_seq, seq_len):
-        """x (n_seq*seq_len, D) bf16; pos_bf (seq_len, D) bf16, shared by every sequence."""
+        """x (n_seq*seq_len, D) bf16; pos_bf (seq_len, D) bf16 shared by every sequence, or (n_seq*seq_len, D) when the
+        encoding differs per sequence (temporal code in joint mode)."""
         w, b = self.attn.in_proj_weight, self.attn.in_proj_bias
         wq = _q(w)
         d = w.shape[1]
@@ -406,8 +417,8 @@ class EncoderAttention(nn.Module):
             pqk = A.linear(pos_bf, w, None, wq[:2 * d], w_rows=(0, 2 * d))
         else:
             pqk = A.linear(pos_bf, w[:2 * d], None, wq[:2 * d])
-        res = torch.cat((pqk, pqk.new_zeros(seq_len, d)), dim=1)
-        qkv = A.linear(x, w, b, wq, residual=res, res_row_mod=seq_len)
+        res = torch.cat((pqk, pqk.new_zeros(pqk.shape[0], d)), dim=1)
+        qkv = A.linear(x, w, b, wq, residual=res, res_row_mod=_pos_mod(pos_bf, seq_len))
         a = A.self_attention(qkv.view(n_seq, seq_len, 3 * d), self.heads, (d // self.heads) ** -0.5)
         op = self.attn.out_proj
         x = A.linear_ln(a.view(-1, d), x, op.weight, op.bias, _q(op.weight), self.norm1.weight, self.norm1.bias,
@@ -478,7 +489,7 @@ class EgodeepAttention(nn.Module):
         """x (n_seq*seq_len, D), ego (n_seq, K, D): attention of every token over K IMU keys (JointEncoder)."""
         d = x.shape[1]
         pq = _lin(pos_bf, self.query_pos)
-        q = _lin(x, self.query_content, residual=pq, res_row_mod=seq_len)
+        q = _lin(x, self.query_content, residual=pq, res_row_mod=_pos_mod(pos_bf, seq_len))
         k = _lin(_rows(ego), self.key).view(n_seq, -1, d)
         v = _lin(_rows(ego), self.value).view(n_seq, -1, d)
         qkv_free = A.PlainAttnFn.apply(q.view(n_seq, seq_len, d), k, v, self.heads, (d // self.heads) ** -0.5)

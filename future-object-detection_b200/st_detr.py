@@ -103,17 +103,24 @@ class FuturePredCore(nn.Module):
 
     def forward(self, images, imu=None, temporal_offsets=None):
         assert images.dim() == 5, "expected (B, L, 3, H, W)"  # paper.py:463
-        if not self.pos_encoder.no_temporal:
-            raise NotImplementedError("temporal encoding (PositionalEncoder(no_temporal=False)) is not wired into the "
-                                      "row-modular positional GEMMs yet; runs/_model.py builds no_temporal=True")
         images = images[:, :-1]  # the last ("future") frame is never seen by the model (paper.py:463-468)
         if imu is not None:
             imu = imu[:, :-1]
+        if temporal_offsets is not None:
+            temporal_offsets = temporal_offsets[:, :-1]
         b, t = images.shape[:2]
         x, pos_bf, ego, h, w = self.separate_encoder.forward_tokens(images, self.pos_encoder, imu)
         s, d = h * w, x.shape[1]
         if self.joint_encoder is not None:
-            x = self.joint_encoder(x, pos_bf, ego, b, t, s)
+            # Temporal code (paper.py:50-55,66-73; off in runs/_model.py:70-72).  It is one vector per (clip, frame),
+            # so it only matters where tokens of DIFFERENT frames share a softmax: the joint encoder.  In the decoder
+            # every cross-attention sees one frame's encoding (paper.py:381-382); there the code shifts all keys by
+            # the same vector and cancels exactly (tests/golden t1: reference ON == OFF), so it is not materialised.
+            tcode = pos_f32 = None
+            if not self.pos_encoder.no_temporal:
+                tcode = self.pos_encoder.temporal_channels(temporal_offsets, b, t, d, x.device)
+                pos_f32 = self.pos_encoder.spatial_tokens(h, w, d, x.device)
+            x = self.joint_encoder(x, pos_bf, ego, b, t, s, tcode, pos_f32)
         self.last_encoder_tokens = x.detach()  # detached: a live graph would pin last step's AccumulateGrad nodes
         # (b, t, s) rows -> one contiguous (B*S, D) token matrix per frame for the decoder's K/V GEMMs
         per_frame = x.view(b, t, s, d).transpose(0, 1).contiguous()
@@ -131,10 +138,15 @@ class JointEncoder(nn.Module):
         super().__init__()
         self.transformer = transformer
 
-    def forward(self, x, pos_bf, ego, b, t, s):
+    def forward(self, x, pos_bf, ego, b, t, s, tcode=None, pos_f32=None):
+        """tcode (B, T, D) fp32: optional temporal code, added to the spatial one (pos_f32, (S, D)) per (clip, frame)."""
         d = x.shape[1]
         xt = x.view(b, t, s, d).permute(0, 2, 1, 3).reshape(b * s * t, d)           # (b, hw, l) token order
-        pos_j = pos_bf.view(s, 1, d).expand(s, t, d).reshape(s * t, d).contiguous()  # spatial code repeated over l
+        if tcode is None:
+            pos_j = pos_bf.view(s, 1, d).expand(s, t, d).reshape(s * t, d).contiguous()  # spatial code repeated over l
+        else:  # one row per token: spatial[hw] + temporal[b, l], summed in fp32 as the reference does
+            sp = pos_f32 if pos_f32 is not None else pos_bf.float()
+            pos_j = (sp.view(1, s, 1, d) + tcode.view(b, 1, t, d)).to(BF16).reshape(b * s * t, d)
         ego_j = ego.view(b, t, d) if ego is not None else None
         y = self.transformer(xt, pos_j, ego_j, b, s * t)
         return y.view(b, s, t, d).permute(0, 2, 1, 3).reshape(b * t * s, d)

@@ -70,9 +70,20 @@ def image_pos_encoding(h, w, c=D_MODEL, temperature=10000.0):
     return torch.cat((ey, ex), dim=-1).permute(2, 0, 1).contiguous()
 
 
-def temporal_encoding(offsets, h, w, c=D_MODEL, temperature=10000.0, extra=0.0):
-    """paper.py:66-73 (only live when PositionalEncoder(no_temporal=False)); offsets (B, L) or None->cumsum."""
-    raise NotImplementedError("temporal encoding is disabled in runs/_model.py (no_temporal=True)")
+def temporal_encoding(offsets, b, t, h, w, c=D_MODEL, temperature=10000.0, extra=0.0):
+    """paper.py:66-73 (live only with PositionalEncoder(no_temporal=False); runs/_model.py:70-72 builds it off).
+
+    offsets (B, T) of the frames the model sees, or None -> frame counter 1..T.  The code is normalised by the LAST
+    frame's value (+1e-6), scaled to 2*pi, and sine-coded over all c channels.  Returns (B, T, c, h, w)."""
+    mask = torch.ones((b, t, h, w), dtype=torch.float32)
+    if offsets is not None:
+        te = mask * offsets.float()[..., None, None] + extra
+    else:
+        te = mask.cumsum(1, dtype=torch.float32)
+    te = te / (te[:, -1:, :, :] + 1e-6) * (2 * math.pi)
+    idx = torch.arange(c, dtype=torch.float32)
+    dim_t = temperature ** (2 * torch.div(idx, 2, rounding_mode="floor") / c)
+    return _sincos_interleave(te[..., None] / dim_t).permute(0, 1, 4, 2, 3).contiguous()
 
 
 def query_sine_embedding(ref_xy, d=D_MODEL):
@@ -269,8 +280,14 @@ def backbone_features(images, sd, pre):
     return F.conv2d(x, sd[pre + ".input_proj.weight"], sd[pre + ".input_proj.bias"])
 
 
-def core_forward(images, imu, sd, pre="_model", all_passes=False):
-    """paper.py:448-485 + :133-170 — images (B, L, 3, H, W), imu (B, L, 14) or None."""
+def core_forward(images, imu, sd, pre="_model", all_passes=False, temporal=None, joint=False):
+    """paper.py:448-485 + :133-170 — images (B, L, 3, H, W), imu (B, L, 14) or None.
+
+    temporal=None is PositionalEncoder(no_temporal=True) (what runs/_model.py builds); temporal={"offsets": (B, L)
+    tensor or None, "extra": float} adds the temporal sine code to the encoding handed to the joint encoder and the
+    decoder (paper.py:50-55,473-482).  In the per-frame configuration that code is constant over the keys of every
+    softmax it enters (each cross-attention sees ONE frame's encoding, paper.py:381-382), so it cancels; it is live
+    only with joint=True — the optional JointEncoder (paper.py:180-203) run with the per-frame encoder's layers."""
     images = images[:, :-1]
     b, t = images.shape[:2]
     feats = backbone_features(images.flatten(0, 1), sd, pre + ".separate_encoder.backbone")
@@ -287,6 +304,16 @@ def core_forward(images, imu, sd, pre="_model", all_passes=False):
     x = encoder(x, p, ego, sd, pre + ".separate_encoder.transformer")
     feats = x.permute(1, 2, 0).reshape(b, t, c, h, w)
     pos_bt = pos.view(1, 1, c, h, w).expand(b, t, -1, -1, -1)
+    if temporal is not None:
+        offs = temporal.get("offsets")
+        pos_bt = pos_bt + temporal_encoding(None if offs is None else offs[:, :-1], b, t, h, w, c,
+                                            extra=temporal.get("extra", 0.0))
+    if joint:
+        xj = feats.permute(3, 4, 1, 0, 2).reshape(h * w * t, b, c)          # "b l c h w -> (h w l) b c"
+        pj = pos_bt.permute(3, 4, 1, 0, 2).reshape(h * w * t, b, c)
+        ej = ego.view(b, t, c).permute(1, 0, 2) if ego is not None else None  # "b l c -> l b c": T keys per clip
+        xj = encoder(xj, pj, ej, sd, pre + ".separate_encoder.transformer")
+        feats = xj.view(h, w, t, b, c).permute(3, 2, 4, 0, 1)
     out = detector(feats, pos_bt, sd, pre + ".detector", all_passes=all_passes)
     out["encoder_features"] = feats
     return out
@@ -475,11 +502,11 @@ def post_process(pred_logits, pred_boxes, data):
 IMU_KEYS = ("translation", "acceleration", "rotation", "rotation_rate", "speed")
 
 
-def forward(data, sd, all_passes=False, with_od_map=True):
+def forward(data, sd, all_passes=False, with_od_map=True, temporal=None):
     """st_detr.py:98-167 — returns (outputs, None, loss, stats, od_map_stuffs) plus the raw core dict."""
     video = data["video"]
     imu = torch.cat([data[k] for k in IMU_KEYS], dim=2) if data.get("translation") is not None else None
-    core = core_forward(video, imu, sd, all_passes=all_passes)
+    core = core_forward(video, imu, sd, all_passes=all_passes, temporal=temporal)
     h, w = video.shape[-2:]
     targets = to_detr_targets(h, w, data["active"], data["boxes"], data["classes"])
     loss, stats, idx = criterion(core, targets)

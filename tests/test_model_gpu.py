@@ -195,3 +195,63 @@ def test_joint_encoder_matches_reference_golden(model):
     err = rel_l2(got, gold["out"])
     print("joint encoder rel L2", err)
     assert err < TOL
+
+
+def test_temporal_code_per_frame_mode_matches_reference_golden(model):
+    """PositionalEncoder(no_temporal=False) + per-sample temporal_offsets in the per-frame configuration (golden t1:
+    the unmodified reference with the switch flipped, tests/golden/make_golden_temporal.py).  The code cancels in
+    every softmax of this configuration, so the drop-in accepts the switch without materialising it."""
+    from fod_b200.synthetic import make_clip
+    gold = load_golden("t1_temporal_b2_l3_128x160")
+    b, l, h, w, seed = gold["case"]
+    data = make_clip(b, l, h, w, seed=seed)
+    data["temporal_offsets"] = gold["temporal_offsets"]
+    pe = model._model.pos_encoder
+    pe.no_temporal, model._encode_offset = False, True
+    try:
+        with torch.no_grad():
+            (_, _, loss, stats, _), core = _run(model, data)
+    finally:
+        pe.no_temporal, model._encode_offset = True, False
+    errs = {"hs": rel_l2(core["hs"][-1].float(), gold["hs_last"]),
+            "pred_logits": rel_l2(core["pred_logits"], gold["pred_logits"]),
+            "pred_boxes": rel_l2(core["pred_boxes"], gold["pred_boxes"]),
+            "loss": abs(float(loss) - float(gold["loss"])) / float(gold["loss"])}
+    print("temporal per-frame", errs)
+    assert max(errs.values()) < TOL, errs
+
+
+def test_temporal_code_joint_mode_matches_reference_golden(model):
+    """Frame-counter temporal code + JointEncoder over all T*h*w tokens (golden t2): the code differs between tokens
+    that share a softmax, so the positional operand of the encoder GEMMs has one row per token."""
+    from fod_b200.st_detr import JointEncoder
+    from fod_b200.synthetic import make_clip
+    gold = load_golden("t2_temporal_joint_b2_l4_96x128")
+    b, l, h, w, seed = gold["case"]
+    data = _to(make_clip(b, l, h, w, seed=seed), DEV)
+    imu = torch.cat([data[k] for k in O.IMU_KEYS], dim=2)
+    core_m = model._model
+    pe = core_m.pos_encoder
+    core_m.joint_encoder = JointEncoder(core_m.separate_encoder.transformer)
+    try:
+        with torch.no_grad():
+            off, _ = core_m(data["video"], imu=imu)
+            pe.no_temporal = False
+            on, _ = core_m(data["video"], imu=imu)
+        # gradients flow through the per-token positional operand (full-row residual of the fused in-projection)
+        model.zero_grad(set_to_none=True)
+        out, _ = core_m(data["video"], imu=imu)
+        (out["pred_logits"].float().square().mean() + out["pred_boxes"].float().square().mean()).backward()
+        g = core_m.separate_encoder.transformer.layers[0].self_attn.attn.in_proj_weight.grad
+        assert g is not None and bool(torch.isfinite(g).all()) and float(g.abs().max()) > 0
+    finally:
+        pe.no_temporal = True
+        core_m.joint_encoder = None
+        model.zero_grad(set_to_none=True)
+    errs = {"hs": rel_l2(on["hs"][-1].float(), gold["hs_last"]),
+            "pred_logits": rel_l2(on["pred_logits"], gold["pred_logits"]),
+            "pred_boxes": rel_l2(on["pred_boxes"], gold["pred_boxes"])}
+    live = rel_l2(off["pred_logits"], gold["pred_logits"])
+    print("temporal joint", errs, "without the code:", live)
+    assert max(errs.values()) < TOL, errs
+    assert live > 2 * errs["pred_logits"]
