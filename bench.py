@@ -92,14 +92,21 @@ def setup_optimizer(model, detr_args):
 
 
 # ---------------------------------------------------------------------------------------------- reference / CPU arm
-def cpu_reference_step_fn(batch):
+def cpu_reference_step_fn(batch, device="cpu", autocast=False):
     """The reference algorithm (oracle/fod_oracle.py, fp32, pinned to the reference's outputs) as a full training step
-    on the host cores: forward, loss, backward, clip 0.1, AdamW."""
+    on the host cores: forward, loss, backward, clip 0.1, AdamW.  device="cuda" (opt-in, `--ref-device cuda`) runs the
+    same eager torch program on the GPU — SURVEY §8d's "reference on the same B200" — with the assignment solved on
+    the host as upstream does (matcher.py:84-86)."""
     from fod_b200.synthetic import make_clip, synthetic_state_dict
     from oracle import fod_oracle as O
 
     torch.set_num_threads(os.cpu_count())
     sd = synthetic_state_dict(_template(), seed=0, residual_gain=0.5)
+    data = make_clip(batch, L_FRAMES, H, W, seed=0)
+    if device != "cpu":
+        torch.set_default_device(device)  # the oracle's factory calls carry no device
+        sd = {k: v.to(device) for k, v in sd.items()}
+        data = {k: (v.to(device) if torch.is_tensor(v) else v) for k, v in data.items()}
     frozen = ("backbone.body.conv1", "backbone.body.bn1", "backbone.body.layer1")
     for k, v in sd.items():
         if v.is_floating_point() and not any(f in k for f in frozen) and "running_" not in k and \
@@ -107,11 +114,11 @@ def cpu_reference_step_fn(batch):
             v.requires_grad_(True)
     leaves = [v for v in sd.values() if v.requires_grad]
     opt = torch.optim.AdamW(leaves, lr=1e-4, weight_decay=1e-4)
-    data = make_clip(batch, L_FRAMES, H, W, seed=0)
 
     def step():
         opt.zero_grad(set_to_none=True)
-        _, _, loss, _, _, _ = O.forward(data, sd, all_passes=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16, enabled=autocast and device != "cpu"):
+            _, _, loss, _, _, _ = O.forward(data, sd, all_passes=True)
         loss.backward()
         torch.nn.utils.clip_grad_norm_(leaves, 0.1)
         opt.step()
@@ -124,6 +131,8 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
+    if args.ref_device != "cpu":
+        return run_reference_on_gpu(args)
     sample_b = 1
     step = cpu_reference_step_fn(sample_b)
     for _ in range(min(args.warmup, 1)):
@@ -141,6 +150,26 @@ def run_reference(args):
                              "sample": "%d steps x 1 clip, fwd+bwd+clip+AdamW, fp32, all %d host threads" % (args.steps, os.cpu_count())},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
+
+
+def run_reference_on_gpu(args):
+    """Opt-in side measurement (never the driver's reference arm): the eager torch restatement of the reference on the
+    same B200, whole 8-clip batch, fp32 or autocast(bf16).  Wall clock around synchronised steps."""
+    step = cpu_reference_step_fn(BATCH, device="cuda:0", autocast=bool(args.ref_autocast))
+    for _ in range(max(args.warmup, 2)):
+        step()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    v = BATCH * args.steps / dt
+    emit({"impl": "reference", "device": "cuda:0 (eager torch, oracle port; dead decoder passes replayed as upstream)",
+          "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 2),
+          "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+          "dtype": "bf16-autocast" if args.ref_autocast else "f32", "data": "synthetic",
+          "config": {"workload": WORKLOAD, "global_batch": BATCH}})
 
 
 # ---------------------------------------------------------------------------------------------- CUDA arm
@@ -351,6 +380,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="fod", choices=["fod", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--ref-device", default="cpu", choices=["cpu", "cuda"],
+                    help="with --impl reference: cuda = opt-in side measurement of the eager torch port on the GPU")
+    ap.add_argument("--ref-autocast", type=int, default=0, help="with --ref-device cuda: run under autocast(bf16)")
     ap.add_argument("--graphs", type=int, default=1, help="1: replay the whole step as one CUDA graph (single GPU)")
     ap.add_argument("--kernel-events", type=int, default=1, help="1: bracket each of our kernel launches with CUDA events")
     ap.add_argument("--flat", type=int, default=1, help="1: flat parameter/gradient arenas with the fused clip+AdamW kernel")
@@ -360,7 +392,8 @@ def main():
     ap.add_argument("--profiler-range", type=int, default=0, help="1: cudaProfilerStart/Stop around the timed steps (for ncu)")
     args = ap.parse_args()
     if args.impl == "reference":
-        args.steps = min(args.steps, 8)
+        if args.ref_device == "cpu":
+            args.steps = min(args.steps, 8)
         return run_reference(args)
     if args.warmup < 3:
         args.warmup = 3

@@ -363,7 +363,7 @@ def hungarian_match(logits, boxes, targets):
             out.append((torch.zeros(0, dtype=torch.int64), torch.zeros(0, dtype=torch.int64)))
             continue
         cost = matcher_cost(logits[b].float(), boxes[b].float(), t["labels"], t["boxes"])
-        r, c = _lsap.linear_sum_assignment(cost.double().numpy())
+        r, c = _lsap.linear_sum_assignment(cost.double().cpu().numpy())  # matcher.py:84: C.cpu()
         out.append((torch.as_tensor(r, dtype=torch.int64), torch.as_tensor(c, dtype=torch.int64)))
     return out
 
