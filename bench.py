@@ -380,6 +380,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="fod", choices=["fod", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--batch", type=int, default=BATCH,
+                    help="clips per GPU; anything but the default 8 is a side measurement (strong-scaling points of "
+                         "configs[3]: global 32 = 32/16/8/4 per GPU at 1/2/4/8 GPUs) and is labelled as such")
     ap.add_argument("--ref-device", default="cpu", choices=["cpu", "cuda"],
                     help="with --impl reference: cuda = opt-in side measurement of the eager torch port on the GPU")
     ap.add_argument("--ref-autocast", type=int, default=0, help="with --ref-device cuda: run under autocast(bf16)")
@@ -391,6 +394,10 @@ def main():
     ap.add_argument("--bucket-mb", type=float, default=32.0)
     ap.add_argument("--profiler-range", type=int, default=0, help="1: cudaProfilerStart/Stop around the timed steps (for ncu)")
     args = ap.parse_args()
+    if args.batch != BATCH:
+        global WORKLOAD
+        WORKLOAD = WORKLOAD.replace("batch 8/GPU", "batch %d/GPU (side measurement, not the headline config)" % args.batch)
+        globals()["BATCH"] = args.batch
     if args.impl == "reference":
         if args.ref_device == "cpu":
             args.steps = min(args.steps, 8)
