@@ -8,7 +8,8 @@ cpu_baseline / `--impl reference` legs may import it; the product package never 
 
 Parity pin: the reference has no tests or golden vectors of its own, so this oracle is
 pinned against outputs of the unmodified reference run in the build container
-(`tests/golden/make_golden.py` -> `tests/golden/*.pt`; `tests/test_oracle_vs_golden.py`).
+(`tests/golden/make_golden.py` -> `tests/golden/g*.pt`, `make_golden_temporal.py` -> `t*.pt` for the temporal code and
+the joint-encoder mode; `tests/test_oracle_vs_golden.py`).
 
 Every function cites the reference lines (relative to /root/reference) it restates.
 Layouts follow the reference: sequences are (tokens, batch, channels).
