@@ -372,6 +372,13 @@ def emit(line):
         os.write(_REAL_STDOUT, data)
 
 
+def _set_batch(b):
+    """Side measurements at another per-GPU batch relabel the workload so the line cannot pass for the headline."""
+    global BATCH, WORKLOAD
+    WORKLOAD = WORKLOAD.replace("batch %d/GPU" % BATCH, "batch %d/GPU (side measurement, not the headline config)" % b)
+    BATCH = b
+
+
 def main():
     _claim_stdout()
     ap = argparse.ArgumentParser()
@@ -395,9 +402,7 @@ def main():
     ap.add_argument("--profiler-range", type=int, default=0, help="1: cudaProfilerStart/Stop around the timed steps (for ncu)")
     args = ap.parse_args()
     if args.batch != BATCH:
-        global WORKLOAD
-        WORKLOAD = WORKLOAD.replace("batch 8/GPU", "batch %d/GPU (side measurement, not the headline config)" % args.batch)
-        globals()["BATCH"] = args.batch
+        _set_batch(args.batch)
     if args.impl == "reference":
         if args.ref_device == "cpu":
             args.steps = min(args.steps, 8)

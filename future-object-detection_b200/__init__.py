@@ -12,4 +12,7 @@ def __getattr__(name):  # lazy: `import fod_b200` stays cheap and CPU-safe
                 "FuturePredCore", "SeparateEncoder", "JointEncoder"):
         from . import st_detr
         return getattr(st_detr, name)
+    if name in ("ApAccumulator", "aggregate_mean_average_precision"):  # future_od/utils/od_map.py, trainer.py:205-236
+        from . import od_map
+        return getattr(od_map, name)
     raise AttributeError(name)

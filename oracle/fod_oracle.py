@@ -489,6 +489,36 @@ def od_map_stuffs(pred_boxes, scores, anno_boxes, anno_classes, anno_active, ims
     return confs, is_pos, size_cat, num_annos
 
 
+def average_precision(confs, is_positive, size_categories, num_annos):
+    """od_map.py:288-312 (_get_ap) for one IoU threshold — confs, is_positive (C, N); size_categories (C, S, N) bool;
+    num_annos (C, S, iterations).  AP = sum over positives of precision-at-rank / number of annotations; 0/0 -> NaN and
+    x/0 -> inf are kept (the caller nan-means over them)."""
+    c, s, n = size_categories.shape
+    order = confs.argsort(dim=1, descending=True).view(c, 1, n).expand(-1, s, -1)
+    pos = (is_positive.view(c, 1, n) * size_categories).gather(2, order)
+    cat = size_categories.gather(2, order)
+    precision = pos.cumsum(dim=2) / (cat.cumsum(dim=2) + 1e-5)
+    return (precision * pos).sum(dim=2) / num_annos.sum(dim=2)
+
+
+def aggregate_ap(confs, is_positive, size_categories, num_annos):
+    """od_map.py:315-364 — confs, is_positive (T, C, N) stacked over iterations; returns the reference's dict
+    (generic class last; nan-means over classes / thresholds) as tensors."""
+    import numpy as np
+    with torch.no_grad():
+        ap = torch.stack([average_precision(confs[t], is_positive[t], size_categories, num_annos)
+                          for t in range(confs.shape[0])])
+    a = ap.numpy()
+    with np.errstate(all="ignore"):
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore", RuntimeWarning)
+            out = {"all": a[:, :-1], "classavg": np.nanmean(a[:, :-1], axis=1), "threshavg": np.nanmean(a[:, :-1], axis=0),
+                   "classavg threshavg": np.nanmean(a[:, :-1], axis=(0, 1)), "generic": a[:, -1],
+                   "generic threshavg": np.nanmean(a[:, -1], axis=0)}
+    return {k: torch.as_tensor(np.ascontiguousarray(v)) for k, v in out.items()}
+
+
 def post_process(pred_logits, pred_boxes, data):
     """st_detr.py:190-234 for the single-output case (pred_* already (B, M, .))."""
     h, w = data["video"].shape[-2:]
