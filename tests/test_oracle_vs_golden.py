@@ -136,3 +136,40 @@ def test_temporal_code_frame_counter_and_normalisation():
     e2 = O.temporal_encoding(offs, 2, 2, 1, 1)
     ang = torch.tensor(-0.8 / (-0.2 + 1e-6) * 2 * math.pi, dtype=torch.float32) / dim_t
     assert torch.allclose(e2[1, 0, :, 0, 0], torch.where(idx.long() % 2 == 0, ang.sin(), ang.cos()), atol=1e-5)
+
+
+@pytest.mark.parametrize("name", ["f1_b1_l4_448x800", "f2_b2_l3_448x800"])
+def test_full_size_forward_matches_reference(name):
+    """BASELINE.json configs[0] (1 clip x 4 frames, 448x800, CPU forward) and the configs[1] shape, at full size, with
+    the weights bench.py trains (residual_gain=0.5).  Golden: tests/golden/make_golden_fullsize.py."""
+    import json
+    import os
+
+    from conftest import GOLDEN
+    from fod_b200.synthetic import synthetic_state_dict
+    gold = load_golden(name)
+    b, l, h, w, seed = gold["case"]
+    with open(os.path.join(GOLDEN, "state_dict_template.json")) as f:
+        sd = synthetic_state_dict(json.load(f), seed=0, residual_gain=gold["residual_gain"])
+    data = make_clip(b, l, h, w, seed=seed)
+    torch.set_num_threads(8)
+    with torch.no_grad():
+        outputs, _, loss, stats, stuffs, core = O.forward(data, sd)
+    assert rel_err(core["hs"][-1], gold["hs_last"]) < TOL
+    assert rel_err(core["pred_logits"], gold["pred_logits"]) < TOL
+    assert rel_err(core["pred_boxes"], gold["pred_boxes"]) < TOL
+    aux_l = torch.stack([a["pred_logits"] for a in core["aux_outputs"]])
+    aux_b = torch.stack([a["pred_boxes"] for a in core["aux_outputs"]])
+    assert rel_err(aux_l, gold["aux_logits"]) < TOL and rel_err(aux_b, gold["aux_boxes"]) < TOL
+    assert rel_err(loss, gold["loss"]) < TOL
+    for k, v in gold["stats"].items():
+        assert rel_err(stats[k], v) < TOL, k
+    for lv_o, lv_g in zip(core["indices"], gold["indices"]):
+        for (i, j), (gi, gj) in zip(lv_o, lv_g):
+            assert torch.equal(i, gi) and torch.equal(j, gj)
+    assert rel_err(outputs["class_scores"], gold["class_scores"]) < TOL
+    assert rel_err(outputs["boxes"], gold["boxes"]) < TOL
+    confs, is_pos, size_cat, num_annos = stuffs
+    g_confs, g_pos, g_size, g_num = gold["od_map"]
+    assert rel_err(confs, g_confs) < TOL and torch.equal(is_pos, g_pos)
+    assert torch.equal(size_cat.bool(), g_size.bool()) and torch.equal(num_annos, g_num)
