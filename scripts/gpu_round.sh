@@ -14,3 +14,7 @@ timeout 600 python scripts/profile_step.py > gpurun_out/profile_step.log 2>&1; e
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none --profile-from-start off --csv --log-file gpurun_out/launches.csv \
   python bench.py --steps 1 --warmup 3 --graphs 0 --kernel-events 0 --no-cpu-baseline --profiler-range 1 > gpurun_out/ncu_bench.log 2>&1; echo "ncu exit $?"
 wc -l gpurun_out/launches.csv
+# stock comparator for the encoder attention and the eager torch port on the same GPU
+timeout 300 python scripts/sdpa_compare.py > gpurun_out/sdpa_compare.jsonl 2> gpurun_out/sdpa_compare.err; echo "sdpa exit $?"
+cat gpurun_out/sdpa_compare.jsonl
+timeout 200 python bench.py --impl reference --ref-device cuda --steps 10 --warmup 3 > gpurun_out/ref_gpu_f32.json 2> gpurun_out/ref_gpu_f32.err; echo "ref-gpu exit $?"
