@@ -106,3 +106,35 @@ def test_frozen_bn_fold_cache_refreshes_in_place():
     assert torch.allclose(s1, scale) and torch.allclose(t1, sd["bias"] - sd["running_mean"] * scale)
     x = torch.randn(2, 6, 3, 3)
     assert torch.allclose(bn(x), x * s1.view(1, -1, 1, 1) + t1.view(1, -1, 1, 1), atol=1e-6)
+
+
+def test_hot_kernels_are_tcgen05_tma_code():
+    """Static guard on the built library: the GEMM, attention and stem kernels must contain tensor-core (`UTC*MMA` =
+    tcgen05.mma), TMEM (`LDTM` = tcgen05.ld) and — where operands come by TMA — `UTMALDG` instructions in their SASS
+    (mnemonics: /opt/skills/guides/B200_PROFILING.md).  A rebuild that silently lost them would still pass parity."""
+    import re
+    import shutil
+    import subprocess
+    exe = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(exe):
+        pytest.skip("cuobjdump not available")
+    from fod_b200 import lib
+    sass = subprocess.run([exe, "-sass", lib.LIB_PATH], capture_output=True, text=True, timeout=300).stdout
+    counts, fn = {}, None
+    for line in sass.splitlines():
+        m = re.search(r"Function : (\S+)", line)
+        if m:
+            fn = m.group(1)
+            counts[fn] = {"mma": 0, "ldtm": 0, "tma": 0}
+        elif fn:
+            counts[fn]["mma"] += bool(re.search(r"UTC[A-Z]*MMA", line))
+            counts[fn]["ldtm"] += "LDTM" in line
+            counts[fn]["tma"] += "UTMALDG" in line
+    families = {"gemm_bf16_kernel": True, "attn_fwd_kernel": True, "attn_bwd_dq_kernel": True,
+                "attn_bwd_dkdv_kernel": True, "stem_conv7x7s2_kernel": False}  # value: operands arrive by TMA
+    for fam, wants_tma in families.items():
+        kernels = {k: v for k, v in counts.items() if fam in k}
+        assert kernels, fam
+        for k, v in kernels.items():
+            assert v["mma"] > 0 and v["ldtm"] > 0, (k, v)
+            assert v["tma"] > 0 or not wants_tma, (k, v)
