@@ -69,6 +69,7 @@ class FlatTrainState:
             p._fod_uses = 0
         self._args = None
         self._partial = None
+        self.lr_version = 0  # bumped by set_lr(): learning rates are kernel ARGUMENTS, so a captured graph must follow
         if dev.type == "cuda":
             self._partial = torch.empty(lib.load().fod_optim_workspace_floats(), dtype=torch.float32, device=dev)
             self.refresh_shadow()
@@ -125,7 +126,10 @@ class FlatTrainState:
         ops.LAUNCH_COUNTS["adamw_flat_kernel"] += 1
 
     def set_lr(self, lr=None, lr_backbone=None):
-        """Learning-rate schedule hook (runs/_helper.py builds a StepLR over both groups)."""
+        """Learning-rate schedule hook (runs/_helper.py builds a StepLR over both groups).  The rates are by-value
+        arguments of the update kernel, i.e. baked into a captured CUDA graph: `lr_version` tells
+        train.GraphedTrainStep to re-capture before its next replay."""
+        before = list(self.group_lr)
         if lr is not None:
             self.group_lr[0] = lr
         if lr_backbone is not None and len(self.group_lr) > 1:
@@ -133,6 +137,8 @@ class FlatTrainState:
         if self._args is not None:
             for i, v in enumerate(self.group_lr):
                 self._args.group_lr[i] = v
+        if self.group_lr != before:
+            self.lr_version += 1
 
     @property
     def grad_norm(self):

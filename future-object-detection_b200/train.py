@@ -80,6 +80,7 @@ class GraphedTrainStep:
         with torch.cuda.graph(self.graph, capture_error_mode="thread_local" if distributed else "global"):
             self.loss = self.eager(self.static)
         torch.cuda.synchronize()
+        self._lr_version = getattr(self.eager.flat, "lr_version", 0)
 
     def __call__(self, data=None):
         """data: a batch (host or device tensors) copied into the static inputs now, or None to consume the oldest
@@ -96,8 +97,26 @@ class GraphedTrainStep:
             for k, v in data.items():
                 if torch.is_tensor(v):
                     self.static[k].copy_(v, non_blocking=True)
+        flat = self.eager.flat
+        if flat is not None and getattr(flat, "lr_version", 0) != getattr(self, "_lr_version", 0):
+            self.recapture()  # FlatTrainState.set_lr() was called: the rates are kernel arguments inside the graph
         self.graph.replay()
         return self.loss
+
+    def recapture(self):
+        """Capture the step again (same static buffers, warm allocator): needed after anything that changes kernel
+        ARGUMENTS baked into the graph — the learning rates of the fused AdamW kernel (FlatTrainState.set_lr, the
+        reference's StepLR, runs/_helper.py:104-106), `max_norm`.  Called automatically for learning-rate changes."""
+        torch.cuda.synchronize()
+        eager = self.eager
+        graph = torch.cuda.CUDAGraph()
+        if eager.reducer is None and hasattr(eager.opt, "zero_grad"):
+            eager.opt.zero_grad(set_to_none=True)
+        with torch.cuda.graph(graph, capture_error_mode="thread_local" if eager.distributed else "global"):
+            loss = eager(self.static)
+        torch.cuda.synchronize()
+        self.graph, self.loss = graph, loss
+        self._lr_version = getattr(eager.flat, "lr_version", 0)
 
     def prefetch(self, host_data):
         """Queue the NEXT batch: pinned host -> device staging buffer on a copy stream, overlapping the step that is
