@@ -1,9 +1,11 @@
 #!/usr/bin/env python
-"""Benchmark of the fod_b200 hot path: training clips/s of the drop-in SpatioTemporalDETR (BASELINE.json configs[1]:
-nusc_spatiotemporal_imu_prevframe, 2 past frames, 448x800, batch 8 per GPU, bf16 kernels) — forward, backward,
-gradient clipping (0.1) and AdamW, exactly the reference's Trainer step (future_od/trainer.py:171-189).
+"""Benchmark of the fod_b200 hot path: training clips/s of the drop-in SpatioTemporalDETR on the largest single-GPU
+configuration of BASELINE.json — configs[2] nusc_spatiotemporal_imu_250ms, stage 1 of its recipe: 2 past frames,
+448x800, batch 32 per GPU (/root/reference/runs/nusc_spatiotemporal_imu_250ms.py:19-25), bf16 kernels — forward,
+backward, gradient clipping (0.1) and AdamW, exactly the reference's Trainer step (future_od/trainer.py:171-189).
 
   python bench.py [--gpus N --steps K --warmup W]            this repo's CUDA path (one rank per GPU under torchrun)
+  python bench.py --stage2                                   stage 2 of the same recipe: 896x1600, batch 16 (:33-39)
   python bench.py --impl reference [...]                     the reference algorithm (CPU oracle port) on host cores
 
 Prints ONE JSON line (rank 0).  See DESIGN.md §Measurement for the definition of every field.
@@ -21,8 +23,9 @@ if ROOT not in sys.path:
 
 import torch  # noqa: E402
 
-WORKLOAD = "nusc_spatiotemporal_imu_prevframe train step (fwd+bwd+clip+AdamW), L=3 (T=2 past frames), 448x800, batch 8/GPU"
-H, W, L_FRAMES, BATCH = 448, 800, 3, 8
+WORKLOAD = "nusc_spatiotemporal_imu_250ms stage 1 train step (fwd+bwd+clip+AdamW), L=3 (T=2 past frames), 448x800, batch 32/GPU"
+H, W, L_FRAMES, BATCH = 448, 800, 3, 32
+DEFAULT_BATCH = BATCH
 METRIC, UNIT = "train clips/s", "clips/s"
 
 
@@ -145,7 +148,7 @@ def run_reference(args):
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": "1 clip per step (bounded sample of the 8-clip batch)"},
+            "config": {"workload": WORKLOAD, "sample": "1 clip per step (bounded sample of the %d-clip batch)" % BATCH},
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
                              "sample": "%d steps x 1 clip, fwd+bwd+clip+AdamW, fp32, all %d host threads" % (args.steps, os.cpu_count())},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -159,16 +162,20 @@ def run_reference_on_gpu(args):
     for _ in range(max(args.warmup, 2)):
         step()
     torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step()
     torch.cuda.synchronize()
     dt = time.perf_counter() - t0
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
     v = BATCH * args.steps / dt
     emit({"impl": "reference", "device": "cuda:0 (eager torch, oracle port; dead decoder passes replayed as upstream)",
           "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": max(args.warmup, 2),
           "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-          "dtype": "bf16-autocast" if args.ref_autocast else "f32", "data": "synthetic",
+          "dtype": "bf16-autocast" if args.ref_autocast else "f32", "data": "synthetic", "clocks": sampler.summary(),
           "config": {"workload": WORKLOAD, "global_batch": BATCH}})
 
 
@@ -189,6 +196,8 @@ def run_cuda(args):
         region[0] += 1
         status_log["region%d" % region[0]] = int(status.item())
 
+    from fod_b200.dist import max_over_ranks, shard_seed
+    from fod_b200.od_map import ApAccumulator
     from fod_b200.synthetic import make_clip, synthetic_state_dict
 
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -223,7 +232,7 @@ def run_cuda(args):
 
     n_pool = 3
     host_pool = [{k: (v.pin_memory() if torch.is_tensor(v) else v)
-                  for k, v in make_clip(BATCH, L_FRAMES, H, W, seed=1000 * rank + i).items()} for i in range(n_pool)]
+                  for k, v in make_clip(BATCH, L_FRAMES, H, W, seed=shard_seed(rank, i)).items()} for i in range(n_pool)]
     dev_pool = [{k: v.to(dev) for k, v in d.items()} for d in host_pool]
     h2d_bytes = sum(v.numel() * v.element_size() for v in host_pool[0].values())
 
@@ -240,10 +249,7 @@ def run_cuda(args):
             fn(i)
         e1.record()
         barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms)
+        return max_over_ranks(e0.elapsed_time(e1), device=dev)  # device-side time, max over ranks
 
     for i in range(args.warmup):
         train_step(dev_pool[i % n_pool])
@@ -285,18 +291,26 @@ def run_cuda(args):
     # end to end through the public API: pinned host batch -> device, step, loss back to the host
     # With the graph, the next batch's H2D copy is queued on a copy stream while the current step runs
     # (GraphedTrainStep.prefetch); every step still moves its own 103 MB inside the timed region.
+    # The step's logging exchange rides along as in trainer.py:191-211: the 5 stat scalars and the AP bookkeeping go
+    # through ONE packed all-gather (N > 1) and an asynchronous copy into pinned host memory (ApAccumulator.add); the
+    # loss is read back synchronously (trainer.py:191 compares it on the host every step).
     if use_graph:
         step.prefetch(host_pool[0])
+    acc = ApAccumulator(distributed=world > 1)
+    eager = step.eager if use_graph else step
 
     def e2e_step(i):
         if use_graph:
             loss = step()                               # consumes the batch queued one step earlier
             step.prefetch(host_pool[(i + 1) % n_pool])  # overlaps the step just launched
-            return float(loss.detach())
-        data = {k: v.to(dev, non_blocking=True) for k, v in host_pool[i % n_pool].items()}
-        return float(step(data))
+        else:
+            loss = step({k: v.to(dev, non_blocking=True) for k, v in host_pool[i % n_pool].items()})
+        acc.add(eager.od_map_stuffs, eager.stats)
+        return float(loss.detach())
 
     ms_e2e = timed(e2e_step, args.steps)
+    d2h_bytes = 4 + acc.d2h_bytes_last
+    acc.stats_history()  # the copies have landed (checked outside the timed region)
     sampler.stop_flag = True
     sampler.join(timeout=2)
     check_match_status(core._criterion.last_status)
@@ -330,12 +344,14 @@ def run_cuda(args):
                        "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": 0.0, "cuda_graph": use_graph,
                        "optimizer": "fused flat clip+AdamW (fod_flat_adamw_step)" if flat is not None else "torch fused AdamW",
                        "grad_allreduce": ("bucketed NCCL AVG, %g MB fp32 buckets, side stream inside the graph" % args.bucket_mb) if world > 1 else None},
-            "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": 4},
+            "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                    "d2h": "loss (4 B, synchronous) + packed stats/AP bookkeeping (async, pinned slab)"},
             "loss_first_last_timed_step": loss_vals, "matcher_status_by_region": status_log, "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
-    # warm, GPU-bound per-launch times of the heaviest (kernel, shape) pairs: each re-issued back to back in a small graph
-    cand = sorted((k for k in kern if k.startswith(("gemm", "attn"))), key=lambda k: -kern[k]["flops"] - 1e3 * kern[k]["bytes"])[:14]
-    isolated = prof.isolated_us(cand) if args.kernel_events else {}
-    line.update(prof.roofline_report(kern, peaks, ms_inst, _traffic(), isolated, n_inst))
+    # warm, GPU-bound per-launch times of EVERY instrumented (kernel, shape) pair: each re-issued back to back in a
+    # small graph; the roofline is then ranked by time per step (launches x isolated time)
+    isolated = prof.isolated_us(list(kern)) if args.kernel_events else {}
+    line.update(prof.roofline_report(kern, peaks, ms_inst, _traffic(), isolated, n_inst,
+                                     attention_s=(H // 32) * (W // 32)))
     line["instrumented_region"] = {"steps": n_inst, "ms_per_step": ms_inst / n_inst if n_inst else None}
     if not args.no_cpu_baseline and world == 1:
         step = cpu_reference_step_fn(1)
@@ -372,6 +388,15 @@ def emit(line):
         os.write(_REAL_STDOUT, data)
 
 
+def _set_stage2():
+    """Stage 2 of the same recipe (runs/nusc_spatiotemporal_imu_250ms.py:33-39): 896x1600, batch 16 — the resolution
+    at which the space-time attention (S = 1400) is tensor-bound."""
+    global H, W, BATCH, DEFAULT_BATCH, WORKLOAD
+    H, W, BATCH = 896, 1600, 16
+    DEFAULT_BATCH = BATCH
+    WORKLOAD = "nusc_spatiotemporal_imu_250ms stage 2 train step (fwd+bwd+clip+AdamW), L=3 (T=2 past frames), 896x1600, batch 16/GPU"
+
+
 def _set_batch(b):
     """Side measurements at another per-GPU batch relabel the workload so the line cannot pass for the headline."""
     global BATCH, WORKLOAD
@@ -387,9 +412,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="fod", choices=["fod", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--batch", type=int, default=BATCH,
-                    help="clips per GPU; anything but the default 8 is a side measurement (strong-scaling points of "
-                         "configs[3]: global 32 = 32/16/8/4 per GPU at 1/2/4/8 GPUs) and is labelled as such")
+    ap.add_argument("--stage2", action="store_true", help="stage 2 of the recipe: 896x1600, batch 16 per GPU")
+    ap.add_argument("--batch", type=int, default=0,
+                    help="clips per GPU; anything but the configuration's own (32, stage 2: 16) is a side measurement "
+                         "(configs[1]: 8; strong-scaling points of configs[3]: global 32 = 32/16/8/4 per GPU at "
+                         "1/2/4/8 GPUs) and is labelled as such")
     ap.add_argument("--ref-device", default="cpu", choices=["cpu", "cuda"],
                     help="with --impl reference: cuda = opt-in side measurement of the eager torch port on the GPU")
     ap.add_argument("--ref-autocast", type=int, default=0, help="with --ref-device cuda: run under autocast(bf16)")
@@ -401,7 +428,9 @@ def main():
     ap.add_argument("--bucket-mb", type=float, default=32.0)
     ap.add_argument("--profiler-range", type=int, default=0, help="1: cudaProfilerStart/Stop around the timed steps (for ncu)")
     args = ap.parse_args()
-    if args.batch != BATCH:
+    if args.stage2:
+        _set_stage2()
+    if args.batch and args.batch != BATCH:
         _set_batch(args.batch)
     if args.impl == "reference":
         if args.ref_device == "cpu":

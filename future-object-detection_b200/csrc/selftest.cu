@@ -111,7 +111,7 @@ static void report(const char* name, double err, double tol, float ms, double fl
     if (!(err <= tol)) g_fail = 1;
 }
 
-static void test_linear(int M, int N, int K, int bias, int res, int res_mod, int relu, int ln, int f32out) {
+static void test_linear(int M, int N, int K, int bias, int res, int res_mod, int relu, int ln, int f32out, int save_pre = 0) {
     __nv_bfloat16* x = dev_bf16((size_t)M * K, 1.f);
     __nv_bfloat16* w = dev_bf16((size_t)N * K, 0.08f);
     float* b = bias ? dev_f32(N, 0.5f) : nullptr;
@@ -125,9 +125,11 @@ static void test_linear(int M, int N, int K, int bias, int res, int res_mod, int
     CK(cudaMalloc(&y, (size_t)M * N * 2));
     CK(cudaMemset(y, 0xff, (size_t)M * N * 2));
     if (f32out) CK(cudaMalloc(&yf32, (size_t)M * N * 4));
+    __nv_bfloat16* pre = nullptr;
     if (ln) {
         CK(cudaMalloc(&mean, M * 4));
         CK(cudaMalloc(&rstd, M * 4));
+        if (save_pre) CK(cudaMalloc(&pre, (size_t)M * N * 2));
     }
     ref_linear<<<dim3((N + 127) / 128, M), 128>>>(x, w, b, r, res_mod, relu, yref, M, N, K);
     if (ln) ref_ln<<<M, 32>>>(yref, g, be, M, N, 1e-5f);
@@ -137,6 +139,7 @@ static void test_linear(int M, int N, int K, int bias, int res, int res_mod, int
     a.out_bf16 = f32out ? nullptr : y; a.out_f32 = yf32; a.ln_mean = mean; a.ln_rstd = rstd;
     a.ldx = K; a.ld_res = N; a.ld_out = N; a.M = M; a.N = N; a.K = K; a.res_row_mod = res_mod; a.relu = relu;
     a.ln_eps = 1e-5f;
+    a.pre_ln_bf16 = pre;
     int rc = fod_linear_fwd(&a, nullptr);
     if (rc) { printf("fod_linear_fwd rc=%d (%s)\n", rc, fod_last_error()); g_fail = 1; return; }
     CK(cudaDeviceSynchronize());
@@ -164,10 +167,10 @@ static void test_linear(int M, int N, int K, int bias, int res, int res_mod, int
         }
     }
     char name[128];
-    snprintf(name, sizeof name, "linear M%d N%d K%d b%d r%d/%d relu%d ln%d f32%d", M, N, K, bias, res, res_mod, relu, ln, f32out);
+    snprintf(name, sizeof name, "linear M%d N%d K%d b%d r%d/%d relu%d ln%d%s f32%d", M, N, K, bias, res, res_mod, relu, ln, save_pre ? "+pre" : "", f32out);
     report(name, err, f32out ? 2e-3 : 1.2e-2, ms, 2.0 * M * N * K);
     cudaFree(x); cudaFree(w); cudaFree(b); cudaFree(r); cudaFree(g); cudaFree(be); cudaFree(yref); cudaFree(y);
-    cudaFree(yf32); cudaFree(mean); cudaFree(rstd);
+    cudaFree(yf32); cudaFree(mean); cudaFree(rstd); cudaFree(pre);
 }
 
 // keys scaled by a ramp over the key index: row maxima keep growing from one key tile to the next, which drives the
@@ -251,6 +254,17 @@ int main(int argc, char** argv) {
         test_linear(1024, 128, 256, 1, 0, 0, 1, 0, 0);
         test_linear(22400, 2048, 256, 1, 0, 0, 1, 0, 0);
         test_linear(22400, 256, 2048, 1, 1, 0, 0, 1, 0);
+    }
+    if (which & 4) {  // the LayerNorm-epilogue GEMMs of the training step (pre-LN sum, mean, rstd saved for backward)
+        test_linear(1024, 256, 256, 1, 1, 0, 0, 1, 0, 1);
+        test_linear(1024, 256, 2048, 1, 1, 0, 0, 1, 0, 1);
+        test_linear(4096, 256, 256, 1, 1, 0, 0, 1, 0, 1);
+        test_linear(4096, 256, 2048, 1, 1, 0, 0, 1, 0, 1);
+        test_linear(22400, 256, 256, 1, 1, 0, 0, 1, 0, 1);
+        test_linear(22400, 256, 2048, 1, 1, 0, 0, 1, 0, 1);
+        test_linear(22400, 768, 256, 1, 1, 350, 0, 0, 0);
+        test_linear(22400, 2048, 256, 1, 0, 0, 1, 0, 0);
+        test_linear(4096, 768, 256, 1, 1, 128, 0, 0, 0);
     }
     if (which & 2) {
         test_attn(1, 1, 128, 128, 0, 0);

@@ -65,8 +65,10 @@ class ApAccumulator:
         self.distributed = bool(distributed) and dist.is_available() and dist.is_initialized()
         self._slab_floats = int(slab_floats)
         self._slabs, self._used = [], 0
-        self._items = []    # (host view (world, numel), event or None, shapes)
+        self._items = []    # (host view (world, numel), event or None, shapes, stat keys)
         self._stream = None
+        self.last_stats_device = None
+        self.d2h_bytes_last = 0
 
     def __len__(self):
         return len(self._items)
@@ -79,18 +81,28 @@ class ApAccumulator:
         self._used += numel
         return view
 
-    def add(self, stuffs):
+    def add(self, stuffs, stats=None):
+        """Queue one step's `od_map_stuffs`.  stats: the step's dict of logged scalars (st_detr.py:181-187) — they ride
+        in the same packed buffer, so the N > 1 path still costs ONE collective per step (replacing the reference's
+        all-reduce of `reduce_distrib_loss`, utils/distributed.py:63-75, plus its four all-gathers, :78-89) and one
+        device->host copy.  The mean over ranks is available without a host sync as `last_stats_device` and, once the
+        step's copy has landed, from `stats_history()`."""
         confs, is_positive, size_categories, num_annos = stuffs
         shapes = (tuple(confs.shape), tuple(is_positive.shape), tuple(size_categories.shape), tuple(num_annos.shape))
+        keys = tuple(sorted(stats)) if stats else ()  # sorted: consistent across processes (distributed.py:69)
         with torch.no_grad():
-            packed = torch.cat([t.detach().reshape(-1).to(torch.float32)
-                                for t in (confs, is_positive, size_categories, num_annos)])
-            if self.distributed:  # one collective for the four tensors; every rank keeps every rank's objects
+            parts = [t.detach().reshape(-1).to(torch.float32) for t in (confs, is_positive, size_categories, num_annos)]
+            if keys:
+                parts.append(torch.stack([stats[k].detach().reshape(()).to(torch.float32) for k in keys]))
+            packed = torch.cat(parts)
+            if self.distributed:  # one collective for everything; every rank keeps every rank's objects
                 gathered = [torch.empty_like(packed) for _ in range(dist.get_world_size())]
                 dist.all_gather(gathered, packed)
                 packed = torch.stack(gathered)
             else:
                 packed = packed[None]
+            if keys:
+                self.last_stats_device = dict(zip(keys, packed[:, -len(keys):].mean(dim=0)))
             host = self._host_view(packed.numel(), pinned=packed.is_cuda).view(packed.shape)
             event = None
             if packed.is_cuda:
@@ -104,7 +116,21 @@ class ApAccumulator:
                 packed.record_stream(self._stream)
             else:
                 host.copy_(packed)
-        self._items.append((host, event, shapes))
+        self._items.append((host, event, shapes, keys))
+        self.d2h_bytes_last = 4 * packed.numel()
+
+    def stats_history(self):
+        """Per step, the logged scalars averaged over ranks (what trainer.py:197-199 feeds its meters), as floats.
+        Synchronises on the steps' copy events only."""
+        out = []
+        for host, event, shapes, keys in self._items:
+            if not keys:
+                out.append({})
+                continue
+            if event is not None:
+                event.synchronize()
+            out.append(dict(zip(keys, host[:, -len(keys):].mean(dim=0).tolist())))
+        return out
 
     def tensors(self):
         """The four epoch tensors in the trainer's order (trainer.py:231-236): objects concatenated step-major with the
@@ -112,7 +138,7 @@ class ApAccumulator:
         if not self._items:
             raise ValueError("ApAccumulator.tensors() called before any add()")
         out = [[], [], [], []]
-        for host, event, shapes in self._items:
+        for host, event, shapes, _keys in self._items:
             if event is not None:
                 event.synchronize()
             for rank_row in host:
@@ -132,7 +158,7 @@ class ApAccumulator:
 
     def reset(self):
         """Start the next epoch; the pinned slabs are kept."""
-        for _, event, _ in self._items:
+        for _, event, _, _ in self._items:
             if event is not None:
                 event.synchronize()
         self._items = []

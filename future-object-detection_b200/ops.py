@@ -216,9 +216,11 @@ def add_ln_fwd(x, gamma, beta, eps=1e-5, bcast=None, rows_per_group=0, save=Fals
         _chk_bf16(bcast, "add_ln bcast")
         assert bcast.is_contiguous() and bcast.numel() * rows_per_group == x.numel()
     _t = prof.begin()
-    lib.check(L.fod_add_ln_fwd(_p(x), _p(bcast), rows_per_group, _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), M,
-                               eps, _stream()), "fod_add_ln_fwd")
-    prof.end(_t, "add_ln_fwd", 0.0, 1024.0 * M)
+    call = lambda: L.fod_add_ln_fwd(_p(x), _p(bcast), rows_per_group, _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), M,
+                                    eps, _stream())
+    lib.check(call(), "fod_add_ln_fwd")
+    prof.end(_t, "add_ln_fwd_%d" % M, 0.0, 1024.0 * M, replay=call if _t is not None else None,
+             keep=(x, bcast, gamma, beta, y, mean, rstd))
     LAUNCH_COUNTS["add_ln_fwd_kernel"] += 1
     return (y, mean, rstd) if save else y
 
@@ -233,9 +235,11 @@ def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows
     M = pre.numel() // 256
     dz = torch.empty_like(pre)
     _t = prof.begin()
-    lib.check(L.fod_ln_bwd(_p(dy), _p(dy2), _p(pre), _p(bcast), rows_per_group, _p(mean), _p(rstd), _p(gamma), _p(dz),
-                           _p(dgamma), _p(dbeta), _p(dzsum), M, _stream()), "fod_ln_bwd")
-    prof.end(_t, "ln_bwd", 0.0, 1536.0 * M)
+    call = lambda: L.fod_ln_bwd(_p(dy), _p(dy2), _p(pre), _p(bcast), rows_per_group, _p(mean), _p(rstd), _p(gamma), _p(dz),
+                                _p(dgamma), _p(dbeta), _p(dzsum), M, _stream())
+    lib.check(call(), "fod_ln_bwd")
+    prof.end(_t, "ln_bwd_%d" % M, 0.0, 1536.0 * M, replay=call if _t is not None else None,
+             keep=(dy, dy2, pre, bcast, mean, rstd, gamma, dz, dgamma, dbeta, dzsum))
     LAUNCH_COUNTS["ln_bwd_kernel"] += 1
     return dz
 
@@ -250,8 +254,9 @@ def colsum(x, rows_per_group=0, out=None):
     if out is None:
         out = torch.zeros((M // rpg, N), dtype=torch.float32, device=x.device)
     _t = prof.begin()
-    lib.check(L.fod_colsum(_p(x), x.stride(0), _p(out), M, N, rpg, _stream()), "fod_colsum")
-    prof.end(_t, "colsum", 0.0, 2.0 * M * N)
+    call = lambda: L.fod_colsum(_p(x), x.stride(0), _p(out), M, N, rpg, _stream())
+    lib.check(call(), "fod_colsum")
+    prof.end(_t, "colsum_%dx%d" % (M, N), 0.0, 2.0 * M * N, replay=call if _t is not None else None, keep=(x, out))
     LAUNCH_COUNTS["colsum_kernel"] += 1
     return out
 
@@ -265,8 +270,10 @@ def maxpool3x3s2_nhwc(x):
     oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
     y = torch.empty((n, c, oh, ow), dtype=BF16, device=x.device, memory_format=torch.channels_last)
     _t = prof.begin()
-    lib.check(L.fod_maxpool3x3s2_nhwc(_p(x), _p(y), n, h, w, c, _stream()), "fod_maxpool3x3s2_nhwc")
-    prof.end(_t, "maxpool", 0.0, 2.0 * (x.numel() + y.numel()))
+    call = lambda: L.fod_maxpool3x3s2_nhwc(_p(x), _p(y), n, h, w, c, _stream())
+    lib.check(call(), "fod_maxpool3x3s2_nhwc")
+    prof.end(_t, "maxpool_%dx%dx%d" % (n, h, w), 0.0, 2.0 * (x.numel() + y.numel()), replay=call if _t is not None else None,
+             keep=(x, y))
     LAUNCH_COUNTS["maxpool3x3s2_nhwc_kernel"] += 1
     return y
 
@@ -328,8 +335,9 @@ class ConvFoldTable:
     def run(self):
         L = lib.load()
         _t = prof.begin()
-        lib.check(L.fod_fold_conv_weights(_p(self.table), len(self.outs), self.max_elems, _stream()), "fod_fold_conv_weights")
-        prof.end(_t, "fold_conv_weights", 0.0, self.bytes)
+        call = lambda: L.fod_fold_conv_weights(_p(self.table), len(self.outs), self.max_elems, _stream())
+        lib.check(call(), "fod_fold_conv_weights")
+        prof.end(_t, "fold_conv_weights", 0.0, self.bytes, replay=call if _t is not None else None, keep=(self.table,))
         LAUNCH_COUNTS["fold_conv_weights_kernel"] += 1
         return self.outs
 
@@ -398,7 +406,9 @@ def match(logits, boxes, tgt_boxes, tgt_labels, tgt_count, w_class=2.0, w_bbox=5
     a.w_class, a.w_bbox, a.w_giou, a.alpha = w_class, w_bbox, w_giou, alpha
     _t = prof.begin()
     lib.check(Lb.fod_match(C.byref(a), _stream()), "fod_match")
-    prof.end(_t, "match", 0.0, 4.0 * Lv * B * M * (Cn + 4 + 1))
+    prof.end(_t, "match", 0.0, 4.0 * Lv * B * M * (Cn + 4 + 1),
+             replay=(lambda: Lb.fod_match(C.byref(a), _stream())) if _t is not None else None,
+             keep=(logits, boxes, tgt_boxes, tgt_labels, tgt_count, out))
     LAUNCH_COUNTS["match_kernel"] += 1
     return out
 
@@ -423,7 +433,9 @@ def set_loss(logits, boxes, match_tgt, tgt_boxes, tgt_labels, tgt_count, num_box
     a.w_ce, a.w_bbox, a.w_giou, a.alpha = w_ce, w_bbox, w_giou, alpha
     _t = prof.begin()
     lib.check(Lb.fod_set_loss(C.byref(a), _stream()), "fod_set_loss")
-    prof.end(_t, "set_loss", 0.0, 8.0 * Lv * B * M * (Cn + 4))
+    prof.end(_t, "set_loss", 0.0, 8.0 * Lv * B * M * (Cn + 4),
+             replay=(lambda: Lb.fod_set_loss(C.byref(a), _stream())) if _t is not None else None,
+             keep=(logits, boxes, match_tgt, tgt_boxes, tgt_labels, tgt_count, num_boxes, dl, db, partial, out))
     LAUNCH_COUNTS["set_loss_kernel"] += 1
     LAUNCH_COUNTS["set_loss_finalize_kernel"] += 1
     return out, dl, db
@@ -464,6 +476,8 @@ def ap_match(pred_boxes, scores, anno_boxes, anno_classes, anno_active, imsize, 
     a.size_lo, a.size_hi = (1 / 24) * (1 / 64) * h * w, (1 / 4) * (1 / 12) * h * w
     _t = prof.begin()
     lib.check(L.fod_ap_match(C.byref(a), _stream()), "fod_ap_match")
-    prof.end(_t, "ap_match", 0.0, 4.0 * B * (M * (Cn + 4) + N * 6))
+    prof.end(_t, "ap_match", 0.0, 4.0 * B * (M * (Cn + 4) + N * 6),
+             replay=(lambda: L.fod_ap_match(C.byref(a), _stream())) if _t is not None else None,
+             keep=(pb, sc, ab, ac, aa, thr, confs, is_pos, size_cat, num_annos))
     LAUNCH_COUNTS["ap_match_kernel"] += 1
     return confs, is_pos, size_cat, num_annos

@@ -120,10 +120,12 @@ def _family(name):
     return "rows"
 
 
-def roofline_report(kern, peaks, total_ms_timed_region=None, traffic=None, isolated=None, steps=1):
-    """-> {"roofline": {...dominant kernel family...}, "kernels": {per-kernel table}}.  Fractions are of the MEASURED
-    peaks (MEASURED_PEAKS.json) unless peaks["source"] == "fallback"; kernels timed inside a long step use the
-    sustained bf16 figure."""
+def roofline_report(kern, peaks, total_ms_timed_region=None, traffic=None, isolated=None, steps=1, attention_s=None):
+    """-> {"roofline": {...the (kernel, shape) with the largest time per step...}, "kernels": {per-kernel table}}.
+    Fractions are of the MEASURED peaks (MEASURED_PEAKS.json) unless peaks["source"] == "fallback": the burst bf16
+    figure for a launch timed alone (graph-replayed back to back), the sustained one for a launch timed inside the
+    eager instrumented step.  attention_s: token count of the encoder's space-time attention; its forward and backward
+    get their own entries under roofline["attention"] (the second half of BASELINE.json's metric)."""
     if not kern:
         return {"roofline": None, "kernels": {}}
     fam = collections.defaultdict(lambda: {"ms": 0.0, "launches": 0, "flops": 0.0, "bytes": 0.0})
@@ -138,10 +140,9 @@ def roofline_report(kern, peaks, total_ms_timed_region=None, traffic=None, isola
                        "tflops": round(r["flops"] / sec / 1e12, 2) if sec > 0 else None,
                        "gbs": round(r["bytes"] / sec / 1e9, 1) if sec > 0 else None}
     ours_ms = sum(f["ms"] for f in fam.values())
-    # The dominant kernel = the (kernel, shape) with the largest time per step.  Where an isolated (graph-replayed,
-    # GPU-bound) per-launch time is available it replaces the eager event bracket, which for kernels of a few
-    # microseconds mostly measures the CPU launch gap.
-    isolated = {k: v for k, v in (isolated or {}).items() if v}
+    # Where an isolated (graph-replayed, GPU-bound) per-launch time is available it replaces the eager event bracket,
+    # which for kernels of a few microseconds mostly measures the CPU launch gap.
+    isolated = {k: v for k, v in (isolated or {}).items() if v and k in kern}
     for name, us in isolated.items():
         table[name]["us_per_launch_isolated"] = round(us, 2)
         r = kern[name]
@@ -153,28 +154,54 @@ def roofline_report(kern, peaks, total_ms_timed_region=None, traffic=None, isola
         r = kern[k]
         return (isolated[k] * 1e-3 * r["launches"] if k in isolated else r["ms"]) / max(1, steps)
 
-    pool = [k for k in kern if k in isolated] or list(kern)
-    top_name = max(pool, key=per_step_ms)
-    top = _family(top_name)
-    f = dict(kern[top_name])
-    if top_name in isolated:
-        f["ms"] = isolated[top_name] * 1e-3 * f["launches"]
-    sec = f["ms"] / 1e3
-    # the bounding roofline of THIS shape: whichever of (algorithmic flops / tensor peak) and (algorithmic bytes / HBM
-    # peak) takes longer; pure row / optimizer / loss kernels have no tensor work
-    t_tensor = f["flops"] / (peaks["bf16_sustained"] * 1e12)
-    t_hbm = f["bytes"] / (peaks["hbm_gbs"] * 1e9)
-    bound = "tensor" if (_BOUND[top] == "tensor" and t_tensor >= t_hbm) else "hbm"
-    if bound == "tensor":
-        achieved, peak, unit = f["flops"] / sec / 1e12, peaks["bf16_sustained"], "TFLOP/s"
-    else:
-        achieved, peak, unit = f["bytes"] / sec / 1e9, peaks["hbm_gbs"], "GB/s"
-    roof = {"kernel": top_name, "family": top, "bound": bound, "achieved": achieved, "peak": peak,
-            "unit": unit, "frac": achieved / peak, "traffic": (traffic or {}).get(top_name, (traffic or {}).get(top)), "peak_source": peaks["source"],
-            "launches_per_step": f["launches"] / max(1, steps), "avg_launch_us": 1e3 * f["ms"] / max(1, f["launches"]),
-            "ms_per_step": per_step_ms(top_name),
-            "timing": "CUDA events around back-to-back graph replays of this launch" if top_name in isolated
-            else "CUDA events around each launch of the eager instrumented steps"}
+    for name in table:
+        table[name]["ms_per_step"] = round(per_step_ms(name), 4)
+
+    def entry(name):
+        famname = _family(name)
+        f = dict(kern[name])
+        iso = name in isolated
+        if iso:
+            f["ms"] = isolated[name] * 1e-3 * f["launches"]
+        sec = f["ms"] / 1e3
+        tensor_peak = peaks["bf16_burst"] if iso else peaks["bf16_sustained"]
+        # the bounding roofline of THIS shape: whichever of (algorithmic flops / tensor peak) and (algorithmic bytes /
+        # HBM peak) takes longer; pure row / optimizer / loss kernels have no tensor work
+        t_tensor = f["flops"] / (tensor_peak * 1e12)
+        t_hbm = f["bytes"] / (peaks["hbm_gbs"] * 1e9)
+        bound = "tensor" if (_BOUND[famname] == "tensor" and t_tensor >= t_hbm) else "hbm"
+        if bound == "tensor":
+            achieved, peak, unit = f["flops"] / sec / 1e12, tensor_peak, "TFLOP/s"
+        else:
+            achieved, peak, unit = f["bytes"] / sec / 1e9, peaks["hbm_gbs"], "GB/s"
+        return {"kernel": name, "family": famname, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit,
+                "frac": achieved / peak, "traffic": (traffic or {}).get(name), "peak_source": peaks["source"],
+                "peak_kind": ("burst (launch timed alone)" if iso else "sustained (launch timed inside the step)"),
+                "launches_per_step": f["launches"] / max(1, steps), "avg_launch_us": 1e3 * f["ms"] / max(1, f["launches"]),
+                "ms_per_step": per_step_ms(name),
+                "algorithmic_flops_per_launch": f["flops"] / max(1, f["launches"]),
+                "algorithmic_bytes_per_launch": f["bytes"] / max(1, f["launches"]),
+                "timing": "CUDA events around back-to-back graph replays of this launch" if iso
+                else "CUDA events around each launch of the eager instrumented steps"}
+
+    # The dominant kernel = the (kernel, shape) with the largest time per step among ALL instrumented launches.
+    top_name = max(kern, key=per_step_ms)
+    roof = entry(top_name)
+    roof["ranked_by"] = "time per step over all %d instrumented (kernel, shape) pairs" % len(kern)
+    roof["runners_up"] = [{"kernel": k, "ms_per_step": round(per_step_ms(k), 4)}
+                          for k in sorted(kern, key=per_step_ms, reverse=True)[1:6]]
+    if attention_s:
+        att = {}
+        for half in ("fwd", "bwd"):
+            name = "attn_%s_p1_%dx%d" % (half, attention_s, attention_s)
+            if name in kern:
+                e = entry(name)
+                # the tensor roofline is the metric's denominator ("ST-attention TFLOP/s vs bf16 peak") whatever bounds it
+                sec = e["avg_launch_us"] * 1e-6
+                e["tflops"] = e["algorithmic_flops_per_launch"] / sec / 1e12
+                e["frac_of_bf16_peak"] = e["tflops"] / (peaks["bf16_burst"] if name in isolated else peaks["bf16_sustained"])
+                att[half] = e
+        roof["attention"] = att
     fams = {k: {"ms_total": round(v["ms"], 3), "launches": v["launches"],
                 "tflops": round(v["flops"] / (v["ms"] / 1e3) / 1e12, 2) if v["ms"] > 0 else None,
                 "gbs": round(v["bytes"] / (v["ms"] / 1e3) / 1e9, 1) if v["ms"] > 0 else None} for k, v in fam.items()}

@@ -30,11 +30,12 @@ class TrainStep:
         self.params = [p for p in model.parameters() if p.requires_grad]
         self.reducer = reducer
         self.flat = optimizer if hasattr(optimizer, "finish_backward") else None
+        self.stats = self.od_map_stuffs = None  # the step's logged scalars / AP bookkeeping (trainer.py:191-211)
 
     def __call__(self, data):
         if self.flat is not None:
             self.flat.begin_step()
-            _, _, loss, stats, _ = self.model(data=data, distributed=self.distributed)
+            _, _, loss, self.stats, self.od_map_stuffs = self.model(data=data, distributed=self.distributed)
             loss.backward()
             self.flat.finish_backward()
             self.flat.step(self.max_norm)
@@ -43,7 +44,7 @@ class TrainStep:
             self.reducer.zero_grad()
         else:
             self.opt.zero_grad(set_to_none=True)
-        _, _, loss, stats, _ = self.model(data=data, distributed=self.distributed)
+        _, _, loss, self.stats, self.od_map_stuffs = self.model(data=data, distributed=self.distributed)
         loss.backward()
         if self.reducer is not None:
             self.reducer.finish()
