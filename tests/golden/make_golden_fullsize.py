@@ -5,6 +5,8 @@
 
   f1  configs[0]  nuim_spatiotemporal_imu forward: 1 clip x 4 frames (3 past), 448x800, S = 350 tokens per frame
   f2  configs[1]  shape (L = 3, 448x800), 2 clips: forward + loss + matcher indices + AP bookkeeping
+  f3  configs[2]  stage-2 resolution (L = 3, 896x1600, S = 1400 tokens per frame), 1 clip: the size at which the
+      space-time attention is tensor-bound           (python tests/golden/make_golden_fullsize.py f3_b1_l3_896x1600)
 
 Weights: the name-keyed synthetic ones with residual_gain=0.5 — what bench.py trains.  Only the small
 outputs are stored (the inputs are regenerated from the seed by fod_b200.synthetic.make_clip).
@@ -25,7 +27,8 @@ from fod_b200.synthetic import make_clip, synthetic_state_dict  # noqa: E402
 from future_od.models.st_detr import SpatioTemporalDETRArgs, to_detr_targets  # noqa: E402
 from runs._model import build_model  # noqa: E402
 
-CASES = {"f1_b1_l4_448x800": (1, 4, 448, 800, 21), "f2_b2_l3_448x800": (2, 3, 448, 800, 22)}
+CASES = {"f1_b1_l4_448x800": (1, 4, 448, 800, 21), "f2_b2_l3_448x800": (2, 3, 448, 800, 22),
+         "f3_b1_l3_896x1600": (1, 3, 896, 1600, 23)}
 IMU = ("translation", "acceleration", "rotation", "rotation_rate", "speed")
 
 
@@ -38,6 +41,8 @@ def main():
         model.load_state_dict(synthetic_state_dict(json.load(f), seed=0, residual_gain=0.5))
     model.eval()
     for name, (b, l, h, w, seed) in CASES.items():
+        if len(sys.argv) > 1 and name not in sys.argv[1:]:
+            continue
         data = make_clip(b, l, h, w, seed=seed)
         store = {}
         hook = model._model.detector.decoder.register_forward_hook(

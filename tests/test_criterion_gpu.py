@@ -60,9 +60,20 @@ def _check_match(logits, boxes, targets, nt_cap):
 
 
 def test_matcher_bit_exact_random():
-    for seed in range(40):
+    """1 200 random (sample, level) problems (SURVEY §7.2 asks >= 1 000): 130 seeds x 4 samples x 2 levels with
+    Nt ~ U[0, 40), plus 20 seeds whose target counts straddle and exceed M = 128 (scipy's transposed branch)."""
+    n = 0
+    for seed in range(130):
         logits, boxes, targets = _case(seed, bsz=4, levels=2)
         _check_match(logits, boxes, targets, 40)
+        n += 4 * 2
+    g = torch.Generator().manual_seed(999)
+    for seed in range(20):
+        nts = [int(torch.randint(100, 200, (1,), generator=g)) for _ in range(4)]
+        logits, boxes, targets = _case(5000 + seed, bsz=4, nts=nts, levels=2)
+        _check_match(logits, boxes, targets, 200)
+        n += 4 * 2
+    assert n >= 1000
 
 
 @pytest.mark.parametrize("nts", [[0, 1, 2], [128, 127], [129, 256], [200, 0, 64]])

@@ -1,6 +1,6 @@
 """GPU parity of the individual C-ABI kernels (through fod_b200.ops -> ctypes -> libfod_b200.so) against plain
-torch fp32 references on the same bf16-rounded inputs.  Tolerances: bf16 outputs 2e-2 relative to max|ref|
-(north star), fp32 statistics 1e-3."""
+torch fp32 references on the same bf16-rounded inputs.  Tolerances: relative L2 per tensor, ||a - b|| / ||b|| — bf16
+outputs 2e-2 (north star), fp32 statistics 1e-3..1e-2 as written at the call."""
 import pytest
 import torch
 
@@ -18,9 +18,12 @@ def _rnd(*shape, scale=1.0, seed=0):
 
 
 def _close(a, b, tol=2e-2, what=""):
-    a, b = a.float(), b.float()
-    err = float((a - b).abs().max() / max(1e-6, float(b.abs().max())))
-    assert err < tol, f"{what}: rel err {err:.4g} >= {tol}"
+    """Relative L2 over the whole tensor: a tensor whose small entries are all wrong cannot pass on
+    the strength of its largest entry.  Non-finite values fail."""
+    a, b = a.detach().double(), b.detach().double()
+    assert a.shape == b.shape, f"{what}: shape {tuple(a.shape)} vs {tuple(b.shape)}"
+    err = float((a - b).norm() / max(1e-30, float(b.norm())))
+    assert err == err and err < tol, f"{what}: relative L2 {err:.4g} >= {tol}"
     return err
 
 
@@ -104,7 +107,9 @@ def test_gemm_unaligned_output_falls_back_to_scalar_stores():
 
 @pytest.mark.parametrize("B,Lq,Lk,two,bcast", [(2, 350, 350, False, False), (3, 128, 350, True, True),
                                                  (2, 128, 128, False, False), (1, 700, 700, False, False),
-                                                 (2, 100, 3, False, False), (2, 128, 1400, True, True)])
+                                                 (2, 100, 3, False, False), (2, 128, 1400, True, True),
+                                                 (2, 1400, 1400, False, False), (1, 2800, 2800, False, False),
+                                                 (1, 1400, 128, False, False)])
 def test_attention_forward_backward(B, Lq, Lk, two, bcast):
     from fod_b200 import ops
     H, C = 8, 256

@@ -125,11 +125,20 @@ def test_backward_matches_reference_gradients(model, ref_state_dict):
     model.eval()
     missing = [k for k, p in model.named_parameters() if p.requires_grad and p.grad is None]
     assert not missing, missing[:5]
-    # Tolerance.  bf16 hand-over of activations/gradients between blocks costs ~3e-2 relative L2 per parameter tensor
-    # against the fp32 reference (measured: tests/test_kernels_gpu.py::test_block_functions explains the mechanism), so
-    # each tensor must satisfy |g - ref| <= 8e-2 |ref| + 1e-4 |ref_all| (the absolute floor covers tensors whose true
-    # gradient is ~0, e.g. key biases — softmax is shift-invariant — and the c = 0 first decoder layer), and the
-    # concatenation of all checked tensors (dominated by the IMU MLP, whose gradient crosses all 12 blocks) to 6e-2.
+    # Tolerance.  SURVEY §8c asks 2e-2 relative L2 per tensor against the fp32 reference.  The
+    # reference's OWN bf16 path does not meet that on gradients: run under torch.autocast(bfloat16) on this very case,
+    # the unmodified reference sits 3.4e-2 (global) from its fp32 gradients, per-tensor median 3.4e-2
+    # (tests/golden/ref_autocast_floor.json, made by tests/golden/make_golden_autocast.py).  The gate is therefore, per
+    # tensor, max(2e-2, GATE x the reference's own autocast error for THAT tensor) — plus an absolute floor of 1e-4 of
+    # the global gradient norm for tensors whose true gradient is ~0 (key biases: softmax is shift-invariant; the c = 0
+    # first decoder layer) — and the same rule on the concatenation of all checked tensors.
+    import json
+    import os
+
+    from conftest import GOLDEN
+    with open(os.path.join(GOLDEN, "ref_autocast_floor.json")) as f:
+        own = json.load(f)["g1_b2_l3_128x160"]
+    GATE = 1.5
     params = dict(model.named_parameters())
     small = {k: g for k, g in gold["grads_small"].items()}
     ref_all = torch.cat([g.flatten().double() for g in small.values()])
@@ -142,11 +151,18 @@ def test_backward_matches_reference_gradients(model, ref_state_dict):
             assert float(mine.norm()) == 0.0, k  # dead egodeep parameters: exact zeros
             continue
         err = float((mine.double() - g.double()).norm())
-        report.append((round(err / (8e-2 * float(g.norm()) + floor), 3), round(err / float(g.norm()), 4), k))
+        budget = max(2e-2, GATE * own["grad"][k])
+        report.append((round(err / (budget * float(g.norm()) + floor), 3), round(err / float(g.norm()), 4),
+                       round(own["grad"][k], 4), k))
     report.sort(reverse=True)
-    print("worst gradient errors (budget fraction, rel L2, name):", report[:6])
+    print("worst gradient errors (budget fraction, rel L2, reference's own autocast rel L2, name):", report[:8])
     glob = float((got_all - ref_all).norm() / ref_all.norm())
-    print("global gradient rel L2 over %d tensors: %.4f" % (len(small), glob))
+    own_all = own["grad_global"]
+    print("global gradient rel L2 over %d tensors: %.4f (reference under autocast, all tensors: %.4f)" % (len(small), glob, own_all))
+    dump = os.environ.get("FOD_TEST_DUMP")
+    if dump:
+        with open(os.path.join(dump, "grad_parity_g1.json"), "w") as f:
+            json.dump({"global": glob, "reference_autocast_global": own_all, "per_tensor": report}, f)
     top = max(float(n) for n in gold["grad_norms"].values())
     norm_bad = []
     for k, n in gold["grad_norms"].items():
@@ -157,7 +173,7 @@ def test_backward_matches_reference_gradients(model, ref_state_dict):
             norm_bad.append((k, round(r, 3)))
     print("gradient-norm ratios outside 10%:", norm_bad[:10], len(norm_bad))
     assert report[0][0] <= 1.0, report[:5]
-    assert glob < 6e-2
+    assert glob < max(2e-2, GATE * own_all), (glob, own_all)
     assert not norm_bad, norm_bad[:10]
 
 
@@ -194,6 +210,31 @@ def test_joint_encoder_matches_reference_golden(model):
     got = y.view(b, l, h, w, d).permute(0, 1, 4, 2, 3).float()
     err = rel_l2(got, gold["out"])
     print("joint encoder rel L2", err)
+    assert err < TOL
+
+
+def test_joint_encoder_t8_full_size_matches_reference_golden(model):
+    """JointEncoder at T = 8 frames of 14x25 tokens (448x800): ONE space-time attention over S = 2800 tokens per clip,
+    the tensor-bound regime.  Golden from the unmodified reference's JointEncoder
+    (tests/golden/make_golden_joint.py; inputs regenerated from the seed, output stored in fp16); 2e-2 relative L2."""
+    import os
+
+    from conftest import GOLDEN
+    from fod_b200.st_detr import JointEncoder
+    gold = torch.load(os.path.join(GOLDEN, "joint_b1_l8_14x25.pt"))
+    b, l, h, w = gold["shape"]
+    s, d = h * w, 256
+    g = torch.Generator().manual_seed(gold["seed"])
+    feats = torch.randn(b, l, d, h, w, generator=g).to(torch.bfloat16).float()
+    ego = torch.randn(b, l, d, generator=g).to(torch.bfloat16).float()
+    se = model._model.separate_encoder
+    x = feats.permute(0, 1, 3, 4, 2).reshape(b * l * s, d).to(DEV).to(torch.bfloat16)
+    pos_bf = model._model.pos_encoder.spatial_tokens(h, w, d, torch.device(DEV)).to(torch.bfloat16)
+    with torch.no_grad():
+        y = JointEncoder(se.transformer)(x, pos_bf, ego.reshape(b * l, d).to(DEV).to(torch.bfloat16), b, l, s)
+    got = y.view(b, l, h, w, d).permute(0, 1, 4, 2, 3).float()
+    err = rel_l2(got, gold["out_f16"].float())
+    print("joint encoder T=8 (S=2800) rel L2", err)
     assert err < TOL
 
 

@@ -138,7 +138,7 @@ def test_temporal_code_frame_counter_and_normalisation():
     assert torch.allclose(e2[1, 0, :, 0, 0], torch.where(idx.long() % 2 == 0, ang.sin(), ang.cos()), atol=1e-5)
 
 
-@pytest.mark.parametrize("name", ["f1_b1_l4_448x800", "f2_b2_l3_448x800"])
+@pytest.mark.parametrize("name", ["f1_b1_l4_448x800", "f2_b2_l3_448x800", "f3_b1_l3_896x1600"])
 def test_full_size_forward_matches_reference(name):
     """BASELINE.json configs[0] (1 clip x 4 frames, 448x800, CPU forward) and the configs[1] shape, at full size, with
     the weights bench.py trains (residual_gain=0.5).  Golden: tests/golden/make_golden_fullsize.py."""

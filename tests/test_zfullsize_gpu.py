@@ -1,5 +1,6 @@
-"""Whole-path parity at BASELINE.json's FULL sizes (448x800, S = 350 tokens per frame): configs[0] (1 clip x 4 frames,
-forward) and the configs[1] shape (L = 3), with the weights bench.py trains (residual_gain=0.5).  The drop-in (bf16
+"""Whole-path parity at BASELINE.json's FULL sizes: configs[0] (1 clip x 4 frames, 448x800, S = 350 tokens per frame,
+forward), the configs[1] shape (L = 3) and configs[2]'s stage-2 resolution (896x1600, S = 1400 — where the space-time
+attention is tensor-bound), with the weights bench.py trains (residual_gain=0.5).  The drop-in (bf16
 kernels) against goldens of the unmodified reference (tests/golden/make_golden_fullsize.py, fp32 CPU): 2e-2 relative L2
 per tensor; matcher assignments, loss and AP bookkeeping exact against the oracle on the model's own fp32 outputs.
 (File name: sorts last, so the kernel- and small-size model tests report first.)"""
@@ -35,7 +36,7 @@ def model():
     return m.eval()
 
 
-@pytest.mark.parametrize("name", ["f1_b1_l4_448x800", "f2_b2_l3_448x800"])
+@pytest.mark.parametrize("name", ["f1_b1_l4_448x800", "f2_b2_l3_448x800", "f3_b1_l3_896x1600"])
 def test_full_size_forward_matches_reference_golden(model, name):
     from fod_b200.st_detr import check_match_status
     from fod_b200.synthetic import make_clip
