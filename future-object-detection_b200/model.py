@@ -137,6 +137,36 @@ def inverse_sigmoid(x, eps=1e-5):
 
 
 # ------------------------------------------------------------------------------------------------ backbone (cuDNN)
+def _is_main_process():
+    """ConditionalDETR/util/misc.py:405-406."""
+    import torch.distributed as dist
+    return not (dist.is_available() and dist.is_initialized()) or dist.get_rank() == 0
+
+
+def _load_pretrained_backbone(backbone, name):
+    """torchvision's ImageNet weights for `name` (what `pretrained=True` means upstream, paper.py:94-98): a local file
+    named by FOD_B200_BACKBONE_WEIGHTS, else torchvision's own cache / download.  Fails with the remedy spelled out."""
+    import os
+
+    import torchvision
+    path = os.environ.get("FOD_B200_BACKBONE_WEIGHTS")
+    try:
+        if path:
+            sd = torch.load(path, map_location="cpu", weights_only=True)
+        else:
+            sd = torchvision.models.get_model_weights(name).DEFAULT.get_state_dict(progress=False)
+    except Exception as e:  # no network and no cached file
+        raise RuntimeError(
+            "pretrained_backbone=True needs torchvision's ImageNet weights for %s and they could not be loaded (%s: %s). "
+            "Either point FOD_B200_BACKBONE_WEIGHTS at a local torchvision state_dict file, or build with "
+            "SpatioTemporalDETRArgs(pretrained_backbone=False) and load_state_dict() a checkpoint (INTEGRATION.md §2)."
+            % (name, type(e).__name__, str(e)[:200])) from e
+    missing, unexpected = backbone.load_state_dict(sd, strict=False)
+    bad = [k for k in missing if "num_batches_tracked" not in k]
+    if bad:
+        raise RuntimeError("backbone weights for %s lack %s" % (name, bad[:5]))
+
+
 class FrozenBatchNorm2d(nn.Module):
     """ConditionalDETR/models/backbone.py:27-63 — statistics and affine are buffers; eps 1e-5."""
 
@@ -216,8 +246,11 @@ class _ConvAffineAct(torch.autograd.Function):
                     y = torch.cudnn_convolution_relu(x, wq, bq, stride, padding, (1, 1), 1)
                 else:
                     y = torch.cudnn_convolution_add_relu(x, wq, z, 1.0, bq, stride, padding, (1, 1), 1)
-            except RuntimeError:
+            except RuntimeError as e:
                 _ConvAffineAct.fused_ok = False
+                import warnings
+                warnings.warn("fod_b200: the fused cuDNN conv+bias(+add)+ReLU call failed (%s); the backbone uses the "
+                              "unfused conv -> add -> relu path for the rest of this process" % str(e)[:200])
         if y is None:
             y = F.conv2d(x, wq, bq, stride, padding)
             if z is not None:
@@ -279,10 +312,13 @@ class CDetrBackbone(nn.Module):
         import torchvision
         from torchvision.models._utils import IntermediateLayerGetter
 
-        if pretrained:
-            raise RuntimeError("pretrained ImageNet weights need network access; load a checkpoint instead")
+        # paper.py:94-98: rank 0 alone loads torchvision's ImageNet weights (`pretrained=is_main_process() and pretrained`);
+        # the other ranks get them through the construction-time broadcast (DDP there, FlatTrainState here).
+        # FOD_B200_BACKBONE_WEIGHTS=<file> names a local torchvision state_dict for boxes without network access.
         backbone = getattr(torchvision.models, name)(
             replace_stride_with_dilation=[False, False, dilation], weights=None, norm_layer=FrozenBatchNorm2d)
+        if pretrained and _is_main_process():
+            _load_pretrained_backbone(backbone, name)
         for pname, p in backbone.named_parameters():
             if not train_backbone or ("layer2" not in pname and "layer3" not in pname and "layer4" not in pname):
                 p.requires_grad_(False)

@@ -67,6 +67,11 @@ class FlatTrainState:
             p._fod_shadow = self.shadow[o:o + p.numel()].view_as(p)
             p._fod_reducer = r   # autograd.py: gradient kernels accumulate straight into the arena slot
             p._fod_uses = 0
+        # runs/_model.py:76-82 wraps the model in DistributedDataParallel, whose constructor broadcasts rank 0's
+        # parameters and buffers (rank 0 alone loads the pretrained backbone, paper.py:96; the transformer is
+        # initialised from each process's own RNG).  This object replaces that wrapper, so it does the same.
+        self.group = group
+        self.broadcast_from_rank0(refresh=False)
         self._args = None
         self._partial = None
         self.lr_version = 0  # bumped by set_lr(): learning rates are kernel ARGUMENTS, so a captured graph must follow
@@ -74,6 +79,23 @@ class FlatTrainState:
             self._partial = torch.empty(lib.load().fod_optim_workspace_floats(), dtype=torch.float32, device=dev)
             self.refresh_shadow()
         self._hook = model.register_load_state_dict_post_hook(lambda m, keys: self.refresh_shadow())
+
+    def broadcast_from_rank0(self, refresh=True):
+        """Rank 0's trainable parameters (the arena, one collective), frozen parameters and buffers -> every rank.
+        No-op without an initialised process group.  Also usable after an out-of-band load on rank 0 only."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(self.group) == 1:
+            return
+        src = dist.get_global_rank(self.group, 0) if self.group is not None else 0
+        with torch.no_grad():
+            dist.broadcast(self.params, src=src, group=self.group)
+            in_arena = set(id(p) for p in self.reducer.order)
+            rest = [p.data for p in self.model.parameters() if id(p) not in in_arena] + list(self.model.buffers())
+            for t in rest:
+                if t.numel():
+                    dist.broadcast(t, src=src, group=self.group)
+        if refresh and self.params.is_cuda:
+            self.refresh_shadow()
 
     # ------------------------------------------------------------------ bf16 operand copies
     def refresh_shadow(self):
@@ -145,16 +167,69 @@ class FlatTrainState:
         return self.state[0]
 
     # ------------------------------------------------------------------ checkpointing
+    def _names(self):
+        return {id(p): n for n, p in self.model.named_parameters()}
+
     def state_dict(self):
-        return {"step": self.state[2].clone(), "exp_avg": self.exp_avg.clone(), "exp_avg_sq": self.exp_avg_sq.clone(),
-                "group_lr": list(self.group_lr), "layout_numel": self.n}
+        """torch.optim.AdamW's own format (`state` keyed by parameter index in param_groups order with `step`,
+        `exp_avg`, `exp_avg_sq`; `param_groups` with lr / betas / eps / weight_decay / params), built the way
+        runs/_helper.py:84-107 builds the reference optimizer — group 0: non-backbone, group 1: backbone, each in
+        named_parameters() order — so the `optimizer` entry of a reference checkpoint (trainer.py:282-299) resumes here
+        and vice versa.  `param_names` (extra key, ignored by torch) pins the order by NAME, so a load never depends on
+        the arena layout."""
+        named = [(n, p) for n, p in self.model.named_parameters() if p.requires_grad]
+        groups = [[(n, p) for n, p in named if "backbone" not in n], [(n, p) for n, p in named if "backbone" in n]]
+        groups = [g for g in groups if g]
+        r, step = self.reducer, self.state[2].detach().clone()
+        state, pgs, names, idx = {}, [], [], 0
+        for gi, g in enumerate(groups):
+            ids = []
+            for n, p in g:
+                o = r.offset[p]
+                state[idx] = {"step": step.clone(), "exp_avg": self.exp_avg[o:o + p.numel()].view_as(p).clone(),
+                              "exp_avg_sq": self.exp_avg_sq[o:o + p.numel()].view_as(p).clone()}
+                ids.append(idx)
+                names.append(n)
+                idx += 1
+            pgs.append({"lr": self.group_lr[min(gi, len(self.group_lr) - 1)], "betas": tuple(self.betas), "eps": self.eps,
+                        "weight_decay": self.group_wd[min(gi, len(self.group_wd) - 1)], "amsgrad": False, "params": ids})
+        return {"state": state, "param_groups": pgs, "param_names": names}
 
     def load_state_dict(self, sd):
-        assert sd["layout_numel"] == self.n, "optimizer arena layout mismatch"
-        self.exp_avg.copy_(sd["exp_avg"])
-        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
-        self.state[2] = sd["step"]
-        self.set_lr(*sd["group_lr"]) if len(sd["group_lr"]) > 1 else self.set_lr(sd["group_lr"][0])
+        """Accepts state_dict() above or a torch.optim.AdamW state_dict of the reference's optimizer.  Every entry is
+        matched to its parameter (by name when `param_names` is present, else by the reference's group order) and its
+        shape is checked; nothing is loaded on a mismatch."""
+        named = [(n, p) for n, p in self.model.named_parameters() if p.requires_grad]
+        order = [(n, p) for n, p in named if "backbone" not in n] + [(n, p) for n, p in named if "backbone" in n]
+        ids = [i for g in sd["param_groups"] for i in g["params"]]
+        if len(ids) != len(order):
+            raise ValueError("optimizer state has %d parameters, the model has %d trainable ones" % (len(ids), len(order)))
+        if "param_names" in sd:
+            by_name = dict(order)
+            if set(sd["param_names"]) != set(by_name):
+                raise ValueError("optimizer state names do not match the model's trainable parameters")
+            order = [(n, by_name[n]) for n in sd["param_names"]]
+        plan = []
+        for i, (n, p) in zip(ids, order):
+            st = sd["state"].get(i)
+            if st is None:
+                continue
+            if tuple(st["exp_avg"].shape) != tuple(p.shape) or tuple(st["exp_avg_sq"].shape) != tuple(p.shape):
+                raise ValueError("optimizer state of %s has shape %s, the parameter %s" % (n, tuple(st["exp_avg"].shape), tuple(p.shape)))
+            plan.append((p, st))
+        r, steps = self.reducer, set()
+        with torch.no_grad():
+            for p, st in plan:
+                o = r.offset[p]
+                self.exp_avg[o:o + p.numel()].view_as(p).copy_(st["exp_avg"])
+                self.exp_avg_sq[o:o + p.numel()].view_as(p).copy_(st["exp_avg_sq"])
+                steps.add(float(st["step"]))
+            if len(steps) > 1:
+                raise ValueError("per-parameter step counts differ (%s): the flat AdamW keeps one counter" % sorted(steps)[:4])
+            if steps:
+                self.state[2] = steps.pop()
+        lrs = [g["lr"] for g in sd["param_groups"]]
+        self.set_lr(lrs[0], lrs[1] if len(lrs) > 1 else None)
 
     def close(self):
         self._hook.remove()

@@ -62,11 +62,16 @@ class GraphedTrainStep:
     branches that overlap backward), so a multi-GPU step is still ONE cudaGraphLaunch per rank.
 
     The optimizer must have been built with capturable=True.  `warmup` eager steps run first on a side stream, as
-    CUDA-graph capture requires (allocator warm-up, cuDNN autotuning, lazily created kernel attributes)."""
+    CUDA-graph capture requires (allocator warm-up, cuDNN autotuning, lazily created kernel attributes).  They are
+    steps on the EXAMPLE batch that the reference's Trainer never takes, so the trainable state (parameters, both
+    AdamW moments, the step counter) is snapshotted before them and restored afterwards (`keep_warmup_updates=True`
+    keeps them): the first replay is the first optimizer step, with bias correction at t = 1."""
 
-    def __init__(self, model, optimizer, example, max_norm=0.1, warmup=3, distributed=False, reducer=None):
+    def __init__(self, model, optimizer, example, max_norm=0.1, warmup=3, distributed=False, reducer=None,
+                 keep_warmup_updates=False):
         self.eager = TrainStep(model, optimizer, max_norm, distributed=distributed, reducer=reducer)
         self.static = {k: (v.clone() if torch.is_tensor(v) else v) for k, v in example.items()}
+        snap = None if keep_warmup_updates else self._snapshot(model, optimizer)
         s = torch.cuda.Stream()
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
@@ -74,6 +79,9 @@ class GraphedTrainStep:
                 self.eager(self.static)
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize()
+        if snap is not None:
+            self._restore(model, optimizer, snap)
+            del snap
         self.graph = torch.cuda.CUDAGraph()
         if reducer is None and hasattr(optimizer, "zero_grad"):
             optimizer.zero_grad(set_to_none=True)
@@ -82,6 +90,32 @@ class GraphedTrainStep:
             self.loss = self.eager(self.static)
         torch.cuda.synchronize()
         self._lr_version = getattr(self.eager.flat, "lr_version", 0)
+
+    @staticmethod
+    def _snapshot(model, optimizer):
+        with torch.no_grad():
+            if hasattr(optimizer, "finish_backward"):  # FlatTrainState: four arenas
+                return ("flat", optimizer.params.clone(), optimizer.exp_avg.clone(), optimizer.exp_avg_sq.clone(),
+                        optimizer.state.clone())
+            import copy
+            return ("torch", [p.detach().clone() for p in model.parameters() if p.requires_grad],
+                    copy.deepcopy(optimizer.state_dict()))
+
+    @staticmethod
+    def _restore(model, optimizer, snap):
+        with torch.no_grad():
+            if snap[0] == "flat":
+                optimizer.params.copy_(snap[1])
+                optimizer.exp_avg.copy_(snap[2])
+                optimizer.exp_avg_sq.copy_(snap[3])
+                optimizer.state.copy_(snap[4])
+                optimizer.grads.zero_()
+                optimizer.refresh_shadow()
+            else:
+                for p, q in zip([p for p in model.parameters() if p.requires_grad], snap[1]):
+                    p.copy_(q)
+                optimizer.load_state_dict(snap[2])
+        torch.cuda.synchronize()
 
     def __call__(self, data=None):
         """data: a batch (host or device tensors) copied into the static inputs now, or None to consume the oldest
@@ -110,6 +144,13 @@ class GraphedTrainStep:
         reference's StepLR, runs/_helper.py:104-106), `max_norm`.  Called automatically for learning-rate changes."""
         torch.cuda.synchronize()
         eager = self.eager
+        # The old graph's private pool holds a full step of activations: it is released BEFORE the new capture so the
+        # two never coexist (B = 32 at 448x800 / B = 16 at 896x1600 would otherwise transiently need twice the memory).
+        # The static outputs (`loss`, `eager.stats`, `eager.od_map_stuffs`) are new tensors afterwards.
+        self.graph = self.loss = None
+        eager.stats = eager.od_map_stuffs = None
+        import gc
+        gc.collect()
         graph = torch.cuda.CUDAGraph()
         if eager.reducer is None and hasattr(eager.opt, "zero_grad"):
             eager.opt.zero_grad(set_to_none=True)

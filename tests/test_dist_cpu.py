@@ -166,3 +166,81 @@ def test_fused_param_groups_get_adjacent_slots_cpu():
     fw._fod_uses = 1
     A._done(fw)
     assert all(p in flat.reducer._ready for p in gw)
+
+
+def _broadcast_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from fod_b200.optim import FlatTrainState
+    torch.manual_seed(100 + rank)  # every process initialises from its OWN RNG, as runs/_model.py does
+    net = torch.nn.ModuleDict({"backbone": torch.nn.Sequential(torch.nn.Linear(5, 3), torch.nn.BatchNorm1d(3)),
+                               "head": torch.nn.Linear(3, 7)})
+    net["backbone"][0].bias.requires_grad_(False)          # frozen parameter: outside the arena
+    net["backbone"][1].running_mean.fill_(float(rank + 1))  # buffer
+    FlatTrainState(net, bucket_mb=1e-5)
+    out[rank] = {k: v.clone() for k, v in net.state_dict().items()}
+    dist.destroy_process_group()
+
+
+def test_flat_train_state_broadcasts_rank0_like_ddp():
+    """runs/_model.py:76-82: DistributedDataParallel's constructor makes every replica start from rank 0's parameters
+    and buffers.  FlatTrainState replaces that wrapper and must do the same (trainable arena, frozen parameters,
+    buffers), or replicas initialised from different RNG streams would silently train different models."""
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_broadcast_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    torch.manual_seed(100)
+    ref = torch.nn.ModuleDict({"backbone": torch.nn.Sequential(torch.nn.Linear(5, 3), torch.nn.BatchNorm1d(3)),
+                               "head": torch.nn.Linear(3, 7)})
+    ref["backbone"][1].running_mean.fill_(1.0)
+    for k, v in ref.state_dict().items():
+        assert torch.equal(out[0][k], v) and torch.equal(out[1][k], v), k
+
+
+def test_flat_train_state_checkpoint_is_torch_adamw_format():
+    """FlatTrainState.state_dict() is torch.optim.AdamW's format in the reference's group order (runs/_helper.py:84-107),
+    keyed by name as well: a reference checkpoint's `optimizer` entry (trainer.py:282-299) resumes here, a changed arena
+    layout cannot misplace moments, and a mismatched entry is refused."""
+    import pytest
+    from fod_b200.optim import FlatTrainState
+
+    def make():
+        torch.manual_seed(0)
+        return torch.nn.ModuleDict({"backbone": torch.nn.Linear(5, 3), "head": torch.nn.Linear(3, 7), "z": torch.nn.Linear(7, 2)})
+
+    ref = make()
+    named = list(ref.named_parameters())
+    opt = torch.optim.AdamW([{"params": [p for n, p in named if "backbone" not in n]},
+                             {"params": [p for n, p in named if "backbone" in n], "lr": 1e-5}], lr=1e-4, weight_decay=1e-4)
+    for _ in range(3):
+        opt.zero_grad()
+        ref["z"](ref["head"](ref["backbone"](torch.ones(2, 5)))).sum().backward()
+        opt.step()
+    sd_ref = opt.state_dict()
+    net = make()
+    flat = FlatTrainState(net, lr=3e-4, lr_backbone=3e-5, bucket_mb=1e-5)
+    flat.load_state_dict(sd_ref)  # torch's own format, no names: the reference's group order
+    assert float(flat.state[2]) == 3.0 and flat.group_lr == [1e-4, 1e-5]
+    idx = 0
+    for grp in (False, True):
+        for n, p in net.named_parameters():
+            if ("backbone" in n) == grp:
+                o = flat.reducer.offset[p]
+                assert torch.equal(flat.exp_avg[o:o + p.numel()].view_as(p), sd_ref["state"][idx]["exp_avg"]), n
+                assert torch.equal(flat.exp_avg_sq[o:o + p.numel()].view_as(p), sd_ref["state"][idx]["exp_avg_sq"]), n
+                idx += 1
+    mine = flat.state_dict()
+    assert mine["param_names"][-2:] == ["backbone.weight", "backbone.bias"] and len(mine["state"]) == 6
+    fresh = torch.optim.AdamW([{"params": [p for n, p in named if "backbone" not in n]},
+                               {"params": [p for n, p in named if "backbone" in n]}])
+    fresh.load_state_dict({k: v for k, v in mine.items() if k != "param_names"})  # torch accepts it back
+    assert torch.equal(fresh.state_dict()["state"][4]["exp_avg"], sd_ref["state"][4]["exp_avg"])
+    net2 = make()
+    flat2 = FlatTrainState(net2, bucket_mb=64.0)  # another bucket layout: names, not offsets, place the moments
+    flat2.load_state_dict(mine)
+    w = net2["z"].weight
+    o = flat2.reducer.offset[w]
+    assert torch.equal(flat2.exp_avg[o:o + w.numel()].view_as(w), sd_ref["state"][2]["exp_avg"])
+    bad = {**mine, "state": {**mine["state"], 0: {**mine["state"][0], "exp_avg": torch.zeros(3, 3)}}}
+    with pytest.raises(ValueError):
+        flat2.load_state_dict(bad)

@@ -82,10 +82,17 @@ def _worker(rank, world, port, out):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from fod_b200.od_map import ApAccumulator
     gold = torch.load(os.path.join(GOLDEN, "ap_aggregate_4x3.pt"), weights_only=False)
+    from fod_b200 import dist as D
     acc = ApAccumulator(distributed=True)
+    merged_live, separate = [], []
     for step in range(2):  # rank r owns iterations r and r + 2
-        acc.add(gold["iterations"][rank + 2 * step]["stuffs"])
-    out[rank] = {"tensors": acc.tensors(), "ap": acc.aggregate()}
+        stats = {"labels": torch.tensor(1.0 + rank + 10 * step), "box_l1": torch.tensor(0.25 * rank),
+                 "box_giou": torch.tensor(3.0), "cardinality": torch.tensor(float(step)), "class_error": torch.tensor(50.0 - rank)}
+        acc.add(gold["iterations"][rank + 2 * step]["stuffs"], stats)
+        merged_live.append({k: float(v) for k, v in acc.last_stats_device.items()})
+        separate.append({k: float(v) for k, v in D.reduce_stats(stats).items()})  # the reference's own all-reduce
+    out[rank] = {"tensors": acc.tensors(), "ap": acc.aggregate(), "stats": acc.stats_history(), "live": merged_live,
+                 "separate": separate}
     dist.destroy_process_group()
 
 
@@ -105,3 +112,7 @@ def test_accumulator_two_ranks_gloo():
             assert torch.equal(got, w)
         for k, v in gold["ap"].items():
             assert _same(out[r]["ap"][k], v, 1e-6), k
+        # the 5 logged scalars rode in the same packed gather: their mean over ranks equals what the
+        # reference's separate all-reduce (utils/distributed.py:63-75) gives, live on the device and in the host history
+        assert out[r]["stats"] == out[r]["live"] == out[r]["separate"]
+        assert out[r]["stats"][1] == {"labels": 11.5, "box_l1": 0.125, "box_giou": 3.0, "cardinality": 1.0, "class_error": 49.5}

@@ -140,6 +140,8 @@ def test_graph_replayed_training_follows_the_eager_trajectory(ref_state_dict):
     graph, ok_g = run(True)
     print("eager", [round(x, 3) for x in eager[::4]], "graph", [round(x, 3) for x in graph[::4]])
     assert ok_e and ok_g and all(l == l for l in graph)
-    # capture consumes one extra step (the captured launch itself is not executed), so compare with a one-step tolerance
+    # the warm-up step of the capture is rolled back (parameters, moments, step counter): both runs start from the same
+    # state, so the first losses agree and the trajectories stay together
+    assert abs(graph[0] - eager[0]) < 2e-3 * abs(eager[0]), (graph[0], eager[0])
     assert graph[-1] < 0.9 * graph[0] and eager[-1] < 0.9 * eager[0], "both must make progress"
     assert abs(graph[-1] - eager[-1]) < 0.15 * abs(eager[-1]), (graph[-1], eager[-1])
