@@ -205,6 +205,8 @@ def run_cuda(args):
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    # utils/distributed.py:58-59: the reference enables cuDNN autotuning for its (static-shape) convolutions
+    torch.backends.cudnn.benchmark = bool(args.cudnn_benchmark)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     detr_args = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
@@ -341,7 +343,7 @@ def run_cuda(args):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "parallelism": "dp%d" % world,
                        "l2": "no explicit flush: one step streams >10 GB of activations through the 126 MB L2",
-                       "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": 0.0, "cuda_graph": use_graph,
+                       "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": 0.0, "cuda_graph": use_graph, "cudnn_benchmark": bool(args.cudnn_benchmark),
                        "optimizer": "fused flat clip+AdamW (fod_flat_adamw_step)" if flat is not None else "torch fused AdamW",
                        "grad_allreduce": ("bucketed NCCL AVG, %g MB fp32 buckets, side stream inside the graph" % args.bucket_mb) if world > 1 else None},
             "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
@@ -426,6 +428,7 @@ def main():
     ap.add_argument("--wgrad-stream", type=int, default=1, help="1: weight/bias gradient kernels on a second stream")
     ap.add_argument("--flat-grads", type=int, default=0, help="1: use the flat-bucket gradient path at N=1 too")
     ap.add_argument("--bucket-mb", type=float, default=32.0)
+    ap.add_argument("--cudnn-benchmark", type=int, default=1, help="torch.backends.cudnn.benchmark, as the reference sets it")
     ap.add_argument("--profiler-range", type=int, default=0, help="1: cudaProfilerStart/Stop around the timed steps (for ncu)")
     args = ap.parse_args()
     if args.stage2:

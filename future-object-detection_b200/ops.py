@@ -216,8 +216,9 @@ def add_ln_fwd(x, gamma, beta, eps=1e-5, bcast=None, rows_per_group=0, save=Fals
         _chk_bf16(bcast, "add_ln bcast")
         assert bcast.is_contiguous() and bcast.numel() * rows_per_group == x.numel()
     _t = prof.begin()
-    call = lambda: L.fod_add_ln_fwd(_p(x), _p(bcast), rows_per_group, _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), M,
-                                    eps, _stream())
+    # the replay closure holds raw pointers only: a tensor captured here would keep this step's autograd graph alive
+    ptrs = (_p(x), _p(bcast), rows_per_group, _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), M, eps)
+    call = lambda: L.fod_add_ln_fwd(*ptrs, _stream())
     lib.check(call(), "fod_add_ln_fwd")
     prof.end(_t, "add_ln_fwd_%d" % M, 0.0, 1024.0 * M, replay=call if _t is not None else None,
              keep=(x, bcast, gamma, beta, y, mean, rstd))
@@ -235,8 +236,9 @@ def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows
     M = pre.numel() // 256
     dz = torch.empty_like(pre)
     _t = prof.begin()
-    call = lambda: L.fod_ln_bwd(_p(dy), _p(dy2), _p(pre), _p(bcast), rows_per_group, _p(mean), _p(rstd), _p(gamma), _p(dz),
-                                _p(dgamma), _p(dbeta), _p(dzsum), M, _stream())
+    ptrs = (_p(dy), _p(dy2), _p(pre), _p(bcast), rows_per_group, _p(mean), _p(rstd), _p(gamma), _p(dz), _p(dgamma),
+            _p(dbeta), _p(dzsum), M)
+    call = lambda: L.fod_ln_bwd(*ptrs, _stream())
     lib.check(call(), "fod_ln_bwd")
     prof.end(_t, "ln_bwd_%d" % M, 0.0, 1536.0 * M, replay=call if _t is not None else None,
              keep=(dy, dy2, pre, bcast, mean, rstd, gamma, dz, dgamma, dbeta, dzsum))
@@ -254,7 +256,8 @@ def colsum(x, rows_per_group=0, out=None):
     if out is None:
         out = torch.zeros((M // rpg, N), dtype=torch.float32, device=x.device)
     _t = prof.begin()
-    call = lambda: L.fod_colsum(_p(x), x.stride(0), _p(out), M, N, rpg, _stream())
+    ptrs = (_p(x), x.stride(0), _p(out), M, N, rpg)
+    call = lambda: L.fod_colsum(*ptrs, _stream())
     lib.check(call(), "fod_colsum")
     prof.end(_t, "colsum_%dx%d" % (M, N), 0.0, 2.0 * M * N, replay=call if _t is not None else None, keep=(x, out))
     LAUNCH_COUNTS["colsum_kernel"] += 1
@@ -270,7 +273,8 @@ def maxpool3x3s2_nhwc(x):
     oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
     y = torch.empty((n, c, oh, ow), dtype=BF16, device=x.device, memory_format=torch.channels_last)
     _t = prof.begin()
-    call = lambda: L.fod_maxpool3x3s2_nhwc(_p(x), _p(y), n, h, w, c, _stream())
+    ptrs = (_p(x), _p(y), n, h, w, c)
+    call = lambda: L.fod_maxpool3x3s2_nhwc(*ptrs, _stream())
     lib.check(call(), "fod_maxpool3x3s2_nhwc")
     prof.end(_t, "maxpool_%dx%dx%d" % (n, h, w), 0.0, 2.0 * (x.numel() + y.numel()), replay=call if _t is not None else None,
              keep=(x, y))
@@ -335,7 +339,8 @@ class ConvFoldTable:
     def run(self):
         L = lib.load()
         _t = prof.begin()
-        call = lambda: L.fod_fold_conv_weights(_p(self.table), len(self.outs), self.max_elems, _stream())
+        ptrs = (_p(self.table), len(self.outs), self.max_elems)
+        call = lambda: L.fod_fold_conv_weights(*ptrs, _stream())
         lib.check(call(), "fod_fold_conv_weights")
         prof.end(_t, "fold_conv_weights", 0.0, self.bytes, replay=call if _t is not None else None, keep=(self.table,))
         LAUNCH_COUNTS["fold_conv_weights_kernel"] += 1
