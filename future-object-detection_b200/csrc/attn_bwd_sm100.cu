@@ -488,6 +488,18 @@ extern "C" int fod_attn_bwd(const fod_attn_bwd_args* g, void* stream) {
                              two ? a->ldq2 : 8, two ? a->ldk2 : 8, two ? a->bsq2 : 0, two ? a->bsk2 : 0};
     for (long long x : chk)
         if (x % 8) return fod_fail(FOD_E_ARG, "attn_bwd: strides must be multiples of 8 elements");
+    {
+        // one fused kernel (attn_bwd_fused_sm100.cu) wherever dQ of all query tiles fits TMEM; FOD_ATTN_BWD_FUSED=0
+        // (or mode 1) keeps the two-kernel path
+        const long long gchk[] = {g->ld_dq, g->ld_dk};
+        for (long long x : gchk)
+            if (x % 8) return fod_fail(FOD_E_ARG, "attn_bwd: gradient strides must be multiples of 8");
+        int mode = g->mode;
+        if (mode < 0 || mode > 2) return fod_fail(FOD_E_ARG, "attn_bwd: mode must be 0, 1 or 2");
+        if (mode == 2 && !attn_bwd_fused_supported(g)) return fod_fail(FOD_E_ARG, "attn_bwd: sequence too long for the fused kernel");
+        if (mode == 0) mode = (fod_env_int("FOD_ATTN_BWD_FUSED", 1) && attn_bwd_fused_supported(g)) ? 2 : 1;
+        if (mode == 2) return launch_attn_bwd_fused(g, reinterpret_cast<cudaStream_t>(stream));
+    }
     const int rowlen = a->H * AB_D;
     CUtensorMap tq1, tk1, tq2, tk2, tv, tdo;
     if (make_seq_tmap_b(&tq1, a->q1, rowlen, a->Lq, a->B, a->ldq1, a->bsq1)) return fod_fail(FOD_E_TMAP, "attn_bwd: q1");

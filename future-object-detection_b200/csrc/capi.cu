@@ -25,7 +25,11 @@ bool fod_pdl_enabled() {
     }();
     return on != 0;
 }
+int fod_env_int(const char* name, int dflt) {
+    const char* e = getenv(name);
+    return e ? atoi(e) : dflt;
+}
 }  // namespace fod
 
-extern "C" int fod_version(void) { return 7; }
+extern "C" int fod_version(void) { return 8; }
 extern "C" const char* fod_last_error(void) { return fod::g_err; }

@@ -6,6 +6,7 @@
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 #include <vector>
 #include "../../include/fod_b200.h"
 
@@ -241,6 +242,95 @@ static void test_attn(int B, int H, int Lq, int Lk, int two, int k2_bcast, float
     cudaFree(lse); cudaFree(o);
 }
 
+// Attention backward: the fused single kernel (mode 2) against the two-kernel path (mode 1) on the same inputs, plus
+// timings of both.  The two paths share no code below the argument checks, so agreement to bf16 rounding pins both.
+static void test_attn_bwd(int B, int H, int Lq, int Lk, int two, int k2_bcast) {
+    const int C = H * 32;
+    __nv_bfloat16* q1 = dev_bf16((size_t)B * Lq * C, 1.5f);
+    __nv_bfloat16* k1 = dev_bf16((size_t)B * Lk * C, 1.5f);
+    __nv_bfloat16* q2 = two ? dev_bf16((size_t)B * Lq * C, 1.5f) : nullptr;
+    __nv_bfloat16* k2 = two ? dev_bf16((size_t)(k2_bcast ? 1 : B) * Lk * C, 1.5f) : nullptr;
+    __nv_bfloat16* v = dev_bf16((size_t)B * Lk * C, 1.f);
+    __nv_bfloat16* dout = dev_bf16((size_t)B * Lq * C, 1.f);
+    __nv_bfloat16* o;
+    float *lse, *delta[2];
+    CK(cudaMalloc(&o, (size_t)B * Lq * C * 2));
+    CK(cudaMalloc(&lse, (size_t)B * H * Lq * 4));
+    const size_t nq = (size_t)B * Lq * C, nk = (size_t)B * Lk * C;
+    __nv_bfloat16* g[2][5];  // dq1, dq2, dk1, dk2, dv per mode
+    for (int m = 0; m < 2; ++m) {
+        CK(cudaMalloc(&delta[m], (size_t)B * H * Lq * 4));
+        for (int t = 0; t < 5; ++t) {
+            const size_t n = (t < 2 ? nq : nk);
+            CK(cudaMalloc(&g[m][t], n * 2));
+            CK(cudaMemset(g[m][t], 0xff, n * 2));
+        }
+    }
+    const float scale = two ? 0.125f : 0.17677669f;
+    fod_attn_bwd_args a = {};
+    a.fwd.q1 = q1; a.fwd.k1 = k1; a.fwd.q2 = q2; a.fwd.k2 = k2; a.fwd.v = v; a.fwd.out = o; a.fwd.lse = lse;
+    a.fwd.ldq1 = a.fwd.ldk1 = a.fwd.ldq2 = a.fwd.ldk2 = a.fwd.ldv = a.fwd.ldo = C;
+    a.fwd.bsq1 = a.fwd.bsq2 = a.fwd.bso = (int64_t)Lq * C;
+    a.fwd.bsk1 = a.fwd.bsv = (int64_t)Lk * C;
+    a.fwd.bsk2 = k2_bcast ? 0 : (int64_t)Lk * C;
+    a.fwd.B = B; a.fwd.H = H; a.fwd.Lq = Lq; a.fwd.Lk = Lk; a.fwd.scale = scale;
+    a.dout = dout; a.lddo = C; a.bsdo = (int64_t)Lq * C;
+    int rc = fod_attn_fwd(&a.fwd, nullptr);
+    if (rc) { printf("fod_attn_fwd rc=%d (%s)\n", rc, fod_last_error()); g_fail = 1; return; }
+    float ms[2] = {0, 0};
+    for (int m = 0; m < 2; ++m) {
+        a.mode = m + 1;
+        a.delta = delta[m];
+        a.dq1 = g[m][0]; a.dq2 = two ? g[m][1] : nullptr; a.dk1 = g[m][2]; a.dk2 = two ? g[m][3] : nullptr; a.dv = g[m][4];
+        rc = fod_attn_bwd(&a, nullptr);
+        if (rc) { printf("fod_attn_bwd mode %d rc=%d (%s)\n", m + 1, rc, fod_last_error()); g_fail = 1; return; }
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("attn_bwd mode %d: %s\n", m + 1, cudaGetErrorString(e)); exit(2); }
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0); cudaEventCreate(&e1);
+        cudaEventRecord(e0);
+        for (int i = 0; i < 10; ++i) fod_attn_bwd(&a, nullptr);
+        cudaEventRecord(e1);
+        CK(cudaDeviceSynchronize());
+        cudaEventElapsedTime(&ms[m], e0, e1); ms[m] /= 10;
+    }
+    double worst = 0;
+    const char* names[5] = {"dq1", "dq2", "dk1", "dk2", "dv"};
+    char detail[256] = "";
+    for (int t = 0; t < 5; ++t) {
+        if (!two && (t == 1 || t == 3)) continue;
+        const size_t n = (t < 2 ? nq : nk);
+        std::vector<__nv_bfloat16> h0(n), h1(n);
+        CK(cudaMemcpy(h0.data(), g[0][t], n * 2, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(h1.data(), g[1][t], n * 2, cudaMemcpyDeviceToHost));
+        double num = 0, den = 0;
+        for (size_t i = 0; i < n; ++i) {
+            const double x = __bfloat162float(h0[i]), y = __bfloat162float(h1[i]);
+            double d = y - x;
+            if (!(d == d)) d = 1e6;
+            num += d * d; den += x * x;
+        }
+        const double rel = sqrt(num / (den > 0 ? den : 1));
+        worst = fmax(worst, rel);
+        snprintf(detail + strlen(detail), sizeof(detail) - strlen(detail), " %s %.2g", names[t], rel);
+    }
+    {
+        std::vector<float> d0((size_t)B * H * Lq), d1(d0.size());
+        CK(cudaMemcpy(d0.data(), delta[0], d0.size() * 4, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(d1.data(), delta[1], d1.size() * 4, cudaMemcpyDeviceToHost));
+        double dm = 0;
+        for (size_t i = 0; i < d0.size(); ++i) dm = fmax(dm, fabs(d0[i] - d1[i]));
+        snprintf(detail + strlen(detail), sizeof(detail) - strlen(detail), " delta %.2g", dm);
+        if (dm > 1e-3) worst = fmax(worst, 1.0);
+    }
+    char name[320];
+    snprintf(name, sizeof name, "attn_bwd B%d H%d Lq%d Lk%d parts%d bc%d two-kernel %.3f ms | fused vs two-kernel rel-L2:%s", B, H, Lq, Lk,
+             two + 1, k2_bcast, ms[0], detail);
+    report(name, worst, 1e-2, ms[1], (two ? 16.0 : 10.0) * B * H * (double)Lq * Lk * 32);
+    cudaFree(q1); cudaFree(k1); cudaFree(q2); cudaFree(k2); cudaFree(v); cudaFree(dout); cudaFree(o); cudaFree(lse);
+    for (int m = 0; m < 2; ++m) { cudaFree(delta[m]); for (int t = 0; t < 5; ++t) cudaFree(g[m][t]); }
+}
+
 int main(int argc, char** argv) {
     int which = argc > 1 ? atoi(argv[1]) : 3;
     printf("fod_b200 selftest, abi %d\n", fod_version());
@@ -265,6 +355,18 @@ int main(int argc, char** argv) {
         test_linear(22400, 768, 256, 1, 1, 350, 0, 0, 0);
         test_linear(22400, 2048, 256, 1, 0, 0, 1, 0, 0);
         test_linear(4096, 768, 256, 1, 1, 128, 0, 0, 0);
+    }
+    if (which & 8) {
+        test_attn_bwd(1, 1, 128, 128, 0, 0);
+        test_attn_bwd(2, 8, 350, 350, 0, 0);
+        test_attn_bwd(2, 8, 128, 350, 1, 1);
+        test_attn_bwd(2, 8, 200, 300, 1, 0);
+        test_attn_bwd(3, 8, 768, 129, 0, 0);
+        test_attn_bwd(16, 8, 350, 350, 0, 0);
+        test_attn_bwd(64, 8, 350, 350, 0, 0);
+        test_attn_bwd(32, 8, 128, 350, 1, 1);
+        test_attn_bwd(32, 8, 128, 128, 0, 0);
+        test_attn_bwd(16, 8, 700, 700, 0, 0);
     }
     if (which & 2) {
         test_attn(1, 1, 128, 128, 0, 0);

@@ -152,8 +152,19 @@ def attn_fwd(q1, k1, v, scale, heads=8, q2=None, k2=None, batch=None):
     return out, lse
 
 
-def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=None):
+def attn_bwd_is_fused(Lq, two_parts, mode=0):
+    """Which kernel path fod_attn_bwd takes (mirrors csrc/attn_bwd_sm100.cu): the one-kernel backward needs the dQ
+    accumulators of every 128-query tile resident in TMEM."""
+    import os
+    fits = (Lq + 127) // 128 <= (2 if two_parts else 6)
+    if mode:
+        return mode == 2
+    return fits and int(os.environ.get("FOD_ATTN_BWD_FUSED", "1")) != 0
+
+
+def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=None, mode=0):
     """Flash attention backward -> (dq1, dk1, dv, dq2, dk2), (B, L, heads*32) bf16 (dq2/dk2 None if unused).
+    mode: 0 library picks, 1 two-kernel path, 2 fused single kernel (include/fod_b200.h).
 
     fused="qkv": dq1/dk1/dv are column slices of ONE (B, L, 3*heads*32) tensor (self-attention on a fused projection);
     fused="kv": dk1/dv are slices of one (B, Lk, 2*heads*32) tensor.  The kernels write the slices in place."""
@@ -188,6 +199,7 @@ def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=
         dq2 = torch.empty((B, Lq, Cw), dtype=BF16, device=dev)
         dk2 = torch.empty((B, Lk, Cw), dtype=BF16, device=dev)
         g.dq2, g.dk2 = _p(dq2), _p(dk2)
+    g.mode = mode
     _t = prof.begin()
     lib.check(L.fod_attn_bwd(C.byref(g), _stream()), "fod_attn_bwd")
     parts = 2 if q2 is not None else 1
@@ -195,9 +207,12 @@ def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=
              2.0 * Cw * (B * Lq * (2 * parts + 2) + B * Lk * (2 * parts + 2)),
              replay=(lambda: L.fod_attn_bwd(C.byref(g), _stream())) if _t is not None else None,
              keep=(q1, k1, v, q2, k2, out, lse, dout, delta, dq1, dk1, dv, dq2, dk2))
-    LAUNCH_COUNTS["attn_delta_kernel"] += 1
-    LAUNCH_COUNTS["attn_bwd_dq_kernel"] += 1
-    LAUNCH_COUNTS["attn_bwd_dkdv_kernel"] += 1
+    if attn_bwd_is_fused(Lq, q2 is not None, mode):
+        LAUNCH_COUNTS["attn_bwd_fused_kernel"] += 1
+    else:
+        LAUNCH_COUNTS["attn_delta_kernel"] += 1
+        LAUNCH_COUNTS["attn_bwd_dq_kernel"] += 1
+        LAUNCH_COUNTS["attn_bwd_dkdv_kernel"] += 1
     return dq1, dk1, dv, dq2, dk2
 
 
@@ -354,8 +369,11 @@ def conv_wgrad_unfold(dwq, scale, grad):
     assert dwq.dtype == BF16 and dwq.shape == grad.shape and dwq.permute(0, 2, 3, 1).is_contiguous()
     assert grad.dtype == torch.float32 and grad.is_contiguous() and scale.dtype == torch.float32
     _t = prof.begin()
-    lib.check(L.fod_conv_wgrad_unfold(_p(dwq), _p(scale), _p(grad), O, I, KH * KW, _stream()), "fod_conv_wgrad_unfold")
-    prof.end(_t, "conv_wgrad_unfold", 0.0, 10.0 * grad.numel())
+    ptrs = (_p(dwq), _p(scale), _p(grad), O, I, KH * KW)
+    call = lambda: L.fod_conv_wgrad_unfold(*ptrs, _stream())
+    lib.check(call(), "fod_conv_wgrad_unfold")
+    prof.end(_t, "conv_wgrad_unfold_%dx%dx%d" % (O, I, KH * KW), 0.0, 10.0 * grad.numel(),
+             replay=call if _t is not None else None, keep=(dwq, scale, grad))
     LAUNCH_COUNTS["conv_wgrad_unfold_kernel"] += 1
 
 

@@ -109,6 +109,10 @@ typedef struct fod_attn_bwd_args {
     void *dq1, *dq2, *dk1, *dk2, *dv;
     int64_t ld_dq;       /* row stride of dq1 (0 = H*32); batch stride = Lq*ld_dq.  dq2 is always dense */
     int64_t ld_dk;       /* row stride of dk1 and dv (0 = H*32); batch stride = Lk*ld_dk.  dk2 is always dense */
+    int32_t mode;        /* 0: the library picks; 1: two kernels (dQ per query tile, dK/dV per key tile: S and dP are
+                            recomputed twice, any length); 2: ONE fused kernel, one recompute, dQ of every query tile
+                            resident in TMEM — needs Lq <= 768 (one part) / Lq <= 256 (two parts) */
+    int32_t pad0;
 } fod_attn_bwd_args;
 int fod_attn_bwd(const fod_attn_bwd_args* a, void* stream);
 

@@ -131,7 +131,7 @@ def test_hot_kernels_are_tcgen05_tma_code():
             counts[fn]["ldtm"] += "LDTM" in line
             counts[fn]["tma"] += "UTMALDG" in line
     families = {"gemm_bf16_kernel": True, "attn_fwd_kernel": True, "attn_bwd_dq_kernel": True,
-                "attn_bwd_dkdv_kernel": True, "stem_conv7x7s2_kernel": False}  # value: operands arrive by TMA
+                "attn_bwd_dkdv_kernel": True, "attn_bwd_fused_kernel": True, "stem_conv7x7s2_kernel": False}  # value: operands arrive by TMA
     for fam, wants_tma in families.items():
         kernels = {k: v for k, v in counts.items() if fam in k}
         assert kernels, fam

@@ -109,7 +109,9 @@ def test_gemm_unaligned_output_falls_back_to_scalar_stores():
                                                  (2, 128, 128, False, False), (1, 700, 700, False, False),
                                                  (2, 100, 3, False, False), (2, 128, 1400, True, True),
                                                  (2, 1400, 1400, False, False), (1, 2800, 2800, False, False),
-                                                 (1, 1400, 128, False, False)])
+                                                 (1, 1400, 128, False, False), (3, 768, 350, False, False),
+                                                 (2, 129, 257, False, False), (2, 256, 350, True, False),
+                                                 (16, 350, 350, False, False)])
 def test_attention_forward_backward(B, Lq, Lk, two, bcast):
     from fod_b200 import ops
     H, C = 8, 256
@@ -133,13 +135,17 @@ def test_attention_forward_backward(B, Lq, Lk, two, bcast):
     _close(lse, torch.logsumexp(s, -1), tol=1e-3, what="lse")
     dout = _rnd(B, Lq, C, seed=9)
     ref.backward(dout.float())
-    dq1, dk1, dv, dq2, dk2 = ops.attn_bwd(q1, k1, v, out, lse, dout, scale, H, q2=q2, k2=k2)
-    _close(dq1, leaves[0].grad, what="dq1")
-    _close(dk1, leaves[1].grad, what="dk1")
-    _close(dv, leaves[2].grad, what="dv")
-    if two:
-        _close(dq2, leaves[3].grad, what="dq2")
-        _close(dk2.sum(0) if bcast else dk2, leaves[4].grad, what="dk2")
+    # both backward paths: two kernels (any length) and the fused single kernel (dQ resident in TMEM) where it applies
+    modes = [1] + ([2] if ops.attn_bwd_is_fused(Lq, two, 0) else [])
+    assert ops.attn_bwd_is_fused(350, False) and not ops.attn_bwd_is_fused(1400, False)
+    for mode in modes:
+        dq1, dk1, dv, dq2, dk2 = ops.attn_bwd(q1, k1, v, out, lse, dout, scale, H, q2=q2, k2=k2, mode=mode)
+        _close(dq1, leaves[0].grad, what="dq1 mode %d" % mode)
+        _close(dk1, leaves[1].grad, what="dk1 mode %d" % mode)
+        _close(dv, leaves[2].grad, what="dv mode %d" % mode)
+        if two:
+            _close(dq2, leaves[3].grad, what="dq2 mode %d" % mode)
+            _close(dk2.sum(0) if bcast else dk2, leaves[4].grad, what="dk2 mode %d" % mode)
 
 
 def test_attention_fused_gradient_layouts():

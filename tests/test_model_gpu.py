@@ -138,7 +138,7 @@ def test_backward_matches_reference_gradients(model, ref_state_dict):
     from conftest import GOLDEN
     with open(os.path.join(GOLDEN, "ref_autocast_floor.json")) as f:
         own = json.load(f)["g1_b2_l3_128x160"]
-    GATE = 1.5
+    GATE = 1.35  # measured on the B200: worst tensor 1.23x its reference-autocast error, global 0.053 vs 0.054
     params = dict(model.named_parameters())
     small = {k: g for k, g in gold["grads_small"].items()}
     ref_all = torch.cat([g.flatten().double() for g in small.values()])

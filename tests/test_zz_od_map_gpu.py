@@ -19,7 +19,7 @@ def test_accumulator_and_aggregation_on_the_device():
         with torch.cuda.stream(side):  # the producer is not the default stream: the copy must order after it
             stuffs = [t.to(DEV, non_blocking=True) for t in it["stuffs"]]
             acc.add(stuffs)
-    assert all(s.is_pinned() for s in acc._slabs) and all(e is not None for _, e, _ in acc._items)
+    assert all(s.is_pinned() for s in acc._slabs) and all(it[1] is not None for it in acc._items)
     for got, want in zip(acc.tensors(), _trainer_concat(gold)):
         assert got.dtype == want.dtype and torch.equal(got, want)
     for ap in (acc.aggregate(device=DEV), aggregate_mean_average_precision(*_trainer_concat(gold), device=DEV)):
