@@ -10,7 +10,8 @@
 //                                                           dQ and as MN-major A operand for dV / dK)
 //   dQ of EVERY query tile stays resident in TMEM for the whole CTA (32 columns per tile and part), dK / dV of the
 //   current key tile likewise; they are read out once.  No atomics, no second pass over S: 10·N·S²·D flop executed.
-//   delta = rowsum(dO ⊙ O) is computed by the softmax warps during the first key tile (no separate kernel).
+//   delta = rowsum(dO ⊙ O) is computed by the softmax warps in a pre-pass that overlaps the first loads (no separate
+//   kernel).
 //
 // TMEM: S 128 + dP 128 + dV 32 + dK 32·NP + dQ 32·NP·nqt  <= 512 columns  =>  nqt <= 6 (one part), nqt <= 2 (two parts).
 // Longer sequences take the two-kernel path of attn_bwd_sm100.cu.
@@ -21,7 +22,22 @@
 #include "sm100_ptx.cuh"
 #include "tmap.h"
 
+#ifndef FOD_AF_TRACE
+#define FOD_AF_TRACE 0
+#endif
+
 namespace fod {
+
+#if FOD_AF_TRACE
+// Timeline probe (debug builds only): clock64 stamps of CTA 0 — [role][tile][event]
+__device__ long long g_af_trace[3 * 16 * 8];
+#define AF_STAMP(role, tile, ev)                                                                   \
+    do {                                                                                           \
+        if (blockIdx.x == 0 && blockIdx.y == 0 && (tile) < 16) g_af_trace[((role) * 16 + (tile)) * 8 + (ev)] = clock64(); \
+    } while (0)
+#else
+#define AF_STAMP(role, tile, ev) do {} while (0)
+#endif
 
 constexpr int AF_T = 128;
 constexpr int AF_D = 32;
@@ -36,12 +52,18 @@ struct FusedBwdSmem {
     static constexpr int kMaxQT = NP == 1 ? 6 : 2;
     static constexpr int kK = 0;                            // K parts, 2 stages
     static constexpr int kV = kK + 2 * NP * AF_TILE;        // V, 2 stages
-    static constexpr int kQ = kV + 2 * AF_TILE;             // Q parts, 2 stages
-    static constexpr int kDO = kQ + 2 * NP * AF_TILE;       // dO, 2 stages
-    static constexpr int kP = kDO + 2 * AF_TILE;            // P tile
-    static constexpr int kDS = kP + AF_PT;                  // dS tile
-    static constexpr int kStat = kDS + AF_PT;               // [2 halves][lse2 | delta][kMaxQT*128] fp32
-    static constexpr int kBars = kStat + 2 * 2 * kMaxQT * AF_T * 4;
+    static constexpr int kQS = 2;                           // Q / dO stages
+    static constexpr int kQ = kV + 2 * AF_TILE;             // Q parts, kQS stages
+    static constexpr int kDO = kQ + kQS * NP * AF_TILE;     // dO, kQS stages
+    // one-part attention double-buffers the P / dS tiles: the softmax warps of tile t only wait for the gradient MMAs
+    // of tile t-2 (those MMAs are operand-fetch bound, ~65 clk each whatever their width: 24 of them outlast the
+    // exponentials of the next tile's first half); with two parts the second buffer does not fit
+    static constexpr int kPBuf = NP == 1 ? 2 : 1;
+    static constexpr int kP = kDO + kQS * AF_TILE;          // P tiles
+    static constexpr int kDS = kP + kPBuf * AF_PT;          // dS tiles
+    static constexpr int kOut = kDS + kPBuf * AF_PT;        // 3 staging tiles [128][32] bf16 of the TMA gradient stores
+    static constexpr int kStat = kOut + 3 * AF_TILE;        // [lse2 | scale*delta][kMaxQT*128] fp32
+    static constexpr int kBars = kStat + 2 * kMaxQT * AF_T * 4;
     static constexpr int kTotal = kBars + 256 + 1024;       // + alignment slack
 };
 
@@ -49,7 +71,8 @@ struct AttnBwdFusedParams {
     const float* lse;            // (B,H,Lq)
     float* delta;                // (B,H,Lq) optional output (kept for API parity with the two-kernel path)
     const __nv_bfloat16* out;    // O (B,Lq,H*32)
-    long long ldo, bso;
+    const __nv_bfloat16* dout;   // dO (B,Lq,H*32)
+    long long ldo, bso, lddo, bsdo;
     __nv_bfloat16 *dq1, *dq2, *dk1, *dk2, *dv;
     long long ld_dq, ld_dk;
     int B, H, Lq, Lk;
@@ -57,15 +80,29 @@ struct AttnBwdFusedParams {
     float scale;
 };
 
-__device__ __forceinline__ void af_store_row32(__nv_bfloat16* dst, const uint32_t (&v)[32]) {
+// One [128][32] fp32 accumulator tile, TMEM -> bf16 -> swizzled staging tile -> TMA store.  Executed by the four warps
+// of a `half` (128 threads, named barrier 2 + half); `issuer` is the one thread of the half that owns its bulk groups.
+__device__ __forceinline__ void af_store_tile(uint32_t taddr_lane, uint8_t* slot, const CUtensorMap* tm, int row0, int row,
+                                              int half, bool issuer, int h, int b) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(taddr_lane, v);
+    if (issuer) bulk_wait_read0();  // the previous store out of a slot of this half has finished reading it
+    asm volatile("bar.sync %0, 128;" ::"r"(2 + half) : "memory");
+    tmem_ld_wait();
 #pragma unroll
-    for (int q = 0; q < 4; ++q) {
+    for (int c = 0; c < 4; ++c) {
         uint4 u;
-        u.x = pack_bf16x2(__uint_as_float(v[q * 8 + 0]), __uint_as_float(v[q * 8 + 1]));
-        u.y = pack_bf16x2(__uint_as_float(v[q * 8 + 2]), __uint_as_float(v[q * 8 + 3]));
-        u.z = pack_bf16x2(__uint_as_float(v[q * 8 + 4]), __uint_as_float(v[q * 8 + 5]));
-        u.w = pack_bf16x2(__uint_as_float(v[q * 8 + 6]), __uint_as_float(v[q * 8 + 7]));
-        reinterpret_cast<uint4*>(dst)[q] = u;
+        u.x = pack_bf16x2(__uint_as_float(v[c * 8 + 0]), __uint_as_float(v[c * 8 + 1]));
+        u.y = pack_bf16x2(__uint_as_float(v[c * 8 + 2]), __uint_as_float(v[c * 8 + 3]));
+        u.z = pack_bf16x2(__uint_as_float(v[c * 8 + 4]), __uint_as_float(v[c * 8 + 5]));
+        u.w = pack_bf16x2(__uint_as_float(v[c * 8 + 6]), __uint_as_float(v[c * 8 + 7]));
+        *reinterpret_cast<uint4*>(slot + swz_off<64>(row, c)) = u;
+    }
+    fence_proxy_async_smem();
+    asm volatile("bar.sync %0, 128;" ::"r"(2 + half) : "memory");
+    if (issuer) {
+        tma_store_3d(tm, slot, h * AF_D, row0, b);
+        bulk_commit();
     }
 }
 
@@ -74,24 +111,29 @@ __global__ void __launch_bounds__(AF_THREADS, 1)
 attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant__ CUtensorMap tmK1,
                       const __grid_constant__ CUtensorMap tmQ2, const __grid_constant__ CUtensorMap tmK2,
                       const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
-                      const AttnBwdFusedParams p) {
+                      const __grid_constant__ CUtensorMap tmDQ1, const __grid_constant__ CUtensorMap tmDQ2,
+                      const __grid_constant__ CUtensorMap tmDK1, const __grid_constant__ CUtensorMap tmDK2,
+                      const __grid_constant__ CUtensorMap tmDV, const AttnBwdFusedParams p) {
     using L = FusedBwdSmem<NP>;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBars);
     uint64_t* kv_full = bars + 0;    // [2]
     uint64_t* kv_empty = bars + 2;   // [2]
-    uint64_t* qdo_full = bars + 4;   // [2]
-    uint64_t* qdo_empty = bars + 6;  // [2]
-    uint64_t* s_full = bars + 8;     // S / dP of tile t are complete in TMEM
-    uint64_t* s_free = bars + 9;     // ... and have been copied into registers by all 256 softmax threads
-    uint64_t* p_full = bars + 10;    // P / dS of tile t are in shared memory
-    uint64_t* g_done = bars + 11;    // the gradient MMAs of tile t have retired (P / dS / operand stages reusable)
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
+    uint64_t* qdo_full = bars + 4;   // [kQS <= 3]
+    uint64_t* qdo_empty = bars + 7;  // [kQS <= 3]
+    uint64_t* s_full = bars + 10;    // S / dP of tile t are complete in TMEM
+    uint64_t* s_free = bars + 11;    // ... and have been copied into registers by all 256 softmax threads
+    uint64_t* p_full = bars + 12;    // P / dS of tile t are in shared memory
+    // the gradient MMAs of tile t have retired (P / dS / operand stages reusable): alternates between two barriers, as
+    // a parity wait can only tell the latest phase from the one before and the softmax warps look two tiles back
+    uint64_t* g_done = bars + 13;    // [2]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 15);
     float* stat = reinterpret_cast<float*>(smem + L::kStat);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int h = blockIdx.x, b = blockIdx.y;
+    if (threadIdx.x == 0) AF_STAMP(2, 0, 0);  // kernel entry
     const int nqt = (p.Lq + AF_T - 1) / AF_T;
     const int nkt = (p.Lk + AF_T - 1) / AF_T;
     const int ntiles = nqt * nkt;
@@ -108,6 +150,8 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
         for (int s = 0; s < 2; ++s) {
             mbar_init(kv_full + s, 1);
             mbar_init(kv_empty + s, 1);
+        }
+        for (int s = 0; s < L::kQS; ++s) {
             mbar_init(qdo_full + s, 1);
             mbar_init(qdo_empty + s, 1);
         }
@@ -115,6 +159,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
         mbar_init(s_free, 256);
         mbar_init(p_full, 256);
         mbar_init(g_done, 1);
+        mbar_init(g_done + 1, 1);
         fence_barrier_init();
     }
     if (warp == AF_MMA) tmem_alloc<512>(tmem_slot);
@@ -122,8 +167,10 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    if (threadIdx.x == 0) AF_STAMP(2, 0, 1);  // barriers initialised, TMEM allocated
     pdl_launch_dependents();
     pdl_wait();
+    if (threadIdx.x == 0) AF_STAMP(2, 0, 2);  // predecessor grid complete
     const uint32_t tmem_S = tmem_base, tmem_dP = tmem_base + 128, tmem_dV = tmem_base + 256, tmem_dK = tmem_base + 288;
     const uint32_t tmem_dQ = tmem_dK + NP * AF_D;  // + (i * NP + part) * 32
 
@@ -139,8 +186,8 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
                 if (NP == 2) tma_load_3d(sk + AF_TILE, &tmK2, kv_full + sj, h * AF_D, j * AF_T, b * p.bm_k2);
                 tma_load_3d(smem + L::kV + sj * AF_TILE, &tmV, kv_full + sj, h * AF_D, j * AF_T, b * p.bm_v);
                 for (int i = 0; i < nqt; ++i, ++t) {
-                    const int s = t & 1;
-                    mbar_wait(qdo_empty + s, ((t >> 1) & 1) ^ 1);
+                    const int s = t % L::kQS;
+                    mbar_wait(qdo_empty + s, ((t / L::kQS) & 1) ^ 1);
                     mbar_arrive_expect_tx(qdo_full + s, (NP + 1) * AF_TILE);
                     uint8_t* sq = smem + L::kQ + s * NP * AF_TILE;
                     tma_load_3d(sq, &tmQ1, qdo_full + s, h * AF_D, i * AF_T, b * p.bm_q1);
@@ -154,69 +201,85 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
             constexpr uint32_t idesc_s = umma_idesc_bf16(AF_T, AF_T, 0, 0);   // S, dP: both operands K-major
             constexpr uint32_t idesc_q = umma_idesc_bf16(AF_T, AF_D, 0, 1);   // dQ: A = dS K-major, B = K_j MN-major
             constexpr uint32_t idesc_k = umma_idesc_bf16(AF_T, AF_D, 1, 1);   // dV, dK: A = Pᵀ / dSᵀ (MN-major view)
-            const uint32_t p_addr = smem_u32(smem + L::kP);
-            const uint32_t ds_addr = smem_u32(smem + L::kDS);
+            // Descriptors of stage 0 of every operand buffer, built once; per tile / per instruction they are stepped
+            // with umma_desc_adv (one add each).
+            //   K-major 64-byte rows (SWIZZLE_64B): LBO 16, SBO 512, 16 contraction elements = +32 B
+            //   MN-major B from the same tiles ([row = contraction][32 d]): LBO 4096, SBO 512, 16 rows = +1024 B
+            //   P / dS tile as K-major A (rows = queries, SWIZZLE_128B slabs of 64 keys): LBO 16, SBO 1024, +32 B / +16 KB
+            //   P / dS tile as MN-major A (contraction = query rows): LBO 16 KB (next 64 keys), SBO 1024, 16 rows = +2048 B
+            const uint64_t dK_k = umma_smem_desc(smem_u32(smem + L::kK), 16, 512, 4);
+            const uint64_t dV_k = umma_smem_desc(smem_u32(smem + L::kV), 16, 512, 4);
+            const uint64_t dQ_k = umma_smem_desc(smem_u32(smem + L::kQ), 16, 512, 4);
+            const uint64_t dDO_k = umma_smem_desc(smem_u32(smem + L::kDO), 16, 512, 4);
+            const uint64_t dK_mn = umma_smem_desc(smem_u32(smem + L::kK), 4096, 512, 4);
+            const uint64_t dQ_mn = umma_smem_desc(smem_u32(smem + L::kQ), 4096, 512, 4);
+            const uint64_t dDO_mn = umma_smem_desc(smem_u32(smem + L::kDO), 4096, 512, 4);
+            const uint64_t dP_mn = umma_smem_desc(smem_u32(smem + L::kP), AF_T * 128, 1024, 2);
+            const uint64_t dDS_mn = umma_smem_desc(smem_u32(smem + L::kDS), AF_T * 128, 1024, 2);
+            const uint64_t dDS_k = umma_smem_desc(smem_u32(smem + L::kDS), 16, 1024, 2);
             auto issue_SP = [&](int t) {
                 const int j = t / nqt, i = t - j * nqt;
-                const int sj = j & 1, s = t & 1;
+                const int sj = j & 1, s = t % L::kQS;
                 if (i == 0) mbar_wait(kv_full + sj, (j >> 1) & 1);
-                mbar_wait(qdo_full + s, (t >> 1) & 1);
+                mbar_wait(qdo_full + s, (t / L::kQS) & 1);
                 tc_fence_after();
-                const uint32_t k_addr = smem_u32(smem + L::kK + sj * NP * AF_TILE);
-                const uint32_t v_addr = smem_u32(smem + L::kV + sj * AF_TILE);
-                const uint32_t q_addr = smem_u32(smem + L::kQ + s * NP * AF_TILE);
-                const uint32_t do_addr = smem_u32(smem + L::kDO + s * AF_TILE);
+                AF_STAMP(1, t, 1);
+                const uint64_t k_d = umma_desc_adv(dK_k, sj * NP * AF_TILE), v_d = umma_desc_adv(dV_k, sj * AF_TILE);
+                const uint64_t q_d = umma_desc_adv(dQ_k, s * NP * AF_TILE), do_d = umma_desc_adv(dDO_k, s * AF_TILE);
 #pragma unroll
                 for (int part = 0; part < NP; ++part)
 #pragma unroll
                     for (int k = 0; k < AF_D / 16; ++k)
-                        umma_bf16_ss(tmem_S, umma_smem_desc(q_addr + part * AF_TILE + k * 32, 16, 512, 4),
-                                     umma_smem_desc(k_addr + part * AF_TILE + k * 32, 16, 512, 4), idesc_s,
-                                     (part | k) ? 1u : 0u);
+                        umma_bf16_ss(tmem_S, umma_desc_adv(q_d, part * AF_TILE + k * 32),
+                                     umma_desc_adv(k_d, part * AF_TILE + k * 32), idesc_s, (part | k) ? 1u : 0u);
 #pragma unroll
                 for (int k = 0; k < AF_D / 16; ++k)
-                    umma_bf16_ss(tmem_dP, umma_smem_desc(do_addr + k * 32, 16, 512, 4),
-                                 umma_smem_desc(v_addr + k * 32, 16, 512, 4), idesc_s, k ? 1u : 0u);
+                    umma_bf16_ss(tmem_dP, umma_desc_adv(do_d, k * 32), umma_desc_adv(v_d, k * 32), idesc_s, k ? 1u : 0u);
                 umma_commit(s_full);
             };
             issue_SP(0);
             for (int t = 0; t < ntiles; ++t) {
                 const int j = t / nqt, i = t - j * nqt;
-                const int sj = j & 1, s = t & 1;
+                const int sj = j & 1, s = t % L::kQS;
                 if (t + 1 < ntiles) {
                     // S(t) / dP(t) live in the softmax warps' registers: the next pair is computed while they work
                     mbar_wait(s_free, t & 1);
                     tc_fence_after();
+                    AF_STAMP(1, t + 1, 0);
                     issue_SP(t + 1);
+                    AF_STAMP(1, t + 1, 2);
                 }
                 mbar_wait(p_full, t & 1);
                 tc_fence_after();
-                const uint32_t k_addr = smem_u32(smem + L::kK + sj * NP * AF_TILE);
-                const uint32_t q_addr = smem_u32(smem + L::kQ + s * NP * AF_TILE);
-                const uint32_t do_addr = smem_u32(smem + L::kDO + s * AF_TILE);
-                // dV_j (+)= Pᵀ·dO_i: contraction over the 128 queries, 16 per instruction.  A: rows of the [query][key]
-                // tile are the contraction index, 64 keys contiguous per slab (MN-major, slabs 16 KB apart).
+                AF_STAMP(1, t, 3);
+                const uint64_t k_mn = umma_desc_adv(dK_mn, sj * NP * AF_TILE);
+                const uint64_t q_mn = umma_desc_adv(dQ_mn, s * NP * AF_TILE), do_mn = umma_desc_adv(dDO_mn, s * AF_TILE);
+                // (every MMA below is issued unconditionally: individually predicated tcgen05.mma in these unrolled loops
+                // — an attempt to stop the contraction at a ragged tile's last valid row — produced wrong dQ and faults)
+                const uint32_t acc_i = i ? 1u : 0u, acc_j = j ? 1u : 0u;
+                const uint32_t pb = (t % L::kPBuf) * AF_PT;  // which P / dS buffer this tile used
+                const uint64_t p_mn = umma_desc_adv(dP_mn, pb), ds_mn = umma_desc_adv(dDS_mn, pb), ds_k = umma_desc_adv(dDS_k, pb);
+                // dV_j (+)= Pᵀ·dO_i: contraction over the 128 queries, 16 per instruction
 #pragma unroll
                 for (int kk = 0; kk < AF_T / 16; ++kk)
-                    umma_bf16_ss(tmem_dV, umma_smem_desc(p_addr + kk * 2048, AF_T * 128, 1024, 2),
-                                 umma_smem_desc(do_addr + kk * 1024, 4096, 512, 4), idesc_k, (i | kk) ? 1u : 0u);
+                    umma_bf16_ss(tmem_dV, umma_desc_adv(p_mn, kk * 2048), umma_desc_adv(do_mn, kk * 1024), idesc_k,
+                                     kk ? 1u : acc_i);
 #pragma unroll
                 for (int part = 0; part < NP; ++part)
 #pragma unroll
                     for (int kk = 0; kk < AF_T / 16; ++kk)
-                        umma_bf16_ss(tmem_dK + part * AF_D, umma_smem_desc(ds_addr + kk * 2048, AF_T * 128, 1024, 2),
-                                     umma_smem_desc(q_addr + part * AF_TILE + kk * 1024, 4096, 512, 4), idesc_k,
-                                     (i | kk) ? 1u : 0u);
+                        umma_bf16_ss(tmem_dK + part * AF_D, umma_desc_adv(ds_mn, kk * 2048),
+                                         umma_desc_adv(q_mn, part * AF_TILE + kk * 1024), idesc_k, kk ? 1u : acc_i);
                 // dQ_i (+)= dS·K_j: contraction over the 128 keys
+                const uint32_t tq = tmem_dQ + i * NP * AF_D;
 #pragma unroll
                 for (int part = 0; part < NP; ++part)
 #pragma unroll
                     for (int kk = 0; kk < AF_T / 16; ++kk)
-                        umma_bf16_ss(tmem_dQ + (i * NP + part) * AF_D,
-                                     umma_smem_desc(ds_addr + (kk >> 2) * (AF_T * 128) + (kk & 3) * 32, 16, 1024, 2),
-                                     umma_smem_desc(k_addr + part * AF_TILE + kk * 1024, 4096, 512, 4), idesc_q,
-                                     (j | kk) ? 1u : 0u);
-                umma_commit(g_done);
+                        umma_bf16_ss(tq + part * AF_D, umma_desc_adv(ds_k, (kk >> 2) * (AF_T * 128) + (kk & 3) * 32),
+                                         umma_desc_adv(k_mn, part * AF_TILE + kk * 1024), idesc_q, kk ? 1u : acc_j);
+                umma_commit(g_done + (t & 1));
+                AF_STAMP(1, t, 4);
                 umma_commit(qdo_empty + s);
                 if (i == nqt - 1) umma_commit(kv_empty + sj);
             }
@@ -227,161 +290,181 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
         const int row = quarter * 32 + lane;
         const uint32_t lane_off = uint32_t(quarter * 32) << 16;
         const float sl2 = p.scale * AF_LOG2E;
-        float* my_lse = stat + (half * 2 + 0) * (L::kMaxQT * AF_T);
-        float* my_dlt = stat + (half * 2 + 1) * (L::kMaxQT * AF_T);
+        float* s_lse = stat;                        // lse·log2(e) per query row (+inf for padded rows: P = 0)
+        float* s_dlt = stat + L::kMaxQT * AF_T;     // scale·delta per query row
         uint8_t* sP = smem + L::kP;
         uint8_t* sDS = smem + L::kDS;
-        const long long C = (long long)p.H * AF_D;
 
-        auto read_out_dkv = [&](int jj) {  // dV / dK of key tile jj: TMEM -> bf16 rows
-            const int key = jj * AF_T + row;
-            const bool k_ok = key < p.Lk;
-            const long long orow = ((long long)b * p.Lk + key) * p.ld_dk + h * AF_D;
-            const long long orow2 = ((long long)b * p.Lk + key) * C + h * AF_D;
-            uint32_t v[32];
-            if (half == 0) {
-                tmem_ld_32x32b_x32(tmem_dV + lane_off, v);
-                tmem_ld_wait();
-                if (k_ok) af_store_row32(p.dv + orow, v);
-                if (NP == 2) {
-                    tmem_ld_32x32b_x32(tmem_dK + lane_off + AF_D, v);
-                    tmem_ld_wait();
-                    if (k_ok) af_store_row32(p.dk2 + orow2, v);
+        // Pre-pass (overlaps the first TMA loads and score MMAs): delta = rowsum(dO ⊙ O) and lse of EVERY query row of
+        // this (batch, head).  Four lanes share a row (16 bytes each: a warp-wide load touches 8 lines instead of 32),
+        // all loads of all query tiles are issued before the first use, partial dot products meet by shuffle.
+        {
+            const __nv_bfloat16* o_base = p.out + (long long)b * p.bso + h * AF_D;
+            const __nv_bfloat16* do_base = p.dout + (long long)b * p.bsdo + h * AF_D;
+            const int tid = threadIdx.x;          // 0..255
+            const int r0 = tid >> 2, ch = tid & 3;
+            uint4 a4[L::kMaxQT][2], d4[L::kMaxQT][2];
+            float l2[L::kMaxQT][2];
+            const long long st0 = ((long long)b * p.H + h) * p.Lq;
+#pragma unroll
+            for (int i = 0; i < L::kMaxQT; ++i)
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    const int q = i * AF_T + u * 64 + r0;
+                    const bool ok = i < nqt && q < p.Lq;
+                    a4[i][u] = ok ? __ldg(reinterpret_cast<const uint4*>(o_base + (long long)q * p.ldo) + ch) : make_uint4(0, 0, 0, 0);
+                    d4[i][u] = ok ? __ldg(reinterpret_cast<const uint4*>(do_base + (long long)q * p.lddo) + ch) : make_uint4(0, 0, 0, 0);
+                    l2[i][u] = (ok && ch == 0) ? __ldg(p.lse + st0 + q) : INFINITY;  // +inf: P = 0 for padded rows
                 }
+#pragma unroll
+            for (int i = 0; i < L::kMaxQT; ++i)
+#pragma unroll
+                for (int u = 0; u < 2; ++u) {
+                    if (i >= nqt) break;  // warp-uniform
+                    const int rr = u * 64 + r0, q = i * AF_T + rr;
+                    const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a4[i][u]);
+                    const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&d4[i][u]);
+                    float acc = 0.f;
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float2 x = __bfloat1622float2(ha[e]), y = __bfloat1622float2(hd[e]);
+                        acc = fmaf(x.x, y.x, acc);
+                        acc = fmaf(x.y, y.y, acc);
+                    }
+                    acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+                    acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+                    if (ch == 0) {
+                        s_lse[i * AF_T + rr] = l2[i][u] * AF_LOG2E;
+                        s_dlt[i * AF_T + rr] = acc * p.scale;  // pre-scaled: dS = P·(scale·dP − scale·delta)
+                        if (q < p.Lq && p.delta) p.delta[st0 + q] = acc;
+                    }
+                }
+            asm volatile("bar.sync 1, 256;" ::: "memory");  // the 8 softmax warps
+        }
+        if (threadIdx.x == 0) AF_STAMP(2, 0, 3);  // delta pre-pass done
+
+        // Gradient tiles leave through TMA: the four warps of a `half` (one per TMEM lane quarter) write their rows of
+        // the [128][32] accumulator into a swizzled staging tile and one thread issues the bulk store (rows beyond the
+        // sequence end are clipped by the tensor map).  Row-per-thread global stores would touch 32 lines per warp
+        // instruction and cost ~1.5 us per CTA in the load/store unit.
+        uint8_t* my_slot = smem + L::kOut + half * AF_TILE;     // half 0: slots 0 and 2, half 1: slot 1
+        const bool issuer = quarter == 0 && lane == 0;
+        // (a force-inlined function, not a lambda: out of line, the tensor-map argument would be a run-time pointer and
+        // the by-reference captures would live in local memory)
+#define AF_STORE_TILE(taddr, slot, tm, row0) \
+    af_store_tile((taddr) + lane_off, (slot), (tm), (row0), row, half, issuer, h, b)
+        auto read_out_dkv = [&](int jj) {  // dV / dK of key tile jj
+            if (half == 0) {
+                AF_STORE_TILE(tmem_dV, my_slot, &tmDV, jj * AF_T);
+                if (NP == 2) AF_STORE_TILE(tmem_dK + AF_D, smem + L::kOut + 2 * AF_TILE, &tmDK2, jj * AF_T);
             } else {
-                tmem_ld_32x32b_x32(tmem_dK + lane_off, v);
-                tmem_ld_wait();
-                if (k_ok) af_store_row32(p.dk1 + orow, v);
+                AF_STORE_TILE(tmem_dK, my_slot, &tmDK1, jj * AF_T);
             }
         };
 
-        uint32_t vs[2][32], vp[2][32];
+        uint32_t vs[32], vp[32];
         for (int t = 0; t < ntiles; ++t) {
             const int j = t / nqt, i = t - j * nqt;
-            const int q = i * AF_T + row;
-            const bool q_ok = q < p.Lq;
+            const float lse2 = s_lse[i * AF_T + row];
+            const float dlt = s_dlt[i * AF_T + row];
+            const int kvalid = p.Lk - j * AF_T;  // >= 1
+            if (threadIdx.x == 0) AF_STAMP(0, t, 0);
             mbar_wait(s_full, t & 1);
             tc_fence_after();
-            tmem_ld_32x32b_x32(tmem_S + lane_off + (2 * half) * 32, vs[0]);
-            tmem_ld_32x32b_x32(tmem_S + lane_off + (2 * half + 1) * 32, vs[1]);
-            tmem_ld_32x32b_x32(tmem_dP + lane_off + (2 * half) * 32, vp[0]);
-            tmem_ld_32x32b_x32(tmem_dP + lane_off + (2 * half + 1) * 32, vp[1]);
-            tmem_ld_wait();
-            tc_fence_before();
-            mbar_arrive(s_free);
-
-            float lse2, dlt;
-            if (j == 0) {
-                // first key tile: this row's lse and delta = sum_d dO[q][d]·O[q][d]; both halves compute their own copy
-                // (no cross-warp hand-over).  dO comes from the staged tile, O from global memory.
-                const int s = t & 1;
-                mbar_wait(qdo_full + s, (t >> 1) & 1);  // completed long ago; makes the TMA writes visible to this thread
-                float acc = 0.f;
-                if (q_ok) {
-                    const uint8_t* sdo = smem + L::kDO + s * AF_TILE;
-                    const uint4* po = reinterpret_cast<const uint4*>(p.out + (long long)b * p.bso + (long long)q * p.ldo + h * AF_D);
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        const uint4 a = __ldg(po + c);
-                        const uint4 d = *reinterpret_cast<const uint4*>(sdo + swz_off<64>(row, c));
-                        const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a);
-                        const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&d);
-#pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const float2 x = __bfloat1622float2(ha[e]), y = __bfloat1622float2(hd[e]);
-                            acc = fmaf(x.x, y.x, acc);
-                            acc = fmaf(x.y, y.y, acc);
-                        }
-                    }
-                }
-                const long long st = ((long long)b * p.H + h) * p.Lq + q;
-                lse2 = q_ok ? __ldg(p.lse + st) * AF_LOG2E : INFINITY;  // +inf -> P = 0 for padded query rows
-                dlt = acc * p.scale;                                     // pre-scaled: dS = P·(scale·dP − scale·delta)
-                my_lse[i * AF_T + row] = lse2;
-                my_dlt[i * AF_T + row] = dlt;
-                if (half == 0 && q_ok && p.delta) p.delta[st] = acc;
-            } else {
-                lse2 = my_lse[i * AF_T + row];
-                dlt = my_dlt[i * AF_T + row];
-            }
-            // P and dS are formed IN PLACE in the registers that hold S and dP, before anything is waited for: the
-            // exponentials of tile t overlap the gradient MMAs of tile t-1
-            const int kvalid = p.Lk - j * AF_T;  // >= 1
-#pragma unroll
-            for (int cc = 0; cc < 2; ++cc) {
-#pragma unroll
-                for (int idx = 0; idx < 32; ++idx) {
-                    const float x = fast_exp2(fmaf(__uint_as_float(vs[cc][idx]), sl2, -lse2));
-                    const float g = fmaf(__uint_as_float(vp[cc][idx]), p.scale, -dlt);
-                    vs[cc][idx] = __float_as_uint(x);
-                    vp[cc][idx] = __float_as_uint(x * g);
-                }
-            }
-            if (kvalid < AF_T) {  // ragged last key tile (warp-uniform): keys beyond Lk contribute nothing
-#pragma unroll
-                for (int cc = 0; cc < 2; ++cc)
-#pragma unroll
-                    for (int idx = 0; idx < 32; ++idx)
-                        if ((2 * half + cc) * 32 + idx >= kvalid) {
-                            vs[cc][idx] = 0u;
-                            vp[cc][idx] = 0u;
-                        }
-            }
-            if (t > 0) {
-                mbar_wait(g_done, (t - 1) & 1);  // gradient MMAs of tile t-1 retired: P / dS tiles may be overwritten
-                tc_fence_after();
-            }
+            if (threadIdx.x == 0) AF_STAMP(0, t, 1);
+            // Two passes of 32 columns (register budget: 168 per thread at 320 threads): P and dS are formed, packed to
+            // bf16 and stored per pass.  The exponentials of the first pass run before anything else is waited for, so
+            // they overlap the gradient MMAs of tile t-1; S / dP in TMEM are released after the second load, so the
+            // next score pair is computed while this one is still being exponentiated.
 #pragma unroll
             for (int cc = 0; cc < 2; ++cc) {
                 const int c = 2 * half + cc;  // 32-column chunk of the 128-wide tile
-                uint8_t* slabP = sP + (c >> 1) * (AF_T * 128);
-                uint8_t* slabD = sDS + (c >> 1) * (AF_T * 128);
+                tmem_ld_32x32b_x32(tmem_S + lane_off + c * 32, vs);
+                tmem_ld_32x32b_x32(tmem_dP + lane_off + c * 32, vp);
+                tmem_ld_wait();
+                if (cc == 1) {
+                    tc_fence_before();
+                    mbar_arrive(s_free);
+                }
+                if (threadIdx.x == 0) AF_STAMP(0, t, cc == 0 ? 2 : 5);
+#pragma unroll
+                for (int idx = 0; idx < 32; ++idx) {
+                    const float x = fast_exp2(fmaf(__uint_as_float(vs[idx]), sl2, -lse2));
+                    const float g = fmaf(__uint_as_float(vp[idx]), p.scale, -dlt);
+                    vs[idx] = __float_as_uint(x);
+                    vp[idx] = __float_as_uint(x * g);
+                }
+                if (kvalid < AF_T) {  // ragged last key tile (warp-uniform): keys beyond Lk contribute nothing
+#pragma unroll
+                    for (int idx = 0; idx < 32; ++idx)
+                        if (c * 32 + idx >= kvalid) {
+                            vs[idx] = 0u;
+                            vp[idx] = 0u;
+                        }
+                }
+                if (cc == 0) {
+                    if (threadIdx.x == 0) AF_STAMP(0, t, 3);
+                    if (t >= L::kPBuf) {  // the gradient MMAs that read this P / dS buffer last have retired
+                        const int tp = t - L::kPBuf;
+                        mbar_wait(g_done + (tp & 1), (tp >> 1) & 1);
+                        tc_fence_after();
+                    }
+                    if (threadIdx.x == 0) AF_STAMP(0, t, 4);
+                }
+                uint8_t* slabP = sP + (t % L::kPBuf) * AF_PT + (c >> 1) * (AF_T * 128);
+                uint8_t* slabD = sDS + (t % L::kPBuf) * AF_PT + (c >> 1) * (AF_T * 128);
 #pragma unroll
                 for (int qd = 0; qd < 4; ++qd) {
                     uint4 up, ud;
-                    up.x = pack_bf16x2(__uint_as_float(vs[cc][qd * 8 + 0]), __uint_as_float(vs[cc][qd * 8 + 1]));
-                    up.y = pack_bf16x2(__uint_as_float(vs[cc][qd * 8 + 2]), __uint_as_float(vs[cc][qd * 8 + 3]));
-                    up.z = pack_bf16x2(__uint_as_float(vs[cc][qd * 8 + 4]), __uint_as_float(vs[cc][qd * 8 + 5]));
-                    up.w = pack_bf16x2(__uint_as_float(vs[cc][qd * 8 + 6]), __uint_as_float(vs[cc][qd * 8 + 7]));
-                    ud.x = pack_bf16x2(__uint_as_float(vp[cc][qd * 8 + 0]), __uint_as_float(vp[cc][qd * 8 + 1]));
-                    ud.y = pack_bf16x2(__uint_as_float(vp[cc][qd * 8 + 2]), __uint_as_float(vp[cc][qd * 8 + 3]));
-                    ud.z = pack_bf16x2(__uint_as_float(vp[cc][qd * 8 + 4]), __uint_as_float(vp[cc][qd * 8 + 5]));
-                    ud.w = pack_bf16x2(__uint_as_float(vp[cc][qd * 8 + 6]), __uint_as_float(vp[cc][qd * 8 + 7]));
+                    up.x = pack_bf16x2(__uint_as_float(vs[qd * 8 + 0]), __uint_as_float(vs[qd * 8 + 1]));
+                    up.y = pack_bf16x2(__uint_as_float(vs[qd * 8 + 2]), __uint_as_float(vs[qd * 8 + 3]));
+                    up.z = pack_bf16x2(__uint_as_float(vs[qd * 8 + 4]), __uint_as_float(vs[qd * 8 + 5]));
+                    up.w = pack_bf16x2(__uint_as_float(vs[qd * 8 + 6]), __uint_as_float(vs[qd * 8 + 7]));
+                    ud.x = pack_bf16x2(__uint_as_float(vp[qd * 8 + 0]), __uint_as_float(vp[qd * 8 + 1]));
+                    ud.y = pack_bf16x2(__uint_as_float(vp[qd * 8 + 2]), __uint_as_float(vp[qd * 8 + 3]));
+                    ud.z = pack_bf16x2(__uint_as_float(vp[qd * 8 + 4]), __uint_as_float(vp[qd * 8 + 5]));
+                    ud.w = pack_bf16x2(__uint_as_float(vp[qd * 8 + 6]), __uint_as_float(vp[qd * 8 + 7]));
                     const uint32_t off = swz_off<128>(row, (c & 1) * 4 + qd);
                     *reinterpret_cast<uint4*>(slabP + off) = up;
                     *reinterpret_cast<uint4*>(slabD + off) = ud;
                 }
             }
-            // dV / dK of the previous key tile are final (g_done above); tile t's gradient MMAs, which restart them,
-            // are only issued after this thread's p_full arrival below
-            if (t > 0 && i == 0) read_out_dkv(j - 1);
+            // dV / dK of the previous key tile are final once tile t-1's gradient MMAs have retired; tile t's, which
+            // restart them, are only issued after this thread's p_full arrival below
+            if (t > 0 && i == 0) {
+                mbar_wait(g_done + ((t - 1) & 1), ((t - 1) >> 1) & 1);
+                tc_fence_after();
+                read_out_dkv(j - 1);
+            }
+            if (threadIdx.x == 0) AF_STAMP(0, t, 6);
             fence_proxy_async_smem();
             tc_fence_before();
             mbar_arrive(p_full);
+            if (threadIdx.x == 0) AF_STAMP(0, t, 7);
         }
-        mbar_wait(g_done, (ntiles - 1) & 1);
+        if (threadIdx.x == 0) AF_STAMP(2, 0, 4);  // main loop done
+        mbar_wait(g_done + ((ntiles - 1) & 1), ((ntiles - 1) >> 1) & 1);
         tc_fence_after();
+        if (threadIdx.x == 0) AF_STAMP(2, 0, 5);  // last gradient MMAs retired
         read_out_dkv(nkt - 1);
-        // dQ of every query tile: (tile, part) pairs alternate between the two warps of a lane quarter
-        uint32_t v[32];
+        // dQ of every query tile: (tile, part) pairs alternate between the two halves
         for (int idx = half; idx < nqt * NP; idx += 2) {
             const int i = idx / NP, part = idx - i * NP;
-            const int q = i * AF_T + row;
-            tmem_ld_32x32b_x32(tmem_dQ + lane_off + idx * AF_D, v);
-            tmem_ld_wait();
-            if (q < p.Lq) {
-                const long long ldg = part ? C : p.ld_dq;
-                __nv_bfloat16* dst = (part ? p.dq2 : p.dq1) + ((long long)b * p.Lq + q) * ldg + h * AF_D;
-                af_store_row32(dst, v);
-            }
+            // (a run-time choice between two tensor-map POINTERS would make the compiler copy the __grid_constant__
+            // maps to local memory, which the TMA unit cannot read: branch instead)
+            if (NP == 2 && part) AF_STORE_TILE(tmem_dQ + idx * AF_D, my_slot, &tmDQ2, i * AF_T);
+            else AF_STORE_TILE(tmem_dQ + idx * AF_D, my_slot, &tmDQ1, i * AF_T);
         }
+        if (issuer) bulk_wait0();  // the staging tiles live in this CTA's shared memory: drain before it is released
         tc_fence_before();
+        if (threadIdx.x == 0) AF_STAMP(2, 0, 6);  // gradients stored
     }
     __syncthreads();
     if (warp == AF_MMA) {
         tc_fence_after();
         tmem_dealloc<512>(tmem_base);
     }
+    if (threadIdx.x == 0) AF_STAMP(2, 0, 7);
 }
 
 static int make_seq_tmap_f(CUtensorMap* tm, const void* base, int rowlen, int L, int B, long long ld, long long bs) {
@@ -416,12 +499,33 @@ int launch_attn_bwd_fused(const fod_attn_bwd_args* g, cudaStream_t st) {
         tq2 = tq1;
         tk2 = tk1;
     }
+    // gradient outputs (always carry a batch dimension; dq1 / dk1 / dv may be column slices of a fused tensor)
+    const long long ld_dq = g->ld_dq ? g->ld_dq : rowlen, ld_dk = g->ld_dk ? g->ld_dk : rowlen;
+    auto out_map = [&](CUtensorMap* tm, const void* base, int Lrows, long long ld) {
+        uint64_t dims[3] = {(uint64_t)rowlen, (uint64_t)Lrows, (uint64_t)a->B};
+        uint64_t str[2] = {(uint64_t)ld * 2, (uint64_t)ld * 2 * Lrows};
+        uint32_t box[3] = {AF_D, AF_T, 1};
+        return make_tmap_bf16(tm, base, 3, dims, str, box, 64);
+    };
+    CUtensorMap tdq1, tdq2, tdk1, tdk2, tdv;
+    if (out_map(&tdq1, g->dq1, a->Lq, ld_dq) || out_map(&tdk1, g->dk1, a->Lk, ld_dk) || out_map(&tdv, g->dv, a->Lk, ld_dk))
+        return fod_fail(FOD_E_TMAP, "attn_bwd: gradient outputs (16-byte aligned bases and row strides needed)");
+    if (two) {
+        if (out_map(&tdq2, g->dq2, a->Lq, rowlen) || out_map(&tdk2, g->dk2, a->Lk, rowlen))
+            return fod_fail(FOD_E_TMAP, "attn_bwd: dq2 / dk2");
+    } else {
+        tdq2 = tdq1;
+        tdk2 = tdk1;
+    }
     AttnBwdFusedParams p;
     p.lse = a->lse;
     p.delta = g->delta;
     p.out = reinterpret_cast<const __nv_bfloat16*>(a->out);
+    p.dout = reinterpret_cast<const __nv_bfloat16*>(g->dout);
     p.ldo = a->ldo;
     p.bso = a->bso;
+    p.lddo = g->lddo;
+    p.bsdo = a->B > 1 ? g->bsdo : 0;
     p.dq1 = reinterpret_cast<__nv_bfloat16*>(g->dq1);
     p.dq2 = reinterpret_cast<__nv_bfloat16*>(g->dq2);
     p.dk1 = reinterpret_cast<__nv_bfloat16*>(g->dk1);
@@ -442,9 +546,18 @@ int launch_attn_bwd_fused(const fod_attn_bwd_args* g, cudaStream_t st) {
         attr[two] = true;
     }
     dim3 grid(a->H, a->B);
-    if (two) fod_launch(attn_bwd_fused_kernel<2>, grid, dim3(AF_THREADS), FusedBwdSmem<2>::kTotal, st, tq1, tk1, tq2, tk2, tv, tdo, p);
-    else fod_launch(attn_bwd_fused_kernel<1>, grid, dim3(AF_THREADS), FusedBwdSmem<1>::kTotal, st, tq1, tk1, tq2, tk2, tv, tdo, p);
+    if (two) fod_launch(attn_bwd_fused_kernel<2>, grid, dim3(AF_THREADS), FusedBwdSmem<2>::kTotal, st, tq1, tk1, tq2, tk2, tv, tdo,
+                        tdq1, tdq2, tdk1, tdk2, tdv, p);
+    else fod_launch(attn_bwd_fused_kernel<1>, grid, dim3(AF_THREADS), FusedBwdSmem<1>::kTotal, st, tq1, tk1, tq2, tk2, tv, tdo,
+                    tdq1, tdq2, tdk1, tdk2, tdv, p);
     return fod_check_launch("attn_bwd_fused_kernel");
 }
 
 }  // namespace fod
+
+#if FOD_AF_TRACE
+extern "C" int fod_debug_af_trace(long long* host_out) {
+    cudaDeviceSynchronize();
+    return (int)cudaMemcpyFromSymbol(host_out, fod::g_af_trace, sizeof(long long) * 3 * 16 * 8);
+}
+#endif

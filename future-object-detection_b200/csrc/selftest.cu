@@ -311,6 +311,19 @@ static void test_attn_bwd(int B, int H, int Lq, int Lk, int two, int k2_bcast) {
             num += d * d; den += x * x;
         }
         const double rel = sqrt(num / (den > 0 ? den : 1));
+        if (rel > 1e-2) {  // where do the two paths part?  first rows of both, and the first differing element
+            printf("  %s two-kernel:", names[t]);
+            for (int i = 0; i < 8; ++i) printf(" %.4f", __bfloat162float(h0[i]));
+            printf("\n  %s fused     :", names[t]);
+            for (int i = 0; i < 8; ++i) printf(" %.4f", __bfloat162float(h1[i]));
+            size_t first = n, cnt = 0;
+            for (size_t i = 0; i < n; ++i) {
+                const float x = __bfloat162float(h0[i]), y = __bfloat162float(h1[i]);
+                if (!(fabsf(x - y) <= 0.02f * (fabsf(x) + 0.05f))) { if (first == n) first = i; ++cnt; }
+            }
+            const size_t Cc = (size_t)H * 32;
+            printf("\n  %zu of %zu differ; first at row %zu col %zu\n", cnt, n, first / Cc, first % Cc);
+        }
         worst = fmax(worst, rel);
         snprintf(detail + strlen(detail), sizeof(detail) - strlen(detail), " %s %.2g", names[t], rel);
     }
@@ -356,6 +369,11 @@ int main(int argc, char** argv) {
         test_linear(22400, 2048, 256, 1, 0, 0, 1, 0, 0);
         test_linear(4096, 768, 256, 1, 1, 128, 0, 0, 0);
     }
+    if (which & 16) test_attn_bwd(2, 8, 128, 350, 1, 1);  // single cases (a device fault ends the process)
+    if (which & 32) test_attn_bwd(2, 8, 128, 350, 1, 0);
+    if (which & 64) test_attn_bwd(2, 8, 128, 350, 0, 0);
+    if (which & 128) test_attn_bwd(2, 8, 128, 128, 1, 1);
+    if (which & 256) test_attn_bwd(1, 1, 128, 128, 1, 0);
     if (which & 8) {
         test_attn_bwd(1, 1, 128, 128, 0, 0);
         test_attn_bwd(2, 8, 350, 350, 0, 0);

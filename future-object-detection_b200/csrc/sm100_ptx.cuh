@@ -86,6 +86,17 @@ __device__ __forceinline__ void tma_load_3d(void* smem, const CUtensorMap* m, ui
         : "memory");
 }
 
+// shared -> global tile store (TMA); rows / columns outside the tensor map's extents are clipped.  Bulk async-groups
+// are per thread: the thread that issues the store commits it and later waits for it.
+__device__ __forceinline__ void tma_store_3d(const CUtensorMap* m, const void* smem, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
+                 ::"l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // ---------------------------------------------------------------- tcgen05 / TMEM
 template <int kCols>
 __device__ __forceinline__ void tmem_alloc(uint32_t* slot_in_smem) {
@@ -173,6 +184,13 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t 
     d |= uint64_t(layout_type & 7) << 61;
     return d;
 }
+
+// A descriptor for `smem_addr + byte_off` given the descriptor of `smem_addr`: the start-address field holds
+// (address >> 4) in the low 14 bits and shared-memory addresses stay below 256 KB, so the sum never carries out of the
+// field.  The MMA-issuing thread builds a descriptor ONCE per operand buffer and steps it with one add per instruction
+// — rebuilding it field by field costs ~70 clk per MMA on the single issuing thread (measured), more than most of the
+// MMAs here take to execute.
+__device__ __forceinline__ uint64_t umma_desc_adv(uint64_t desc, uint32_t byte_off) { return desc + uint64_t(byte_off >> 4); }
 
 // byte offset of (row, 16-byte chunk) inside a swizzled tile whose rows are `kRowBytes` wide
 // (kRowBytes = 128 -> SWIZZLE_128B, 64 -> SWIZZLE_64B). Same XOR the TMA unit applies.
