@@ -237,7 +237,37 @@ __device__ __forceinline__ void drain_f32(const uint8_t* stage_warp, float* out,
     }
 }
 
-template <int BN, bool A_MN, bool B_MN>
+// acc + bias + residual of 32 columns of one row for the LayerNorm epilogue (the only terms that epilogue admits)
+__device__ __forceinline__ void ln_chunk(float (&z)[32], const uint32_t (&v)[32], const GemmEpi& p, const uint8_t* aux_row,
+                                         long long mod_row, int c, const float* s_bias, bool row_ok) {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+        const float4 b4 = *reinterpret_cast<const float4*>(s_bias + c * 32 + q * 4);  // zeros when there is no bias
+        z[q * 4] = __uint_as_float(v[q * 4]) + b4.x;
+        z[q * 4 + 1] = __uint_as_float(v[q * 4 + 1]) + b4.y;
+        z[q * 4 + 2] = __uint_as_float(v[q * 4 + 2]) + b4.z;
+        z[q * 4 + 3] = __uint_as_float(v[q * 4 + 3]) + b4.w;
+    }
+    if (p.aux_mode == 1 && row_ok) {
+        if (p.vec_ok) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                float f[8];
+                unpack8(*reinterpret_cast<const uint4*>(aux_row + c * 64 + q * 16), f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) z[q * 8 + j] += f[j];
+            }
+        } else {
+            const __nv_bfloat16* r = p.aux + mod_row * p.ld_aux + c * 32;
+#pragma unroll
+            for (int i = 0; i < 32; ++i) z[i] += __bfloat162float(r[i]);
+        }
+    }
+}
+
+// LN = true: the LayerNorm epilogue (N == BN == 256) and nothing else — a separate instantiation, so that neither
+// variant drags the other's code through the instruction cache.
+template <int BN, bool A_MN, bool B_MN, bool LN>
 __global__ void __launch_bounds__(GemmThreads<BN>::kThreads, BN == 256 ? 1 : 2)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmEpi p) {
     using Cfg = GemmCfg<BN>;
@@ -318,23 +348,22 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+            // K-major: 128-byte rows of 64 k, 8-row groups 1024 B apart, 16 k per instruction = +32 B.  MN-major: [64 k][64 mn]
+            // slabs of 8 KB (LBO = next 64 mn), 8-k groups 1024 B apart (SBO), 16 k per instruction = +2048 B.
+            // Stage-0 descriptors are built once and stepped with one add per instruction (umma_desc_adv).
+            const uint32_t a0 = smem_u32(smem);
+            const uint64_t dA0 = A_MN ? umma_smem_desc(a0, 8192, 1024, 2) : umma_smem_desc(a0, 16, 1024, 2);
+            const uint64_t dB0 = B_MN ? umma_smem_desc(a0 + Cfg::kABytes, 8192, 1024, 2) : umma_smem_desc(a0 + Cfg::kABytes, 16, 1024, 2);
+            constexpr uint32_t kStepA = A_MN ? 2048 : 32, kStepB = B_MN ? 2048 : 32;
             int s = 0;
             uint32_t ph = 0;
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(full_bar + s, ph);
                 tc_fence_after();
-                const uint32_t a_addr = smem_u32(smem + s * Cfg::kStageBytes);
-                const uint32_t b_addr = a_addr + Cfg::kABytes;
+                const uint64_t da = umma_desc_adv(dA0, s * Cfg::kStageBytes), db = umma_desc_adv(dB0, s * Cfg::kStageBytes);
 #pragma unroll
-                for (int k = 0; k < GEMM_BK / 16; ++k) {
-                    // K-major: 128-byte rows of 64 k, 8-row groups 1024 B apart.  MN-major: [64 k][64 mn] slabs of
-                    // 8 KB (LBO = next 64 mn), 8-k groups 1024 B apart (SBO), 16 k per instruction = 2048 B.
-                    const uint64_t da = A_MN ? umma_smem_desc(a_addr + k * 2048, 8192, 1024, 2)
-                                             : umma_smem_desc(a_addr + k * 32, 16, 1024, 2);
-                    const uint64_t db = B_MN ? umma_smem_desc(b_addr + k * 2048, 8192, 1024, 2)
-                                             : umma_smem_desc(b_addr + k * 32, 16, 1024, 2);
-                    umma_bf16_ss(tmem_base, da, db, idesc, (kb | k) ? 1u : 0u);
-                }
+                for (int k = 0; k < GEMM_BK / 16; ++k)
+                    umma_bf16_ss(tmem_base, umma_desc_adv(da, k * kStepA), umma_desc_adv(db, k * kStepB), idesc, (kb | k) ? 1u : 0u);
                 umma_commit(empty_bar + s);  // frees the smem stage when these MMAs retire
                 if (++s == num_stages) {
                     s = 0;
@@ -388,7 +417,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint8_t* stage_a = smem;
         uint32_t v[32];
         float z[32];
-        if (p.ln_gamma == nullptr) {
+        if constexpr (!LN) {
             const bool f32out = p.out_f32 != nullptr;
             const int rowb = f32out ? Cfg::kRowF32 : Cfg::kRowBf16;
             uint8_t* my_row = stage_a + row_in_tile * rowb;
@@ -413,63 +442,80 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 drain_bf16<BN, WCOLS>(stage_warp, p.out_bf16, p.ld_out, p.M, p.N, (long long)m0 + quarter * 32,
                                       n0 + c_begin * 32, lane, p.vec_ok != 0, p.colsum_out);
         } else {
-            // LayerNorm over the whole row (N == BN == 256, n0 == 0).  Each of the two warps of a lane quarter keeps
-            // its 128 columns of the row in registers (one TMEM pass); row statistics are combined through smem.
-            if constexpr (BN == 256) {
-                uint8_t* stage_b = stage_a + GEMM_BM * Cfg::kRowBf16;  // pre-LN copy
-                uint8_t* my_a = stage_a + row_in_tile * Cfg::kRowBf16;
-                uint8_t* my_b = stage_b + row_in_tile * Cfg::kRowBf16;
-                float zr[CPW * 32];
-                float sum = 0.f;
+            // LayerNorm over the whole row (N == BN == 256, n0 == 0).  The two warps of a lane quarter own 128 columns of
+            // the row each.  Two passes over the accumulator IN TMEM (reading it costs ~1 KB/clk per SM, a fraction of
+            // what holding 128 values per thread in registers cost in unrolled code: that version was 7 700 SASS
+            // instructions executed once per CTA and spent ~45 % of its issue slots waiting for instruction fetch):
+            //   pass 1: z = acc + bias + residual -> shifted sums for mean / variance, pre-LN copy staged and drained
+            //   pass 2: z again -> (z - mean) * rstd * gamma + beta staged and drained
+            // Loops are kept rolled (32 columns per iteration).
+            static_assert(BN == 256, "LayerNorm epilogue needs the whole 256-wide row in one tile");
+            uint8_t* my_a = stage_a + row_in_tile * Cfg::kRowBf16;
+            const long long row0 = (long long)m0 + quarter * 32;
+            const int off = c_begin * 64;  // byte offset of this warp's column half inside a staged bf16 row
+            float shift = 0.f, s1 = 0.f, s2 = 0.f;
+#pragma unroll 1
+            for (int cc = 0; cc < CPW; ++cc) {
+                const int c = c_begin + cc;
+                tmem_ld_32x32b_x32(taddr + c * 32, v);
+                tmem_ld_wait();
+                ln_chunk(z, v, p, aux_row, mod_row, c, s_bias, row_ok);
+                if (cc == 0) shift = z[0];  // sums are taken about a value inside the data: no cancellation in the variance
+                float a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
-                for (int cc = 0; cc < CPW; ++cc) {
-                    const int c = c_begin + cc;
-                    tmem_ld_32x32b_x32(taddr + c * 32, v);
-                    tmem_ld_wait();
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) z[i] = __uint_as_float(v[i]);
-                    if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, c * 32, c, s_bias);
-#pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        sum += z[i];
-                        zr[cc * 32 + i] = z[i];
-                    }
-                    if (p.pre_ln) stage_bf16(my_b + c * 64, z);
+                for (int i = 0; i < 32; i += 2) {
+                    const float d0 = z[i] - shift, d1 = z[i + 1] - shift;
+                    a0 += d0;
+                    a1 += d1;
+                    q0 = fmaf(d0, d0, q0);
+                    q1 = fmaf(d1, d1, q1);
                 }
-                s_stat[half * GEMM_BM + row_in_tile] = sum;
-                asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
-                const float mean = (s_stat[row_in_tile] + s_stat[GEMM_BM + row_in_tile]) * (1.f / BN);
-                float var = 0.f;
-#pragma unroll
-                for (int i = 0; i < CPW * 32; ++i) {
-                    const float d = zr[i] - mean;
-                    var += d * d;
-                }
-                s_stat[(2 + half) * GEMM_BM + row_in_tile] = var;
-                asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
-                var = s_stat[2 * GEMM_BM + row_in_tile] + s_stat[3 * GEMM_BM + row_in_tile];
-                const float rstd = rsqrtf(var * (1.f / BN) + p.ln_eps);
-                if (row_ok && half == 0) {
-                    if (p.ln_mean) p.ln_mean[row] = mean;
-                    if (p.ln_rstd) p.ln_rstd[row] = rstd;
-                }
-#pragma unroll
-                for (int cc = 0; cc < CPW; ++cc) {
-                    const int c = c_begin + cc;
-#pragma unroll
-                    for (int i = 0; i < 32; ++i)
-                        z[i] = (zr[cc * 32 + i] - mean) * rstd * s_gamma[c * 32 + i] + s_beta[c * 32 + i];
-                    stage_bf16(my_a + c * 64, z);
-                }
-                __syncwarp();
-                const long long row0 = (long long)m0 + quarter * 32;
-                const int off = c_begin * 64;  // byte offset of this warp's column half inside a staged bf16 row
-                drain_bf16<BN, WCOLS>(stage_a + quarter * 32 * Cfg::kRowBf16 + off, p.out_bf16, p.ld_out, p.M, p.N, row0,
-                                      c_begin * 32, lane, p.vec_ok != 0, nullptr);
-                if (p.pre_ln)
-                    drain_bf16<BN, WCOLS>(stage_b + quarter * 32 * Cfg::kRowBf16 + off, p.pre_ln, p.ld_out, p.M, p.N, row0,
-                                          c_begin * 32, lane, p.vec_ok != 0, nullptr);
+                s1 += a0 + a1;
+                s2 += q0 + q1;
+                if (p.pre_ln) stage_bf16(my_a + c * 64, z);
             }
+            constexpr float kInvHalf = 1.f / (CPW * 32);
+            const float m_half = shift + s1 * kInvHalf;           // mean of this warp's 128 columns
+            const float m2_half = s2 - s1 * s1 * kInvHalf;        // sum of squared deviations about it
+            s_stat[half * GEMM_BM + row_in_tile] = m_half;
+            s_stat[(2 + half) * GEMM_BM + row_in_tile] = m2_half;
+            if (p.pre_ln) {
+                __syncwarp();
+                drain_bf16<BN, WCOLS>(stage_a + quarter * 32 * Cfg::kRowBf16 + off, p.pre_ln, p.ld_out, p.M, p.N, row0,
+                                      c_begin * 32, lane, p.vec_ok != 0, nullptr);
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
+            const float m_other = s_stat[(half ^ 1) * GEMM_BM + row_in_tile];
+            const float m2_other = s_stat[(2 + (half ^ 1)) * GEMM_BM + row_in_tile];
+            const float mean = 0.5f * (m_half + m_other);
+            const float dm = m_half - m_other;
+            // Chan's pairwise combination of two equal halves of n = 128: M2 = M2a + M2b + dm^2 * n / 2
+            const float var = (m2_half + m2_other + dm * dm * (0.5f * CPW * 32)) * (1.f / BN);
+            const float rstd = rsqrtf(var + p.ln_eps);
+            if (row_ok && half == 0) {
+                if (p.ln_mean) p.ln_mean[row] = mean;
+                if (p.ln_rstd) p.ln_rstd[row] = rstd;
+            }
+#pragma unroll 1
+            for (int cc = 0; cc < CPW; ++cc) {
+                const int c = c_begin + cc;
+                tmem_ld_32x32b_x32(taddr + c * 32, v);
+                tmem_ld_wait();
+                ln_chunk(z, v, p, aux_row, mod_row, c, s_bias, row_ok);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const float4 g4 = *reinterpret_cast<const float4*>(s_gamma + c * 32 + q * 4);
+                    const float4 b4 = *reinterpret_cast<const float4*>(s_beta + c * 32 + q * 4);
+                    z[q * 4] = (z[q * 4] - mean) * rstd * g4.x + b4.x;
+                    z[q * 4 + 1] = (z[q * 4 + 1] - mean) * rstd * g4.y + b4.y;
+                    z[q * 4 + 2] = (z[q * 4 + 2] - mean) * rstd * g4.z + b4.z;
+                    z[q * 4 + 3] = (z[q * 4 + 3] - mean) * rstd * g4.w + b4.w;
+                }
+                stage_bf16(my_a + c * 64, z);  // (this warp's pre-LN rows have been drained: same lanes, program order)
+            }
+            __syncwarp();
+            drain_bf16<BN, WCOLS>(stage_a + quarter * 32 * Cfg::kRowBf16 + off, p.out_bf16, p.ld_out, p.M, p.N, row0,
+                                  c_begin * 32, lane, p.vec_ok != 0, nullptr);
         }
         tc_fence_before();
     }
@@ -480,7 +526,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool LN = false>
 static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     using Cfg = GemmCfg<BN>;
     CUtensorMap tmA, tmB;
@@ -526,7 +572,7 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     // CTAs fit one SM (smem and the 512 TMEM columns), so one CTA's epilogue overlaps the other's main loop.  The
     // stages must still hold the staged output tile (and the pre-LN copy for the LayerNorm epilogue).
     {
-        const int need = a->out_f32 ? GEMM_BM * Cfg::kRowF32 : GEMM_BM * Cfg::kRowBf16 * (a->pre_ln_bf16 ? 2 : 1);
+        const int need = a->out_f32 ? GEMM_BM * Cfg::kRowF32 : GEMM_BM * Cfg::kRowBf16;  // (pre-LN copy and output share it)
         int min_stages = (need + Cfg::kStageBytes - 1) / Cfg::kStageBytes;
         if (min_stages < 2) min_stages = 2;
         const int want = epi.kb_per_split < min_stages ? min_stages : epi.kb_per_split;
@@ -546,7 +592,7 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
         const int a1 = Cfg::smem_bytes(BN == 256 ? 3 : (BN == 128 ? 4 : 3), true), a2 = Cfg::smem_bytes(BN == 64 ? 3 : 4, false);
-        cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN, LN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              a1 > a2 ? a1 : a2);
         attr_set = true;
     }
@@ -561,12 +607,18 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = (fod_pdl_enabled() && !memset_before) ? 1 : 0;  // a memset node cannot be a programmatic predecessor
-    cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, A_MN, B_MN>, tmA, tmB, epi);
+    cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, A_MN, B_MN, LN>, tmA, tmB, epi);
     return fod_check_launch("gemm_bf16_kernel");
 }
 
 template <int BN>
 static int launch_gemm_major(const fod_linear_args* a, const GemmEpi& e, cudaStream_t st) {
+    if constexpr (BN == 256) {
+        if (a->ln_gamma) {
+            if (a->a_mn || a->b_mn) return fod_fail(FOD_E_ARG, "gemm: the LayerNorm epilogue takes K-major operands");
+            return launch_gemm<256, false, false, true>(a, e, st);
+        }
+    }
     if (a->a_mn && a->b_mn) return launch_gemm<BN, true, true>(a, e, st);
     if (a->b_mn) return launch_gemm<BN, false, true>(a, e, st);
     if (a->a_mn) return fod_fail(FOD_E_ARG, "gemm: A MN-major with B K-major is not instantiated");
