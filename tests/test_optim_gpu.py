@@ -107,7 +107,7 @@ def test_arena_gradients_equal_autograd_gradients(ref_state_dict):
     print("worst per-tensor gradient deviation / global norm:", worst)
 
 
-def test_graph_replayed_training_follows_the_eager_trajectory(ref_state_dict):
+def test_graph_replayed_training_follows_the_eager_trajectory():
     """The captured step (side-stream weight gradients, fused optimizer, in-graph zero_grad) must train like the plain
     eager step with torch's AdamW: a race between the streams of the graph shows up as a diverging or non-finite loss
     within a few replays (it did: autograd accumulated in place into tensors the weight-gradient stream still read)."""
@@ -117,13 +117,23 @@ def test_graph_replayed_training_follows_the_eager_trajectory(ref_state_dict):
     from fod_b200 import train as T
     from fod_b200.optim import FlatTrainState
     from fod_b200.synthetic import make_clip
+    import json
+    import os
+
+    from conftest import GOLDEN
+    from fod_b200.synthetic import synthetic_state_dict
     dev = "cuda:0"
     dargs = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
     pool = [{k: v.to(dev) for k, v in make_clip(2, 3, 128, 160, seed=30 + i).items()} for i in range(2)]
+    # The well-conditioned synthetic backbone of the training workloads (residual_gain=0.5): with the
+    # fixtures' plain He initialisation the un-normalised frozen-BN ResNet overflows bf16 within ~20-50 Adam steps on a
+    # fraction of the runs (backbone gradients go non-finite first), whatever the kernels do.
+    with open(os.path.join(GOLDEN, "state_dict_template.json")) as f:
+        weights = synthetic_state_dict(json.load(f), seed=0, residual_gain=0.5)
 
     def run(graph):
         model = build_model(Namespace(device=dev, distributed=False), dargs)
-        model.load_state_dict(ref_state_dict)
+        model.load_state_dict(weights)
         model.train()
         if graph:
             opt = FlatTrainState(model, lr=dargs.lr, lr_backbone=dargs.lr_backbone, weight_decay=dargs.weight_decay)
@@ -133,8 +143,10 @@ def test_graph_replayed_training_follows_the_eager_trajectory(ref_state_dict):
         losses = []
         for i in range(24):
             losses.append(float(step(pool[i % 2]).detach()))
-        finite = all(bool(torch.isfinite(p).all()) for p in model.parameters())
-        return losses, finite
+        bad = [n for n, p in model.named_parameters() if not bool(torch.isfinite(p).all())]
+        if bad:
+            print("graph" if graph else "eager", "non-finite parameters:", bad[:8], len(bad))
+        return losses, not bad
 
     eager, ok_e = run(False)
     graph, ok_g = run(True)
