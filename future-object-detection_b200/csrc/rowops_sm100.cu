@@ -323,3 +323,48 @@ extern "C" int fod_maxpool3x3s2_nhwc(const void* x, void* y, int32_t N, int32_t 
         reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(y), N, H, W, C / 8, OH, OW);
     return fod::fod_check_launch("maxpool3x3s2_nhwc_kernel");
 }
+
+// ---------------------------------------------------------------- fused ReLU backward (+ gradient add) for the backbone
+// out = (a [+ b]) * (y > 0), flat bf16 arrays of n elements (n % 8 == 0, identical layouts).  In a bottleneck's backward
+// the gradient of the block output arrives as two addends (the conv1 input gradient and the identity-path gradient of
+// the NEXT block, torchvision resnet.py Bottleneck.forward / ConditionalDETR/models/backbone.py:88-96): autograd would add
+// them in one pass (3 tensors of traffic) and mask them in another (3 more); this does both in one (4).  HBM-bound:
+// 8 bytes per element with b, 6 without.
+namespace fod {
+__global__ void __launch_bounds__(256)
+relu_bwd_add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, const uint4* __restrict__ y, uint4* __restrict__ out,
+                    long long n8) {
+    const __nv_bfloat162 zero = __floats2bfloat162_rn(0.f, 0.f);
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n8; i += (long long)gridDim.x * 256) {
+        uint4 ua = __ldg(a + i);
+        const uint4 uy = __ldg(y + i);
+        __nv_bfloat162* ha = reinterpret_cast<__nv_bfloat162*>(&ua);
+        const __nv_bfloat162* hy = reinterpret_cast<const __nv_bfloat162*>(&uy);
+        if (b) {
+            const uint4 ub = __ldg(b + i);
+            const __nv_bfloat162* hb = reinterpret_cast<const __nv_bfloat162*>(&ub);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ha[j] = __hadd2(ha[j], hb[j]);  // bf16 add, as torch's accumulation of two bf16 gradients
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat162 m = __hgt2(hy[j], zero);  // 1.0 where y > 0 (a NaN activation masks to 0, as threshold_backward)
+            ha[j] = __hmul2(ha[j], m);
+        }
+        out[i] = ua;
+    }
+}
+}  // namespace fod
+
+extern "C" int fod_relu_bwd_add(const void* a, const void* b, const void* y, void* out, int64_t n, void* stream) {
+    if (!a || !y || !out || n <= 0 || n % 8) return fod::fod_fail(FOD_E_ARG, "relu_bwd_add: null/empty or n % 8 != 0");
+    if ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(out)) & 15)
+        return fod::fod_fail(FOD_E_ARG, "relu_bwd_add: 16-byte alignment");
+    const long long n8 = n / 8;
+    long long blocks = (n8 + 255) / 256;
+    if (blocks > 148LL * 16) blocks = 148LL * 16;
+    fod::relu_bwd_add_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const uint4*>(a), reinterpret_cast<const uint4*>(b), reinterpret_cast<const uint4*>(y),
+        reinterpret_cast<uint4*>(out), n8);
+    return fod::fod_check_launch("relu_bwd_add_kernel");
+}

@@ -9,7 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfod_b200.so")
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 FOD_OK, FOD_E_ARG, FOD_E_TMAP, FOD_E_LAUNCH, FOD_E_NUMERIC = 0, 1, 2, 3, 4
 
@@ -111,6 +111,7 @@ SYMBOLS = {
     "fod_ln_bwd": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_colsum": (C.c_int, [_VP, _I64, _VP, _I64, _I32, _I32, _VP]),
     "fod_maxpool3x3s2_nhwc": (C.c_int, [_VP, _VP, _I32, _I32, _I32, _I32, _VP]),
+    "fod_relu_bwd_add": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_stem_conv7x7s2": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),
     "fod_fold_conv_weights": (C.c_int, [_VP, _I32, _I64, _VP]),
     "fod_conv_wgrad_unfold": (C.c_int, [_VP, _VP, _VP, _I32, _I32, _I32, _VP]),

@@ -290,6 +290,95 @@ class _ConvAffineAct(torch.autograd.Function):
         return dx, dw, None, None, None, None, None, (g if has_z else None), None
 
 
+class _BottleneckStackFn(torch.autograd.Function):
+    """All bottleneck blocks of the trainable ResNet stages (layer2-4) as ONE autograd node — library convolutions (cuDNN
+    fused conv+bias(+add)+ReLU forward, dgrad / wgrad backward; SURVEY.md §8 f2: not hand-written kernels) with the
+    element-wise glue of the backward pass done by fod_relu_bwd_add.
+
+    Per block autograd would run: threshold_backward on the block output (a full-size pass), two more on the mid
+    activations, and an add of the two input-gradient contributions (conv1's dgrad and the identity / downsample path) —
+    at batch 32 and 448x800 these passes move ~1.1 GB each on layer2.  Here the add is deferred into the NEXT mask pass
+    (out = (a + b) * (y > 0): 4 tensors of traffic instead of 6) and the block-to-block gradients never become autograd
+    tensors.  Weight gradients are produced exactly as in _ConvAffineAct (dW = dW_folded * s, written into the arena on
+    the weight-gradient stream when the parameter owns a slot)."""
+
+    @staticmethod
+    def forward(ctx, x, blocks, *weights):
+        """blocks: list of dicts {convs: [(widx, scale, shift_bf16 or None, stride, padding, wq)] for conv1, conv2, conv3,
+        ds: the same tuple for the downsample conv or None}; `weights` are the fp32 parameters (widx indexes them)."""
+        acts = []
+        for blk in blocks:
+            c1, c2, c3 = blk["convs"]
+            if blk["ds"] is not None:
+                d = blk["ds"]
+                idt = F.conv2d(x, d[5], None, d[3], d[4])
+            else:
+                idt = x
+            o1 = torch.cudnn_convolution_relu(x, c1[5], c1[2], c1[3], c1[4], (1, 1), 1)
+            o2 = torch.cudnn_convolution_relu(o1, c2[5], c2[2], c2[3], c2[4], (1, 1), 1)
+            out = torch.cudnn_convolution_add_relu(o2, c3[5], idt, 1.0, c3[2], c3[3], c3[4], (1, 1), 1)
+            acts.append((x, o1, o2, out))
+            x = out
+        ctx.blocks, ctx.acts, ctx.weights = blocks, acts, weights
+        ctx.direct = [A._use(w)[0] if ctx.needs_input_grad[2 + i] else False for i, w in enumerate(weights)]
+        return x
+
+    @staticmethod
+    def _wgrad(ctx, grads, conv, g, x):
+        widx, scale, _, stride, padding, wq = conv
+        w = ctx.weights[widx]
+        if not ctx.needs_input_grad[2 + widx]:
+            return
+        cb = torch.ops.aten.convolution_backward
+        s4 = scale.view(-1, 1, 1, 1)
+        if ctx.direct[widx]:
+            with A._OffCriticalPath(w._fod_reducer, g, x):
+                dwq = cb(g, x, wq, None, stride, padding, (1, 1), False, (0, 0), 1, (False, True, False))[1]
+                if dwq.dtype == BF16 and dwq.permute(0, 2, 3, 1).is_contiguous() and w.grad.is_contiguous():
+                    ops.conv_wgrad_unfold(dwq, s4.view(-1), w.grad)
+                else:
+                    w.grad.addcmul_(dwq.float(), s4)
+            A._done(w)
+        else:
+            dwq = cb(g, x, wq, None, stride, padding, (1, 1), False, (0, 0), 1, (False, True, False))[1]
+            grads[widx] = dwq.float() * s4
+
+    @staticmethod
+    def backward(ctx, dy):
+        cb = torch.ops.aten.convolution_backward
+        grads = [None] * len(ctx.weights)
+
+        def dgrad(conv, g, x):
+            return cb(g, x, conv[5], None, conv[3], conv[4], (1, 1), False, (0, 0), 1, (True, False, False))[0]
+
+        def like(t, ref):  # the fused mask kernel wants identical dense layouts
+            return t if t.stride() == ref.stride() else t.contiguous(memory_format=torch.channels_last)
+
+        ga, gb = dy, None
+        for bi in range(len(ctx.blocks) - 1, -1, -1):
+            blk = ctx.blocks[bi]
+            x, o1, o2, out = ctx.acts[bi]
+            c1, c2, c3 = blk["convs"]
+            g3 = ops.relu_bwd_add(like(ga, out), None if gb is None else like(gb, out), out)
+            need_dx = bi > 0 or ctx.needs_input_grad[0]
+            g2 = ops.relu_bwd_add(like(dgrad(c3, g3, o2), o2), None, o2)
+            _BottleneckStackFn._wgrad(ctx, grads, c3, g3, o2)
+            g1 = ops.relu_bwd_add(like(dgrad(c2, g2, o1), o1), None, o1)
+            _BottleneckStackFn._wgrad(ctx, grads, c2, g2, o1)
+            ga = dgrad(c1, g1, x) if need_dx else None
+            _BottleneckStackFn._wgrad(ctx, grads, c1, g1, x)
+            if blk["ds"] is not None:
+                gb = dgrad(blk["ds"], g3, x) if need_dx else None
+                _BottleneckStackFn._wgrad(ctx, grads, blk["ds"], g3, x)
+            else:
+                gb = g3
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = ga + gb
+        ctx.acts = None
+        return (dx, None) + tuple(grads)
+
+
 def _conv_bn(x, conv, bn, relu, z=None, wq=None, shift=True, extra_shift=None):
     """Frozen-BN fold: conv(x, W)·s + t == conv(x, W·s) + t (backbone.py:53-63).  shift=False leaves t out (the caller
     adds it elsewhere); extra_shift is added to t."""
@@ -327,6 +416,7 @@ class CDetrBackbone(nn.Module):
         self.input_proj = nn.Conv2d(self.num_channels, hidden_dim, kernel_size=(1, 1))
         self.compute_dtype = BF16
         self.fold_frozen_bn = name not in ("resnet18", "resnet34")  # Bottleneck layout; BasicBlock uses the stock path
+        self.fuse_backbone_backward = True  # layer2-4 as one autograd node with fused mask(+add) passes (training)
 
     def _body_folded(self, x):
         """torchvision ResNet (Bottleneck) forward with every conv+FrozenBN(+add)+ReLU group as one fused op."""
@@ -353,8 +443,28 @@ class CDetrBackbone(nn.Module):
             x = ops.maxpool3x3s2_nhwc(x)  # frozen stem (paper.py:102-109): forward only, one HBM-bound kernel
         else:
             x = mp(x)
+        stack, weights = [], []
         for name in ("layer1", "layer2", "layer3", "layer4"):
             for blk in b[name]:
+                trainable = blk.conv1.weight.requires_grad
+                if (trainable and torch.is_grad_enabled() and x.is_cuda and x.dtype == BF16 and _ConvAffineAct.fused_ok
+                        and self.fuse_backbone_backward and all(c.weight in pre for c in self._block_convs(blk))):
+                    # trainable stages (layer2-4) in training: collected and run as ONE autograd node below
+                    def spec(conv, bn, shift=True, extra=None):
+                        s_, _ = bn.fold()
+                        t = bn._fold_tq if shift else None
+                        if t is not None and extra is not None:
+                            t = t + extra
+                        weights.append(conv.weight)
+                        return (len(weights) - 1, s_, t, conv.stride, conv.padding, pre[conv.weight])
+                    ds = blk.downsample
+                    stack.append({"convs": [spec(blk.conv1, blk.bn1), spec(blk.conv2, blk.bn2),
+                                            spec(blk.conv3, blk.bn3, extra=ds[1]._fold_tq if ds is not None else None)],
+                                  "ds": spec(ds[0], ds[1], shift=False) if ds is not None else None})
+                    continue
+                if stack:  # (not reached with torchvision's layer order: trainable stages come last)
+                    x = _BottleneckStackFn.apply(x, stack, *weights)
+                    stack, weights = [], []
                 extra = None
                 if blk.downsample is None:
                     idt = x
@@ -367,7 +477,16 @@ class CDetrBackbone(nn.Module):
                 o = _conv_bn(x, blk.conv1, blk.bn1, True, wq=pre.get(blk.conv1.weight))
                 o = _conv_bn(o, blk.conv2, blk.bn2, True, wq=pre.get(blk.conv2.weight))
                 x = _conv_bn(o, blk.conv3, blk.bn3, True, idt, wq=pre.get(blk.conv3.weight), extra_shift=extra)
+        if stack:
+            x = _BottleneckStackFn.apply(x, stack, *weights)
         return x
+
+    @staticmethod
+    def _block_convs(blk):
+        convs = [blk.conv1, blk.conv2, blk.conv3]
+        if blk.downsample is not None:
+            convs.append(blk.downsample[0])
+        return convs
 
     def _prefold(self, x):
         """W·s (bf16, channels_last) of every TRAINABLE body conv for this step in one launch (ops.ConvFoldTable);

@@ -297,6 +297,24 @@ def maxpool3x3s2_nhwc(x):
     return y
 
 
+def relu_bwd_add(a, b, y):
+    """(a [+ b]) * (y > 0) in one pass; a, b, y bf16 CUDA tensors of one shape AND one memory layout (dense)."""
+    L = lib.load()
+    _chk_bf16(a, "relu_bwd_add a")
+    _chk_bf16(y, "relu_bwd_add y")
+    assert a.shape == y.shape and a.stride() == y.stride() and (b is None or (b.shape == a.shape and b.stride() == a.stride()))
+    out = torch.empty_like(a)  # preserves the (dense) strides
+    assert out.stride() == a.stride() and a.numel() % 8 == 0
+    _t = prof.begin()
+    ptrs = (_p(a), _p(b), _p(y), _p(out), a.numel())
+    call = lambda: L.fod_relu_bwd_add(*ptrs, _stream())
+    lib.check(call(), "fod_relu_bwd_add")
+    prof.end(_t, "relu_bwd_add%d_%d" % (3 if b is not None else 2, a.numel()), 0.0, (8.0 if b is not None else 6.0) * a.numel(),
+             replay=call if _t is not None else None, keep=(a, b, y, out))
+    LAUNCH_COUNTS["relu_bwd_add_kernel"] += 1
+    return out
+
+
 def stem_weights(w, scale):
     """(64,3,7,7) fp32 conv weight and (64) fold scale -> the (64,192) bf16 operand of fod_stem_conv7x7s2:
     [o][kh*24 + 1 + kw*3 + c] = w[o][c][kh][kw] * scale[o], zeros elsewhere."""

@@ -135,6 +135,12 @@ int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int
  * everything before layer2).  y is (N, (H-1)/2+1, (W-1)/2+1, C). */
 int fod_maxpool3x3s2_nhwc(const void* x, void* y, int32_t N, int32_t H, int32_t W, int32_t C, void* stream);
 
+/* Fused ReLU backward with an optional gradient add for the backbone's bottleneck blocks: out = (a [+ b]) * (y > 0) on
+ * flat bf16 arrays of n elements with identical layouts (n % 8 == 0, 16-byte aligned).  Replaces autograd's gradient
+ * accumulation (block input used by conv1 and by the identity path, torchvision Bottleneck.forward as built by
+ * future_od/models/paper.py:94-98) followed by threshold_backward with one pass. */
+int fod_relu_bwd_add(const void* a, const void* b /* or NULL */, const void* y, void* out, int64_t n, void* stream);
+
 /* ResNet stem: conv 7x7 / stride 2 / pad 3, 3 -> 64 channels, frozen BatchNorm folded, ReLU
  * (ConditionalDETR/models/backbone.py:88-96 -> torchvision resnet conv1+bn1+relu; frozen, forward only: paper.py:102-109).
  * x (N,H,W,3) bf16 NHWC, W % 8 == 0; wk (64,192) bf16 with wk[o][kh*24 + 1 + kw*3 + c] = W[o][c][kh][kw]*scale[o] and
