@@ -158,22 +158,27 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
     } else if (warp == 5) {
         if (lane == 0) {
             constexpr uint32_t idesc_s = umma_idesc_bf16(AT_BM, AT_BN, 0, 0);
-            constexpr uint32_t idesc_pv = umma_idesc_bf16(AT_BM, AT_D, 0, 1);  // B = V is MN-major
-            const uint32_t q_addr = smem_u32(smem + L::kQ);
-            const uint32_t p_addr = smem_u32(smem + L::kP);
+            // O += P·V and L += P·1 are ONE instruction per 16 keys: B = [V | ones] with N = 64 (two MN-major chunks of 32
+            // columns, the second one LBO bytes after the first), D = the adjacent O and L column blocks.  These skinny
+            // MMAs are bound by the fetch of their A operand (the 128x16 P slice, ~65 clk whatever N is): issuing the
+            // row-sum product separately doubled that cost.
+            constexpr uint32_t idesc_pv = umma_idesc_bf16(AT_BM, 2 * AT_D, 0, 1);  // B is MN-major
+            // stage-0 descriptors, built once and stepped with one add per instruction
+            const uint64_t dQ0 = umma_smem_desc(smem_u32(smem + L::kQ), 16, 512, 4);
+            const uint64_t dK0 = umma_smem_desc(smem_u32(smem + L::kK), 16, 512, 4);
+            const uint64_t dP0 = umma_smem_desc(smem_u32(smem + L::kP), 16, 1024, 2);
+            const uint32_t v0_addr = smem_u32(smem + L::kV), ones_addr = smem_u32(smem + L::kOnes);
             auto issue_S = [&](int j) {
                 const int s = j % AT_KV_STAGES;
                 mbar_wait(kv_full + s, (j / AT_KV_STAGES) & 1);
                 tc_fence_after();
-                const uint32_t k_addr = smem_u32(smem + L::kK + s * NPARTS * AT_TILE_BYTES);
+                const uint64_t dk = umma_desc_adv(dK0, s * NPARTS * AT_TILE_BYTES);
 #pragma unroll
                 for (int part = 0; part < NPARTS; ++part) {
 #pragma unroll
-                    for (int k = 0; k < AT_D / 16; ++k) {
-                        const uint64_t da = umma_smem_desc(q_addr + part * AT_TILE_BYTES + k * 32, 16, 512, 4);
-                        const uint64_t db = umma_smem_desc(k_addr + part * AT_TILE_BYTES + k * 32, 16, 512, 4);
-                        umma_bf16_ss(tmem_S, da, db, idesc_s, (part | k) ? 1u : 0u);
-                    }
+                    for (int k = 0; k < AT_D / 16; ++k)
+                        umma_bf16_ss(tmem_S, umma_desc_adv(dQ0, part * AT_TILE_BYTES + k * 32),
+                                     umma_desc_adv(dk, part * AT_TILE_BYTES + k * 32), idesc_s, (part | k) ? 1u : 0u);
                 }
                 umma_commit(s_full);
             };
@@ -192,17 +197,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
 #endif
                 mbar_wait(p_full, j & 1);
                 tc_fence_after();
-                const uint32_t v_addr = smem_u32(smem + L::kV + s * AT_TILE_BYTES);
-                const uint32_t ones_addr = smem_u32(smem + L::kOnes);
+                const uint32_t v_addr = v0_addr + s * AT_TILE_BYTES;
+                // [V | ones]: 16 keys per instruction = 16 rows of 64 B (+1024 B in both chunks); chunk 1 (the ones tile,
+                // every element equal, so row offsets inside it do not matter) lies ones_addr - v_addr bytes after chunk 0
+                const uint64_t dv = umma_smem_desc(v_addr, ones_addr - v_addr, 512, 4);
+                const uint64_t dp = umma_desc_adv(dP0, (j % L::kPBuf) * AT_P_BYTES);
 #pragma unroll
-                for (int kk = 0; kk < AT_BN / 16; ++kk) {
-                    const uint64_t da = umma_smem_desc(p_addr + (j % L::kPBuf) * AT_P_BYTES + (kk >> 2) * (AT_BM * 128) + (kk & 3) * 32, 16, 1024, 2);
-                    const uint64_t db = umma_smem_desc(v_addr + kk * 1024, 4096, 512, 4);
-                    const uint64_t d1 = umma_smem_desc(ones_addr + kk * 1024, 4096, 512, 4);
-                    const uint32_t acc = (j | kk) ? 1u : 0u;  // O and L accumulate across key tiles
-                    umma_bf16_ss(tmem_O, da, db, idesc_pv, acc);
-                    umma_bf16_ss(tmem_L, da, d1, idesc_pv, acc);
-                }
+                for (int kk = 0; kk < AT_BN / 16; ++kk)
+                    umma_bf16_ss(tmem_O, umma_desc_adv(dp, (kk >> 2) * (AT_BM * 128) + (kk & 3) * 32), umma_desc_adv(dv, kk * 1024),
+                                 idesc_pv, (j | kk) ? 1u : 0u);  // O and L accumulate across key tiles
                 umma_commit(pv_full(j));
                 umma_commit(kv_empty + s);
 #if !FOD_ATTN_EARLY_S
