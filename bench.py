@@ -210,7 +210,9 @@ def run_cuda(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     detr_args = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
-    model = build_model(Namespace(device=dev, distributed=False), detr_args)
+    # dropout 0.1 is what the reference trains with (runs/_model.py:52, transformer.py layer defaults): the headline
+    # is measured with it ON; the dropout-free step is re-measured below and reported beside it (`dropout_off`)
+    model = build_model(Namespace(device=dev, distributed=False), detr_args, dropout=args.dropout)
     model.load_state_dict(synthetic_state_dict(_template(), seed=0, residual_gain=0.5))
     model.train()
     core = model
@@ -317,6 +319,18 @@ def run_cuda(args):
     sampler.join(timeout=2)
     check_match_status(core._criterion.last_status)
 
+    # the same step with dropout off (the egodeep block then collapses to one row per sequence)
+    ms_off = None
+    if args.dropout > 0 and args.dropout_off_leg:
+        from fod_b200 import set_dropout
+        set_dropout(core, 0.0)
+        if use_graph:
+            step.recapture()
+        for i in range(3):
+            step(dev_pool[i % n_pool])
+        ms_off = timed(lambda i: step(dev_pool[i % n_pool]), args.steps)
+        check_match_status(core._criterion.last_status)
+
     def finish():
         # Captured NCCL kernels keep the communicator busy: tearing the process group down with the graph alive can
         # block forever.  All ranks meet at a barrier, flush, and leave without the NCCL teardown.
@@ -343,7 +357,7 @@ def run_cuda(args):
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": {"workload": WORKLOAD, "global_batch": BATCH * world, "parallelism": "dp%d" % world,
                        "l2": "no explicit flush: one step streams >10 GB of activations through the 126 MB L2",
-                       "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": 0.0, "cuda_graph": use_graph, "cudnn_benchmark": bool(args.cudnn_benchmark),
+                       "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": args.dropout, "cuda_graph": use_graph, "cudnn_benchmark": bool(args.cudnn_benchmark),
                        "optimizer": "fused flat clip+AdamW (fod_flat_adamw_step)" if flat is not None else "torch fused AdamW",
                        "grad_allreduce": ("bucketed NCCL AVG, %g MB fp32 buckets, side stream inside the graph" % args.bucket_mb) if world > 1 else None},
             "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
@@ -354,6 +368,9 @@ def run_cuda(args):
     isolated = prof.isolated_us(list(kern)) if args.kernel_events else {}
     line.update(prof.roofline_report(kern, peaks, ms_inst, _traffic(), isolated, n_inst,
                                      attention_s=(H // 32) * (W // 32)))
+    if ms_off is not None:
+        line["dropout_off"] = {"value": clips / (ms_off / 1e3), "unit": UNIT, "ms_per_step": ms_off / args.steps,
+                               "note": "same step with every dropout probability set to 0 (device-timed, resident inputs)"}
     line["instrumented_region"] = {"steps": n_inst, "ms_per_step": ms_inst / n_inst if n_inst else None}
     if not args.no_cpu_baseline and world == 1:
         step = cpu_reference_step_fn(1)
@@ -422,6 +439,8 @@ def main():
     ap.add_argument("--ref-device", default="cpu", choices=["cpu", "cuda"],
                     help="with --impl reference: cuda = opt-in side measurement of the eager torch port on the GPU")
     ap.add_argument("--ref-autocast", type=int, default=0, help="with --ref-device cuda: run under autocast(bf16)")
+    ap.add_argument("--dropout", type=float, default=0.1, help="dropout probability of every transformer block (reference: 0.1)")
+    ap.add_argument("--dropout-off-leg", type=int, default=1, help="1: also time the step with dropout off")
     ap.add_argument("--graphs", type=int, default=1, help="1: replay the whole step as one CUDA graph (single GPU)")
     ap.add_argument("--kernel-events", type=int, default=1, help="1: bracket each of our kernel launches with CUDA events")
     ap.add_argument("--flat", type=int, default=1, help="1: flat parameter/gradient arenas with the fused clip+AdamW kernel")

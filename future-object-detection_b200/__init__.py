@@ -9,7 +9,7 @@ __version__ = "0.2.0"
 
 def __getattr__(name):  # lazy: `import fod_b200` stays cheap and CPU-safe
     if name in ("build_model", "SpatioTemporalDETRArgs", "SpatioTemporalDETR", "HungarianMatcher", "SetCriterion",
-                "FuturePredCore", "SeparateEncoder", "JointEncoder"):
+                "FuturePredCore", "SeparateEncoder", "JointEncoder", "set_dropout"):
         from . import st_detr
         return getattr(st_detr, name)
     if name in ("ApAccumulator", "aggregate_mean_average_precision"):  # future_od/utils/od_map.py, trainer.py:205-236

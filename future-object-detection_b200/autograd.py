@@ -3,7 +3,9 @@
 Conventions: activations are 2-D (rows, channels) bf16, contiguous; `w` is the fp32 weight (a Parameter, or a
 cat/pad of Parameters — it only routes the gradient), `wq` its bf16 copy that the kernels read.  Weight gradients
 are produced in fp32 by the split-K MN-major GEMM (dW = dYᵀ·X, atomically reduced), activation gradients in bf16.
-Dropout is not implemented (p = 0): parity with the reference is defined with dropout disabled.
+Train-mode dropout (ops.drop_site) is applied inside the GEMM epilogues and on the attention weights; the masks are
+regenerated in backward from the site's (p, call) pair (include/fod_b200.h fod_dropout) — nothing is stored.  Parity with
+the reference is defined with dropout disabled and statistical with it on.
 """
 import torch
 from torch.autograd import Function
@@ -149,7 +151,7 @@ def bias_grad_into(p, dy):
     _done(p)
 
 
-def input_grad(dy, wq, **kw):
+def input_grad(dy, wq, **kw):  # kw: relu_mask / mask_scale / residual / colsum_out
     """dX (rows, K) bf16 = dy (rows, N) · W (N, K), W read in its nn.Linear layout (MN-major B operand)."""
     return ops.gemm(dy, wq, b_mn=True, **kw)
 
@@ -204,36 +206,42 @@ class LinearLNFn(Function):
     """y = LayerNorm(res + x·Wᵀ + b): attention out_proj + residual + norm (transformer.py:417, 272, 286)."""
 
     @staticmethod
-    def forward(ctx, x, res, w, b, wq, gamma, beta, eps, need_grad):
+    def forward(ctx, x, res, w, b, wq, gamma, beta, eps, need_grad, drop=None):
+        """drop: dropout on the sub-block output x·Wᵀ + b before the residual (transformer.py:271,285,417: dropout_sa /
+        dropout_ia / attn_dropout)."""
         if need_grad:
-            y, pre, mean, rstd = ops.gemm(x, wq, bias=b, residual=res, ln=(gamma, beta, eps), save_ln=True)
+            y, pre, mean, rstd = ops.gemm(x, wq, bias=b, residual=res, ln=(gamma, beta, eps), save_ln=True, drop=drop)
             ctx.save_for_backward(x, wq, pre, mean, rstd, gamma)
             ctx.direct = _use_all(w, b, gamma, beta)
             ctx.params = (w, b, gamma, beta)
+            ctx.drop = drop
         else:
-            y = ops.gemm(x, wq, bias=b, residual=res, ln=(gamma, beta, eps))
+            y = ops.gemm(x, wq, bias=b, residual=res, ln=(gamma, beta, eps), drop=drop)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x, wq, pre, mean, rstd, gamma = ctx.saved_tensors
+        drop = ctx.drop
         if ctx.direct:  # all four parameters own arena slots: every gradient kernel accumulates in place
             w, b, g, bt = ctx.params
-            dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, g.grad, bt.grad, dzsum=b.grad)
-            dx = input_grad(dz, wq)
-            weight_grad_into(w, dz, x)
+            dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, g.grad, bt.grad, dzsum=b.grad, drop=drop)
+            dz, du = dz if drop is not None else (dz, dz)  # gradients of the residual and of the (dropped-out) linear output
+            dx = input_grad(du, wq)
+            weight_grad_into(w, du, x)
             for q in (b, g, bt):
                 _done(q)
-            return dx, dz, None, None, None, None, None, None, None
+            return dx, dz, None, None, None, None, None, None, None, None
         acc = torch.zeros((3, gamma.numel()), dtype=torch.float32, device=gamma.device)  # dgamma, dbeta, db
-        dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, acc[0], acc[1], dzsum=acc[2])
-        dx = input_grad(dz, wq)
-        dw = weight_grad(dz, x)
-        return dx, dz, dw, acc[2], None, acc[0], acc[1], None, None
+        dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, acc[0], acc[1], dzsum=acc[2], drop=drop)
+        dz, du = dz if drop is not None else (dz, dz)
+        dx = input_grad(du, wq)
+        dw = weight_grad(du, x)
+        return dx, dz, dw, acc[2], None, acc[0], acc[1], None, None, None
 
 
-def linear_ln(x, res, w, b, wq, gamma, beta, eps=1e-5):
-    return LinearLNFn.apply(x, res, w, b, wq, gamma, beta, eps, torch.is_grad_enabled())
+def linear_ln(x, res, w, b, wq, gamma, beta, eps=1e-5, drop=None):
+    return LinearLNFn.apply(x, res, w, b, wq, gamma, beta, eps, torch.is_grad_enabled(), drop)
 
 
 class FFNLNFn(Function):
@@ -241,43 +249,50 @@ class FFNLNFn(Function):
     :103-108,116-118 (egodeep MLP).  Backward: LN bwd -> dH GEMM with fused ReLU mask -> dX GEMM with fused residual."""
 
     @staticmethod
-    def forward(ctx, x, w1, b1, w1q, w2, b2, w2q, gamma, beta, eps, need_grad):
-        h = ops.gemm(x, w1q, bias=b1, relu=True)
+    def forward(ctx, x, w1, b1, w1q, w2, b2, w2q, gamma, beta, eps, need_grad, drop_h=None, drop_o=None):
+        """drop_h: dropout on the hidden after the ReLU, drop_o: on the FFN output before the residual
+        (transformer.py:407-412 mlp = Linear, ReLU, Dropout, Linear, Dropout; :228-235,310 decoder)."""
+        h = ops.gemm(x, w1q, bias=b1, relu=True, drop=drop_h)  # saved AFTER dropout: its zeros cover both masks
         if need_grad:
-            y, pre, mean, rstd = ops.gemm(h, w2q, bias=b2, residual=x, ln=(gamma, beta, eps), save_ln=True)
+            y, pre, mean, rstd = ops.gemm(h, w2q, bias=b2, residual=x, ln=(gamma, beta, eps), save_ln=True, drop=drop_o)
             ctx.save_for_backward(x, h, w1q, w2q, pre, mean, rstd, gamma)
             ctx.direct = _use_all(w1, b1, w2, b2, gamma, beta)
             ctx.params = (w1, b1, w2, b2, gamma, beta)
+            ctx.drops = (drop_h, drop_o)
         else:
-            y = ops.gemm(h, w2q, bias=b2, residual=x, ln=(gamma, beta, eps))
+            y = ops.gemm(h, w2q, bias=b2, residual=x, ln=(gamma, beta, eps), drop=drop_o)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x, h, w1q, w2q, pre, mean, rstd, gamma = ctx.saved_tensors
+        drop_h, drop_o = ctx.drops
+        hs = 1.0 / (1.0 - drop_h[0]) if drop_h is not None else 1.0  # kept hidden elements carry 1/(1-p)
         if ctx.direct:
             w1, b1, w2, b2, g, bt = ctx.params
-            dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, g.grad, bt.grad, dzsum=b2.grad)
-            dh = input_grad(dz, w2q, relu_mask=h, colsum_out=b1.grad)
-            weight_grad_into(w2, dz, h)
+            dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, g.grad, bt.grad, dzsum=b2.grad, drop=drop_o)
+            dz, du = dz if drop_o is not None else (dz, dz)
+            dh = input_grad(du, w2q, relu_mask=h, colsum_out=b1.grad, mask_scale=hs)
+            weight_grad_into(w2, du, h)
             dx = input_grad(dh, w1q, residual=dz)
             weight_grad_into(w1, dh, x)
             for q in (b1, b2, g, bt):
                 _done(q)
-            return dx, None, None, None, None, None, None, None, None, None, None
+            return dx, None, None, None, None, None, None, None, None, None, None, None, None
         d = gamma.numel()
         acc = torch.zeros((3 * d + h.shape[1],), dtype=torch.float32, device=gamma.device)  # dgamma, dbeta, db2, db1
         dgamma, dbeta, db2, db1 = acc[:d], acc[d:2 * d], acc[2 * d:3 * d], acc[3 * d:]
-        dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, dgamma, dbeta, dzsum=db2)
-        dh = input_grad(dz, w2q, relu_mask=h, colsum_out=db1)  # ReLU mask and the bias-1 gradient ride in the epilogue
-        dw2 = weight_grad(dz, h)
+        dz = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, dgamma, dbeta, dzsum=db2, drop=drop_o)
+        dz, du = dz if drop_o is not None else (dz, dz)
+        dh = input_grad(du, w2q, relu_mask=h, colsum_out=db1, mask_scale=hs)  # ReLU mask and the bias-1 gradient ride in the epilogue
+        dw2 = weight_grad(du, h)
         dx = input_grad(dh, w1q, residual=dz)
         dw1 = weight_grad(dh, x)
-        return dx, dw1, db1, None, dw2, db2, None, dgamma, dbeta, None, None
+        return dx, dw1, db1, None, dw2, db2, None, dgamma, dbeta, None, None, None, None
 
 
-def ffn_ln(x, w1, b1, w1q, w2, b2, w2q, gamma, beta, eps=1e-5):
-    return FFNLNFn.apply(x, w1, b1, w1q, w2, b2, w2q, gamma, beta, eps, torch.is_grad_enabled())
+def ffn_ln(x, w1, b1, w1q, w2, b2, w2q, gamma, beta, eps=1e-5, drop_h=None, drop_o=None):
+    return FFNLNFn.apply(x, w1, b1, w1q, w2, b2, w2q, gamma, beta, eps, torch.is_grad_enabled(), drop_h, drop_o)
 
 
 class AddLNFn(Function):
@@ -322,43 +337,44 @@ class SelfAttnFn(Function):
     torch.nn.MultiheadAttention core (transformer.py:404) and SlotToSlotAttention's (transformer.py:79-81)."""
 
     @staticmethod
-    def forward(ctx, qkv, heads, scale):
+    def forward(ctx, qkv, heads, scale, drop=None):
         c = heads * 32
-        out, lse = ops.attn_fwd(qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:], scale, heads)
+        out, lse = ops.attn_fwd(qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:], scale, heads, drop=drop)
         ctx.save_for_backward(qkv, out, lse)
-        ctx.cfg = (heads, scale)
+        ctx.cfg = (heads, scale, drop)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         qkv, out, lse = ctx.saved_tensors
-        heads, scale = ctx.cfg
+        heads, scale, drop = ctx.cfg
         c = heads * 32
         dq, _, _, _, _ = ops.attn_bwd(qkv[..., :c], qkv[..., c:2 * c], qkv[..., 2 * c:], out, lse, _bf(dout), scale,
-                                      heads, fused="qkv")
-        return dq._base if dq._base is not None else dq, None, None
+                                      heads, fused="qkv", drop=drop)
+        return dq._base if dq._base is not None else dq, None, None, None
 
 
-def self_attention(qkv, heads=8, scale=32 ** -0.5):
-    return SelfAttnFn.apply(qkv, heads, scale)
+def self_attention(qkv, heads=8, scale=32 ** -0.5, drop=None):
+    """drop: dropout on the softmax weights (torch.nn.MultiheadAttention(dropout=...), attention.py:370)."""
+    return SelfAttnFn.apply(qkv, heads, scale, drop)
 
 
 class PlainAttnFn(Function):
     """Single-part attention on separate dense q (B,Lq,C), k, v (B,Lk,C) — EgodeepAttention with several IMU keys."""
 
     @staticmethod
-    def forward(ctx, q, k, v, heads, scale):
-        out, lse = ops.attn_fwd(q, k, v, scale, heads)
+    def forward(ctx, q, k, v, heads, scale, drop=None):
+        out, lse = ops.attn_fwd(q, k, v, scale, heads, drop=drop)
         ctx.save_for_backward(q, k, v, out, lse)
-        ctx.cfg = (heads, scale)
+        ctx.cfg = (heads, scale, drop)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         q, k, v, out, lse = ctx.saved_tensors
-        heads, scale = ctx.cfg
-        dq, dk, dv, _, _ = ops.attn_bwd(q, k, v, out, lse, _bf(dout), scale, heads)
-        return dq, dk, dv, None, None
+        heads, scale, drop = ctx.cfg
+        dq, dk, dv, _, _ = ops.attn_bwd(q, k, v, out, lse, _bf(dout), scale, heads, drop=drop)
+        return dq, dk, dv, None, None, None
 
 
 class CrossAttnFn(Function):
@@ -367,28 +383,28 @@ class CrossAttnFn(Function):
     kp (S, 256) batch-invariant; qs (B, M, 256) or batch-invariant (M, 256)."""
 
     @staticmethod
-    def forward(ctx, qc, qs, kv, kp, heads, scale):
+    def forward(ctx, qc, qs, kv, kp, heads, scale, drop=None):
         c = heads * 32
-        out, lse = ops.attn_fwd(qc, kv[..., :c], kv[..., c:], scale, heads, q2=qs, k2=kp, batch=kv.shape[0])
+        out, lse = ops.attn_fwd(qc, kv[..., :c], kv[..., c:], scale, heads, q2=qs, k2=kp, batch=kv.shape[0], drop=drop)
         ctx.save_for_backward(qc, qs, kv, kp, out, lse)
-        ctx.cfg = (heads, scale)
+        ctx.cfg = (heads, scale, drop)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         qc, qs, kv, kp, out, lse = ctx.saved_tensors
-        heads, scale = ctx.cfg
+        heads, scale, drop = ctx.cfg
         c = heads * 32
         dq1, dk1, _, dq2, dk2 = ops.attn_bwd(qc, kv[..., :c], kv[..., c:], out, lse, _bf(dout), scale, heads, q2=qs,
-                                             k2=kp, fused="kv")
+                                             k2=kp, fused="kv", drop=drop)
         dkv = dk1._base
         dqs = dq2 if qs.dim() == 3 else dq2.sum(0)
         dkp = dk2.sum(0) if kp.dim() == 2 else dk2
-        return dq1, dqs, dkv, dkp, None, None
+        return dq1, dqs, dkv, dkp, None, None, None
 
 
-def cross_attention(qc, qs, kv, kp, heads=8, scale=64 ** -0.5):
-    return CrossAttnFn.apply(qc, qs, kv, kp, heads, scale)
+def cross_attention(qc, qs, kv, kp, heads=8, scale=64 ** -0.5, drop=None):
+    return CrossAttnFn.apply(qc, qs, kv, kp, heads, scale, drop)
 
 
 class SetLossFn(Function):

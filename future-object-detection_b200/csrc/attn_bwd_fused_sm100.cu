@@ -21,6 +21,7 @@
 #include "fod_internal.h"
 #include "sm100_ptx.cuh"
 #include "tmap.h"
+#include "dropout.cuh"
 
 #ifndef FOD_AF_TRACE
 #define FOD_AF_TRACE 0
@@ -78,6 +79,7 @@ struct AttnBwdFusedParams {
     int B, H, Lq, Lk;
     int bm_q1, bm_k1, bm_q2, bm_k2, bm_v;
     float scale;
+    DropoutCfg drop;             // DROP kernels: the forward call's dropout on P, regenerated here
 };
 
 // One [128][32] fp32 accumulator tile, TMEM -> bf16 -> swizzled staging tile -> TMA store.  Executed by the four warps
@@ -106,7 +108,9 @@ __device__ __forceinline__ void af_store_tile(uint32_t taddr_lane, uint8_t* slot
     }
 }
 
-template <int NP>
+// DROP: out = dropout(P)·V in the forward pass (mask m, scale c = 1/(1-p)): dV takes P·m·c, dP = (dO·Vᵀ)·m·c, and
+// dS = P ⊙ (dP − delta) with the UNdropped P; delta = rowsum(dO ⊙ O) is unchanged.
+template <int NP, bool DROP>
 __global__ void __launch_bounds__(AF_THREADS, 1)
 attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant__ CUtensorMap tmK1,
                       const __grid_constant__ CUtensorMap tmQ2, const __grid_constant__ CUtensorMap tmK2,
@@ -363,10 +367,15 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
         };
 
         uint32_t vs[32], vp[32];
+        PhiloxKey key = {0u, 0u, 0u, 0u};
+        if (DROP) key = dropout_key(p.drop);
+        const unsigned long long lkp8 = (unsigned long long)((p.Lk + 7) >> 3);  // Philox groups per (padded) score row
         for (int t = 0; t < ntiles; ++t) {
             const int j = t / nqt, i = t - j * nqt;
             const float lse2 = s_lse[i * AF_T + row];
             const float dlt = s_dlt[i * AF_T + row];
+            const unsigned long long g_row =
+                (((unsigned long long)b * p.H + h) * p.Lq + (unsigned long long)min(i * AF_T + row, p.Lq - 1)) * lkp8;
             const int kvalid = p.Lk - j * AF_T;  // >= 1
             if (threadIdx.x == 0) AF_STAMP(0, t, 0);
             mbar_wait(s_full, t & 1);
@@ -387,12 +396,28 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
                     mbar_arrive(s_free);
                 }
                 if (threadIdx.x == 0) AF_STAMP(0, t, cc == 0 ? 2 : 5);
+                if (DROP) {
 #pragma unroll
-                for (int idx = 0; idx < 32; ++idx) {
-                    const float x = fast_exp2(fmaf(__uint_as_float(vs[idx]), sl2, -lse2));
-                    const float g = fmaf(__uint_as_float(vp[idx]), p.scale, -dlt);
-                    vs[idx] = __float_as_uint(x);
-                    vp[idx] = __float_as_uint(x * g);
+                    for (int qd = 0; qd < 4; ++qd) {
+                        const uint32_t keep = dropout_keep8(key, g_row + (unsigned long long)(j * (AF_T / 8) + c * 4 + qd), p.drop.thresh);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const int idx = qd * 8 + e;
+                            const float mk = ((keep >> e) & 1u) ? p.drop.scale : 0.f;
+                            const float x = fast_exp2(fmaf(__uint_as_float(vs[idx]), sl2, -lse2));
+                            const float g = fmaf(__uint_as_float(vp[idx]) * mk, p.scale, -dlt);
+                            vs[idx] = __float_as_uint(x * mk);  // dropout(P): the operand of dV
+                            vp[idx] = __float_as_uint(x * g);   // dS from the undropped P
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int idx = 0; idx < 32; ++idx) {
+                        const float x = fast_exp2(fmaf(__uint_as_float(vs[idx]), sl2, -lse2));
+                        const float g = fmaf(__uint_as_float(vp[idx]), p.scale, -dlt);
+                        vs[idx] = __float_as_uint(x);
+                        vp[idx] = __float_as_uint(x * g);
+                    }
                 }
                 if (kvalid < AF_T) {  // ragged last key tile (warp-uniform): keys beyond Lk contribute nothing
 #pragma unroll
@@ -539,17 +564,31 @@ int launch_attn_bwd_fused(const fod_attn_bwd_args* g, cudaStream_t st) {
     p.bm_q2 = two ? has_b(a->bsq2) : 0; p.bm_k2 = two ? has_b(a->bsk2) : 0;
     p.bm_v = has_b(a->bsv);
     p.scale = a->scale;
-    static bool attr[2] = {false, false};
-    if (!attr[two]) {
-        if (two) cudaFuncSetAttribute(attn_bwd_fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, FusedBwdSmem<2>::kTotal);
-        else cudaFuncSetAttribute(attn_bwd_fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, FusedBwdSmem<1>::kTotal);
-        attr[two] = true;
+    p.drop = {nullptr, 0u, 0u, 1.f};
+    const bool drop = a->drop.rng_state && a->drop.p > 0.f;
+    if (drop) {
+        if (!(a->drop.p < 1.f)) return fod_fail(FOD_E_ARG, "attn_bwd: dropout p must be in [0, 1)");
+        p.drop.state = reinterpret_cast<const unsigned long long*>(a->drop.rng_state);
+        p.drop.call = (unsigned int)a->drop.call;
+        p.drop.thresh = (unsigned int)(a->drop.p * 65536.f + 0.5f);
+        p.drop.scale = 1.f / (1.f - a->drop.p);
     }
     dim3 grid(a->H, a->B);
-    if (two) fod_launch(attn_bwd_fused_kernel<2>, grid, dim3(AF_THREADS), FusedBwdSmem<2>::kTotal, st, tq1, tk1, tq2, tk2, tv, tdo,
-                        tdq1, tdq2, tdk1, tdk2, tdv, p);
-    else fod_launch(attn_bwd_fused_kernel<1>, grid, dim3(AF_THREADS), FusedBwdSmem<1>::kTotal, st, tq1, tk1, tq2, tk2, tv, tdo,
-                    tdq1, tdq2, tdk1, tdk2, tdv, p);
+    auto launch = [&](auto kernel, int smem_bytes, bool& attr_done) {
+        if (!attr_done) {
+            cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+            attr_done = true;
+        }
+        fod_launch(kernel, grid, dim3(AF_THREADS), (size_t)smem_bytes, st, tq1, tk1, tq2, tk2, tv, tdo, tdq1, tdq2, tdk1, tdk2, tdv, p);
+    };
+    static bool attr[4] = {false, false, false, false};
+    if (two) {
+        if (drop) launch(attn_bwd_fused_kernel<2, true>, FusedBwdSmem<2>::kTotal, attr[3]);
+        else launch(attn_bwd_fused_kernel<2, false>, FusedBwdSmem<2>::kTotal, attr[2]);
+    } else {
+        if (drop) launch(attn_bwd_fused_kernel<1, true>, FusedBwdSmem<1>::kTotal, attr[1]);
+        else launch(attn_bwd_fused_kernel<1, false>, FusedBwdSmem<1>::kTotal, attr[0]);
+    }
     return fod_check_launch("attn_bwd_fused_kernel");
 }
 

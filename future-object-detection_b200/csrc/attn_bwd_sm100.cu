@@ -9,6 +9,7 @@
 #include "fod_internal.h"
 #include "sm100_ptx.cuh"
 #include "tmap.h"
+#include "dropout.cuh"
 
 namespace fod {
 
@@ -30,6 +31,7 @@ struct AttnBwdParams {
     int B, H, Lq, Lk;
     int bm_q1, bm_k1, bm_q2, bm_k2, bm_v;
     float scale;
+    DropoutCfg drop;  // state != nullptr: the forward call's dropout on P (mask index ((b*H+h)*Lq + q) * roundup8(Lk) + k)
 };
 
 __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
@@ -195,6 +197,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
         const float sl2 = p.scale * AB_LOG2E;
         uint8_t* sDS = smem + L::kDS;
         uint32_t vs[32], vp[32];
+        PhiloxKey key = {0u, 0u, 0u, 0u};
+        if (p.drop.state) key = dropout_key(p.drop);
+        const unsigned long long g_row =
+            (((unsigned long long)b * p.H + h) * p.Lq + (unsigned long long)min(q, p.Lq - 1)) * (unsigned long long)((p.Lk + 7) >> 3);
         for (int j = 0; j < nkt; ++j) {
             mbar_wait(s_full, j & 1);  // also implies the dQ MMAs of tile j-1 (reading sDS) have retired
             tc_fence_after();
@@ -205,6 +211,15 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
                 tmem_ld_32x32b_x32(tmem_dP + lane_off + c * 32, vp);
                 tmem_ld_wait();
                 float ds[32];
+                if (p.drop.state) {  // dP = (dO·Vᵀ) ⊙ mask / (1-p)
+#pragma unroll
+                    for (int qd = 0; qd < 4; ++qd) {
+                        const uint32_t keep = dropout_keep8(key, g_row + (unsigned long long)(j * (AB_T / 8) + c * 4 + qd), p.drop.thresh);
+#pragma unroll
+                        for (int e = 0; e < 8; ++e)
+                            vp[qd * 8 + e] = __float_as_uint(((keep >> e) & 1u) ? __uint_as_float(vp[qd * 8 + e]) * p.drop.scale : 0.f);
+                    }
+                }
 #pragma unroll
                 for (int i = 0; i < 32; ++i) {
                     const float pr = fast_exp2(fmaf(__uint_as_float(vs[i]), sl2, -lse2));
@@ -377,6 +392,10 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
         uint8_t* sDST = smem + L::kDST;
         uint32_t vs[32], vp[32];
         const long long st0 = ((long long)b * p.H + h) * p.Lq;
+        PhiloxKey key = {0u, 0u, 0u, 0u};
+        if (p.drop.state) key = dropout_key(p.drop);
+        const unsigned long long lkp8 = (unsigned long long)((p.Lk + 7) >> 3);
+        const unsigned long long kgrp = (unsigned long long)((k0 + row) >> 3);  // this key's group of 8 within a score row
         for (int i = 0; i < nqt; ++i) {
             float* lse_s = stat + (i & 1) * 2 * AB_T;
             float* dl_s = lse_s + AB_T;
@@ -395,11 +414,29 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
                 tmem_ld_32x32b_x32(tmem_dP + lane_off + c * 32, vp);
                 tmem_ld_wait();
                 float pt[32], ds[32];
+                uint32_t keepbits = 0xffffffffu;  // bit j: the weight of (query c*32 + j, this key) was kept
+                if (p.drop.state) {
+                    // The mask groups run along the keys: the 8 lanes that share a key group each draw the group of ONE of
+                    // 8 consecutive queries and hand the byte round by shuffle — one Philox call per 8 elements, as in
+                    // the forward kernel.
+                    keepbits = 0u;
+#pragma unroll
+                    for (int q8 = 0; q8 < 4; ++q8) {
+                        const int qq = min(i * AB_T + c * 32 + q8 * 8 + (lane & 7), p.Lq - 1);
+                        const uint32_t mine = dropout_keep8(key, ((unsigned long long)st0 + qq) * lkp8 + kgrp, p.drop.thresh);
+#pragma unroll
+                        for (int t = 0; t < 8; ++t) {
+                            const uint32_t m = __shfl_sync(0xffffffffu, mine, (lane & ~7) | t);
+                            keepbits |= ((m >> (row & 7)) & 1u) << (q8 * 8 + t);
+                        }
+                    }
+                }
 #pragma unroll
                 for (int j = 0; j < 32; ++j) {
+                    const float mk = p.drop.state ? (((keepbits >> j) & 1u) ? p.drop.scale : 0.f) : 1.f;
                     const float pr = fast_exp2(fmaf(__uint_as_float(vs[j]), sl2, -lse_s[c * 32 + j]));
-                    pt[j] = pr;
-                    ds[j] = pr * (__uint_as_float(vp[j]) - dl_s[c * 32 + j]) * p.scale;
+                    pt[j] = pr * mk;
+                    ds[j] = pr * (__uint_as_float(vp[j]) * mk - dl_s[c * 32 + j]) * p.scale;
                 }
                 store_tile_chunk(sPT, row, c, pt);
                 store_tile_chunk(sDST, row, c, ds);
@@ -410,10 +447,10 @@ attn_bwd_dkdv_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_cons
         }
         mbar_wait(done, 0);
         tc_fence_after();
-        const int key = k0 + row;
-        const bool k_ok = key < p.Lk;
-        const long long orow = ((long long)b * p.Lk + key) * p.ld_dk + h * AB_D;
-        const long long orow2 = ((long long)b * p.Lk + key) * (p.H * AB_D) + h * AB_D;
+        const int key_row = k0 + row;
+        const bool k_ok = key_row < p.Lk;
+        const long long orow = ((long long)b * p.Lk + key_row) * p.ld_dk + h * AB_D;
+        const long long orow2 = ((long long)b * p.Lk + key_row) * (p.H * AB_D) + h * AB_D;
         if (half == 0) {  // warp-uniform split of the read-out: dV (and dK part 1) by warps 0-3, dK part 0 by warps 4-7
             tmem_ld_32x32b_x32(tmem_dV + lane_off, vs);
             tmem_ld_wait();
@@ -531,6 +568,14 @@ extern "C" int fod_attn_bwd(const fod_attn_bwd_args* g, void* stream) {
     p.bm_q2 = two ? has_b(a->bsq2) : 0; p.bm_k2 = two ? has_b(a->bsk2) : 0;
     p.bm_v = has_b(a->bsv);
     p.scale = a->scale;
+    p.drop = {nullptr, 0u, 0u, 1.f};
+    if (a->drop.rng_state && a->drop.p > 0.f) {
+        if (!(a->drop.p < 1.f)) return fod_fail(FOD_E_ARG, "attn_bwd: dropout p must be in [0, 1)");
+        p.drop.state = reinterpret_cast<const unsigned long long*>(a->drop.rng_state);
+        p.drop.call = (unsigned int)a->drop.call;
+        p.drop.thresh = (unsigned int)(a->drop.p * 65536.f + 0.5f);
+        p.drop.scale = 1.f / (1.f - a->drop.p);
+    }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     {
         const long long total = (long long)a->B * a->Lq * a->H;

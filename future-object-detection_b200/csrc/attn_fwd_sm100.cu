@@ -18,6 +18,7 @@
 #include "fod_internal.h"
 #include "sm100_ptx.cuh"
 #include "tmap.h"
+#include "dropout.cuh"
 
 namespace fod {
 
@@ -72,9 +73,13 @@ struct AttnParams {
     int bm_q1, bm_k1, bm_q2, bm_k2, bm_v;  // 1 if the tensor has a batch dimension, 0 if broadcast
     float scale_log2;                      // scale * log2(e)
     float scale;
+    DropoutCfg drop;                       // DROP kernels: dropout on the softmax weights (attention.py:370)
 };
 
-template <int NPARTS>
+// DROP: train-mode dropout on P.  out = dropout(P)·V / sum(P): the row sums must be those of the UNdropped weights, so
+// they are accumulated in a register of the row's thread instead of by the [V | ones] MMA (whose L block then holds the
+// dropped sums and is ignored).  Mask element index: ((b*H + h)*Lq + q) * roundup8(Lk) + k.
+template <int NPARTS, bool DROP>
 __global__ void __launch_bounds__(AT_THREADS, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant__ CUtensorMap tmK1,
                 const __grid_constant__ CUtensorMap tmQ2, const __grid_constant__ CUtensorMap tmK2,
@@ -219,6 +224,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
         const uint32_t lane_off = uint32_t(warp * 32) << 16;
         uint8_t* sP = smem + L::kP;
         float m_used = -INFINITY;  // exponent offset in use for this row (raw score units)
+        float l_reg = 0.f;         // DROP: running sum of the undropped weights of this row
+        PhiloxKey key = {0u, 0u, 0u, 0u};
+        unsigned long long g_row = 0;
+        if (DROP) {
+            key = dropout_key(p.drop);
+            const unsigned long long lkp = (unsigned long long)((p.Lk + 7) & ~7);
+            g_row = ((((unsigned long long)b * p.H + h) * p.Lq + (unsigned long long)min(q0 + row, p.Lq - 1)) * lkp) >> 3;
+        }
         uint32_t v[4][32];
         for (int j = 0; j < nkt; ++j) {
             mbar_wait(s_full, j & 1);
@@ -277,6 +290,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                     tmem_st_32x32b_x32(tmem_O + lane_off, o);
                     tmem_st_32x32b_x1(tmem_L + lane_off, l1);
                     tmem_st_wait();
+                    if (DROP) l_reg *= alpha;
                 }
                 if (grow) m_used = mx;
             }
@@ -292,6 +306,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                     float e[8];
 #pragma unroll
                     for (int t = 0; t < 8; ++t) e[t] = fast_exp2(fmaf(__uint_as_float(v[c][q * 8 + t]), p.scale_log2, -moff));
+                    if (DROP) {
+                        l_reg += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
+                        const uint32_t keep = dropout_keep8(key, g_row + (unsigned long long)(j * (AT_BN / 8) + c * 4 + q), p.drop.thresh);
+#pragma unroll
+                        for (int t = 0; t < 8; ++t) e[t] = ((keep >> t) & 1u) ? e[t] * p.drop.scale : 0.f;
+                    }
                     uint4 u;
                     u.x = pack_bf16x2(e[0], e[1]);
                     u.y = pack_bf16x2(e[2], e[3]);
@@ -314,7 +334,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
         tmem_ld_wait();
         const int q = q0 + row;
         if (q < p.Lq) {
-            const float l_run = __uint_as_float(l1[0]);
+            const float l_run = DROP ? l_reg : __uint_as_float(l1[0]);
             const float inv = 1.f / l_run;
 #if FOD_ATTN_DEBUG
             {
@@ -407,21 +427,31 @@ extern "C" int fod_attn_fwd(const fod_attn_args* a, void* stream) {
     p.bm_v = has_b(a->bsv);
     p.scale = a->scale;
     p.scale_log2 = a->scale * 1.4426950408889634f;
+    p.drop = {nullptr, 0u, 0u, 1.f};
+    const bool drop = a->drop.rng_state && a->drop.p > 0.f;
+    if (drop) {
+        if (!(a->drop.p < 1.f)) return fod_fail(FOD_E_ARG, "attn: dropout p must be in [0, 1)");
+        p.drop.state = reinterpret_cast<const unsigned long long*>(a->drop.rng_state);
+        p.drop.call = (unsigned int)a->drop.call;
+        p.drop.thresh = (unsigned int)(a->drop.p * 65536.f + 0.5f);
+        p.drop.scale = 1.f / (1.f - a->drop.p);
+    }
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     dim3 grid((a->Lq + AT_BM - 1) / AT_BM, a->H, a->B);
-    static bool attr1 = false, attr2 = false;
+    auto launch = [&](auto kernel, int smem_bytes, bool& attr_done) {
+        if (!attr_done) {
+            cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
+            attr_done = true;
+        }
+        fod_launch(kernel, grid, dim3(AT_THREADS), (size_t)smem_bytes, st, tq1, tk1, tq2, tk2, tv, p);
+    };
+    static bool attr[4] = {false, false, false, false};
     if (two) {
-        if (!attr2) {
-            cudaFuncSetAttribute(attn_fwd_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnSmem<2>::kTotal);
-            attr2 = true;
-        }
-        fod_launch(attn_fwd_kernel<2>, grid, dim3(AT_THREADS), AttnSmem<2>::kTotal, st, tq1, tk1, tq2, tk2, tv, p);
+        if (drop) launch(attn_fwd_kernel<2, true>, AttnSmem<2>::kTotal, attr[3]);
+        else launch(attn_fwd_kernel<2, false>, AttnSmem<2>::kTotal, attr[2]);
     } else {
-        if (!attr1) {
-            cudaFuncSetAttribute(attn_fwd_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, AttnSmem<1>::kTotal);
-            attr1 = true;
-        }
-        fod_launch(attn_fwd_kernel<1>, grid, dim3(AT_THREADS), AttnSmem<1>::kTotal, st, tq1, tk1, tq2, tk2, tv, p);
+        if (drop) launch(attn_fwd_kernel<1, true>, AttnSmem<1>::kTotal, attr[1]);
+        else launch(attn_fwd_kernel<1, false>, AttnSmem<1>::kTotal, attr[0]);
     }
     return fod_check_launch("attn_fwd_kernel");
 }

@@ -8,6 +8,7 @@
 #include "fod_internal.h"
 #include "sm100_ptx.cuh"
 #include "tmap.h"
+#include "dropout.cuh"
 
 namespace fod {
 
@@ -33,7 +34,20 @@ struct GemmEpi {
     int num_stages;
     int vec_ok;                      // 1: 16-byte vector paths are legal for out / aux (alignment + N % 8 == 0)
     float ln_eps;
+    float mask_scale;                // aux_mode 2: kept elements are multiplied by this (1/(1-p) of a dropped-out ReLU output)
+    DropoutCfg drop;                 // state != nullptr: dropout on (acc + bias [ReLU]) — before the residual of the LN epilogue
 };
+
+// dropout on 32 consecutive columns [col0, col0 + 32) of global row `row` (element index row * N + col, N % 8 == 0)
+__device__ __forceinline__ void drop_chunk(float (&z)[32], const PhiloxKey& key, const DropoutCfg& d, long long row, int N, int col0) {
+    const unsigned long long g0 = ((unsigned long long)row * (unsigned long long)N + (unsigned long long)col0) >> 3;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint32_t keep = dropout_keep8(key, g0 + q, d.thresh);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) z[q * 8 + j] = ((keep >> j) & 1u) ? z[q * 8 + j] * d.scale : 0.f;
+    }
+}
 
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
@@ -79,7 +93,7 @@ __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
 // bias, col_scale, staged residual, ReLU, staged mask on 32 accumulator columns [col0, col0+32) of one row
 template <int BN>
 __device__ __forceinline__ void epi_chunk(float (&z)[32], const GemmEpi& p, const uint8_t* aux_row, long long row,
-                                          long long mod_row, int col0, int c, const float* s_bias) {
+                                          long long mod_row, int col0, int c, const float* s_bias, const PhiloxKey& key) {
     if (p.bias) {
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
@@ -132,7 +146,12 @@ __device__ __forceinline__ void epi_chunk(float (&z)[32], const GemmEpi& p, cons
             for (int i = 0; i < 32; ++i)
                 if (col0 + i < p.N && !(__bfloat162float(mk[i]) > 0.f)) z[i] = 0.f;
         }
+        if (p.mask_scale != 1.f) {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) z[i] *= p.mask_scale;
+        }
     }
+    if (p.drop.state) drop_chunk(z, key, p.drop, row, p.N, col0);  // (host: no residual together with dropout here)
 }
 
 __device__ __forceinline__ void stage_bf16(uint8_t* dst, const float (&z)[32]) {
@@ -239,7 +258,8 @@ __device__ __forceinline__ void drain_f32(const uint8_t* stage_warp, float* out,
 
 // acc + bias + residual of 32 columns of one row for the LayerNorm epilogue (the only terms that epilogue admits)
 __device__ __forceinline__ void ln_chunk(float (&z)[32], const uint32_t (&v)[32], const GemmEpi& p, const uint8_t* aux_row,
-                                         long long mod_row, int c, const float* s_bias, bool row_ok) {
+                                         long long row, long long mod_row, int c, const float* s_bias, bool row_ok,
+                                         const PhiloxKey& key) {
 #pragma unroll
     for (int q = 0; q < 8; ++q) {
         const float4 b4 = *reinterpret_cast<const float4*>(s_bias + c * 32 + q * 4);  // zeros when there is no bias
@@ -248,6 +268,7 @@ __device__ __forceinline__ void ln_chunk(float (&z)[32], const uint32_t (&v)[32]
         z[q * 4 + 2] = __uint_as_float(v[q * 4 + 2]) + b4.z;
         z[q * 4 + 3] = __uint_as_float(v[q * 4 + 3]) + b4.w;
     }
+    if (p.drop.state && row_ok) drop_chunk(z, key, p.drop, row, p.N, c * 32);  // x + dropout(sublayer(x)): before the residual
     if (p.aux_mode == 1 && row_ok) {
         if (p.vec_ok) {
 #pragma unroll
@@ -384,6 +405,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const long long mod_row = p.aux_row_mod > 0 ? (row % p.aux_row_mod) : row;
         const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16);
         const uint8_t* aux_row = aux_stage + row_in_tile * Cfg::kRowBf16;
+        PhiloxKey key = {0u, 0u, 0u, 0u};
+        if (p.drop.state) key = dropout_key(p.drop);
 
         // phase 0 (overlaps the main loop): per-column parameters of this N tile -> shared memory (coalesced, once),
         const int et = threadIdx.x - 64;  // 0..127 over the four epilogue warps
@@ -429,7 +452,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 tmem_ld_wait();
 #pragma unroll
                 for (int i = 0; i < 32; ++i) z[i] = __uint_as_float(v[i]);
-                if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, col0, c, s_bias);
+                if (row_ok) epi_chunk<BN>(z, p, aux_row, row, mod_row, col0, c, s_bias, key);
                 if (f32out) stage_f32(my_row + c * 128, z);
                 else stage_bf16(my_row + c * 64, z);
             }
@@ -459,7 +482,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 const int c = c_begin + cc;
                 tmem_ld_32x32b_x32(taddr + c * 32, v);
                 tmem_ld_wait();
-                ln_chunk(z, v, p, aux_row, mod_row, c, s_bias, row_ok);
+                ln_chunk(z, v, p, aux_row, row, mod_row, c, s_bias, row_ok, key);
                 if (cc == 0) shift = z[0];  // sums are taken about a value inside the data: no cancellation in the variance
                 float a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f;
 #pragma unroll
@@ -501,7 +524,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 const int c = c_begin + cc;
                 tmem_ld_32x32b_x32(taddr + c * 32, v);
                 tmem_ld_wait();
-                ln_chunk(z, v, p, aux_row, mod_row, c, s_bias, row_ok);
+                ln_chunk(z, v, p, aux_row, row, mod_row, c, s_bias, row_ok, key);
 #pragma unroll
                 for (int q = 0; q < 8; ++q) {
                     const float4 g4 = *reinterpret_cast<const float4*>(s_gamma + c * 32 + q * 4);
@@ -683,6 +706,20 @@ extern "C" int fod_linear_fwd(const fod_linear_args* a, void* stream) {
     e.K = a->K;
     e.relu = a->relu;
     e.ln_eps = a->ln_eps;
+    e.mask_scale = a->mask_scale != 0.f ? a->mask_scale : 1.f;
+    e.drop.state = nullptr;
+    e.drop.call = 0;
+    e.drop.thresh = 0;
+    e.drop.scale = 1.f;
+    if (a->drop.rng_state && a->drop.p > 0.f) {
+        if (!(a->drop.p < 1.f) || a->N % 8) return fod_fail(FOD_E_ARG, "linear: dropout needs 0 <= p < 1 and N % 8 == 0");
+        if (a->out_f32 || a->relu_mask || (a->residual && !a->ln_gamma))
+            return fod_fail(FOD_E_ARG, "linear: dropout goes with a bf16 output, and with a residual only under the LayerNorm epilogue");
+        e.drop.state = reinterpret_cast<const unsigned long long*>(a->drop.rng_state);
+        e.drop.call = (unsigned int)a->drop.call;
+        e.drop.thresh = (unsigned int)(a->drop.p * 65536.f + 0.5f);
+        e.drop.scale = 1.f / (1.f - a->drop.p);
+    }
     e.aux = nullptr;
     e.ld_aux = 0;
     e.aux_mode = 0;

@@ -6,6 +6,7 @@
 // Algorithmic bytes per row: fwd 512 B read + 512 B write; bwd 1024 B read + 512 B write (bf16, D = 256).
 #include "fod_internal.h"
 #include "sm100_ptx.cuh"
+#include "dropout.cuh"
 
 namespace fod {
 
@@ -89,10 +90,12 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
               const __nv_bfloat16* __restrict__ pre, const __nv_bfloat16* __restrict__ bcast, int rows_per_group,
               const float* __restrict__ mean_in, const float* __restrict__ rstd_in, const float* __restrict__ gamma,
               __nv_bfloat16* __restrict__ dz, float* __restrict__ dgamma, float* __restrict__ dbeta,
-              float* __restrict__ dzsum, long long M) {
+              float* __restrict__ dzsum, long long M, __nv_bfloat16* __restrict__ dz_drop, const DropoutCfg drop) {
     pdl_launch_dependents();
     pdl_wait();
     __shared__ float red[3][RO_WARPS][RO_D];
+    PhiloxKey key = {0u, 0u, 0u, 0u};
+    if (drop.state) key = dropout_key(drop);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int c0 = lane * 8;
     float g[8], ag[8], ab[8], az[8];
@@ -135,11 +138,16 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
         s2 = warp_sum(s2) * (1.f / RO_D);
         float o[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            o[j] = rstd * (d[j] * g[j] - s1 - xh[j] * s2);
-            az[j] += o[j];
-        }
+        for (int j = 0; j < 8; ++j) o[j] = rstd * (d[j] * g[j] - s1 - xh[j] * s2);
         store8(dz + row * RO_D + c0, o);
+        if (drop.state) {  // gradient of the dropped-out addend: this lane's 8 columns are one Philox group (row * 32 + lane)
+            const uint32_t keep = dropout_keep8(key, (unsigned long long)row * (RO_D / 8) + lane, drop.thresh);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) o[j] = ((keep >> j) & 1u) ? o[j] * drop.scale : 0.f;
+            if (dz_drop) store8(dz_drop + row * RO_D + c0, o);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) az[j] += o[j];
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -237,16 +245,41 @@ extern "C" int fod_add_ln_fwd(const void* x, const void* bcast, int32_t rows_per
     return fod_check_launch("add_ln_fwd_kernel");
 }
 
-extern "C" int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bcast, int32_t rows_per_group,
-                          const float* mean, const float* rstd, const float* gamma, void* dz, float* dgamma,
-                          float* dbeta, float* dzsum, int64_t M, void* stream) {
+extern "C" int fod_ln_bwd_drop(const void* dy, const void* dy2, const void* pre, const void* bcast, int32_t rows_per_group,
+                               const float* mean, const float* rstd, const float* gamma, void* dz, void* dz_drop,
+                               float* dgamma, float* dbeta, float* dzsum, int64_t M, const fod_dropout* drop, void* stream) {
     if (!dy || !pre || !mean || !rstd || !gamma || !dz || M <= 0) return fod_fail(FOD_E_ARG, "ln_bwd: null/empty");
     if (bcast && rows_per_group <= 0) return fod_fail(FOD_E_ARG, "ln_bwd: rows_per_group");
+    DropoutCfg d = {nullptr, 0u, 0u, 1.f};
+    if (drop && drop->rng_state && drop->p > 0.f) {
+        if (!(drop->p < 1.f)) return fod_fail(FOD_E_ARG, "ln_bwd: dropout p must be in [0, 1)");
+        d.state = reinterpret_cast<const unsigned long long*>(drop->rng_state);
+        d.call = (unsigned int)drop->call;
+        d.thresh = (unsigned int)(drop->p * 65536.f + 0.5f);
+        d.scale = 1.f / (1.f - drop->p);
+    }
     fod_launch(ln_bwd_kernel, dim3(ro_grid(M)), dim3(RO_WARPS * 32), 0, reinterpret_cast<cudaStream_t>(stream),
         reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(dy2),
         reinterpret_cast<const __nv_bfloat16*>(pre), reinterpret_cast<const __nv_bfloat16*>(bcast), rows_per_group, mean,
-        rstd, gamma, reinterpret_cast<__nv_bfloat16*>(dz), dgamma, dbeta, dzsum, M);
+        rstd, gamma, reinterpret_cast<__nv_bfloat16*>(dz), dgamma, dbeta, dzsum, M, reinterpret_cast<__nv_bfloat16*>(dz_drop), d);
     return fod_check_launch("ln_bwd_kernel");
+}
+
+extern "C" int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bcast, int32_t rows_per_group,
+                          const float* mean, const float* rstd, const float* gamma, void* dz, float* dgamma,
+                          float* dbeta, float* dzsum, int64_t M, void* stream) {
+    return fod_ln_bwd_drop(dy, dy2, pre, bcast, rows_per_group, mean, rstd, gamma, dz, nullptr, dgamma, dbeta, dzsum, M, nullptr,
+                           stream);
+}
+
+namespace fod {
+__global__ void rng_advance_kernel(unsigned long long* state) { state[1] += 1ull; }
+}  // namespace fod
+
+extern "C" int fod_rng_advance(void* rng_state, void* stream) {
+    if (!rng_state) return fod_fail(FOD_E_ARG, "rng_advance: null");
+    fod::rng_advance_kernel<<<1, 1, 0, reinterpret_cast<cudaStream_t>(stream)>>>(reinterpret_cast<unsigned long long*>(rng_state));
+    return fod_check_launch("rng_advance_kernel");
 }
 
 extern "C" int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int32_t rows_per_group,

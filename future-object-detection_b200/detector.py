@@ -10,6 +10,7 @@ import torch
 import torch.nn as nn
 
 from . import autograd as A
+from . import ops
 from .model import BF16, MLP, _lin, _lin_padded, _OutProjOnly, _q, _rows, _xavier_, gen_sineembed_for_position, \
     inverse_sigmoid
 
@@ -26,6 +27,7 @@ class SlotToSlotAttention(nn.Module):
         self.value = nn.Linear(D, D)
         self.fun = _OutProjOnly(D)
         self.heads = Nhead
+        self.p = dropout
 
     def fused_param_groups(self):
         """Parameters read as one concatenated operand (optim.FlatTrainState gives them adjacent arena slots)."""
@@ -48,7 +50,8 @@ class SlotToSlotAttention(nn.Module):
             b = torch.cat((self.query_content.bias, self.key_content.bias, self.value.bias), dim=0)
             wq = torch.cat((_q(self.query_content.weight), _q(self.key_content.weight), _q(self.value.weight)), dim=0)
             qkv = A.linear(c, w, b, wq, residual=res, res_row_mod=m)
-        a = A.self_attention(qkv.view(batch, m, 3 * d), self.heads, (d // self.heads) ** -0.5)
+        a = A.self_attention(qkv.view(batch, m, 3 * d), self.heads, (d // self.heads) ** -0.5,
+                             drop=ops.drop_site(self.p, self.training))
         return a.view(-1, d)
 
 
@@ -66,6 +69,7 @@ class SlotToImageAttention(nn.Module):
         self.query_sine = nn.Linear(D, D)
         self.fun = _OutProjOnly(D)
         self.heads = Nhead
+        self.p = dropout
         self.store_attention = False
         self.stored_attention = None
 
@@ -94,7 +98,8 @@ class SlotToImageAttention(nn.Module):
         qs = _lin(qsine, self.query_sine)
         qs = qs.view(batch, m, d) if qs.shape[0] == batch * m else qs
         scale = (2 * d // self.heads) ** -0.5
-        a = A.cross_attention(qc.view(batch, m, d), qs, kv.view(batch, s, 2 * d), kp, self.heads, scale)
+        a = A.cross_attention(qc.view(batch, m, d), qs, kv.view(batch, s, 2 * d), kp, self.heads, scale,
+                              drop=ops.drop_site(self.p, self.training))
         if self.store_attention:
             self.stored_attention = self._averaged_weights(qc.view(batch, m, d), qs, kv.view(batch, s, 2 * d), kp, scale)
         return a.view(-1, d)
@@ -126,20 +131,23 @@ class TransformerDecoderLayer(nn.Module):
         self.feedforward = nn.Sequential(nn.Linear(D, Dff), nn.ReLU(inplace=True), nn.Dropout(dropout),
                                          nn.Linear(Dff, D))
         self.norm_out = nn.LayerNorm(D)
+        self.p = dropout
 
     def forward(self, c, qpos_bf, qsine, images, img_pos_bf, is_first, batch, m, s):
+        site = lambda: ops.drop_site(self.p, self.training)  # noqa: E731 — dropout_sa / _ia / feedforward / _out
         sa = self.self_attend
         a = sa(c, qpos_bf, batch, m)
         op = sa.fun.out_proj
-        c = A.linear_ln(a, c, op.weight, op.bias, _q(op.weight), self.norm_sa.weight, self.norm_sa.bias, self.norm_sa.eps)
+        c = A.linear_ln(a, c, op.weight, op.bias, _q(op.weight), self.norm_sa.weight, self.norm_sa.bias, self.norm_sa.eps,
+                        drop=site())
         for i, img in enumerate(images):
             ia, nrm = self.image_attend[i], self.norm_ia[i]
             a = ia(c, qpos_bf, qsine, img, img_pos_bf, is_first, batch, m, s)
             op = ia.fun.out_proj
-            c = A.linear_ln(a, c, op.weight, op.bias, _q(op.weight), nrm.weight, nrm.bias, nrm.eps)
+            c = A.linear_ln(a, c, op.weight, op.bias, _q(op.weight), nrm.weight, nrm.bias, nrm.eps, drop=site())
         l1, l2 = self.feedforward[0], self.feedforward[3]
         return A.ffn_ln(c, l1.weight, l1.bias, _q(l1.weight), l2.weight, l2.bias, _q(l2.weight), self.norm_out.weight,
-                        self.norm_out.bias, self.norm_out.eps)
+                        self.norm_out.bias, self.norm_out.eps, drop_h=site(), drop_o=site())
 
 
 class TransformerDecoder(nn.Module):

@@ -9,13 +9,18 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfod_b200.so")
-ABI_VERSION = 9
+ABI_VERSION = 10
 
 FOD_OK, FOD_E_ARG, FOD_E_TMAP, FOD_E_LAUNCH, FOD_E_NUMERIC = 0, 1, 2, 3, 4
 
 
 class FodError(RuntimeError):
     pass
+
+
+class Dropout(C.Structure):
+    """fod_dropout (include/fod_b200.h)."""
+    _fields_ = [("rng_state", C.c_void_p), ("p", C.c_float), ("call", C.c_int32)]
 
 
 class LinearArgs(C.Structure):
@@ -28,7 +33,7 @@ class LinearArgs(C.Structure):
         ("ln_eps", C.c_float),
         ("relu_mask", C.c_void_p), ("col_scale", C.c_void_p), ("ldw", C.c_int64),
         ("a_mn", C.c_int32), ("b_mn", C.c_int32), ("split_k", C.c_int32), ("atomic_out", C.c_int32),
-        ("colsum_out", C.c_void_p),
+        ("colsum_out", C.c_void_p), ("drop", Dropout), ("mask_scale", C.c_float), ("pad1", C.c_int32),
     ]
 
 
@@ -41,6 +46,7 @@ class AttnArgs(C.Structure):
         ("bsq1", C.c_int64), ("bsk1", C.c_int64), ("bsq2", C.c_int64), ("bsk2", C.c_int64), ("bsv", C.c_int64),
         ("bso", C.c_int64),
         ("B", C.c_int32), ("H", C.c_int32), ("Lq", C.c_int32), ("Lk", C.c_int32), ("scale", C.c_float),
+        ("pad0", C.c_int32), ("drop", Dropout),
     ]
 
 
@@ -110,6 +116,8 @@ SYMBOLS = {
     "fod_add_ln_fwd": (C.c_int, [_VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _I64, _F, _VP]),
     "fod_ln_bwd": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_colsum": (C.c_int, [_VP, _I64, _VP, _I64, _I32, _I32, _VP]),
+    "fod_ln_bwd_drop": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, C.POINTER(Dropout), _VP]),
+    "fod_rng_advance": (C.c_int, [_VP, _VP]),
     "fod_maxpool3x3s2_nhwc": (C.c_int, [_VP, _VP, _I32, _I32, _I32, _I32, _VP]),
     "fod_relu_bwd_add": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_stem_conv7x7s2": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),

@@ -9,8 +9,10 @@ so a reference checkpoint loads with `load_state_dict` and `runs/_model.py:build
 unchanged (see fod_b200.build_model).  Internally tokens are batch-first (rows = batch*tokens, 256 channels, bf16)
 and every Linear / LayerNorm / attention / loss op is a C-ABI kernel call (autograd.py); torch is used for the
 ResNet body (cuDNN), for weight casts and for a few 128-row element-wise ops in the decoder.
-Dropout is not implemented: the modules behave as the reference does with dropout disabled (eval-mode numerics in
-both train and eval), which is the parity definition of SURVEY.md §8c.
+Dropout (p = 0.1 in training, as the reference hard-codes) is drawn inside the kernels from a counter-based generator
+(csrc/dropout.cuh): every dropout site of a forward pass takes a call id from ops.drop_site(), the masks are a function
+of (seed, step, call id, element) and backward regenerates them.  `set_dropout(model, 0.0)` gives the reference's
+dropout-free numerics, which is what the parity tests compare.
 """
 import math
 
@@ -560,6 +562,7 @@ class EncoderAttention(nn.Module):
         self.mlp = nn.Sequential(nn.Linear(D, Dff), nn.ReLU(inplace=True), nn.Dropout(dropout), nn.Linear(Dff, D))
         self.norm2 = nn.LayerNorm(D)
         self.heads = Nhead
+        self.p = dropout
 
     def forward(self, x, pos_bf, n_seq, seq_len):
         """x (n_seq*seq_len, D) bf16; pos_bf (seq_len, D) bf16 shared by every sequence, or (n_seq*seq_len, D) when the
@@ -574,13 +577,14 @@ class EncoderAttention(nn.Module):
             pqk = A.linear(pos_bf, w[:2 * d], None, wq[:2 * d])
         res = torch.cat((pqk, pqk.new_zeros(pqk.shape[0], d)), dim=1)
         qkv = A.linear(x, w, b, wq, residual=res, res_row_mod=_pos_mod(pos_bf, seq_len))
-        a = A.self_attention(qkv.view(n_seq, seq_len, 3 * d), self.heads, (d // self.heads) ** -0.5)
+        site = lambda: ops.drop_site(self.p, self.training)  # noqa: E731 — transformer.py:403-412 dropout sites
+        a = A.self_attention(qkv.view(n_seq, seq_len, 3 * d), self.heads, (d // self.heads) ** -0.5, drop=site())
         op = self.attn.out_proj
         x = A.linear_ln(a.view(-1, d), x, op.weight, op.bias, _q(op.weight), self.norm1.weight, self.norm1.bias,
-                        self.norm1.eps)
+                        self.norm1.eps, drop=site())
         l1, l2 = self.mlp[0], self.mlp[3]
         return A.ffn_ln(x, l1.weight, l1.bias, _q(l1.weight), l2.weight, l2.bias, _q(l2.weight), self.norm2.weight,
-                        self.norm2.bias, self.norm2.eps)
+                        self.norm2.bias, self.norm2.eps, drop_h=site(), drop_o=site())
 
 
 class _OutProjOnly(nn.Module):
@@ -619,24 +623,44 @@ class EgodeepAttention(nn.Module):
         self.value = nn.Linear(D, D)
         self.fun = _OutProjOnly(D)
         self.heads = Nhead
+        self.p = dropout
         self.use_mlp = Dff is not None
         if self.use_mlp:
             self.norm1 = nn.LayerNorm(D)
             self.mlp = nn.Sequential(nn.Linear(D, Dff), nn.ReLU(inplace=True), nn.Dropout(dropout), nn.Linear(Dff, D))
             self.norm2 = nn.LayerNorm(D)
 
+    def _site(self):
+        return ops.drop_site(self.p, self.training)
+
     def _post(self, o):
         if not self.use_mlp:
             return o
-        o = A.add_ln(o * 2, self.norm1.weight, self.norm1.bias, eps=self.norm1.eps)
+        # transformer.py:116-118: out = norm1(out + attn_dropout(out)); out = norm2(out + mlp(out))
+        drop = self.training and self.p > 0
+        o = A.add_ln(o + F.dropout(o, self.p, True) if drop else o * 2, self.norm1.weight, self.norm1.bias,
+                     eps=self.norm1.eps)
         l1, l2 = self.mlp[0], self.mlp[3]
         return A.ffn_ln(o, l1.weight, l1.bias, _q(l1.weight), l2.weight, l2.bias, _q(l2.weight), self.norm2.weight,
-                        self.norm2.bias, self.norm2.eps)
+                        self.norm2.bias, self.norm2.eps, drop_h=self._site(), drop_o=self._site())
 
     def forward_single_key(self, ego):
         """ego (n_seq, D) bf16 -> per-sequence update vector (n_seq, D) bf16."""
         o = _lin(_lin(ego, self.value), self.fun.out_proj)
         o = self._post(o)
+        dead = [p for m in (self.query_content, self.query_pos, self.key) for p in m.parameters() if p.requires_grad]
+        return _ZeroGrad.apply(o, *dead) if dead and torch.is_grad_enabled() else o
+
+    def forward_single_key_dropout(self, ego, n_seq, seq_len):
+        """ego (n_seq, D) -> per-TOKEN update (n_seq*seq_len, D) with dropout on.  The softmax weight over one key is
+        still exactly 1, so dropout(P)·V is the sequence's value row with every HEAD kept with probability 1-p and
+        scaled by 1/(1-p), independently per token (attention.py:370 drops entries of the (B·heads, Lq, Lk) weights);
+        the sub-block dropouts after it (transformer.py:95-103,117) are per element, hence per-token rows from here on."""
+        d, h = ego.shape[1], self.heads
+        v = _lin(ego, self.value)
+        keep = (torch.rand((n_seq, seq_len, h, 1), device=ego.device) >= self.p).to(BF16) * (1.0 / (1.0 - self.p))
+        a = (v.view(n_seq, 1, h, d // h) * keep).view(n_seq * seq_len, d)
+        o = self._post(_lin(a, self.fun.out_proj))
         dead = [p for m in (self.query_content, self.query_pos, self.key) for p in m.parameters() if p.requires_grad]
         return _ZeroGrad.apply(o, *dead) if dead and torch.is_grad_enabled() else o
 
@@ -647,7 +671,8 @@ class EgodeepAttention(nn.Module):
         q = _lin(x, self.query_content, residual=pq, res_row_mod=_pos_mod(pos_bf, seq_len))
         k = _lin(_rows(ego), self.key).view(n_seq, -1, d)
         v = _lin(_rows(ego), self.value).view(n_seq, -1, d)
-        qkv_free = A.PlainAttnFn.apply(q.view(n_seq, seq_len, d), k, v, self.heads, (d // self.heads) ** -0.5)
+        qkv_free = A.PlainAttnFn.apply(q.view(n_seq, seq_len, d), k, v, self.heads, (d // self.heads) ** -0.5,
+                                       self._site())
         o = _lin(qkv_free.view(-1, d), self.fun.out_proj)
         return self._post(o)
 
@@ -659,6 +684,7 @@ class TransformerEncoderLayer(nn.Module):
         super().__init__()
         self.self_attn = EncoderAttention(D, Nhead, Dff, dropout)
         self.use_egodeep = use_egodeep
+        self.p = dropout
         if use_egodeep:
             self.egodeep_attend = EgodeepAttention(D, Nhead, Dff, dropout)
             self.norm_eda = nn.LayerNorm(D)
@@ -666,13 +692,21 @@ class TransformerEncoderLayer(nn.Module):
     def forward(self, x, pos_bf, ego, n_seq, seq_len):
         x = self.self_attn(x, pos_bf, n_seq, seq_len)
         if self.use_egodeep and ego is not None:
-            if ego.dim() == 2:
+            drop = self.training and self.p > 0
+            if ego.dim() == 2 and not drop:
                 o = self.egodeep_attend.forward_single_key(ego)
                 x = A.add_ln(x, self.norm_eda.weight, self.norm_eda.bias, bcast=o, rows_per_group=seq_len,
                              eps=self.norm_eda.eps)
             else:
-                o = self.egodeep_attend.forward_multi_key(x, pos_bf, ego, n_seq, seq_len)
-                x = A.add_ln(x + o, self.norm_eda.weight, self.norm_eda.bias, eps=self.norm_eda.eps)
+                # With dropout on, the masks differ per token (attention weights, transformer.py:92; attn_dropout and
+                # the MLP, :95-103; dropout_eda, :485), so the one-key collapse no longer holds: every token runs the
+                # general path, as in the reference.
+                if ego.dim() == 2:
+                    o = self.egodeep_attend.forward_single_key_dropout(ego, n_seq, seq_len)
+                else:
+                    o = self.egodeep_attend.forward_multi_key(x, pos_bf, ego, n_seq, seq_len)
+                x = A.add_ln(x + (F.dropout(o, self.p, True) if drop else o), self.norm_eda.weight, self.norm_eda.bias,
+                             eps=self.norm_eda.eps)
         return x
 
 

@@ -17,6 +17,59 @@ LAUNCH_COUNTS = collections.Counter()
 BF16 = torch.bfloat16
 
 
+# ---------------------------------------------------------------------------------------------- dropout RNG state
+# One device-resident {seed, step} pair per device (include/fod_b200.h fod_dropout).  A dropout site is a (p, call)
+# pair: `call` numbers the sites of one forward pass in execution order (the backward of a site reuses its number, saved
+# in the autograd context), `step` is advanced on the device by rng_advance() once per training forward, so a captured
+# CUDA graph — whose kernel arguments, `call` included, are frozen — draws fresh masks on every replay.
+_RNG = {}
+_CALL = [0]
+
+
+def rng_state(device):
+    key = str(device)
+    if key not in _RNG:
+        _RNG[key] = torch.tensor([0x5EED5EED, 0], dtype=torch.int64, device=device)
+    return _RNG[key]
+
+
+def set_dropout_seed(seed, device="cuda"):
+    """Seed of the dropout masks (default 0x5EED5EED); also resets the step counter."""
+    st = rng_state(torch.device(device) if not isinstance(device, torch.device) else device)
+    st.copy_(torch.tensor([int(seed), 0], dtype=torch.int64))
+
+
+def begin_forward():
+    """Start of a model forward pass (FuturePredCore.forward): dropout call ids restart at 1, and the first dropout
+    site of the pass advances the device-side step counter, so every pass — and every replay of a captured graph —
+    draws fresh masks.  The backward pass must run before the next training forward: it regenerates its masks from
+    the same (seed, step, call id)."""
+    _CALL[0] = 0
+
+
+def drop_site(p, training):
+    """(p, call id) of the next dropout site of this forward pass, or None when dropout is off."""
+    if not training or not p or p <= 0.0:
+        return None
+    if not 0.0 < p < 1.0:
+        raise ValueError("dropout probability has to be in [0, 1), got %r" % (p,))
+    if _CALL[0] == 0:
+        rng_advance(torch.device("cuda", torch.cuda.current_device()))
+    _CALL[0] += 1
+    return (float(p), _CALL[0])
+
+
+def rng_advance(device):
+    L = lib.load()
+    lib.check(L.fod_rng_advance(_p(rng_state(device)), _stream()), "fod_rng_advance")
+    LAUNCH_COUNTS["rng_advance_kernel"] += 1
+
+
+def _fill_drop(d, drop, device):
+    if drop is not None:
+        d.rng_state, d.p, d.call = _p(rng_state(device)), drop[0], drop[1]
+
+
 def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
@@ -32,13 +85,15 @@ def _chk_bf16(t, name):
 
 def gemm(x, w, bias=None, residual=None, res_row_mod=0, relu=False, ln=None, out_f32=False, save_ln=False,
          relu_mask=None, col_scale=None, a_mn=False, b_mn=False, split_k=1, accum_into=None, M=None, N=None, K=None,
-         colsum_out=None, out=None):
+         colsum_out=None, out=None, drop=None, mask_scale=1.0):
     """Y = epi(op(x) · op(w)ᵀ) on the tcgen05 GEMM.  x (M,K) [or (K,M) if a_mn], w (N,K) [or (K,N) if b_mn].
 
     Returns y (bf16, or fp32 if out_f32); with ln=(gamma, beta, eps) and save_ln also (pre_ln, mean, rstd).
     accum_into: fp32 (M,N) tensor that receives vector reductions (weight gradients accumulated in place; the library
     picks the split-K factor).  split_k=-1 with out_f32: library-chosen split-K with overwrite semantics.
-    colsum_out: fp32 (N,) that receives += column sums of the bf16 output (a fused bias gradient)."""
+    colsum_out: fp32 (N,) that receives += column sums of the bf16 output (a fused bias gradient).
+    drop=(p, call): dropout on (acc + bias [ReLU]) — before the residual under the LayerNorm epilogue; mask_scale: factor
+    on the elements a relu_mask keeps (1/(1-p) when the mask is a dropped-out ReLU output)."""
     L = lib.load()
     _chk_bf16(x, "gemm x")
     _chk_bf16(w, "gemm w")
@@ -64,6 +119,8 @@ def gemm(x, w, bias=None, residual=None, res_row_mod=0, relu=False, ln=None, out
         _chk_bf16(relu_mask, "gemm relu_mask")
         assert relu_mask.is_contiguous() and relu_mask.shape == (M, N)
         a.relu_mask = _p(relu_mask)
+        a.mask_scale = mask_scale
+    _fill_drop(a.drop, drop, x.device)
     if col_scale is not None:
         assert col_scale.dtype == torch.float32 and col_scale.is_contiguous()
         a.col_scale = _p(col_scale)
@@ -116,7 +173,7 @@ def _seq(t, B):
     return _p(t), t.stride(1), (t.stride(0) if t.shape[0] == B and B > 1 else 0)
 
 
-def _fill_attn(a, q1, k1, v, q2, k2, out, lse, scale, heads):
+def _fill_attn(a, q1, k1, v, q2, k2, out, lse, scale, heads, drop=None):
     B, Lq = out.shape[0], out.shape[1]
     Lk = v.shape[-2]
     a.q1, a.ldq1, a.bsq1 = _seq(q1, B)
@@ -128,9 +185,10 @@ def _fill_attn(a, q1, k1, v, q2, k2, out, lse, scale, heads):
     a.out, a.ldo, a.bso = _p(out), out.stride(1), out.stride(0)
     a.lse = _p(lse)
     a.B, a.H, a.Lq, a.Lk, a.scale = B, heads, Lq, Lk, scale
+    _fill_drop(a.drop, drop, out.device)
 
 
-def attn_fwd(q1, k1, v, scale, heads=8, q2=None, k2=None, batch=None):
+def attn_fwd(q1, k1, v, scale, heads=8, q2=None, k2=None, batch=None, drop=None):
     """Flash attention forward.  Operands (B, L, heads*32) bf16 (row-strided views allowed) or (L, heads*32) when
     batch-invariant.  Returns out (B, Lq, heads*32) bf16 and lse (B, heads, Lq) fp32."""
     L = lib.load()
@@ -139,7 +197,7 @@ def attn_fwd(q1, k1, v, scale, heads=8, q2=None, k2=None, batch=None):
     out = torch.empty((B, Lq, heads * 32), dtype=BF16, device=v.device)
     lse = torch.empty((B, heads, Lq), dtype=torch.float32, device=v.device)
     a = lib.AttnArgs()
-    _fill_attn(a, q1, k1, v, q2, k2, out, lse, scale, heads)
+    _fill_attn(a, q1, k1, v, q2, k2, out, lse, scale, heads, drop)
     _t = prof.begin()
     lib.check(L.fod_attn_fwd(C.byref(a), _stream()), "fod_attn_fwd")
     Lk, parts, D = v.shape[-2], (2 if q2 is not None else 1), heads * 32
@@ -162,7 +220,7 @@ def attn_bwd_is_fused(Lq, two_parts, mode=0):
     return fits and int(os.environ.get("FOD_ATTN_BWD_FUSED", "1")) != 0
 
 
-def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=None, mode=0):
+def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=None, mode=0, drop=None):
     """Flash attention backward -> (dq1, dk1, dv, dq2, dk2), (B, L, heads*32) bf16 (dq2/dk2 None if unused).
     mode: 0 library picks, 1 two-kernel path, 2 fused single kernel (include/fod_b200.h).
 
@@ -173,7 +231,7 @@ def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=
     Lk = v.shape[-2]
     dev = out.device
     g = lib.AttnBwdArgs()
-    _fill_attn(g.fwd, q1, k1, v, q2, k2, out, lse, scale, heads)
+    _fill_attn(g.fwd, q1, k1, v, q2, k2, out, lse, scale, heads, drop)
     _chk_bf16(dout, "attn dout")
     assert dout.shape == out.shape and dout.stride(-1) == 1
     g.dout, g.lddo, g.bsdo = _p(dout), dout.stride(1), dout.stride(0)
@@ -241,24 +299,29 @@ def add_ln_fwd(x, gamma, beta, eps=1e-5, bcast=None, rows_per_group=0, save=Fals
     return (y, mean, rstd) if save else y
 
 
-def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows_per_group=0, dzsum=None):
+def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows_per_group=0, dzsum=None, drop=None):
     """LayerNorm backward: returns dz (bf16); accumulates into fp32 dgamma / dbeta (256,) and, if given, the column
-    sums of dz into dzsum (256,) — the bias gradient of the linear layer that feeds the norm."""
+    sums of dz into dzsum (256,) — the bias gradient of the linear layer that feeds the norm.
+    drop=(p, call) of the forward GEMM epilogue (y = LN(res + dropout(u))): returns (dz, dz_drop) — the gradients of res
+    and of u — and dzsum sums dz_drop."""
     L = lib.load()
     _chk_bf16(dy, "ln_bwd dy")
     _chk_bf16(pre, "ln_bwd pre")
     assert dy.is_contiguous() and pre.is_contiguous() and pre.shape[-1] == 256
     M = pre.numel() // 256
     dz = torch.empty_like(pre)
+    dzd = torch.empty_like(pre) if drop is not None else None
+    dstruct = lib.Dropout()
+    _fill_drop(dstruct, drop, pre.device)
     _t = prof.begin()
-    ptrs = (_p(dy), _p(dy2), _p(pre), _p(bcast), rows_per_group, _p(mean), _p(rstd), _p(gamma), _p(dz), _p(dgamma),
+    ptrs = (_p(dy), _p(dy2), _p(pre), _p(bcast), rows_per_group, _p(mean), _p(rstd), _p(gamma), _p(dz), _p(dzd), _p(dgamma),
             _p(dbeta), _p(dzsum), M)
-    call = lambda: L.fod_ln_bwd(*ptrs, _stream())
+    call = lambda: L.fod_ln_bwd_drop(*ptrs, C.byref(dstruct), _stream())
     lib.check(call(), "fod_ln_bwd")
     prof.end(_t, "ln_bwd_%d" % M, 0.0, 1536.0 * M, replay=call if _t is not None else None,
-             keep=(dy, dy2, pre, bcast, mean, rstd, gamma, dz, dgamma, dbeta, dzsum))
+             keep=(dy, dy2, pre, bcast, mean, rstd, gamma, dz, dzd, dgamma, dbeta, dzsum))
     LAUNCH_COUNTS["ln_bwd_kernel"] += 1
-    return dz
+    return dz if drop is None else (dz, dzd)
 
 
 def colsum(x, rows_per_group=0, out=None):

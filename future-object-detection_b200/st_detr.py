@@ -103,6 +103,7 @@ class FuturePredCore(nn.Module):
 
     def forward(self, images, imu=None, temporal_offsets=None):
         assert images.dim() == 5, "expected (B, L, 3, H, W)"  # paper.py:463
+        ops.begin_forward()
         images = images[:, :-1]  # the last ("future") frame is never seen by the model (paper.py:463-468)
         if imu is not None:
             imu = imu[:, :-1]
@@ -350,8 +351,24 @@ class SpatioTemporalDETR(nn.Module):
         return stuffs, {"class_scores": sc[:, :, None], "boxes": bx[:, :, None]}
 
 
-def build_model(args, detr_args):
-    """runs/_model.py:14-83 with the fod_b200 modules: same arguments, same module tree, same DDP wrapping."""
+def set_dropout(model, p):
+    """Set the dropout probability of every transformer block (the reference hard-codes 0.1: runs/_model.py:42-55 and
+    the layer defaults of transformer.py).  p = 0 gives the deterministic numerics the parity tests compare."""
+    n = 0
+    for m in model.modules():
+        if isinstance(m, (M.EncoderAttention, M.EgodeepAttention, M.TransformerEncoderLayer, D.SlotToSlotAttention,
+                          D.SlotToImageAttention, D.TransformerDecoderLayer)):
+            m.p = float(p)
+            n += 1
+        elif isinstance(m, nn.Dropout):
+            m.p = float(p)
+    return n
+
+
+def build_model(args, detr_args, dropout=None):
+    """runs/_model.py:14-83 with the fod_b200 modules: same arguments, same module tree, same DDP wrapping.
+    dropout=None keeps the reference's hard-coded 0.1 (runs/_model.py:52 and the encoder layer defaults);
+    a number overrides every site (set_dropout) — 0.0 for deterministic parity runs."""
     lib.load()  # fail loudly before any weights are allocated if the CUDA library is missing
     d = detr_args.hidden_dim
     model = SpatioTemporalDETR(
@@ -378,6 +395,8 @@ def build_model(args, detr_args):
             pos_encoder=M.PositionalEncoder(no_temporal=True),
         ),
     )
+    if dropout is not None:
+        set_dropout(model, dropout)
     model.to(args.device)
     if getattr(args, "distributed", False):
         model = nn.parallel.DistributedDataParallel(model, device_ids=[args.device], output_device=args.device,

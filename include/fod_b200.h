@@ -27,6 +27,21 @@ int fod_version(void);                  /* ABI version, bumped on signature chan
 const char* fod_last_error(void);       /* thread-local message for the last non-zero status */
 
 /* ------------------------------------------------------------------------------------------------
+ * Train-mode dropout (p = 0.1 in the reference: on the attention weights, ConditionalDETR/models/attention.py:370 and
+ * torch.nn.MultiheadAttention; after every sub-block and inside the FFNs, future_od/models/transformer.py:201,207,234,
+ * 271,285,310,405-412).  Masks are never stored: forward and backward regenerate them with Philox4x32-7 from
+ * rng_state = device uint64[2] {seed, step}, the call-site id `call` and the element index.  `step` is advanced on the
+ * device once per training step (fod_rng_advance), so a captured CUDA graph draws fresh masks on every replay.
+ * RNG streams cannot match torch's: parity with the reference is statistical (keep rate, scale), exact at p = 0.
+ */
+typedef struct fod_dropout {
+    const void* rng_state;   /* NULL or p == 0: no dropout */
+    float p;                 /* drop probability in [0, 1) */
+    int32_t call;            /* call-site id, unique per dropout site within a step */
+} fod_dropout;
+int fod_rng_advance(void* rng_state, void* stream);   /* rng_state[1] += 1 (one thread) */
+
+/* ------------------------------------------------------------------------------------------------
  * Linear + fused epilogue on tcgen05 tensor cores:  Y = epi(X · Wᵀ)
  *   epi: (+bias) (+residual[row % res_row_mod]) (ReLU) (LayerNorm over the N=256 row) -> bf16 and/or fp32
  * Replaces: nn.Linear / F.relu / residual add / nn.LayerNorm chains in
@@ -64,6 +79,12 @@ typedef struct fod_linear_args {
     int32_t atomic_out;     /* 1: out_f32 += result (vector reductions into a caller-initialised buffer) */
     float* colsum_out;      /* (N) fp32 or NULL: += column sums of the stored bf16 output — the bias gradient of the
                                layer that produced the GEMM's input gradient (transformer.py:407-410 backward) */
+    fod_dropout drop;       /* dropout on (acc + bias [ReLU]) — x + dropout(sublayer(x)) with the LayerNorm epilogue (the
+                               residual is never dropped), dropout(relu(.)) for an FFN hidden; N % 8 == 0, no residual
+                               outside the LayerNorm epilogue */
+    float mask_scale;       /* with relu_mask: kept elements are multiplied by it (0 = 1): 1/(1-p) when the saved hidden
+                               is a dropped-out ReLU output, whose zeros cover both masks */
+    int32_t pad1;
 } fod_linear_args;
 int fod_linear_fwd(const fod_linear_args* a, void* stream);  /* also the backward GEMMs via a_mn / b_mn */
 
@@ -90,6 +111,9 @@ typedef struct fod_attn_args {
     int64_t bsq1, bsk1, bsq2, bsk2, bsv, bso;          /* batch strides in elements (0 = broadcast) */
     int32_t B, H, Lq, Lk;
     float scale;
+    int32_t pad0;
+    fod_dropout drop;  /* dropout on the softmax weights P (out = dropout(P)·V; lse is that of the undropped P); the
+                          backward call must carry the same descriptor */
 } fod_attn_args;
 int fod_attn_fwd(const fod_attn_args* a, void* stream);
 
@@ -130,6 +154,12 @@ int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bca
                float* dzsum /* (256) or NULL: += column sums of dz = bias gradient of the linear feeding the norm */,
                int64_t M, void* stream);
 int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int32_t rows_per_group, void* stream);
+/* fod_ln_bwd for y = LayerNorm(res + dropout(u)): dz is the gradient of res, dz_drop (optional) = dz masked and scaled
+ * by the SAME dropout mask the forward GEMM epilogue drew (`drop`: element index row*256 + col) = the gradient of u;
+ * dzsum then sums dz_drop (the bias sits inside the dropout). */
+int fod_ln_bwd_drop(const void* dy, const void* dy2, const void* pre, const void* bcast, int32_t rows_per_group,
+                    const float* mean, const float* rstd, const float* gamma, void* dz, void* dz_drop, float* dgamma,
+                    float* dbeta, float* dzsum, int64_t M, const fod_dropout* drop, void* stream);
 /* 3x3 / stride 2 / pad 1 max pooling, NHWC bf16, C % 8 == 0: the ResNet stem pool in front of the frozen layer1
  * (ConditionalDETR/models/backbone.py:88-96 -> torchvision resnet `maxpool`); forward only (paper.py:102-109 freezes
  * everything before layer2).  y is (N, (H-1)/2+1, (W-1)/2+1, C). */

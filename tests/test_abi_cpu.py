@@ -36,7 +36,7 @@ def test_library_exports_every_declared_symbol():
 @pytest.mark.parametrize("struct,cls", [("fod_linear_args", "LinearArgs"), ("fod_attn_args", "AttnArgs"),
                                         ("fod_attn_bwd_args", "AttnBwdArgs"), ("fod_match_args", "MatchArgs"),
                                         ("fod_set_loss_args", "SetLossArgs"), ("fod_adamw_args", "AdamWArgs"), ("fod_ap_args", "ApArgs"),
-                                        ("fod_fold_desc", "FoldDesc")])
+                                        ("fod_fold_desc", "FoldDesc"), ("fod_dropout", "Dropout")])
 def test_ctypes_structs_follow_the_header(struct, cls):
     from fod_b200 import lib
     body = re.search(r"typedef struct %s \{(.*?)\} %s;" % (struct, struct), _header_text(), flags=re.S).group(1)
@@ -45,7 +45,7 @@ def test_ctypes_structs_follow_the_header(struct, cls):
         stmt = stmt.strip()
         if not stmt:
             continue
-        stmt = re.sub(r"^(const\s+)?(void|float|int32_t|int64_t|fod_attn_args)\s*\**", "", stmt)
+        stmt = re.sub(r"^(const\s+)?(void|float|int32_t|int64_t|fod_attn_args|fod_dropout)\s*\**", "", stmt)
         names += [re.sub(r"\[\d+\]$", "", n.strip().lstrip("*")) for n in stmt.split(",")]
     assert names == [f[0] for f in getattr(lib, cls)._fields_]
 

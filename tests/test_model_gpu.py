@@ -25,7 +25,8 @@ def rel_l2(a, b):
 def model(ref_state_dict):
     from fod_b200 import SpatioTemporalDETRArgs, build_model
     m = build_model(Namespace(device=DEV, distributed=False),
-                    SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4))
+                    SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4),
+                    dropout=0.0)
     m.load_state_dict(ref_state_dict, strict=True)
     return m.eval()
 

@@ -81,12 +81,12 @@ def test_arena_gradients_equal_autograd_gradients(ref_state_dict):
     dev = "cuda:0"
     dargs = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
     data = {k: v.to(dev) for k, v in make_clip(2, 3, 128, 160, seed=3).items()}
-    plain = build_model(Namespace(device=dev, distributed=False), dargs)
+    plain = build_model(Namespace(device=dev, distributed=False), dargs, dropout=0.0)
     plain.load_state_dict(ref_state_dict)
     plain.train()
     plain(data)[2].backward()
     ref = {n: p.grad.clone() for n, p in plain.named_parameters() if p.requires_grad}
-    model = build_model(Namespace(device=dev, distributed=False), dargs)
+    model = build_model(Namespace(device=dev, distributed=False), dargs, dropout=0.0)
     model.load_state_dict(ref_state_dict)
     model.train()
     flat = FlatTrainState(model, bucket_mb=8.0)
@@ -132,7 +132,7 @@ def test_graph_replayed_training_follows_the_eager_trajectory():
         weights = synthetic_state_dict(json.load(f), seed=0, residual_gain=0.5)
 
     def run(graph):
-        model = build_model(Namespace(device=dev, distributed=False), dargs)
+        model = build_model(Namespace(device=dev, distributed=False), dargs, dropout=0.0)
         model.load_state_dict(weights)
         model.train()
         if graph:

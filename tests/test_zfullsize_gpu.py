@@ -31,7 +31,8 @@ def model():
     with open(os.path.join(GOLDEN, "state_dict_template.json")) as f:
         sd = synthetic_state_dict(json.load(f), seed=0, residual_gain=0.5)
     m = build_model(Namespace(device=DEV, distributed=False),
-                    SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4))
+                    SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4),
+                    dropout=0.0)
     m.load_state_dict(sd, strict=True)
     return m.eval()
 

@@ -16,7 +16,7 @@ def test_set_lr_reaches_the_captured_step(ref_state_dict):
     from fod_b200.synthetic import make_clip
     dev = "cuda:0"
     dargs = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
-    model = build_model(Namespace(device=dev, distributed=False), dargs)
+    model = build_model(Namespace(device=dev, distributed=False), dargs, dropout=0.0)
     model.load_state_dict(ref_state_dict)
     model.train()
     batch = {k: v.to(dev) for k, v in make_clip(2, 3, 128, 160, seed=31).items()}
