@@ -399,11 +399,11 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
                 if (DROP) {
 #pragma unroll
                     for (int qd = 0; qd < 4; ++qd) {
-                        const uint32_t keep = dropout_keep8(key, g_row + (unsigned long long)(j * (AF_T / 8) + c * 4 + qd), p.drop.thresh);
+                        const Keep8 keep = dropout_draw8(key, g_row + (unsigned long long)(j * (AF_T / 8) + c * 4 + qd), p.drop.thresh);
 #pragma unroll
                         for (int e = 0; e < 8; ++e) {
                             const int idx = qd * 8 + e;
-                            const float mk = ((keep >> e) & 1u) ? p.drop.scale : 0.f;
+                            const float mk = keep[e] ? p.drop.scale : 0.f;
                             const float x = fast_exp2(fmaf(__uint_as_float(vs[idx]), sl2, -lse2));
                             const float g = fmaf(__uint_as_float(vp[idx]) * mk, p.scale, -dlt);
                             vs[idx] = __float_as_uint(x * mk);  // dropout(P): the operand of dV

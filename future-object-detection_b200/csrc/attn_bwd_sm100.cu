@@ -214,10 +214,10 @@ attn_bwd_dq_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_consta
                 if (p.drop.state) {  // dP = (dO·Vᵀ) ⊙ mask / (1-p)
 #pragma unroll
                     for (int qd = 0; qd < 4; ++qd) {
-                        const uint32_t keep = dropout_keep8(key, g_row + (unsigned long long)(j * (AB_T / 8) + c * 4 + qd), p.drop.thresh);
+                        const Keep8 keep = dropout_draw8(key, g_row + (unsigned long long)(j * (AB_T / 8) + c * 4 + qd), p.drop.thresh);
 #pragma unroll
                         for (int e = 0; e < 8; ++e)
-                            vp[qd * 8 + e] = __float_as_uint(((keep >> e) & 1u) ? __uint_as_float(vp[qd * 8 + e]) * p.drop.scale : 0.f);
+                            vp[qd * 8 + e] = __float_as_uint(keep[e] ? __uint_as_float(vp[qd * 8 + e]) * p.drop.scale : 0.f);
                     }
                 }
 #pragma unroll

@@ -308,9 +308,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                     for (int t = 0; t < 8; ++t) e[t] = fast_exp2(fmaf(__uint_as_float(v[c][q * 8 + t]), p.scale_log2, -moff));
                     if (DROP) {
                         l_reg += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
-                        const uint32_t keep = dropout_keep8(key, g_row + (unsigned long long)(j * (AT_BN / 8) + c * 4 + q), p.drop.thresh);
+                        // dropped weights are zeroed here; the 1/(1-p) of the kept ones is folded into the final 1/l
+                        const Keep8 keep = dropout_draw8(key, g_row + (unsigned long long)(j * (AT_BN / 8) + c * 4 + q), p.drop.thresh);
 #pragma unroll
-                        for (int t = 0; t < 8; ++t) e[t] = ((keep >> t) & 1u) ? e[t] * p.drop.scale : 0.f;
+                        for (int t = 0; t < 8; ++t) e[t] = keep[t] ? e[t] : 0.f;
                     }
                     uint4 u;
                     u.x = pack_bf16x2(e[0], e[1]);
@@ -335,7 +336,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
         const int q = q0 + row;
         if (q < p.Lq) {
             const float l_run = DROP ? l_reg : __uint_as_float(l1[0]);
-            const float inv = 1.f / l_run;
+            const float inv = (DROP ? p.drop.scale : 1.f) / l_run;
 #if FOD_ATTN_DEBUG
             {
                 bool bad = !(l_run >= 0.5f) || !(l_run < 3.0e38f) || !(fabsf(m_used) < 3.0e38f);

@@ -73,4 +73,28 @@ __device__ __forceinline__ uint32_t dropout_keep8(const PhiloxKey& key, unsigned
     return m;
 }
 
+// The same decisions without materialising the bit mask: lane j of a group is the low (j even) or high (j odd) half of
+// word j / 2, and  half >= thresh  is one unsigned compare of the word (shifted up for the low half) with thresh << 16.
+struct Keep8 {
+    uint32_t w[4];
+    uint32_t th;
+    __device__ __forceinline__ bool operator[](int j) const { return ((j & 1) ? w[j >> 1] : (w[j >> 1] << 16)) >= th; }
+};
+__device__ __forceinline__ Keep8 dropout_draw8(const PhiloxKey& key, unsigned long long g, uint32_t thresh) {
+    const uint4 r = philox4x32(key, g);
+    Keep8 k;
+    k.w[0] = r.x;
+    k.w[1] = r.y;
+    k.w[2] = r.z;
+    k.w[3] = r.w;
+    k.th = thresh << 16;
+    return k;
+}
+// z[j] = kept ? z[j] * scale : 0 for the 8 elements of group g
+__device__ __forceinline__ void dropout_apply8(float* z, const PhiloxKey& key, unsigned long long g, uint32_t thresh, float scale) {
+    const Keep8 k = dropout_draw8(key, g, thresh);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) z[j] = k[j] ? z[j] * scale : 0.f;
+}
+
 }  // namespace fod

@@ -43,9 +43,7 @@ __device__ __forceinline__ void drop_chunk(float (&z)[32], const PhiloxKey& key,
     const unsigned long long g0 = ((unsigned long long)row * (unsigned long long)N + (unsigned long long)col0) >> 3;
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-        const uint32_t keep = dropout_keep8(key, g0 + q, d.thresh);
-#pragma unroll
-        for (int j = 0; j < 8; ++j) z[q * 8 + j] = ((keep >> j) & 1u) ? z[q * 8 + j] * d.scale : 0.f;
+        dropout_apply8(&z[q * 8], key, g0 + q, d.thresh, d.scale);
     }
 }
 
@@ -634,6 +632,369 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     return fod_check_launch("gemm_bf16_kernel");
 }
 
+// =====================================================================================================================
+// Persistent weight-stationary kernel for the short contractions (K <= 256: every projection OUT of the 256-wide model —
+// FFN up-projection and its dX twin dH = dU·W2, the fused QKV projection).  The one-tile-per-CTA kernel above spends a
+// K = 256 tile mostly on things that are not the 16 MMAs: CTA launch, barrier / TMEM set-up, the first TMA round trip,
+// 128 KB of W re-fetched from L2 for every tile, and an epilogue nothing overlaps (one CTA per SM at BN = 256).  Here
+//   * one CTA per SM lives for the whole GEMM and keeps ITS 256-column slab of W (<= 128 KB) in shared memory: only
+//     the 64 KB activation tiles stream (3-stage ring of 16 KB k-blocks) — a third of the L2 -> SM bytes per tile;
+//   * the accumulator is double-buffered in TMEM (2 x 256 columns): the MMAs of tile i+1 run while the eight epilogue
+//     warps drain tile i, so bias / ReLU / mask / dropout arithmetic and the stores are off the critical path;
+//   * the epilogue works on 32-column chunks through small per-warp staging buffers (coalesced 64-byte row segments
+//     out, coalesced cp.async of the residual / mask chunk in, one chunk ahead), and bias-gradient column sums stay
+//     in registers for the CTA's whole column slab: one atomic per column per warp instead of one per tile.
+// CTA c keeps W slab c / ctas_per_n and takes the M tiles first, first + ctas_per_n, ... of that slab.
+constexpr int WS_BN = 256;
+constexpr int WS_EPI_WARPS = 8;
+constexpr int WS_THREADS = 64 + 32 * WS_EPI_WARPS;
+constexpr int WS_A_STAGES = 3;
+constexpr int WS_A_BYTES = GEMM_BM * GEMM_BK * 2;           // 16 KB: one k-block of the activation tile
+constexpr int WS_B_KB_BYTES = WS_BN * GEMM_BK * 2;          // 32 KB: one k-block of the resident weight slab
+constexpr int WS_B_BYTES = 4 * WS_B_KB_BYTES;               // K <= 256
+constexpr int WS_ROWB = 80;                                 // staged row: 32 bf16 + 16 B padding (conflict-free both ways)
+constexpr int WS_XBUF = 32 * WS_ROWB;
+constexpr int WS_X_BYTES = WS_EPI_WARPS * 2 * WS_XBUF;      // two chunk buffers per epilogue warp
+constexpr int WS_CS_BYTES = WS_EPI_WARPS * 128 * 4;            // per-warp column-sum accumulators (bias gradients)
+constexpr int WS_SMEM = 1024 + WS_B_BYTES + WS_A_STAGES * WS_A_BYTES + WS_X_BYTES + 256 + WS_BN * 4 + WS_CS_BYTES;
+
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 u;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(u.x), "=r"(u.y), "=r"(u.z), "=r"(u.w) : "r"(addr) : "memory");
+    return u;
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& u) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(u.x), "r"(u.y), "r"(u.z), "r"(u.w) : "memory");
+}
+
+// residual / mask chunk (32 rows x 32 columns of this warp) -> staging buffer, 4 lanes per 64-byte row segment
+__device__ __forceinline__ void ws_aux_load(uint32_t xb, const GemmEpi& p, long long row0, int col0, int lane) {
+    const int piece = lane & 3, r0 = lane >> 2;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int r = r0 + 8 * i;
+        const long long grow = row0 + r;
+        const bool ok = grow < p.M;
+        const long long srow = (p.aux_mode == 1 && p.aux_row_mod > 0) ? (grow % p.aux_row_mod) : grow;
+        const __nv_bfloat16* src = p.aux + srow * p.ld_aux + col0 + piece * 8;
+        cp_async_16(xb + r * WS_ROWB + piece * 16, ok ? static_cast<const void*>(src) : static_cast<const void*>(p.aux),
+                    ok ? 16u : 0u);
+    }
+}
+
+template <bool DROP>
+__device__ __forceinline__ void ws_epi_chunk(float (&z)[32], const GemmEpi& p, uint32_t xrow, long long row, int col0,
+                                             const float* bias32, const PhiloxKey& key) {
+    if (p.bias) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const float4 b4 = *reinterpret_cast<const float4*>(bias32 + q * 4);
+            z[q * 4] += b4.x;
+            z[q * 4 + 1] += b4.y;
+            z[q * 4 + 2] += b4.z;
+            z[q * 4 + 3] += b4.w;
+        }
+    }
+    if (p.aux_mode == 1) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            float f[8];
+            unpack8(lds128(xrow + q * 16), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) z[q * 8 + j] += f[j];
+        }
+    }
+    if (p.relu) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) z[i] = fmaxf(z[i], 0.f);
+    }
+    if (p.aux_mode == 2) {
+        const float ms = p.mask_scale;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            float f[8];
+            unpack8(lds128(xrow + q * 16), f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) z[q * 8 + j] = (f[j] > 0.f) ? z[q * 8 + j] * ms : 0.f;
+        }
+    }
+    if constexpr (DROP) drop_chunk(z, key, p.drop, row, p.N, col0);
+}
+
+__device__ __forceinline__ void ws_stage(uint32_t xrow, const float (&z)[32]) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        uint4 u;
+        u.x = pack_bf16x2(z[q * 8 + 0], z[q * 8 + 1]);
+        u.y = pack_bf16x2(z[q * 8 + 2], z[q * 8 + 3]);
+        u.z = pack_bf16x2(z[q * 8 + 4], z[q * 8 + 5]);
+        u.w = pack_bf16x2(z[q * 8 + 6], z[q * 8 + 7]);
+        sts128(xrow + q * 16, u);
+    }
+}
+
+// staged chunk -> global memory: one warp instruction stores 8 row segments of 64 bytes.  The four shared-memory reads
+// are issued together, the stores are predicated (no branch per row).
+__device__ __forceinline__ void ws_drain(uint32_t xb, const GemmEpi& p, long long row0, int col0, int lane, float* cs32) {
+    const int piece = lane & 3, r0 = lane >> 2;
+    uint4 u[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) u[i] = lds128(xb + (r0 + 8 * i) * WS_ROWB + piece * 16);
+    __nv_bfloat16* dst = p.out_bf16 + (row0 + r0) * p.ld_out + col0 + piece * 8;
+    const long long left = p.M - (row0 + r0);  // rows r0 + 8 i are valid while 8 i < left
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (8 * i < left) {
+            *reinterpret_cast<uint4*>(dst + (long long)(8 * i) * p.ld_out) = u[i];
+        } else {
+            u[i] = make_uint4(0u, 0u, 0u, 0u);
+        }
+    }
+    if (p.colsum_out) {  // column sums of the stored bf16 values: 4 rows per lane, then the 8 lanes that share a piece
+        float cs[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) cs[j] = 0.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            float f[8];
+            unpack8(u[i], f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) cs[j] += f[j];
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float v = cs[j];
+            v += __shfl_xor_sync(0xffffffffu, v, 4);
+            v += __shfl_xor_sync(0xffffffffu, v, 8);
+            v += __shfl_xor_sync(0xffffffffu, v, 16);
+            if (lane < 4) cs32[lane * 8 + j] += v;  // lane-private slots of this warp's accumulator row
+        }
+    }
+}
+
+template <bool B_MN, bool DROP>
+__global__ void __launch_bounds__(WS_THREADS, 1)
+gemm_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmEpi p, int mt,
+               int ctas_per_n) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* sB = smem;
+    uint8_t* sA = sB + WS_B_BYTES;
+    uint8_t* sX = sA + WS_A_STAGES * WS_A_BYTES;
+    uint64_t* a_full = reinterpret_cast<uint64_t*>(sX + WS_X_BYTES);
+    uint64_t* a_empty = a_full + WS_A_STAGES;
+    uint64_t* b_full = a_empty + WS_A_STAGES;
+    uint64_t* t_full = b_full + 1;
+    uint64_t* t_empty = t_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+    float* s_bias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(a_full) + 256);
+    float* s_cs = s_bias + WS_BN;
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int n0 = (int)(blockIdx.x / ctas_per_n) * WS_BN;
+    const int first = blockIdx.x % ctas_per_n;
+    const int num_kb = (p.K + GEMM_BK - 1) / GEMM_BK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        for (int s = 0; s < WS_A_STAGES; ++s) {
+            mbar_init(a_full + s, 1);
+            mbar_init(a_empty + s, 1);
+        }
+        mbar_init(b_full, 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(t_full + b, 1);
+            mbar_init(t_empty + b, WS_EPI_WARPS);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<512>(tmem_slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_launch_dependents();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_arrive_expect_tx(b_full, (uint32_t)num_kb * WS_B_KB_BYTES);
+            for (int kb = 0; kb < num_kb; ++kb) {
+                uint8_t* sb = sB + kb * WS_B_KB_BYTES;
+                if constexpr (B_MN) {
+#pragma unroll
+                    for (int c = 0; c < WS_BN / 64; ++c) tma_load_2d(sb + c * 8192, &tmB, b_full, n0 + c * 64, kb * GEMM_BK);
+                } else {
+                    tma_load_2d(sb, &tmB, b_full, kb * GEMM_BK, n0);
+                }
+            }
+            int s = 0;
+            uint32_t ph = 0;
+            for (int t = first; t < mt; t += ctas_per_n) {
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(a_empty + s, ph ^ 1);
+                    mbar_arrive_expect_tx(a_full + s, WS_A_BYTES);
+                    tma_load_2d(sA + s * WS_A_BYTES, &tmA, a_full + s, kb * GEMM_BK, t * GEMM_BM);
+                    if (++s == WS_A_STAGES) {
+                        s = 0;
+                        ph ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, WS_BN, 0, B_MN ? 1 : 0);
+            const uint64_t dA0 = umma_smem_desc(smem_u32(sA), 16, 1024, 2);
+            const uint64_t dB0 = B_MN ? umma_smem_desc(smem_u32(sB), 8192, 1024, 2) : umma_smem_desc(smem_u32(sB), 16, 1024, 2);
+            constexpr uint32_t kStepB = B_MN ? 2048 : 32;
+            mbar_wait(b_full, 0);
+            int s = 0, it = 0;
+            uint32_t ph = 0;
+            for (int t = first; t < mt; t += ctas_per_n, ++it) {
+                const int buf = it & 1;
+                mbar_wait(t_empty + buf, ((it >> 1) & 1) ^ 1);  // the epilogue has drained this accumulator buffer
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + buf * WS_BN;
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(a_full + s, ph);
+                    tc_fence_after();
+                    const uint64_t da = umma_desc_adv(dA0, s * WS_A_BYTES), db = umma_desc_adv(dB0, kb * WS_B_KB_BYTES);
+#pragma unroll
+                    for (int k = 0; k < GEMM_BK / 16; ++k)
+                        umma_bf16_ss(d_tmem, umma_desc_adv(da, k * 32), umma_desc_adv(db, k * kStepB), idesc, (kb | k) ? 1u : 0u);
+                    umma_commit(a_empty + s);
+                    if (++s == WS_A_STAGES) {
+                        s = 0;
+                        ph ^= 1;
+                    }
+                }
+                umma_commit(t_full + buf);
+            }
+        }
+    } else {
+        const int quarter = warp & 3;        // TMEM lane quarter this warp may read
+        const int half = (warp - 2) >> 2;    // which 128 columns of the tile
+        const uint32_t X = smem_u32(sX + (warp - 2) * 2 * WS_XBUF);
+        for (int i = threadIdx.x - 64; i < WS_BN; i += WS_EPI_WARPS * 32) s_bias[i] = p.bias ? __ldg(p.bias + n0 + i) : 0.f;
+        asm volatile("bar.sync 1, %0;" ::"n"(WS_EPI_WARPS * 32) : "memory");
+        PhiloxKey key = {0u, 0u, 0u, 0u};
+        if constexpr (DROP) key = dropout_key(p.drop);
+        float* cs_w = s_cs + (warp - 2) * 128;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) cs_w[lane * 4 + i] = 0.f;
+        __syncwarp();
+        const int colw = n0 + half * 128;  // first column of this warp
+        int it = 0;
+        for (int t = first; t < mt; t += ctas_per_n, ++it) {
+            const int buf = it & 1;
+            const long long row0 = (long long)t * GEMM_BM + quarter * 32;
+            const long long row = row0 + lane;
+            const bool row_ok = row < p.M;
+            if (p.aux_mode) ws_aux_load(X, p, row0, colw, lane);
+            cp_async_commit();
+            mbar_wait(t_full + buf, (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + buf * WS_BN + half * 128 + (uint32_t(quarter * 32) << 16);
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                const uint32_t xb = X + (c & 1) * WS_XBUF;
+                if (c < 3 && p.aux_mode) ws_aux_load(X + ((c + 1) & 1) * WS_XBUF, p, row0, colw + (c + 1) * 32, lane);
+                cp_async_commit();
+                uint32_t v[32];
+                float z[32];
+                tmem_ld_32x32b_x32(taddr + c * 32, v);
+                tmem_ld_wait();
+                if (c == 3) {  // the whole accumulator is in registers: hand the buffer back to the MMA warp
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(t_empty + buf);
+                }
+                cp_async_wait_group<1>();
+                __syncwarp();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) z[i] = __uint_as_float(v[i]);
+                const uint32_t xrow = xb + lane * WS_ROWB;
+                if (row_ok) ws_epi_chunk<DROP>(z, p, xrow, row, colw + c * 32, s_bias + half * 128 + c * 32, key);
+                ws_stage(xrow, z);
+                __syncwarp();
+                ws_drain(xb, p, row0, colw + c * 32, lane, cs_w + c * 32);
+                __syncwarp();
+            }
+        }
+        if (p.colsum_out) {
+            __syncwarp();
+#pragma unroll
+            for (int i = 0; i < 4; ++i) atomicAdd(p.colsum_out + colw + i * 32 + lane, cs_w[i * 32 + lane]);
+        }
+        tc_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<512>(tmem_base);
+    }
+}
+
+// shapes the persistent kernel takes: see the dispatch in fod_linear_fwd
+static bool gemm_ws_eligible(const fod_linear_args* a, const GemmEpi& e) {
+    static const int enabled = [] { const char* v = getenv("FOD_GEMM_WS"); return v ? atoi(v) : 1; }();
+    if (!enabled) return false;
+    if (a->a_mn || a->ln_gamma || !a->out_bf16 || a->col_scale || a->split_k > 1 || a->split_k < 0 || !e.vec_ok) return false;
+    if (a->K > 256 || a->K % GEMM_BK || a->N % WS_BN) return false;
+    const long long tiles = (long long)((a->M + GEMM_BM - 1) / GEMM_BM) * (a->N / WS_BN);
+    return tiles >= 2 * 148;  // at least two tiles per SM: something to overlap
+}
+
+template <bool B_MN, bool DROP>
+static int launch_gemm_ws(const fod_linear_args* a, const GemmEpi& epi, cudaStream_t st) {
+    CUtensorMap tmA, tmB;
+    const long long ldw = a->ldw ? a->ldw : (B_MN ? a->N : a->K);
+    {
+        uint64_t dims[2] = {(uint64_t)a->K, (uint64_t)a->M};
+        uint64_t str[1] = {(uint64_t)a->ldx * 2};
+        uint32_t box[2] = {GEMM_BK, GEMM_BM};
+        if (make_tmap_bf16(&tmA, a->x, 2, dims, str, box, 128)) return fod_fail(FOD_E_TMAP, "gemm(ws): tmap A");
+    }
+    if (B_MN) {
+        uint64_t dims[2] = {(uint64_t)a->N, (uint64_t)a->K};
+        uint64_t str[1] = {(uint64_t)ldw * 2};
+        uint32_t box[2] = {64, GEMM_BK};
+        if (make_tmap_bf16(&tmB, a->w, 2, dims, str, box, 128)) return fod_fail(FOD_E_TMAP, "gemm(ws): tmap B (MN-major)");
+    } else {
+        uint64_t dims[2] = {(uint64_t)a->K, (uint64_t)a->N};
+        uint64_t str[1] = {(uint64_t)ldw * 2};
+        uint32_t box[2] = {GEMM_BK, (uint32_t)WS_BN};
+        if (make_tmap_bf16(&tmB, a->w, 2, dims, str, box, 128)) return fod_fail(FOD_E_TMAP, "gemm(ws): tmap B");
+    }
+    const int mt = (a->M + GEMM_BM - 1) / GEMM_BM, nt = a->N / WS_BN;
+    int cpn = 148 / nt;
+    if (cpn < 1) cpn = 1;
+    if (cpn > mt) cpn = mt;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(gemm_ws_kernel<B_MN, DROP>, cudaFuncAttributeMaxDynamicSharedMemorySize, WS_SMEM);
+        attr_set = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(nt * cpn);
+    cfg.blockDim = dim3(WS_THREADS);
+    cfg.dynamicSmemBytes = WS_SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = fod_pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, gemm_ws_kernel<B_MN, DROP>, tmA, tmB, epi, mt, cpn);
+    return fod_check_launch("gemm_ws_kernel");
+}
+
 template <int BN>
 static int launch_gemm_major(const fod_linear_args* a, const GemmEpi& e, cudaStream_t st) {
     if constexpr (BN == 256) {
@@ -741,6 +1102,10 @@ extern "C" int fod_linear_fwd(const fod_linear_args* a, void* stream) {
     if (e.aux) vec = vec && (e.ld_aux % 8 == 0) && !(reinterpret_cast<uintptr_t>(e.aux) & 15);
     e.vec_ok = vec ? 1 : 0;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (gemm_ws_eligible(a, e)) {
+        if (e.drop.state) return a->b_mn ? launch_gemm_ws<true, true>(a, e, st) : launch_gemm_ws<false, true>(a, e, st);
+        return a->b_mn ? launch_gemm_ws<true, false>(a, e, st) : launch_gemm_ws<false, false>(a, e, st);
+    }
     switch (pick_bn(a)) {
         case 256: return launch_gemm_major<256>(a, e, st);
         case 128: return launch_gemm_major<128>(a, e, st);

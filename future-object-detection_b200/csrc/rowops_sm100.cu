@@ -141,9 +141,7 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restr
         for (int j = 0; j < 8; ++j) o[j] = rstd * (d[j] * g[j] - s1 - xh[j] * s2);
         store8(dz + row * RO_D + c0, o);
         if (drop.state) {  // gradient of the dropped-out addend: this lane's 8 columns are one Philox group (row * 32 + lane)
-            const uint32_t keep = dropout_keep8(key, (unsigned long long)row * (RO_D / 8) + lane, drop.thresh);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) o[j] = ((keep >> j) & 1u) ? o[j] * drop.scale : 0.f;
+            dropout_apply8(o, key, (unsigned long long)row * (RO_D / 8) + lane, drop.thresh, drop.scale);
             if (dz_drop) store8(dz_drop + row * RO_D + c0, o);
         }
 #pragma unroll

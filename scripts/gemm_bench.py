@@ -1,0 +1,76 @@
+"""Per-launch times of the transformer GEMM shapes (B = 32 stage 1: 22400 token rows), each epilogue variant,
+back-to-back launches in one CUDA graph (warm L2 where the operands fit).  usage: python scripts/gemm_bench.py"""
+import json
+import sys
+
+import torch
+
+sys.path.insert(0, ".")
+from fod_b200 import ops  # noqa: E402
+
+dev = torch.device("cuda:0")
+BF = torch.bfloat16
+
+
+def timed(fn, reps=20):
+    fn()
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        fn()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(g):
+            for _ in range(reps):
+                fn()
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / (3 * reps)
+
+
+M = int(sys.argv[1]) if len(sys.argv) > 1 else 22400
+x256 = torch.randn(M, 256, device=dev).to(BF)
+x2048 = torch.randn(M, 2048, device=dev).to(BF).relu()
+w1 = (torch.randn(2048, 256, device=dev) * 0.05).to(BF)
+w2 = (torch.randn(256, 2048, device=dev) * 0.05).to(BF)
+wqkv = (torch.randn(768, 256, device=dev) * 0.05).to(BF)
+wo = (torch.randn(256, 256, device=dev) * 0.05).to(BF)
+b2048, b256, b768 = (torch.randn(n, device=dev) for n in (2048, 256, 768))
+gam, bet = torch.ones(256, device=dev), torch.zeros(256, device=dev)
+cs = torch.zeros(2048, device=dev)
+ops.set_dropout_seed(1, dev)
+cases = {
+    "fwd 2048x256 bias+relu": lambda: ops.gemm(x256, w1, bias=b2048, relu=True),
+    "fwd 2048x256 bias+relu+drop": lambda: ops.gemm(x256, w1, bias=b2048, relu=True, drop=(0.1, 3)),
+    "fwd 2048x256 plain": lambda: ops.gemm(x256, w1),
+    "dx 2048x256 mask+colsum": lambda: ops.gemm(x256, w2, b_mn=True, relu_mask=x2048, colsum_out=cs),
+    "dx 2048x256 plain": lambda: ops.gemm(x256, w2, b_mn=True),
+    "fwd 768x256 bias": lambda: ops.gemm(x256, wqkv, bias=b768),
+    "fwd 256x256 bias": lambda: ops.gemm(x256, wo, bias=b256),
+    "fwd_ln 256x2048": lambda: ops.gemm(x2048, w2, bias=b256, residual=x256, ln=(gam, bet, 1e-5)),
+    "fwd_ln 256x2048 drop": lambda: ops.gemm(x2048, w2, bias=b256, residual=x256, ln=(gam, bet, 1e-5), drop=(0.1, 4)),
+    "fwd_ln 256x256": lambda: ops.gemm(x256, wo, bias=b256, residual=x256, ln=(gam, bet, 1e-5)),
+    "dx 256x2048 residual": lambda: ops.gemm(x2048, w1, b_mn=True, residual=x256),
+    "dx 256x2048 plain": lambda: ops.gemm(x2048, w1, b_mn=True),
+}
+flops = {"2048x256": 2.0 * M * 2048 * 256, "768x256": 2.0 * M * 768 * 256, "256x256": 2.0 * M * 256 * 256,
+         "256x2048": 2.0 * M * 2048 * 256}
+import os
+only = os.environ.get("GEMM_CASE")
+for name, fn in cases.items():
+    if only and only != name:
+        continue
+    if os.environ.get("GEMM_EAGER"):  # under ncu: plain launches, no graph
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        continue
+    us = timed(fn)
+    f = flops[name.split()[1]]
+    print(json.dumps({"case": name, "M": M, "us": round(us, 2), "tflops": round(f / us / 1e6, 1)}))

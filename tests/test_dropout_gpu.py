@@ -42,7 +42,7 @@ def _gemm_mask(M, N, drop):
     return keep
 
 
-@pytest.mark.parametrize("M,N", [(5600, 2048), (300, 256), (77, 768)])
+@pytest.mark.parametrize("M,N", [(5600, 2048), (300, 256), (77, 768), (22400, 2048)])
 def test_gemm_dropout_rate_scaling_and_streams(M, N):
     from fod_b200 import ops
     ops.set_dropout_seed(1234, _dev())

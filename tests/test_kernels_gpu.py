@@ -314,3 +314,34 @@ def test_stem_conv7x7s2_matches_torch(N, H, W):
     y1 = ops.stem_conv7x7s2(ones, wk, t)
     ref1 = torch.nn.functional.conv2d(ones.float(), wq, t, stride=2, padding=3).relu()
     _close(y1, ref1, tol=1e-2, what="stem conv borders")
+
+
+@pytest.mark.parametrize("M,N,K", [(22400, 2048, 256), (22400, 768, 256), (6001, 2048, 256), (12800, 1024, 128),
+                                   (40000, 256, 64), (5000, 2048, 192)])
+def test_gemm_persistent_weight_stationary_path(M, N, K):
+    """Shapes the persistent K <= 256 kernel takes (csrc/gemm_sm100.cu: gemm_ws_kernel — >= 2 tiles per SM, N % 256 == 0):
+    every epilogue it implements, both operand layouts of W, ragged last M tile."""
+    from fod_b200 import ops
+    x, w = _rnd(M, K, seed=1), _rnd(N, K, scale=0.06, seed=2)
+    b = torch.randn(N, device=_dev())
+    ref = x.float() @ w.float().t() + b
+    _close(ops.gemm(x, w, bias=b), ref, what="bias")
+    _close(ops.gemm(x, w), ref - b, what="plain")
+    _close(ops.gemm(x, w, bias=b, relu=True), ref.relu(), what="relu")
+    mod = 350 if M % 350 == 0 else 0
+    res = _rnd(mod or M, N, seed=3)
+    rr = res.float().repeat(M // mod, 1) if mod else res.float()
+    _close(ops.gemm(x, w, bias=b, residual=res, res_row_mod=mod), ref + rr, what="residual")
+    # dX form: dy (M, K) · W (K, N) read MN-major, ReLU mask with scale, fused bias-gradient column sums
+    wt = _rnd(K, N, scale=0.06, seed=4)
+    mask = _rnd(M, N, seed=5).relu()
+    cs = torch.zeros(N, device=_dev())
+    dx = ops.gemm(x, wt, b_mn=True, relu_mask=mask, mask_scale=1.25, colsum_out=cs)
+    ref_dx = (x.float() @ wt.float()) * (mask.float() > 0) * 1.25
+    _close(dx, ref_dx, what="dX mask")
+    _close(cs, dx.float().sum(0), tol=2e-3, what="colsum")
+    _close(ops.gemm(x, wt, b_mn=True), x.float() @ wt.float(), what="dX plain")
+    # twice in a row on one stream: the second launch must not see stale barriers / TMEM
+    y1 = ops.gemm(x, w, bias=b, relu=True)
+    y2 = ops.gemm(x, w, bias=b, relu=True)
+    assert torch.equal(y1, y2)
