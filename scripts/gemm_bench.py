@@ -1,6 +1,7 @@
 """Per-launch times of the transformer GEMM shapes (B = 32 stage 1: 22400 token rows), each epilogue variant,
 back-to-back launches in one CUDA graph (warm L2 where the operands fit).  usage: python scripts/gemm_bench.py"""
 import json
+import os
 import sys
 
 import torch
@@ -59,9 +60,45 @@ cases = {
     "dx 256x2048 residual": lambda: ops.gemm(x2048, w1, b_mn=True, residual=x256),
     "dx 256x2048 plain": lambda: ops.gemm(x2048, w1, b_mn=True),
 }
+# attention / element-wise cases (one encoder layer at B = 32: 64 sequences of 350 tokens; stage 2: S = 1400)
+def _attn_case(nseq, S, drop, bwd, mode=0):
+    st = {}
+    d = (0.1, 9) if drop else None
+
+    def run():
+        if not st:  # built on first use, so a GEMM_CASE filter launches nothing else
+            qkv = torch.randn(nseq, S, 768, device=dev).to(BF)
+            st["q"], st["k"], st["v"] = qkv[..., :256], qkv[..., 256:512], qkv[..., 512:]
+            if bwd:
+                st["o"], st["lse"] = ops.attn_fwd(st["q"], st["k"], st["v"], 32 ** -0.5, 8, drop=d)
+                st["do"] = torch.randn_like(st["o"])
+        if bwd:
+            return ops.attn_bwd(st["q"], st["k"], st["v"], st["o"], st["lse"], st["do"], 32 ** -0.5, 8, mode=mode, drop=d)
+        return ops.attn_fwd(st["q"], st["k"], st["v"], 32 ** -0.5, 8, drop=d)
+    return run
+
+
+def _relu_case(n):
+    st = {}
+
+    def run():
+        if not st:
+            st["t"] = [torch.randn(n, device=dev).to(BF) for _ in range(3)]
+        return ops.relu_bwd_add(*st["t"])
+    return run
+
+
+cases["fwd_ln_save 256x2048 drop"] = lambda: ops.gemm(x2048, w2, bias=b256, residual=x256, ln=(gam, bet, 1e-5), save_ln=True, drop=(0.1, 4))
+cases["attn_fwd 64x350 drop"] = _attn_case(64, 350, True, False)
+cases["attn_fwd 64x350"] = _attn_case(64, 350, False, False)
+cases["attn_bwd 64x350 drop"] = _attn_case(64, 350, True, True)
+cases["attn_bwd 64x350"] = _attn_case(64, 350, False, True)
+cases["attn_fwd 32x1400"] = _attn_case(32, 1400, False, False)
+cases["attn_bwd 32x1400"] = _attn_case(32, 1400, False, True)
+cases["relu_bwd_add3 183500800"] = _relu_case(183500800)
+
 flops = {"2048x256": 2.0 * M * 2048 * 256, "768x256": 2.0 * M * 768 * 256, "256x256": 2.0 * M * 256 * 256,
          "256x2048": 2.0 * M * 2048 * 256}
-import os
 only = os.environ.get("GEMM_CASE")
 for name, fn in cases.items():
     if only and only != name:
@@ -72,5 +109,8 @@ for name, fn in cases.items():
         torch.cuda.synchronize()
         continue
     us = timed(fn)
-    f = flops[name.split()[1]]
-    print(json.dumps({"case": name, "M": M, "us": round(us, 2), "tflops": round(f / us / 1e6, 1)}))
+    f = flops.get(name.split()[1])
+    if f is None and name.startswith("attn"):
+        nseq, S = (int(v) for v in name.split()[1].split("x"))
+        f = (4.0 if "fwd" in name else 10.0) * nseq * S * S * 256
+    print(json.dumps({"case": name, "M": M, "us": round(us, 2), "tflops": round(f / us / 1e6, 1) if f else None}))
