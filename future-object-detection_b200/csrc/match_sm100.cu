@@ -493,3 +493,48 @@ extern "C" int fod_set_loss(const fod_set_loss_args* a, void* stream) {
                                                a->main_level, a->w_ce, a->w_bbox, a->w_giou);
     return fod_check_launch("set_loss_finalize_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of fod_set_loss: the (L,B,8) partial-sum workspace lives in a file-scope device array instead of
+// caller memory, for callers that cannot allocate (CUDA-graph capture, serving loops, harnesses that forbid cudaMalloc).
+// Every GPU that loads the library holds the array (128 KB) until exit.  In host code `g_set_loss_partial` is only a
+// stand-in for the symbol, not a device address: the address is looked up once per device with that device current.
+// All calls share the array and it keeps the last call's contents; the region a call uses is cleared on the caller's
+// stream first.  Calls that overlap on the GPU (different streams, no ordering) race on it.
+static __device__ __align__(256) float g_set_loss_partial[FOD_SET_LOSS_STATIC_MAX_LB * 8];
+
+static int set_loss_static_scratch(float** out) {
+    constexpr int kMaxDev = 64;
+    static float* ptr[kMaxDev] = {};
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= kMaxDev) return fod_fail(FOD_E_LAUNCH, "set_loss_static: cudaGetDevice failed");
+    float* p = __atomic_load_n(&ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_set_loss_partial);
+        if (e != cudaSuccess || !p) {
+            (void)cudaGetLastError();
+            return fod_fail(FOD_E_LAUNCH, "set_loss_static: cudaGetSymbolAddress(g_set_loss_partial) failed");
+        }
+        __atomic_store_n(&ptr[dev], p, __ATOMIC_RELEASE);  // the same value from every thread that gets here
+    }
+    *out = p;
+    return FOD_OK;
+}
+
+extern "C" int fod_set_loss_static(const fod_set_loss_args* a, void* stream) {
+    if (!a) return fod_fail(FOD_E_ARG, "set_loss_static: null args");
+    if (a->L <= 0 || a->B <= 0 || (long long)a->L * a->B > FOD_SET_LOSS_STATIC_MAX_LB)
+        return fod_fail(FOD_E_ARG, "set_loss_static: L*B exceeds FOD_SET_LOSS_STATIC_MAX_LB (4096); use fod_set_loss with a caller workspace");
+    float* scratch = nullptr;
+    int rc = set_loss_static_scratch(&scratch);
+    if (rc) return rc;
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (cudaMemsetAsync(scratch, 0, sizeof(float) * 8 * (size_t)a->L * a->B, st) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return fod_fail(FOD_E_LAUNCH, "set_loss_static: clearing the scratch failed");
+    }
+    fod_set_loss_args b = *a;
+    b.partial = scratch;  // a->partial is ignored
+    return fod_set_loss(&b, stream);
+}

@@ -126,6 +126,7 @@ SYMBOLS = {
     "fod_targets_compact": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _F, _F, _VP]),
     "fod_match": (C.c_int, [C.POINTER(MatchArgs), _VP]),
     "fod_set_loss": (C.c_int, [C.POINTER(SetLossArgs), _VP]),
+    "fod_set_loss_static": (C.c_int, [C.POINTER(SetLossArgs), _VP]),
     "fod_ap_match": (C.c_int, [C.POINTER(ApArgs), _VP]),
     "fod_flat_adamw_step": (C.c_int, [C.POINTER(AdamWArgs), _VP]),
     "fod_optim_workspace_floats": (C.c_int, []),

@@ -314,6 +314,17 @@ typedef struct fod_set_loss_args {
 } fod_set_loss_args;
 int fod_set_loss(const fod_set_loss_args* a, void* stream);
 
+/* fod_set_loss_static — no counterpart in the reference; added for callers that
+ *   cannot allocate device memory (code under CUDA-graph capture, tight serving loops, harnesses that forbid
+ *   cudaMalloc).  Same computation and outputs as fod_set_loss, but the (L,B,8) partial-sum workspace is a file-scope
+ *   device array inside the library (128 KB per GPU that loads it, held until exit) and `a->partial` is ignored; the
+ *   call allocates nothing.  Limit: L*B <= FOD_SET_LOSS_STATIC_MAX_LB, larger problems are rejected with FOD_E_ARG.
+ *   All calls on a device share the array: it is cleared on `stream` at the start of every call, and two calls that
+ *   may overlap on the GPU (different streams without ordering) race — serialise them or use fod_set_loss.
+ */
+#define FOD_SET_LOSS_STATIC_MAX_LB 4096
+int fod_set_loss_static(const fod_set_loss_args* a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
