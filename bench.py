@@ -224,7 +224,7 @@ def run_cuda(args):
         from fod_b200.optim import FlatTrainState
         flat = FlatTrainState(core, lr=detr_args.lr, lr_backbone=detr_args.lr_backbone,
                               weight_decay=detr_args.weight_decay, bucket_mb=args.bucket_mb,
-                              wgrad_stream=bool(args.wgrad_stream))
+                              wgrad_stream=bool(args.wgrad_stream), tail_mb=args.tail_mb)
     opt = flat if flat is not None else T.setup_optimizer(core, detr_args, capturable=use_graph)
     # N > 1: gradients are averaged by the graph-capturable bucketed reducer (fod_b200/ddp.py: flat fp32 buckets,
     # NCCL AVG on a side stream overlapping backward) instead of torch's host-driven DDP wrapper
@@ -447,6 +447,7 @@ def main():
     ap.add_argument("--wgrad-stream", type=int, default=1, help="1: weight/bias gradient kernels on a second stream")
     ap.add_argument("--flat-grads", type=int, default=0, help="1: use the flat-bucket gradient path at N=1 too")
     ap.add_argument("--bucket-mb", type=float, default=32.0)
+    ap.add_argument("--tail-mb", type=float, default=0.0, help="size of a separate last (unhideable) gradient bucket; 0: none (measured: no gain at 8 GPUs)")
     ap.add_argument("--cudnn-benchmark", type=int, default=1, help="torch.backends.cudnn.benchmark, as the reference sets it")
     ap.add_argument("--profiler-range", type=int, default=0, help="1: cudaProfilerStart/Stop around the timed steps (for ncu)")
     args = ap.parse_args()

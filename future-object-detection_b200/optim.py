@@ -23,7 +23,7 @@ BF16 = torch.bfloat16
 
 class FlatTrainState:
     def __init__(self, model, lr=1e-4, lr_backbone=1e-5, weight_decay=1e-4, betas=(0.9, 0.999), eps=1e-8,
-                 bucket_mb=32.0, group=None, overlap=True, wgrad_stream=True):
+                 bucket_mb=32.0, group=None, overlap=True, wgrad_stream=True, tail_mb=0.0):
         """Parameter groups as runs/_helper.py:84-107: names containing "backbone" train at lr_backbone."""
         self.model = model
         named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
@@ -45,7 +45,7 @@ class FlatTrainState:
                 placed.add(q)
         order = new_order
         self.reducer = BucketedGradReducer([p for _, p in named], bucket_mb=bucket_mb, group=group, overlap=overlap,
-                                           order=order, wgrad_stream=wgrad_stream)
+                                           order=order, wgrad_stream=wgrad_stream, tail_mb=tail_mb)
         r = self.reducer
         dev = r.arena.device
         self.n = r.numel
