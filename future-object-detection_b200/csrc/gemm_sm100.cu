@@ -583,6 +583,7 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     if (a->split_k > 1) splits = a->split_k;
     else if (a->split_k < 0) {  // auto: fill the 148 SMs, at least two k-blocks per split
         splits = (148 + mt * nt - 1) / (mt * nt);
+        if (BN == 256 && mt * nt <= 148) splits = 148 / (mt * nt);  // one CTA per SM at this tile width: no partial second wave
         if (splits > total_kb / 2) splits = total_kb / 2;
         if (splits < 1) splits = 1;
     }
@@ -1017,6 +1018,16 @@ static int pick_bn(const fod_linear_args* a) {
     static const int forced = [] { const char* e = getenv("FOD_GEMM_BN"); return e ? atoi(e) : 0; }();  // tuning probe
     if (forced == 64 || forced == 128 || (forced == 256 && a->N > 128)) return forced;
     const int mt = (a->M + GEMM_BM - 1) / GEMM_BM;
+    // Contractions the library may split (weight gradients: K = token rows): the SMs are filled by split-K, so take the
+    // widest tile as long as every split keeps >= 6 k-blocks of work — an M128 x K16 MMA costs ~52 clk for any N <= 64
+    // and 132 clk for N = 256 (csrc/microbench.cu), the A tile is fetched once per 256 instead of per 64 columns, and
+    // 148 / tiles splits make exactly one wave.  Measured (us, before -> after): K = 22 400: dW 2048x256 45.7 -> 22.9,
+    // 256x2048 48.6 -> 25.1, 768x256 19.8 -> 11.8; K = 4 096: 2048x256 11.2 -> 9.1; below the threshold the narrow tile wins
+    // (K = 4 096: 768x256 7.1 vs 7.7, 256x256 4.7 vs 6.7).
+    if ((a->split_k < 0 || a->atomic_out) && a->split_k <= 1 && a->N >= 256) {
+        const long long total_kb = (a->K + GEMM_BK - 1) / GEMM_BK, tiles = (long long)mt * ((a->N + 255) / 256);
+        if (tiles <= 148 && total_kb * tiles >= 6 * 148) return 256;
+    }
     const int cands[3] = {256, 128, 64};
     for (int i = 0; i < 3; ++i) {
         const int bn = cands[i];

@@ -81,6 +81,54 @@ __global__ void __launch_bounds__(512, 1) exp_kernel(int iters, unsigned long lo
     if (acc == 123.456f) sink[0] = acc;
 }
 
+// Issue rate of tcgen05.mma (M = 128, K = 16, bf16) by N, with the A operand in shared memory (SS) or in tensor memory (TS):
+// one thread issues kPer MMAs, commits, waits; smem / TMEM contents are whatever is there (timing only).
+template <int N, bool TS>
+__global__ void __launch_bounds__(128, 1) mma_rate_kernel(int iters, unsigned long long* cycles) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    __shared__ uint32_t slot;
+    __shared__ uint64_t bar;
+    const int warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < (16384 + 32768) / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc<512>(&slot);
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t base = slot;
+    constexpr int kPer = 32;
+    if (threadIdx.x == 0) {
+        constexpr uint32_t idesc = umma_idesc_bf16(128, N, 0, 0);
+        const uint64_t dA = umma_smem_desc(smem_u32(smem), 16, 1024, 2);            // 128 x 64 bf16, K-major, SWIZZLE_128B
+        const uint64_t dB = umma_smem_desc(smem_u32(smem) + 16384, 16, 1024, 2);    // N x 64
+        uint32_t ph = 0;
+        const long long t0 = clock64();
+        for (int i = 0; i < iters; ++i) {
+#pragma unroll
+            for (int k = 0; k < kPer; ++k) {
+                if (TS) umma_bf16_ts(base, base + 256 + (k & 3) * 8, umma_desc_adv(dB, (k & 3) * 32), idesc, 1u);
+                else umma_bf16_ss(base, umma_desc_adv(dA, (k & 3) * 32), umma_desc_adv(dB, (k & 3) * 32), idesc, 1u);
+            }
+            umma_commit(&bar);
+            mbar_wait(&bar, ph);
+            ph ^= 1;
+        }
+        const long long t1 = clock64();
+        cycles[blockIdx.x] = (unsigned long long)(t1 - t0);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) {
+        tc_fence_after();
+        tmem_dealloc<512>(base);
+    }
+}
+
 template <typename F>
 static double run(F launch, unsigned long long* d_cyc) {
     launch();
@@ -120,5 +168,15 @@ int main() {
         c = run([&] { exp_kernel<1><<<148, 512>>>(iters, d_cyc, fs); }, d_cyc);
         printf("  FMA-pipe poly-3 : %.0f cycles -> %.2f exp/clk/SM\n", c, (double)iters * 8 * 512 / c);
     }
+    printf("tcgen05.mma issue rate, M128 K16 bf16, 148 CTAs, 32 MMAs per commit\n");
+    const int mi = 200;
+#define MR(NN, TSV)                                                                                             \
+    {                                                                                                           \
+        cudaFuncSetAttribute(mma_rate_kernel<NN, TSV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 52000);     \
+        double c = run([&] { mma_rate_kernel<NN, TSV><<<148, 128, 52000>>>(mi, d_cyc); }, d_cyc);               \
+        printf("  N %3d  A in %s: %.1f clk per MMA -> %.0f flop/clk/SM\n", NN, TSV ? "TMEM" : "smem", c / (mi * 32.0), \
+               2.0 * 128 * NN * 16 / (c / (mi * 32.0)));                                                        \
+    }
+    MR(32, false) MR(64, false) MR(128, false) MR(256, false) MR(32, true) MR(64, true) MR(128, true) MR(256, true)
     return 0;
 }

@@ -89,6 +89,14 @@ def _relu_case(n):
 
 
 cases["fwd_ln_save 256x2048 drop"] = lambda: ops.gemm(x2048, w2, bias=b256, residual=x256, ln=(gam, bet, 1e-5), save_ln=True, drop=(0.1, 4))
+# weight gradients: dW (N, K) += dYᵀ (N, rows) · X (rows, K), both operands MN-major, split-K with fp32 reductions
+_gw1, _gw2 = torch.zeros(2048, 256, device=dev), torch.zeros(256, 2048, device=dev)
+_gqkv, _go = torch.zeros(768, 256, device=dev), torch.zeros(256, 256, device=dev)
+_x768 = torch.randn(M, 768, device=dev).to(BF)
+cases["dw 2048x256"] = lambda: ops.gemm(x2048, x256, a_mn=True, b_mn=True, accum_into=_gw1)
+cases["dw 256x2048"] = lambda: ops.gemm(x256, x2048, a_mn=True, b_mn=True, accum_into=_gw2)
+cases["dw 768x256"] = lambda: ops.gemm(_x768, x256, a_mn=True, b_mn=True, accum_into=_gqkv)
+cases["dw 256x256"] = lambda: ops.gemm(x256, x256, a_mn=True, b_mn=True, accum_into=_go)
 cases["attn_fwd 64x350 drop"] = _attn_case(64, 350, True, False)
 cases["attn_fwd 64x350"] = _attn_case(64, 350, False, False)
 cases["attn_bwd 64x350 drop"] = _attn_case(64, 350, True, True)
@@ -110,6 +118,9 @@ for name, fn in cases.items():
         continue
     us = timed(fn)
     f = flops.get(name.split()[1])
+    if name.startswith("dw"):
+        nn, kk = (int(v) for v in name.split()[1].split("x"))
+        f = 2.0 * M * nn * kk
     if f is None and name.startswith("attn"):
         nseq, S = (int(v) for v in name.split()[1].split("x"))
         f = (4.0 if "fwd" in name else 10.0) * nseq * S * S * 256
