@@ -24,6 +24,7 @@ BF16 = torch.bfloat16
 # CUDA graph — whose kernel arguments, `call` included, are frozen — draws fresh masks on every replay.
 _RNG = {}
 _CALL = [0]
+_SNAP = [None]
 
 
 def rng_state(device):
@@ -41,22 +42,26 @@ def set_dropout_seed(seed, device="cuda"):
 
 def begin_forward():
     """Start of a model forward pass (FuturePredCore.forward): dropout call ids restart at 1, and the first dropout
-    site of the pass advances the device-side step counter, so every pass — and every replay of a captured graph —
-    draws fresh masks.  The backward pass must run before the next training forward: it regenerates its masks from
-    the same (seed, step, call id)."""
+    site of the pass advances the device-side step counter and takes a SNAPSHOT of {seed, step}, so every pass — and
+    every replay of a captured graph — draws fresh masks.  The snapshot travels with each site's (p, call id) into the
+    autograd context: backward regenerates its masks from it, so several forward passes may precede their backward
+    passes (gradient accumulation) without mixing up masks."""
     _CALL[0] = 0
+    _SNAP[0] = None
 
 
 def drop_site(p, training):
-    """(p, call id) of the next dropout site of this forward pass, or None when dropout is off."""
+    """(p, call id, state snapshot) of the next dropout site of this forward pass, or None when dropout is off."""
     if not training or not p or p <= 0.0:
         return None
     if not 0.0 < p < 1.0:
         raise ValueError("dropout probability has to be in [0, 1), got %r" % (p,))
-    if _CALL[0] == 0:
-        rng_advance(torch.device("cuda", torch.cuda.current_device()))
+    if _CALL[0] == 0 or _SNAP[0] is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+        rng_advance(dev)
+        _SNAP[0] = rng_state(dev).clone()
     _CALL[0] += 1
-    return (float(p), _CALL[0])
+    return (float(p), _CALL[0], _SNAP[0])
 
 
 def rng_advance(device):
@@ -66,8 +71,10 @@ def rng_advance(device):
 
 
 def _fill_drop(d, drop, device):
+    """drop = (p, call id[, state tensor]): without a state tensor the device's live {seed, step} is read."""
     if drop is not None:
-        d.rng_state, d.p, d.call = _p(rng_state(device)), drop[0], drop[1]
+        st = drop[2] if len(drop) > 2 and drop[2] is not None else rng_state(device)
+        d.rng_state, d.p, d.call = _p(st), drop[0], drop[1]
 
 
 def _stream():
@@ -158,7 +165,7 @@ def gemm(x, w, bias=None, residual=None, res_row_mod=0, relu=False, ln=None, out
                                     M, N, K), 2.0 * M * N * K,
              2.0 * (M * K + N * K) + M * N * (4 if (out_f32 or accum_into is not None) else 2),
              replay=(lambda: L.fod_linear_fwd(C.byref(a), _stream())) if _t is not None else None,
-             keep=(x, w, bias, residual, relu_mask, col_scale, accum_into, colsum_out, ln, outs))
+             keep=(x, w, bias, residual, relu_mask, col_scale, accum_into, colsum_out, ln, outs, drop))
     LAUNCH_COUNTS["gemm_bf16_kernel"] += 1
     return outs[0] if len(outs) == 1 else tuple(outs)
 
@@ -205,7 +212,7 @@ def attn_fwd(q1, k1, v, scale, heads=8, q2=None, k2=None, batch=None, drop=None)
     prof.end(_t, "attn_fwd_p%d_%dx%d" % (parts, Lq, Lk), (2.0 + 2.0 * parts) * B * Lq * Lk * D,
              2.0 * D * (B * Lq * (parts + 1) + B * Lk * 2 + (parts - 1) * kb * Lk),
              replay=(lambda: L.fod_attn_fwd(C.byref(a), _stream())) if _t is not None else None,
-             keep=(q1, k1, v, q2, k2, out, lse))
+             keep=(q1, k1, v, q2, k2, out, lse, drop))
     LAUNCH_COUNTS["attn_fwd_kernel"] += 1
     return out, lse
 
@@ -264,7 +271,7 @@ def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=
     prof.end(_t, "attn_bwd_p%d_%dx%d" % (parts, Lq, Lk), (4.0 + 6.0 * parts) * B * Lq * Lk * Cw,
              2.0 * Cw * (B * Lq * (2 * parts + 2) + B * Lk * (2 * parts + 2)),
              replay=(lambda: L.fod_attn_bwd(C.byref(g), _stream())) if _t is not None else None,
-             keep=(q1, k1, v, q2, k2, out, lse, dout, delta, dq1, dk1, dv, dq2, dk2))
+             keep=(q1, k1, v, q2, k2, out, lse, dout, delta, dq1, dk1, dv, dq2, dk2, drop))
     if attn_bwd_is_fused(Lq, q2 is not None, mode):
         LAUNCH_COUNTS["attn_bwd_fused_kernel"] += 1
     else:
@@ -319,7 +326,7 @@ def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows
     call = lambda: L.fod_ln_bwd_drop(*ptrs, C.byref(dstruct), _stream())
     lib.check(call(), "fod_ln_bwd")
     prof.end(_t, "ln_bwd_%d" % M, 0.0, 1536.0 * M, replay=call if _t is not None else None,
-             keep=(dy, dy2, pre, bcast, mean, rstd, gamma, dz, dzd, dgamma, dbeta, dzsum))
+             keep=(dy, dy2, pre, bcast, mean, rstd, gamma, dz, dzd, dgamma, dbeta, dzsum, drop))
     LAUNCH_COUNTS["ln_bwd_kernel"] += 1
     return dz if drop is None else (dz, dzd)
 

@@ -3,6 +3,7 @@
 SpatioTemporalDETR with the reference's forward signature and return tuple (st_detr.py:98-167), plus
 `build_model(args, detr_args)` mirroring runs/_model.py:14-83.
 """
+import os
 from dataclasses import dataclass
 
 import torch
@@ -381,7 +382,7 @@ class SpatioTemporalDETR(nn.Module):
 # Measured at 8 GPUs on one box: device-timed step unchanged (28.44 / 28.46 vs 28.52 / 28.47 ms), end-to-end
 # throughput WORSE (8 430 -> 7 070-7 740 clips/s: ranks that launch late now stall everyone at the first kernel), so
 # the reference's placement inside the criterion stays the default.
-_EARLY_NUM_BOXES = int(__import__("os").environ.get("FOD_EARLY_NUM_BOXES", "0")) != 0
+_EARLY_NUM_BOXES = int(os.environ.get("FOD_EARLY_NUM_BOXES", "0")) != 0
 
 
 def set_dropout(model, p):

@@ -97,6 +97,23 @@ cases["dw 2048x256"] = lambda: ops.gemm(x2048, x256, a_mn=True, b_mn=True, accum
 cases["dw 256x2048"] = lambda: ops.gemm(x256, x2048, a_mn=True, b_mn=True, accum_into=_gw2)
 cases["dw 768x256"] = lambda: ops.gemm(_x768, x256, a_mn=True, b_mn=True, accum_into=_gqkv)
 cases["dw 256x256"] = lambda: ops.gemm(x256, x256, a_mn=True, b_mn=True, accum_into=_go)
+def _ln_bwd_case(rows, drop):
+    st = {}
+
+    def run():
+        if not st:
+            st["dy"], st["pre"] = (torch.randn(rows, 256, device=dev).to(BF) for _ in range(2))
+            st["mean"], st["rstd"] = torch.zeros(rows, device=dev), torch.ones(rows, device=dev)
+            st["acc"] = torch.zeros(3, 256, device=dev)
+        a = st["acc"]
+        return ops.ln_bwd(st["dy"], st["pre"], st["mean"], st["rstd"], gam, a[0], a[1], dzsum=a[2], drop=(0.1, 5) if drop else None)
+    return run
+
+
+cases["ln_bwd 22400"] = _ln_bwd_case(22400, False)
+cases["ln_bwd 22400 drop"] = _ln_bwd_case(22400, True)
+cases["ln_bwd 4096 drop"] = _ln_bwd_case(4096, True)
+cases["ln_bwd 128 drop"] = _ln_bwd_case(128, True)
 cases["attn_fwd 64x350 drop"] = _attn_case(64, 350, True, False)
 cases["attn_fwd 64x350"] = _attn_case(64, 350, False, False)
 cases["attn_bwd 64x350 drop"] = _attn_case(64, 350, True, True)

@@ -134,6 +134,37 @@ def test_ffn_ln_dropout_matches_torch_with_same_masks(M):
         assert _rel(a, r) < 2e-2, (name, _rel(a, r))
 
 
+def test_backward_uses_the_masks_of_its_own_forward_pass():
+    """Two forward passes before the first backward (gradient accumulation): every dropout site carries a snapshot of
+    {seed, step} of ITS pass, so the first pass's backward regenerates the first pass's masks."""
+    from fod_b200 import autograd as A
+    from fod_b200 import ops
+    D, M = 256, 600
+    x, res = _rnd(M, D, seed=1), _rnd(M, D, seed=2)
+    w = (torch.randn(D, D, device=_dev()) * 0.06)
+    b, gam, bet = torch.randn(D, device=_dev()), torch.rand(D, device=_dev()) + 0.5, torch.randn(D, device=_dev())
+    dy = _rnd(M, D, seed=3)
+
+    def forward():
+        ops.begin_forward()
+        xg = x.clone().requires_grad_()
+        y = A.linear_ln(xg, res, w, b, w.to(BF), gam, bet, 1e-5, drop=ops.drop_site(P, True))
+        return xg, y
+
+    ops.set_dropout_seed(321, _dev())
+    xg, y = forward()
+    y.backward(dy)
+    y_ref, g_ref = y.detach().clone(), xg.grad.clone()
+    ops.set_dropout_seed(321, _dev())
+    xg1, y1 = forward()
+    xg2, y2 = forward()                      # advances the step: other masks
+    assert torch.equal(y1, y_ref) and not torch.equal(y2, y_ref)
+    y1.backward(dy)                           # after the second forward
+    assert torch.equal(xg1.grad, g_ref)
+    y2.backward(dy)
+    assert not torch.equal(xg2.grad, g_ref)
+
+
 def _attn_mask(B, H, Lq, Lk, scale, q1, k1, drop, q2=None, k2=None):
     """Dropped-out attention weights read back through one-hot values, 32 keys per probe launch: (B, H, Lq, Lk)."""
     from fod_b200 import ops
