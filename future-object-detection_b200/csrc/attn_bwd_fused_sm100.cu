@@ -120,7 +120,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
                       const __grid_constant__ CUtensorMap tmDV, const AttnBwdFusedParams p) {
     using L = FusedBwdSmem<NP>;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBars);
     uint64_t* kv_full = bars + 0;    // [2]
     uint64_t* kv_empty = bars + 2;   // [2]

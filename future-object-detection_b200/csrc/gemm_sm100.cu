@@ -291,7 +291,7 @@ __global__ void __launch_bounds__(GemmThreads<BN>::kThreads, BN == 256 ? 1 : 2)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmEpi p) {
     using Cfg = GemmCfg<BN>;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* aux_stage = smem + p.num_stages * Cfg::kStageBytes;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(aux_stage + (p.aux_mode ? Cfg::kAuxBytes : 0));
     uint64_t* empty_bar = full_bar + GEMM_MAX_STAGES;
@@ -781,7 +781,7 @@ __global__ void __launch_bounds__(WS_THREADS, 1)
 gemm_ws_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmEpi p, int mt,
                int ctas_per_n) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* sB = smem;
     uint8_t* sA = sB + WS_B_BYTES;
     uint8_t* sX = sA + WS_A_STAGES * WS_A_BYTES;

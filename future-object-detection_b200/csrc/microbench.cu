@@ -86,7 +86,7 @@ __global__ void __launch_bounds__(512, 1) exp_kernel(int iters, unsigned long lo
 template <int N, bool TS>
 __global__ void __launch_bounds__(128, 1) mma_rate_kernel(int iters, unsigned long long* cycles) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     __shared__ uint32_t slot;
     __shared__ uint64_t bar;
     const int warp = threadIdx.x >> 5;

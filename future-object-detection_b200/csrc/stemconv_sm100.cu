@@ -65,7 +65,7 @@ __device__ __forceinline__ void stem_issue_patch(const StemParams& p, int tile, 
 __global__ void __launch_bounds__(128, 2)
 stem_conv7x7s2_kernel(const StemParams p) {
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint8_t* sA = smem;
     uint8_t* sB = sA + ST_A_BYTES;
     uint8_t* sPatch = sB + ST_B_BYTES;

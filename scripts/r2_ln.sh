@@ -1,5 +1,5 @@
 #!/bin/bash
-timeout 600 python -m pytest tests/test_kernels_gpu.py tests/test_dropout_gpu.py -q -m gpu -k "ln or block or linear or ffn" 2>&1 | tail -2
-for c in "ln_bwd 22400" "ln_bwd 22400 drop" "ln_bwd 4096 drop" "ln_bwd 128 drop"; do
-GEMM_CASE="$c" timeout 120 python scripts/gemm_bench.py 2>&1 | tail -1
-done
+mkdir -p gpurun_out
+(cd future-object-detection_b200 && timeout 300 ./selftest_fod 255 > ../gpurun_out/selftest_all.log 2>&1; echo "selftest exit $?"; tail -2 ../gpurun_out/selftest_all.log | cut -c1-150)
+timeout 300 python scripts/gemm_bench.py > gpurun_out/op_bench.jsonl 2> gpurun_out/op_bench.err; cat gpurun_out/op_bench.jsonl
+bash scripts/r2_full_bench.sh | grep -E "passed|failed|exit|value|dropout_off" | cut -c1-300
