@@ -80,6 +80,12 @@ struct AttnBwdFusedParams {
     int bm_q1, bm_k1, bm_q2, bm_k2, bm_v;
     float scale;
     DropoutCfg drop;             // DROP kernels: the forward call's dropout on P, regenerated here
+    // Query groups (grid.z > 1, one-part attention longer than kMaxQT query tiles): CTA z owns query tiles
+    // [z*kMaxQT, z*kMaxQT + kMaxQT) and ALL key tiles.  dQ is complete per CTA; dK / dV are partial sums over the
+    // group's queries and are reduced with fp32 vector atomics into these (B,H,Lk,32) workspaces (zeroed by the host
+    // side, converted to bf16 by attn_ws_to_bf16_kernel afterwards).  nullptr: direct bf16 TMA stores.
+    float* ws_dk;
+    float* ws_dv;
 };
 
 // One [128][32] fp32 accumulator tile, TMEM -> bf16 -> swizzled staging tile -> TMA store.  Executed by the four warps
@@ -105,6 +111,21 @@ __device__ __forceinline__ void af_store_tile(uint32_t taddr_lane, uint8_t* slot
     if (issuer) {
         tma_store_3d(tm, slot, h * AF_D, row0, b);
         bulk_commit();
+    }
+}
+
+// One [128][32] fp32 accumulator tile added into a (.., Lk, 32) fp32 workspace: a thread owns one key row (128 contiguous
+// bytes) and issues eight 16-byte vector reductions.
+__device__ __forceinline__ void af_red_tile(uint32_t taddr_lane, float* ws_row, bool valid) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(taddr_lane, v);
+    tmem_ld_wait();
+    if (valid) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+            atomicAdd(reinterpret_cast<float4*>(ws_row) + c,
+                      make_float4(__uint_as_float(v[c * 4]), __uint_as_float(v[c * 4 + 1]), __uint_as_float(v[c * 4 + 2]),
+                                  __uint_as_float(v[c * 4 + 3])));
     }
 }
 
@@ -138,7 +159,8 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int h = blockIdx.x, b = blockIdx.y;
     if (threadIdx.x == 0) AF_STAMP(2, 0, 0);  // kernel entry
-    const int nqt = (p.Lq + AF_T - 1) / AF_T;
+    const int qt0 = blockIdx.z * L::kMaxQT;                                   // first query tile of this CTA's group
+    const int nqt = min(L::kMaxQT, (p.Lq + AF_T - 1) / AF_T - qt0);           // its query tiles (local index i)
     const int nkt = (p.Lk + AF_T - 1) / AF_T;
     const int ntiles = nqt * nkt;
 
@@ -194,9 +216,9 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
                     mbar_wait(qdo_empty + s, ((t / L::kQS) & 1) ^ 1);
                     mbar_arrive_expect_tx(qdo_full + s, (NP + 1) * AF_TILE);
                     uint8_t* sq = smem + L::kQ + s * NP * AF_TILE;
-                    tma_load_3d(sq, &tmQ1, qdo_full + s, h * AF_D, i * AF_T, b * p.bm_q1);
-                    if (NP == 2) tma_load_3d(sq + AF_TILE, &tmQ2, qdo_full + s, h * AF_D, i * AF_T, b * p.bm_q2);
-                    tma_load_3d(smem + L::kDO + s * AF_TILE, &tmDO, qdo_full + s, h * AF_D, i * AF_T, b);
+                    tma_load_3d(sq, &tmQ1, qdo_full + s, h * AF_D, (qt0 + i) * AF_T, b * p.bm_q1);
+                    if (NP == 2) tma_load_3d(sq + AF_TILE, &tmQ2, qdo_full + s, h * AF_D, (qt0 + i) * AF_T, b * p.bm_q2);
+                    tma_load_3d(smem + L::kDO + s * AF_TILE, &tmDO, qdo_full + s, h * AF_D, (qt0 + i) * AF_T, b);
                 }
             }
         }
@@ -314,7 +336,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
             for (int i = 0; i < L::kMaxQT; ++i)
 #pragma unroll
                 for (int u = 0; u < 2; ++u) {
-                    const int q = i * AF_T + u * 64 + r0;
+                    const int q = (qt0 + i) * AF_T + u * 64 + r0;
                     const bool ok = i < nqt && q < p.Lq;
                     a4[i][u] = ok ? __ldg(reinterpret_cast<const uint4*>(o_base + (long long)q * p.ldo) + ch) : make_uint4(0, 0, 0, 0);
                     d4[i][u] = ok ? __ldg(reinterpret_cast<const uint4*>(do_base + (long long)q * p.lddo) + ch) : make_uint4(0, 0, 0, 0);
@@ -325,7 +347,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
 #pragma unroll
                 for (int u = 0; u < 2; ++u) {
                     if (i >= nqt) break;  // warp-uniform
-                    const int rr = u * 64 + r0, q = i * AF_T + rr;
+                    const int rr = u * 64 + r0, q = (qt0 + i) * AF_T + rr;
                     const __nv_bfloat162* ha = reinterpret_cast<const __nv_bfloat162*>(&a4[i][u]);
                     const __nv_bfloat162* hd = reinterpret_cast<const __nv_bfloat162*>(&d4[i][u]);
                     float acc = 0.f;
@@ -358,6 +380,12 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
 #define AF_STORE_TILE(taddr, slot, tm, row0) \
     af_store_tile((taddr) + lane_off, (slot), (tm), (row0), row, half, issuer, h, b)
         auto read_out_dkv = [&](int jj) {  // dV / dK of key tile jj
+            if (NP == 1 && p.ws_dk) {  // query groups: partial sums into the fp32 workspaces
+                const int key = jj * AF_T + row;
+                float* dst = (half == 0 ? p.ws_dv : p.ws_dk) + (((long long)b * p.H + h) * p.Lk + key) * AF_D;
+                af_red_tile((half == 0 ? tmem_dV : tmem_dK) + lane_off, dst, key < p.Lk);
+                return;
+            }
             if (half == 0) {
                 AF_STORE_TILE(tmem_dV, my_slot, &tmDV, jj * AF_T);
                 if (NP == 2) AF_STORE_TILE(tmem_dK + AF_D, smem + L::kOut + 2 * AF_TILE, &tmDK2, jj * AF_T);
@@ -375,7 +403,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
             const float lse2 = s_lse[i * AF_T + row];
             const float dlt = s_dlt[i * AF_T + row];
             const unsigned long long g_row =
-                (((unsigned long long)b * p.H + h) * p.Lq + (unsigned long long)min(i * AF_T + row, p.Lq - 1)) * lkp8;
+                (((unsigned long long)b * p.H + h) * p.Lq + (unsigned long long)min((qt0 + i) * AF_T + row, p.Lq - 1)) * lkp8;
             const int kvalid = p.Lk - j * AF_T;  // >= 1
             if (threadIdx.x == 0) AF_STAMP(0, t, 0);
             mbar_wait(s_full, t & 1);
@@ -477,8 +505,8 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
             const int i = idx / NP, part = idx - i * NP;
             // (a run-time choice between two tensor-map POINTERS would make the compiler copy the __grid_constant__
             // maps to local memory, which the TMA unit cannot read: branch instead)
-            if (NP == 2 && part) AF_STORE_TILE(tmem_dQ + idx * AF_D, my_slot, &tmDQ2, i * AF_T);
-            else AF_STORE_TILE(tmem_dQ + idx * AF_D, my_slot, &tmDQ1, i * AF_T);
+            if (NP == 2 && part) AF_STORE_TILE(tmem_dQ + idx * AF_D, my_slot, &tmDQ2, (qt0 + i) * AF_T);
+            else AF_STORE_TILE(tmem_dQ + idx * AF_D, my_slot, &tmDQ1, (qt0 + i) * AF_T);
         }
         if (issuer) bulk_wait0();  // the staging tiles live in this CTA's shared memory: drain before it is released
         tc_fence_before();
@@ -492,6 +520,38 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
     if (threadIdx.x == 0) AF_STAMP(2, 0, 7);
 }
 
+// Query-group launches: zero the fp32 dK / dV workspaces, and afterwards write them as bf16 into the (strided) outputs.
+__global__ void attn_ws_zero_kernel(float4* __restrict__ ws, long long n4) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x)
+        ws[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+// one thread per 8 consecutive channels of one (batch, key, head)
+__global__ void attn_ws_to_bf16_kernel(const float* __restrict__ ws_dk, const float* __restrict__ ws_dv,
+                                       __nv_bfloat16* __restrict__ dk, __nv_bfloat16* __restrict__ dv, long long ld, int B,
+                                       int H, int Lk) {
+    const long long n = (long long)B * Lk * H * 4;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        const int c = (int)(t & 3);
+        const int h = (int)((t >> 2) % H);
+        const long long bk = (t >> 2) / H;  // b * Lk + key
+        const int key = (int)(bk % Lk);
+        const int b = (int)(bk / Lk);
+        const long long src = ((((long long)b * H + h) * Lk + key) * AF_D) + c * 8;
+        const long long dst = bk * ld + h * AF_D + c * 8;
+#pragma unroll
+        for (int w = 0; w < 2; ++w) {
+            const float4 x = *reinterpret_cast<const float4*>((w ? ws_dv : ws_dk) + src);
+            const float4 y = *reinterpret_cast<const float4*>((w ? ws_dv : ws_dk) + src + 4);
+            uint4 u;
+            u.x = pack_bf16x2(x.x, x.y);
+            u.y = pack_bf16x2(x.z, x.w);
+            u.z = pack_bf16x2(y.x, y.y);
+            u.w = pack_bf16x2(y.z, y.w);
+            *reinterpret_cast<uint4*>((w ? dv : dk) + dst) = u;
+        }
+    }
+}
+
 static int make_seq_tmap_f(CUtensorMap* tm, const void* base, int rowlen, int L, int B, long long ld, long long bs) {
     const bool bcast = (bs == 0) || (B == 1);
     uint64_t dims[3] = {(uint64_t)rowlen, (uint64_t)L, (uint64_t)(bcast ? 1 : B)};
@@ -500,10 +560,19 @@ static int make_seq_tmap_f(CUtensorMap* tm, const void* base, int rowlen, int L,
     return make_tmap_bf16(tm, base, 3, dims, str, box, 64);
 }
 
+// floats of workspace a query-group launch needs (0: the call runs as one group and needs none)
+static long long attn_bwd_fused_ws_floats(const fod_attn_args* a) {
+    const int nqt = (a->Lq + AF_T - 1) / AF_T;
+    if (a->q2 || nqt <= FusedBwdSmem<1>::kMaxQT) return 0;
+    return 2ll * a->B * a->H * a->Lk * AF_D;
+}
+
 bool attn_bwd_fused_supported(const fod_attn_bwd_args* g) {
     const fod_attn_args* a = &g->fwd;
     const int nqt = (a->Lq + AF_T - 1) / AF_T;
-    return nqt <= (a->q2 ? FusedBwdSmem<2>::kMaxQT : FusedBwdSmem<1>::kMaxQT);
+    if (nqt <= (a->q2 ? FusedBwdSmem<2>::kMaxQT : FusedBwdSmem<1>::kMaxQT)) return true;
+    // longer one-part sequences: query groups with dK / dV reduced through the caller's fp32 workspace
+    return !a->q2 && g->ws && g->ws_floats >= attn_bwd_fused_ws_floats(a) && !(reinterpret_cast<uintptr_t>(g->ws) & 15);
 }
 
 // Arguments were validated by fod_attn_bwd.
@@ -573,7 +642,16 @@ int launch_attn_bwd_fused(const fod_attn_bwd_args* g, cudaStream_t st) {
         p.drop.thresh = (unsigned int)(a->drop.p * 65536.f + 0.5f);
         p.drop.scale = 1.f / (1.f - a->drop.p);
     }
-    dim3 grid(a->H, a->B);
+    const int nqt_all = (a->Lq + AF_T - 1) / AF_T;
+    const int groups = two ? 1 : (nqt_all + FusedBwdSmem<1>::kMaxQT - 1) / FusedBwdSmem<1>::kMaxQT;
+    p.ws_dk = p.ws_dv = nullptr;
+    if (groups > 1) {
+        const long long half = (long long)a->B * a->H * a->Lk * AF_D;
+        p.ws_dk = g->ws;
+        p.ws_dv = g->ws + half;
+        attn_ws_zero_kernel<<<148 * 4, 256, 0, st>>>(reinterpret_cast<float4*>(g->ws), 2 * half / 4);
+    }
+    dim3 grid(a->H, a->B, groups);
     auto launch = [&](auto kernel, int smem_bytes, bool& attr_done) {
         if (!attr_done) {
             cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes);
@@ -589,7 +667,10 @@ int launch_attn_bwd_fused(const fod_attn_bwd_args* g, cudaStream_t st) {
         if (drop) launch(attn_bwd_fused_kernel<1, true>, FusedBwdSmem<1>::kTotal, attr[1]);
         else launch(attn_bwd_fused_kernel<1, false>, FusedBwdSmem<1>::kTotal, attr[0]);
     }
-    return fod_check_launch("attn_bwd_fused_kernel");
+    int rc = fod_check_launch("attn_bwd_fused_kernel");
+    if (rc || groups == 1) return rc;
+    attn_ws_to_bf16_kernel<<<148 * 8, 256, 0, st>>>(p.ws_dk, p.ws_dv, p.dk1, p.dv, p.ld_dk, a->B, a->H, a->Lk);
+    return fod_check_launch("attn_ws_to_bf16_kernel");
 }
 
 }  // namespace fod

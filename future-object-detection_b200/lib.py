@@ -9,7 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfod_b200.so")
-ABI_VERSION = 10
+ABI_VERSION = 11
 
 FOD_OK, FOD_E_ARG, FOD_E_TMAP, FOD_E_LAUNCH, FOD_E_NUMERIC = 0, 1, 2, 3, 4
 
@@ -55,6 +55,7 @@ class AttnBwdArgs(C.Structure):
         ("fwd", AttnArgs), ("dout", C.c_void_p), ("lddo", C.c_int64), ("bsdo", C.c_int64), ("delta", C.c_void_p),
         ("dq1", C.c_void_p), ("dq2", C.c_void_p), ("dk1", C.c_void_p), ("dk2", C.c_void_p), ("dv", C.c_void_p),
         ("ld_dq", C.c_int64), ("ld_dk", C.c_int64), ("mode", C.c_int32), ("pad0", C.c_int32),
+        ("ws", C.c_void_p), ("ws_floats", C.c_int64),
     ]
 
 

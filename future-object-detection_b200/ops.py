@@ -221,7 +221,8 @@ def attn_bwd_is_fused(Lq, two_parts, mode=0):
     """Which kernel path fod_attn_bwd takes (mirrors csrc/attn_bwd_sm100.cu): the one-kernel backward needs the dQ
     accumulators of every 128-query tile resident in TMEM."""
     import os
-    fits = (Lq + 127) // 128 <= (2 if two_parts else 6)
+    # one-part calls beyond 6 query tiles run the fused kernel in query groups (attn_bwd always hands it a workspace)
+    fits = (Lq + 127) // 128 <= (2 if two_parts else 6) or not two_parts
     if mode:
         return mode == 2
     return fits and int(os.environ.get("FOD_ATTN_BWD_FUSED", "1")) != 0
@@ -265,15 +266,22 @@ def attn_bwd(q1, k1, v, out, lse, dout, scale, heads=8, q2=None, k2=None, fused=
         dk2 = torch.empty((B, Lk, Cw), dtype=BF16, device=dev)
         g.dq2, g.dk2 = _p(dq2), _p(dk2)
     g.mode = mode
+    ws = None
+    if q2 is None and (Lq + 127) // 128 > 6 and mode != 1:  # query groups: fp32 dK / dV partial sums (include/fod_b200.h)
+        ws = torch.empty((2 * B * heads * Lk * 32,), dtype=torch.float32, device=dev)
+        g.ws, g.ws_floats = _p(ws), ws.numel()
     _t = prof.begin()
     lib.check(L.fod_attn_bwd(C.byref(g), _stream()), "fod_attn_bwd")
     parts = 2 if q2 is not None else 1
     prof.end(_t, "attn_bwd_p%d_%dx%d" % (parts, Lq, Lk), (4.0 + 6.0 * parts) * B * Lq * Lk * Cw,
              2.0 * Cw * (B * Lq * (2 * parts + 2) + B * Lk * (2 * parts + 2)),
              replay=(lambda: L.fod_attn_bwd(C.byref(g), _stream())) if _t is not None else None,
-             keep=(q1, k1, v, q2, k2, out, lse, dout, delta, dq1, dk1, dv, dq2, dk2, drop))
+             keep=(q1, k1, v, q2, k2, out, lse, dout, delta, dq1, dk1, dv, dq2, dk2, drop, ws))
     if attn_bwd_is_fused(Lq, q2 is not None, mode):
         LAUNCH_COUNTS["attn_bwd_fused_kernel"] += 1
+        if ws is not None:
+            LAUNCH_COUNTS["attn_ws_zero_kernel"] += 1
+            LAUNCH_COUNTS["attn_ws_to_bf16_kernel"] += 1
     else:
         LAUNCH_COUNTS["attn_delta_kernel"] += 1
         LAUNCH_COUNTS["attn_bwd_dq_kernel"] += 1

@@ -135,8 +135,14 @@ typedef struct fod_attn_bwd_args {
     int64_t ld_dk;       /* row stride of dk1 and dv (0 = H*32); batch stride = Lk*ld_dk.  dk2 is always dense */
     int32_t mode;        /* 0: the library picks; 1: two kernels (dQ per query tile, dK/dV per key tile: S and dP are
                             recomputed twice, any length); 2: ONE fused kernel, one recompute, dQ of every query tile
-                            resident in TMEM — needs Lq <= 768 (one part) / Lq <= 256 (two parts) */
+                            resident in TMEM — Lq <= 768 (one part) / Lq <= 256 (two parts) per CTA; longer one-part
+                            sequences run it in query groups of 768 and need `ws` */
     int32_t pad0;
+    float* ws;           /* optional fp32 workspace of >= 2*B*H*Lk*32 floats, 16-byte aligned (may be NULL): with it, one-part
+                            calls with Lq > 768 take the fused kernel in query groups (dK / dV partial sums are reduced
+                            in `ws` with fp32 vector atomics — 2 addends at Lq <= 1536, so bit-reproducible there — and
+                            then written as bf16); without it they take the two-kernel path */
+    int64_t ws_floats;   /* capacity of ws in floats */
 } fod_attn_bwd_args;
 int fod_attn_bwd(const fod_attn_bwd_args* a, void* stream);
 

@@ -137,7 +137,8 @@ def test_attention_forward_backward(B, Lq, Lk, two, bcast):
     ref.backward(dout.float())
     # both backward paths: two kernels (any length) and the fused single kernel (dQ resident in TMEM) where it applies
     modes = [1] + ([2] if ops.attn_bwd_is_fused(Lq, two, 0) else [])
-    assert ops.attn_bwd_is_fused(350, False) and not ops.attn_bwd_is_fused(1400, False)
+    # one-part calls of any length take the fused kernel (in query groups beyond 768 queries); two-part ones up to 256
+    assert ops.attn_bwd_is_fused(350, False) and ops.attn_bwd_is_fused(1400, False) and not ops.attn_bwd_is_fused(1400, True)
     for mode in modes:
         dq1, dk1, dv, dq2, dk2 = ops.attn_bwd(q1, k1, v, out, lse, dout, scale, H, q2=q2, k2=k2, mode=mode)
         _close(dq1, leaves[0].grad, what="dq1 mode %d" % mode)
@@ -345,3 +346,24 @@ def test_gemm_persistent_weight_stationary_path(M, N, K):
     y1 = ops.gemm(x, w, bias=b, relu=True)
     y2 = ops.gemm(x, w, bias=b, relu=True)
     assert torch.equal(y1, y2)
+
+
+@pytest.mark.parametrize("B,S", [(2, 1400), (1, 900), (1, 1664)])
+def test_attention_backward_query_groups_write_fused_slices(B, S):
+    """Self-attention longer than 768 queries: the fused backward runs in query groups, dK / dV go through the fp32
+    workspace and the conversion kernel writes them into the strided k / v slices of the fused qkv gradient tensor."""
+    from fod_b200 import ops
+    H, C = 8, 256
+    qkv = _rnd(B, S, 3 * C, seed=11)
+    q, k, v = qkv[..., :C], qkv[..., C:2 * C], qkv[..., 2 * C:]
+    scale = 32 ** -0.5
+    out, lse = ops.attn_fwd(q, k, v, scale, H)
+    dout = _rnd(B, S, C, seed=12)
+    ref = ops.attn_bwd(q, k, v, out, lse, dout, scale, H, mode=1)                  # two-kernel path, dense outputs
+    got = ops.attn_bwd(q, k, v, out, lse, dout, scale, H, fused="qkv")             # library's choice: query groups
+    assert got[0].stride(1) == 3 * C and got[1].stride(1) == 3 * C
+    for name, a, b in zip(("dq", "dk", "dv"), got[:3], ref[:3]):
+        _close(a, b, tol=1e-2, what=name)
+    again = ops.attn_bwd(q, k, v, out, lse, dout, scale, H, fused="qkv")
+    if S <= 1536:  # two query groups: two addends per element, so the fp32 reduction is order-independent
+        assert all(torch.equal(x, y) for x, y in zip(got[:3], again[:3]))
