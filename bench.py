@@ -215,6 +215,7 @@ def run_cuda(args):
     model = build_model(Namespace(device=dev, distributed=False), detr_args, dropout=args.dropout)
     model.load_state_dict(synthetic_state_dict(_template(), seed=0, residual_gain=0.5))
     model.train()
+    ops.set_dropout_seed(0x5EED5EED + rank, dev)  # every rank draws its own masks, as per-rank torch seeds would
     core = model
     use_graph = bool(args.graphs)
     flat = None
