@@ -310,3 +310,35 @@ def test_model_dropout_statistics_and_graph_replay(ref_state_dict):
     replay = [float(step(data)) for _ in range(6)]
     assert len(set(replay)) == len(replay), replay
     assert all(abs(v - l_eval) < 0.6 * abs(l_eval) for v in replay), (replay, l_eval)
+
+
+def test_joint_mode_trains_with_dropout(ref_state_dict):
+    """JointEncoder mode with dropout on: the egodeep block attends over T IMU keys per token (PlainAttnFn with dropout
+    on the weights, Lk = T) and the space-time self-attention runs at S = T*h*w: finite loss, every trainable parameter
+    gets a finite gradient, and two steps differ."""
+    from argparse import Namespace
+
+    from fod_b200 import SpatioTemporalDETRArgs, build_model, ops
+    from fod_b200.st_detr import JointEncoder
+    from fod_b200.synthetic import make_clip
+    dev = _dev()
+    dargs = SpatioTemporalDETRArgs(pretrained_backbone=False, num_classes=8, num_queries=128, lr_backbone=1e-4)
+    model = build_model(Namespace(device=dev, distributed=False), dargs)   # p = 0.1
+    model.load_state_dict(ref_state_dict)
+    core = model._model
+    core.joint_encoder = JointEncoder(core.separate_encoder.transformer)
+    data = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in make_clip(2, 4, 96, 128, seed=5, fixed_targets=4).items()}
+    ops.set_dropout_seed(7, dev)
+    model.train()
+    losses = []
+    for _ in range(2):
+        model.zero_grad(set_to_none=True)
+        loss = model(data)[2]
+        loss.backward()
+        losses.append(float(loss.detach()))
+    assert all(v == v and abs(v) < 1e6 for v in losses) and losses[0] != losses[1], losses
+    bad = [k for k, p in model.named_parameters() if p.requires_grad and (p.grad is None or not bool(torch.isfinite(p.grad).all()))]
+    assert not bad, bad[:5]
+    # with several keys the egodeep query / key projections are live
+    g = dict(model.named_parameters())["_model.separate_encoder.transformer.layers.0.egodeep_attend.key.weight"].grad
+    assert float(g.abs().max()) > 0
