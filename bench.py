@@ -315,6 +315,40 @@ def run_cuda(args):
 
     ms_e2e = timed(e2e_step, args.steps)
     d2h_bytes = 4 + acc.d2h_bytes_last
+
+    # The same loop with the loss read software-pipelined by one step: step i's loss is copied to pinned host memory
+    # on a side stream and read after step i+1 has been launched, so the ~1 ms launch latency of the ~1 500-node graph
+    # (scripts/profile_e2e.py) is hidden behind the running step.  Every step's loss still reaches the host inside the
+    # timed region (the last one after the loop); reported beside the synchronous figure, not instead of it.
+    ms_e2e_pipe = None
+    if use_graph:
+        pending, pipe_losses = [], []
+
+        def e2e_pipe_step(i):
+            step()
+            pending.append(step.read_loss_async())
+            step.prefetch(host_pool[(i + 1) % n_pool])
+            acc.add(eager.od_map_stuffs, eager.stats)
+            if len(pending) > 1:
+                h, ev = pending.pop(0)
+                ev.synchronize()
+                pipe_losses.append(float(h))
+
+        def e2e_pipe(steps):
+            for i in range(steps):
+                e2e_pipe_step(i)
+            h, ev = pending.pop(0)
+            ev.synchronize()
+            pipe_losses.append(float(h))
+
+        barrier()
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        e2e_pipe(args.steps)
+        p1.record()
+        barrier()
+        ms_e2e_pipe = max_over_ranks(p0.elapsed_time(p1), device=dev)
+        assert len(pipe_losses) == args.steps
     acc.stats_history()  # the copies have landed (checked outside the timed region)
     sampler.stop_flag = True
     sampler.join(timeout=2)
@@ -362,7 +396,10 @@ def run_cuda(args):
                        "optimizer": "fused flat clip+AdamW (fod_flat_adamw_step)" if flat is not None else "torch fused AdamW",
                        "grad_allreduce": ("bucketed NCCL AVG, %g MB fp32 buckets, side stream inside the graph" % args.bucket_mb) if world > 1 else None},
             "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                    "d2h": "loss (4 B, synchronous) + packed stats/AP bookkeeping (async, pinned slab)"},
+                    "d2h": "loss (4 B, synchronous) + packed stats/AP bookkeeping (async, pinned slab)",
+                    "pipelined": None if ms_e2e_pipe is None else {
+                        "value": clips / (ms_e2e_pipe / 1e3), "unit": UNIT,
+                        "note": "same copies and reads; the loss of step i is read (pinned copy on a side stream) after step i+1 was launched"}},
             "loss_first_last_timed_step": loss_vals, "matcher_status_by_region": status_log, "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
     # warm, GPU-bound per-launch times of EVERY instrumented (kernel, shape) pair: each re-issued back to back in a
     # small graph; the roofline is then ranked by time per step (launches x isolated time)
