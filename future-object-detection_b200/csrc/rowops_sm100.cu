@@ -355,6 +355,64 @@ extern "C" int fod_maxpool3x3s2_nhwc(const void* x, void* y, int32_t N, int32_t 
     return fod::fod_check_launch("maxpool3x3s2_nhwc_kernel");
 }
 
+// ---------------------------------------------------------------- input frames: fp32 planar -> bf16 NHWC
+// The model receives `video` (B, L, 3, H, W) fp32 and drops the last frame (paper.py:463-468); the backbone wants the
+// remaining B*(L-1) frames as channels-last bf16.  torch does this as three full passes (frame-slice copy, channels-last
+// copy, cast: 188 + 199 + 59 us at batch 32 and 448x800); here it is one: a thread takes 8 consecutive pixels of a row,
+// reads 2 x 16 bytes from each of the 3 planes and writes 48 contiguous bytes (pixel-major).  HBM-bound: 18 B per pixel.
+namespace fod {
+__global__ void __launch_bounds__(256)
+frames_to_nhwc_bf16_kernel(const float* __restrict__ video, long long stride_b, long long stride_t, int T, int H, int W,
+                           __nv_bfloat16* __restrict__ out, long long groups) {
+    const long long hw = (long long)H * W;
+    const int wg = W / 8;
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += (long long)gridDim.x * blockDim.x) {
+        const int xg = (int)(g % wg);
+        const long long r = g / wg;          // frame * H + row
+        const int y = (int)(r % H);
+        const long long n = r / H;           // frame index b * T + t
+        const float* src = video + (n / T) * stride_b + (n % T) * stride_t + (long long)y * W + xg * 8;
+        float c[3][8];
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(src + ch * hw));
+            const float4 b = __ldg(reinterpret_cast<const float4*>(src + ch * hw) + 1);
+            c[ch][0] = a.x; c[ch][1] = a.y; c[ch][2] = a.z; c[ch][3] = a.w;
+            c[ch][4] = b.x; c[ch][5] = b.y; c[ch][6] = b.z; c[ch][7] = b.w;
+        }
+        float f[24];
+#pragma unroll
+        for (int px = 0; px < 8; ++px)
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) f[px * 3 + ch] = c[ch][px];
+        uint4* dst = reinterpret_cast<uint4*>(out + ((n * H + y) * (long long)W + xg * 8) * 3);
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            uint4 u;
+            u.x = pack_bf16x2(f[q * 8 + 0], f[q * 8 + 1]);
+            u.y = pack_bf16x2(f[q * 8 + 2], f[q * 8 + 3]);
+            u.z = pack_bf16x2(f[q * 8 + 4], f[q * 8 + 5]);
+            u.w = pack_bf16x2(f[q * 8 + 6], f[q * 8 + 7]);
+            dst[q] = u;
+        }
+    }
+}
+}  // namespace fod
+
+extern "C" int fod_frames_to_nhwc_bf16(const float* video, int64_t stride_b, int64_t stride_t, int32_t B, int32_t T,
+                                       int32_t H, int32_t W, void* out, void* stream) {
+    if (!video || !out || B <= 0 || T <= 0 || H <= 0 || W <= 0) return fod_fail(FOD_E_ARG, "frames_to_nhwc: null/empty");
+    if (W % 8 || stride_b % 4 || stride_t % 4 || ((long long)H * W) % 4 ||
+        ((reinterpret_cast<uintptr_t>(video) | reinterpret_cast<uintptr_t>(out)) & 15))
+        return fod_fail(FOD_E_ARG, "frames_to_nhwc: W % 8 == 0 and 16-byte aligned planes / frames needed");
+    const long long groups = (long long)B * T * H * (W / 8);
+    long long blocks = (groups + 255) / 256;
+    if (blocks > 148LL * 16) blocks = 148LL * 16;
+    fod::frames_to_nhwc_bf16_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        video, stride_b, stride_t, T, H, W, reinterpret_cast<__nv_bfloat16*>(out), groups);
+    return fod::fod_check_launch("frames_to_nhwc_bf16_kernel");
+}
+
 // ---------------------------------------------------------------- fused ReLU backward (+ gradient add) for the backbone
 // out = (a [+ b]) * (y > 0), flat bf16 arrays of n elements (n % 8 == 0, identical layouts).  In a bottleneck's backward
 // the gradient of the block output arrives as two addends (the conv1 input gradient and the identity-path gradient of

@@ -375,6 +375,24 @@ def maxpool3x3s2_nhwc(x):
     return y
 
 
+def frames_to_nhwc_bf16(video, frames=None):
+    """video (B, L, 3, H, W) fp32 with dense (3, H, W) frames -> the first `frames` (default L) frames of every clip as a
+    channels-last bf16 (B*frames, 3, H, W) tensor, in one pass (fod_frames_to_nhwc_bf16)."""
+    L = lib.load()
+    b, l, c, h, w = video.shape
+    t = l if frames is None else frames
+    assert video.dtype == torch.float32 and c == 3 and 0 < t <= l and video.stride()[2:] == (h * w, w, 1) and w % 8 == 0
+    out = torch.empty((b * t, h, w, 3), dtype=BF16, device=video.device)
+    _t = prof.begin()
+    args = (_p(video), video.stride(0), video.stride(1), b, t, h, w, _p(out))
+    call = lambda: L.fod_frames_to_nhwc_bf16(*args, _stream())
+    lib.check(call(), "fod_frames_to_nhwc_bf16")
+    prof.end(_t, "frames_to_nhwc_%dx%dx%d" % (b * t, h, w), 0.0, 18.0 * b * t * h * w, replay=call if _t is not None else None,
+             keep=(video, out))
+    LAUNCH_COUNTS["frames_to_nhwc_bf16_kernel"] += 1
+    return out.permute(0, 3, 1, 2)  # logical (N, 3, H, W), channels-last strides
+
+
 def relu_bwd_add(a, b, y):
     """(a [+ b]) * (y > 0) in one pass; a, b, y bf16 CUDA tensors of one shape AND one memory layout (dense)."""
     L = lib.load()

@@ -74,7 +74,17 @@ class SeparateEncoder(nn.Module):
     def forward_tokens(self, images, pos_encoder, imu=None):
         """images (B,T,3,H,W) -> encoded tokens (B*T*S, D) bf16 in (b, t, h, w) row order, pos (S, D) bf16, (h, w)."""
         b, t = images.shape[:2]
-        x, h, w = self.backbone.forward_tokens(images.flatten(0, 1))
+        bk = self.backbone
+        ih, iw = images.shape[3:]
+        if (images.is_cuda and images.dtype == torch.float32 and not images.requires_grad and images.shape[2] == 3
+                and getattr(bk, "fold_frozen_bn", False) and getattr(bk, "compute_dtype", None) == BF16 and iw % 8 == 0
+                and images.stride()[2:] == (ih * iw, iw, 1) and images.stride(0) % 4 == 0 and images.stride(1) % 4 == 0
+                and (ih * iw) % 4 == 0 and images.data_ptr() % 16 == 0):
+            # (B, T, 3, H, W) fp32 planar (possibly a frame slice of the loader's tensor) -> channels-last bf16 in one pass
+            frames = ops.frames_to_nhwc_bf16(images)
+        else:
+            frames = images.flatten(0, 1)
+        x, h, w = self.backbone.forward_tokens(frames)
         d = x.shape[1]
         pos_bf = pos_encoder.spatial_tokens(h, w, d, x.device).to(BF16)
         ego = None

@@ -170,6 +170,12 @@ int fod_ln_bwd_drop(const void* dy, const void* dy2, const void* pre, const void
  * (ConditionalDETR/models/backbone.py:88-96 -> torchvision resnet `maxpool`); forward only (paper.py:102-109 freezes
  * everything before layer2).  y is (N, (H-1)/2+1, (W-1)/2+1, C). */
 int fod_maxpool3x3s2_nhwc(const void* x, void* y, int32_t N, int32_t H, int32_t W, int32_t C, void* stream);
+/* Input frames for the backbone: video (B, L, 3, H, W) fp32 planar, of which frames [0, T) of every clip are used (the
+ * model drops the last, "future" frame: future_od/models/paper.py:463-468) -> out (B*T, H, W, 3) bf16 = a channels-last
+ * (B*T, 3, H, W) tensor, what the frozen stem consumes.  stride_b / stride_t: element strides between clips / frames;
+ * planes are dense (H*W), W % 8 == 0.  One pass instead of torch's slice copy + channels_last copy + cast. */
+int fod_frames_to_nhwc_bf16(const float* video, int64_t stride_b, int64_t stride_t, int32_t B, int32_t T, int32_t H,
+                            int32_t W, void* out, void* stream);
 
 /* Fused ReLU backward with an optional gradient add for the backbone's bottleneck blocks: out = (a [+ b]) * (y > 0) on
  * flat bf16 arrays of n elements with identical layouts (n % 8 == 0, 16-byte aligned).  Replaces autograd's gradient

@@ -367,3 +367,16 @@ def test_attention_backward_query_groups_write_fused_slices(B, S):
     again = ops.attn_bwd(q, k, v, out, lse, dout, scale, H, fused="qkv")
     if S <= 1536:  # two query groups: two addends per element, so the fp32 reduction is order-independent
         assert all(torch.equal(x, y) for x, y in zip(got[:3], again[:3]))
+
+
+@pytest.mark.parametrize("B,L,H,W", [(2, 3, 64, 96), (1, 4, 448, 800), (3, 2, 30, 8)])
+def test_frames_to_nhwc_bf16_matches_torch(B, L, H, W):
+    """The input conversion (drop the last frame, planar fp32 -> channels-last bf16) equals torch's three passes bit for bit."""
+    from fod_b200 import ops
+    video = torch.randn(B, L, 3, H, W, device=_dev())
+    part = video[:, :-1] if L > 1 else video
+    got = ops.frames_to_nhwc_bf16(part)
+    ref = part.flatten(0, 1).contiguous(memory_format=torch.channels_last).to(BF)
+    assert got.shape == ref.shape and got.is_contiguous(memory_format=torch.channels_last)
+    assert torch.equal(got, ref)
+    assert torch.equal(ops.frames_to_nhwc_bf16(video, frames=1), video[:, :1].flatten(0, 1).to(BF))
