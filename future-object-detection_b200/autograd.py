@@ -328,6 +328,45 @@ class AddLNFn(Function):
         return dz, db, None, dgamma, dbeta, None, None
 
 
+class AddLNDropFn(Function):
+    """y = LayerNorm(x + dropout(x2)) — norm1(out + attn_dropout(out)) of EgodeepAttention (transformer.py:117, x2 is x)
+    and norm_eda(features + dropout_eda(new)) of the encoder layer (:485-486).  Mask regenerated in backward."""
+
+    @staticmethod
+    def forward(ctx, x, x2, gamma, beta, eps, need_grad, drop):
+        if need_grad:
+            y, pre, mean, rstd = ops.add_ln_fwd_drop(x, x2, gamma, beta, eps, drop, save=True)
+            ctx.save_for_backward(pre, mean, rstd, gamma)
+            ctx.direct = _use_all(gamma, beta)
+            ctx.params = (gamma, beta)
+            ctx.drop = drop
+        else:
+            y = ops.add_ln_fwd_drop(x, x2, gamma, beta, eps, drop)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        pre, mean, rstd, gamma = ctx.saved_tensors
+        if ctx.direct:
+            g, bt = ctx.params
+            dgamma, dbeta = g.grad, bt.grad
+        else:
+            dgamma = torch.zeros_like(gamma)
+            dbeta = torch.zeros_like(gamma)
+        dz, dzd = ops.ln_bwd(_bf(dy), pre, mean, rstd, gamma, dgamma, dbeta, drop=ctx.drop)
+        if ctx.direct:
+            _done(g)
+            _done(bt)
+            return dz, dzd, None, None, None, None, None
+        return dz, dzd, dgamma, dbeta, None, None, None
+
+
+def add_ln_drop(x, x2, gamma, beta, eps=1e-5, drop=None):
+    """drop must be a dropout site (ops.drop_site); without one use add_ln(x + x2)."""
+    assert drop is not None
+    return AddLNDropFn.apply(x, x2, gamma, beta, eps, torch.is_grad_enabled(), drop)
+
+
 def add_ln(x, gamma, beta, bcast=None, rows_per_group=0, eps=1e-5):
     return AddLNFn.apply(x, bcast, rows_per_group, gamma, beta, eps, torch.is_grad_enabled())
 

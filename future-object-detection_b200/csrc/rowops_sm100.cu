@@ -40,9 +40,15 @@ __device__ __forceinline__ float warp_sum(float v) {
 __global__ void __launch_bounds__(RO_WARPS * 32)
 add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ bcast, int rows_per_group,
                   const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
-                  float* __restrict__ mean_out, float* __restrict__ rstd_out, long long M, float eps) {
+                  float* __restrict__ mean_out, float* __restrict__ rstd_out, long long M, float eps,
+                  const __nv_bfloat16* x2, __nv_bfloat16* __restrict__ pre_out, const DropoutCfg drop) {
+    // x2 (may alias x): a second full-size addend that goes through dropout first — y = LN(x + dropout(x2) [+ bcast]),
+    // the "x + dropout(sublayer(x))" of blocks whose sub-layer output is not a GEMM epilogue (transformer.py:117,485);
+    // pre_out receives the pre-LayerNorm sum for ln_bwd.  Mask index: row * 32 + lane, as fod_ln_bwd_drop regenerates it.
     pdl_launch_dependents();
     pdl_wait();
+    PhiloxKey key = {0u, 0u, 0u, 0u};
+    if (drop.state) key = dropout_key(drop);
     const int lane = threadIdx.x & 31;
     const int c0 = lane * 8;
     float g[8], bt[8];
@@ -55,12 +61,20 @@ add_ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __re
     for (long long row = (long long)blockIdx.x * RO_WARPS + (threadIdx.x >> 5); row < M; row += stride) {
         float z[8];
         load8(x + row * RO_D + c0, z);
+        if (x2) {
+            float u[8];
+            load8(x2 + row * RO_D + c0, u);
+            if (drop.state) dropout_apply8(u, key, (unsigned long long)row * (RO_D / 8) + lane, drop.thresh, drop.scale);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) z[j] += u[j];
+        }
         if (bcast) {
             float o[8];
             load8(bcast + (row / rows_per_group) * RO_D + c0, o);
 #pragma unroll
             for (int j = 0; j < 8; ++j) z[j] += o[j];
         }
+        if (pre_out) store8(pre_out + row * RO_D + c0, z);
         float s = 0.f;
 #pragma unroll
         for (int j = 0; j < 8; ++j) s += z[j];
@@ -239,7 +253,28 @@ extern "C" int fod_add_ln_fwd(const void* x, const void* bcast, int32_t rows_per
     if (bcast && rows_per_group <= 0) return fod_fail(FOD_E_ARG, "add_ln_fwd: rows_per_group");
     fod_launch(add_ln_fwd_kernel, dim3(ro_grid(M)), dim3(RO_WARPS * 32), 0, reinterpret_cast<cudaStream_t>(stream),
         reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(bcast), rows_per_group,
-        gamma, beta, reinterpret_cast<__nv_bfloat16*>(y), mean_out, rstd_out, M, eps);
+        gamma, beta, reinterpret_cast<__nv_bfloat16*>(y), mean_out, rstd_out, M, eps,
+        static_cast<const __nv_bfloat16*>(nullptr), static_cast<__nv_bfloat16*>(nullptr), DropoutCfg{nullptr, 0u, 0u, 1.f});
+    return fod_check_launch("add_ln_fwd_kernel");
+}
+
+extern "C" int fod_add_ln_fwd_drop(const void* x, const void* x2, const void* bcast, int32_t rows_per_group,
+                                   const float* gamma, const float* beta, void* y, void* pre_out, float* mean_out,
+                                   float* rstd_out, int64_t M, float eps, const fod_dropout* drop, void* stream) {
+    if (!x || !x2 || !gamma || !beta || !y || M <= 0) return fod_fail(FOD_E_ARG, "add_ln_fwd_drop: null/empty");
+    if (bcast && rows_per_group <= 0) return fod_fail(FOD_E_ARG, "add_ln_fwd_drop: rows_per_group");
+    DropoutCfg d = {nullptr, 0u, 0u, 1.f};
+    if (drop && drop->rng_state && drop->p > 0.f) {
+        if (!(drop->p < 1.f)) return fod_fail(FOD_E_ARG, "add_ln_fwd_drop: dropout p must be in [0, 1)");
+        d.state = reinterpret_cast<const unsigned long long*>(drop->rng_state);
+        d.call = (unsigned int)drop->call;
+        d.thresh = (unsigned int)(drop->p * 65536.f + 0.5f);
+        d.scale = 1.f / (1.f - drop->p);
+    }
+    fod_launch(add_ln_fwd_kernel, dim3(ro_grid(M)), dim3(RO_WARPS * 32), 0, reinterpret_cast<cudaStream_t>(stream),
+        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<const __nv_bfloat16*>(bcast), rows_per_group,
+        gamma, beta, reinterpret_cast<__nv_bfloat16*>(y), mean_out, rstd_out, M, eps,
+        reinterpret_cast<const __nv_bfloat16*>(x2), reinterpret_cast<__nv_bfloat16*>(pre_out), d);
     return fod_check_launch("add_ln_fwd_kernel");
 }
 

@@ -115,6 +115,7 @@ SYMBOLS = {
     "fod_attn_fwd": (C.c_int, [C.POINTER(AttnArgs), _VP]),
     "fod_attn_bwd": (C.c_int, [C.POINTER(AttnBwdArgs), _VP]),
     "fod_add_ln_fwd": (C.c_int, [_VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _I64, _F, _VP]),
+    "fod_add_ln_fwd_drop": (C.c_int, [_VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _F, C.POINTER(Dropout), _VP]),
     "fod_ln_bwd": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_colsum": (C.c_int, [_VP, _I64, _VP, _I64, _I32, _I32, _VP]),
     "fod_ln_bwd_drop": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, C.POINTER(Dropout), _VP]),

@@ -637,9 +637,11 @@ class EgodeepAttention(nn.Module):
         if not self.use_mlp:
             return o
         # transformer.py:116-118: out = norm1(out + attn_dropout(out)); out = norm2(out + mlp(out))
-        drop = self.training and self.p > 0
-        o = A.add_ln(o + F.dropout(o, self.p, True) if drop else o * 2, self.norm1.weight, self.norm1.bias,
-                     eps=self.norm1.eps)
+        site = self._site()
+        if site is not None:  # out + attn_dropout(out): residual, dropout and norm in one kernel
+            o = A.add_ln_drop(o, o, self.norm1.weight, self.norm1.bias, eps=self.norm1.eps, drop=site)
+        else:
+            o = A.add_ln(o * 2, self.norm1.weight, self.norm1.bias, eps=self.norm1.eps)
         l1, l2 = self.mlp[0], self.mlp[3]
         return A.ffn_ln(o, l1.weight, l1.bias, _q(l1.weight), l2.weight, l2.bias, _q(l2.weight), self.norm2.weight,
                         self.norm2.bias, self.norm2.eps, drop_h=self._site(), drop_o=self._site())
@@ -705,8 +707,11 @@ class TransformerEncoderLayer(nn.Module):
                     o = self.egodeep_attend.forward_single_key_dropout(ego, n_seq, seq_len)
                 else:
                     o = self.egodeep_attend.forward_multi_key(x, pos_bf, ego, n_seq, seq_len)
-                x = A.add_ln(x + (F.dropout(o, self.p, True) if drop else o), self.norm_eda.weight, self.norm_eda.bias,
-                             eps=self.norm_eda.eps)
+                site = ops.drop_site(self.p, self.training)
+                if site is not None:  # features + dropout_eda(new) -> norm_eda in one kernel
+                    x = A.add_ln_drop(x, o, self.norm_eda.weight, self.norm_eda.bias, eps=self.norm_eda.eps, drop=site)
+                else:
+                    x = A.add_ln(x + o, self.norm_eda.weight, self.norm_eda.bias, eps=self.norm_eda.eps)
         return x
 
 

@@ -314,6 +314,31 @@ def add_ln_fwd(x, gamma, beta, eps=1e-5, bcast=None, rows_per_group=0, save=Fals
     return (y, mean, rstd) if save else y
 
 
+def add_ln_fwd_drop(x, x2, gamma, beta, eps=1e-5, drop=None, save=False):
+    """y = LayerNorm(x + dropout(x2)); x, x2 (M,256) bf16 (x2 may be x).  save -> also (pre, mean, rstd) for ln_bwd."""
+    L = lib.load()
+    _chk_bf16(x, "add_ln_drop x")
+    _chk_bf16(x2, "add_ln_drop x2")
+    assert x.is_contiguous() and x2.is_contiguous() and x.shape == x2.shape and x.shape[-1] == 256
+    M = x.numel() // 256
+    y = torch.empty_like(x)
+    pre = mean = rstd = None
+    if save:
+        pre = torch.empty_like(x)
+        mean = torch.empty((M,), dtype=torch.float32, device=x.device)
+        rstd = torch.empty((M,), dtype=torch.float32, device=x.device)
+    dstruct = lib.Dropout()
+    _fill_drop(dstruct, drop, x.device)
+    _t = prof.begin()
+    ptrs = (_p(x), _p(x2), None, 0, _p(gamma), _p(beta), _p(y), _p(pre), _p(mean), _p(rstd), M, eps)
+    call = lambda: L.fod_add_ln_fwd_drop(*ptrs, C.byref(dstruct), _stream())
+    lib.check(call(), "fod_add_ln_fwd_drop")
+    prof.end(_t, "add_ln_fwd_drop_%d" % M, 0.0, (2048.0 if save else 1536.0) * M, replay=call if _t is not None else None,
+             keep=(x, x2, gamma, beta, y, pre, mean, rstd, drop))
+    LAUNCH_COUNTS["add_ln_fwd_kernel"] += 1
+    return (y, pre, mean, rstd) if save else y
+
+
 def ln_bwd(dy, pre, mean, rstd, gamma, dgamma, dbeta, dy2=None, bcast=None, rows_per_group=0, dzsum=None, drop=None):
     """LayerNorm backward: returns dz (bf16); accumulates into fp32 dgamma / dbeta (256,) and, if given, the column
     sums of dz into dzsum (256,) — the bias gradient of the linear layer that feeds the norm.

@@ -160,6 +160,14 @@ int fod_ln_bwd(const void* dy, const void* dy2, const void* pre, const void* bca
                float* dzsum /* (256) or NULL: += column sums of dz = bias gradient of the linear feeding the norm */,
                int64_t M, void* stream);
 int fod_colsum(const void* x, int64_t ldx, float* out, int64_t M, int32_t N, int32_t rows_per_group, void* stream);
+/* y = LayerNorm(x + dropout(x2) [+ bcast[row / rows_per_group]]): the residual + dropout + norm of blocks whose
+ * sub-layer output is not the epilogue of a GEMM — EgodeepAttention's norm1(out + attn_dropout(out)) (x2 == x) and
+ * the encoder layer's norm_eda(features + dropout_eda(new)) (future_od/models/transformer.py:117,485-486).  x2 may alias
+ * x; pre_out (optional) receives the pre-LayerNorm sum that fod_ln_bwd_drop takes as `pre`; the mask is the one
+ * fod_ln_bwd_drop regenerates (element index row*256 + col of `drop`). */
+int fod_add_ln_fwd_drop(const void* x, const void* x2, const void* bcast, int32_t rows_per_group, const float* gamma,
+                        const float* beta, void* y, void* pre_out, float* mean_out, float* rstd_out, int64_t M, float eps,
+                        const fod_dropout* drop, void* stream);
 /* fod_ln_bwd for y = LayerNorm(res + dropout(u)): dz is the gradient of res, dz_drop (optional) = dz masked and scaled
  * by the SAME dropout mask the forward GEMM epilogue drew (`drop`: element index row*256 + col) = the gradient of u;
  * dzsum then sums dz_drop (the bias sits inside the dropout). */

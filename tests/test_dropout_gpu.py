@@ -342,3 +342,32 @@ def test_joint_mode_trains_with_dropout(ref_state_dict):
     # with several keys the egodeep query / key projections are live
     g = dict(model.named_parameters())["_model.separate_encoder.transformer.layers.0.egodeep_attend.key.weight"].grad
     assert float(g.abs().max()) > 0
+
+
+@pytest.mark.parametrize("M,same", [(5600, True), (700, False)])
+def test_add_ln_dropout_matches_torch_with_same_mask(M, same):
+    """y = LN(x + dropout(x2)) (transformer.py:117 with x2 = x, :485-486) forward and gradients of x, x2, gamma, beta."""
+    from fod_b200 import autograd as A
+    from fod_b200 import ops
+    ops.set_dropout_seed(17, _dev())
+    D, drop = 256, (P, 9)
+    keep = _gemm_mask(M, D, drop).float() / (1 - P)          # same element indexing: row * 256 + col
+    x = _rnd(M, D, seed=1)
+    x2 = x if same else _rnd(M, D, seed=2)
+    gam = (torch.rand(D, device=_dev()) + 0.5).requires_grad_()
+    bet = torch.randn(D, device=_dev()).requires_grad_()
+    xg = x.clone().requires_grad_()
+    x2g = xg if same else x2.clone().requires_grad_()
+    y = A.add_ln_drop(xg, x2g, gam, bet, 1e-5, drop=drop)
+    dy = _rnd(M, D, seed=3)
+    y.backward(dy)
+    a32 = x.float().requires_grad_()
+    b32 = a32 if same else x2.float().requires_grad_()
+    g32, be32 = gam.detach().clone().requires_grad_(), bet.detach().clone().requires_grad_()
+    yr = torch.nn.functional.layer_norm(a32 + b32 * keep, (D,), g32, be32, 1e-5)
+    yr.backward(dy.float())
+    pairs = [("y", y, yr), ("dx", xg.grad, a32.grad), ("dgamma", gam.grad, g32.grad), ("dbeta", bet.grad, be32.grad)]
+    if not same:
+        pairs.append(("dx2", x2g.grad, b32.grad))
+    for name, a, r in pairs:
+        assert _rel(a, r) < 2e-2, (name, _rel(a, r))
