@@ -194,7 +194,7 @@ class LinearFn(Function):
             db = ops.colsum(dy).view(-1)
         dres = None
         if has_res and ctx.needs_input_grad[4]:
-            dres = dy if mod == 0 else dy.view(-1, mod, dy.shape[1]).sum(0)
+            dres = dy if mod == 0 else ops.batch_sum(dy.view(-1, mod, dy.shape[1]))
         return dx, dw, db, None, dres, None, None, None, None
 
 
@@ -437,8 +437,8 @@ class CrossAttnFn(Function):
         dq1, dk1, _, dq2, dk2 = ops.attn_bwd(qc, kv[..., :c], kv[..., c:], out, lse, _bf(dout), scale, heads, q2=qs,
                                              k2=kp, fused="kv", drop=drop)
         dkv = dk1._base
-        dqs = dq2 if qs.dim() == 3 else dq2.sum(0)
-        dkp = dk2.sum(0) if kp.dim() == 2 else dk2
+        dqs = dq2 if qs.dim() == 3 else ops.batch_sum(dq2)
+        dkp = ops.batch_sum(dk2) if kp.dim() == 2 else dk2
         return dq1, dqs, dkv, dkp, None, None, None
 
 

@@ -390,6 +390,60 @@ extern "C" int fod_maxpool3x3s2_nhwc(const void* x, void* y, int32_t N, int32_t 
     return fod::fod_check_launch("maxpool3x3s2_nhwc_kernel");
 }
 
+// ---------------------------------------------------------------- sum over the leading (batch) dimension
+// out[i] = sum_g x[g * n + i]: the gradient of a batch-invariant operand that entered a GEMM as a row-modular residual
+// (positional projections shared by every sequence, transformer.py:459-460,160-166) or an attention call as a broadcast
+// part (query_sine / key_pos).  Thread = 8 consecutive elements, fp32 accumulation over g with 8 loads in flight.
+namespace fod {
+__global__ void __launch_bounds__(256)
+batch_sum_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, long long G, long long n8) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+        float acc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+        const uint4* src = reinterpret_cast<const uint4*>(x) + i;
+        long long g = 0;
+        for (; g + 8 <= G; g += 8) {
+            uint4 u[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) u[k] = __ldg(src + (g + k) * n8);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u[k]);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 t = __bfloat1622float2(h[j]);
+                    acc[2 * j] += t.x;
+                    acc[2 * j + 1] += t.y;
+                }
+            }
+        }
+        for (; g < G; ++g) {
+            const uint4 u = __ldg(src + g * n8);
+            const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float2 t = __bfloat1622float2(h[j]);
+                acc[2 * j] += t.x;
+                acc[2 * j + 1] += t.y;
+            }
+        }
+        store8(out + i * 8, acc);
+    }
+}
+}  // namespace fod
+
+extern "C" int fod_batch_sum(const void* x, void* out, int64_t G, int64_t n, void* stream) {
+    if (!x || !out || G <= 0 || n <= 0 || n % 8) return fod_fail(FOD_E_ARG, "batch_sum: null/empty or n % 8 != 0");
+    if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(out)) & 15) return fod_fail(FOD_E_ARG, "batch_sum: alignment");
+    const long long n8 = n / 8;
+    long long blocks = (n8 + 255) / 256;
+    if (blocks > 148LL * 8) blocks = 148LL * 8;
+    fod::batch_sum_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const __nv_bfloat16*>(x), reinterpret_cast<__nv_bfloat16*>(out), G, n8);
+    return fod::fod_check_launch("batch_sum_kernel");
+}
+
 // ---------------------------------------------------------------- input frames: fp32 planar -> bf16 NHWC
 // The model receives `video` (B, L, 3, H, W) fp32 and drops the last frame (paper.py:463-468); the backbone wants the
 // remaining B*(L-1) frames as channels-last bf16.  torch does this as three full passes (frame-slice copy, channels-last

@@ -121,6 +121,7 @@ SYMBOLS = {
     "fod_ln_bwd_drop": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _I64, C.POINTER(Dropout), _VP]),
     "fod_rng_advance": (C.c_int, [_VP, _VP]),
     "fod_maxpool3x3s2_nhwc": (C.c_int, [_VP, _VP, _I32, _I32, _I32, _I32, _VP]),
+    "fod_batch_sum": (C.c_int, [_VP, _VP, _I64, _I64, _VP]),
     "fod_frames_to_nhwc_bf16": (C.c_int, [_VP, _I64, _I64, _I32, _I32, _I32, _I32, _VP, _VP]),
     "fod_relu_bwd_add": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_stem_conv7x7s2": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),

@@ -400,6 +400,24 @@ def maxpool3x3s2_nhwc(x):
     return y
 
 
+def batch_sum(x):
+    """x (G, ...) bf16 contiguous -> sum over dim 0 (fp32 accumulation, bf16 result): fod_batch_sum."""
+    L = lib.load()
+    _chk_bf16(x, "batch_sum x")
+    assert x.dim() >= 2
+    G, n = x.shape[0], x[0].numel()
+    if n % 8 or G == 1 or not x.is_contiguous() or x.data_ptr() % 16:
+        return x.sum(0) if G > 1 else x[0]
+    out = torch.empty(x.shape[1:], dtype=BF16, device=x.device)
+    _t = prof.begin()
+    ptrs = (_p(x), _p(out), G, n)
+    call = lambda: L.fod_batch_sum(*ptrs, _stream())
+    lib.check(call(), "fod_batch_sum")
+    prof.end(_t, "batch_sum_%dx%d" % (G, n), 0.0, 2.0 * (G + 1) * n, replay=call if _t is not None else None, keep=(x, out))
+    LAUNCH_COUNTS["batch_sum_kernel"] += 1
+    return out
+
+
 def frames_to_nhwc_bf16(video, frames=None):
     """video (B, L, 3, H, W) fp32 with dense (3, H, W) frames -> the first `frames` (default L) frames of every clip as a
     channels-last bf16 (B*frames, 3, H, W) tensor, in one pass (fod_frames_to_nhwc_bf16)."""

@@ -178,6 +178,11 @@ int fod_ln_bwd_drop(const void* dy, const void* dy2, const void* pre, const void
  * (ConditionalDETR/models/backbone.py:88-96 -> torchvision resnet `maxpool`); forward only (paper.py:102-109 freezes
  * everything before layer2).  y is (N, (H-1)/2+1, (W-1)/2+1, C). */
 int fod_maxpool3x3s2_nhwc(const void* x, void* y, int32_t N, int32_t H, int32_t W, int32_t C, void* stream);
+/* out[i] = sum over g < G of x[g*n + i] (bf16 in / out, fp32 accumulation; n % 8 == 0): gradient of a batch-invariant
+ * operand — the positional projections every sequence shares (future_od/models/transformer.py:459-460,160-166,
+ * paper.py:370) entered the GEMMs as row-modular residuals and the attention calls as broadcast parts, so their
+ * gradient is the sum over the batch of the per-sequence gradient. */
+int fod_batch_sum(const void* x, void* out, int64_t G, int64_t n, void* stream);
 /* Input frames for the backbone: video (B, L, 3, H, W) fp32 planar, of which frames [0, T) of every clip are used (the
  * model drops the last, "future" frame: future_od/models/paper.py:463-468) -> out (B*T, H, W, 3) bf16 = a channels-last
  * (B*T, 3, H, W) tensor, what the frozen stem consumes.  stride_b / stride_t: element strides between clips / frames;

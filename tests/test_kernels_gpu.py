@@ -380,3 +380,10 @@ def test_frames_to_nhwc_bf16_matches_torch(B, L, H, W):
     assert got.shape == ref.shape and got.is_contiguous(memory_format=torch.channels_last)
     assert torch.equal(got, ref)
     assert torch.equal(ops.frames_to_nhwc_bf16(video, frames=1), video[:, :1].flatten(0, 1).to(BF))
+
+
+@pytest.mark.parametrize("G,R,C", [(64, 350, 768), (32, 128, 256), (3, 7, 8), (17, 350, 512)])
+def test_batch_sum_matches_torch(G, R, C):
+    from fod_b200 import ops
+    x = _rnd(G, R, C, seed=5)
+    _close(ops.batch_sum(x), x.float().sum(0), tol=5e-3, what="batch_sum")
