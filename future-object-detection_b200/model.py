@@ -653,6 +653,15 @@ class EgodeepAttention(nn.Module):
         dead = [p for m in (self.query_content, self.query_pos, self.key) for p in m.parameters() if p.requires_grad]
         return _ZeroGrad.apply(o, *dead) if dead and torch.is_grad_enabled() else o
 
+    def _out_proj_of_masked_heads(self, v, keep):
+        """v (n_seq, D) value rows, keep (n_seq, seq_len, H) per-token head multipliers -> out_proj(v with heads scaled)
+        for every token, (n_seq*seq_len, D) bf16, through the (n_seq, H, D) table of per-head out_proj contributions."""
+        n_seq, seq_len, h = keep.shape
+        d = v.shape[1]
+        op = self.fun.out_proj
+        table = torch.einsum("shk,ohk->sho", v.float().view(n_seq, h, d // h), op.weight.view(d, h, d // h)).to(BF16)
+        return torch.baddbmm(op.bias.to(BF16).view(1, 1, d), keep, table).view(n_seq * seq_len, d)
+
     def forward_single_key_dropout(self, ego, n_seq, seq_len):
         """ego (n_seq, D) -> per-TOKEN update (n_seq*seq_len, D) with dropout on.  The softmax weight over one key is
         still exactly 1, so dropout(P)·V is the sequence's value row with every HEAD kept with probability 1-p and
@@ -660,9 +669,12 @@ class EgodeepAttention(nn.Module):
         the sub-block dropouts after it (transformer.py:95-103,117) are per element, hence per-token rows from here on."""
         d, h = ego.shape[1], self.heads
         v = _lin(ego, self.value)
-        keep = (torch.rand((n_seq, seq_len, h, 1), device=ego.device) >= self.p).to(BF16) * (1.0 / (1.0 - self.p))
-        a = (v.view(n_seq, 1, h, d // h) * keep).view(n_seq * seq_len, d)
-        o = self._post(_lin(a, self.fun.out_proj))
+        # out_proj is linear and a token's attention output is its sequence's value row with heads switched off, so
+        #   out_proj(a_token) = sum_h keep[token, h] * (W_o[:, head h] · v_seq[head h]) + b_o = keep_token (1 x H) · M_seq (H x D) + b_o:
+        # the per-sequence table M is 8 rows (tiny torch ops), and the per-token out_proj GEMM (K = 256), its input, its
+        # dX / dW GEMMs and the mask multiply become one K = 8 batched library product and its transpose in backward.
+        keep = (torch.rand((n_seq, seq_len, h), device=ego.device) >= self.p).to(BF16) * (1.0 / (1.0 - self.p))
+        o = self._post(self._out_proj_of_masked_heads(v, keep))
         dead = [p for m in (self.query_content, self.query_pos, self.key) for p in m.parameters() if p.requires_grad]
         return _ZeroGrad.apply(o, *dead) if dead and torch.is_grad_enabled() else o
 

@@ -371,3 +371,27 @@ def test_add_ln_dropout_matches_torch_with_same_mask(M, same):
         pairs.append(("dx2", x2g.grad, b32.grad))
     for name, a, r in pairs:
         assert _rel(a, r) < 2e-2, (name, _rel(a, r))
+
+
+def test_egodeep_head_dropout_table_equals_the_per_token_projection():
+    """One IMU key per sequence, dropout on the (single) attention weight of every (token, head): the per-token
+    out_proj is computed from an (n_seq, H, D) table of per-head contributions; it must equal out_proj applied to the
+    value row with the dropped heads zeroed, forward and in the gradients of value rows and out_proj parameters."""
+    from fod_b200.model import EgodeepAttention
+    torch.manual_seed(3)
+    n_seq, seq_len, D, H = 6, 50, 256, 8
+    eg = EgodeepAttention(D, H, Dff=None, dropout=P).to(_dev())
+    v = torch.randn(n_seq, D, device=_dev()).to(BF).requires_grad_()
+    keep = (torch.rand(n_seq, seq_len, H, device=_dev()) >= P).to(BF) / (1 - P)
+    o = eg._out_proj_of_masked_heads(v, keep)
+    g = _rnd(n_seq * seq_len, D, seed=4)
+    o.backward(g)
+    got = [o, v.grad, eg.fun.out_proj.weight.grad, eg.fun.out_proj.bias.grad]
+    v32 = v.detach().float().requires_grad_()
+    W = eg.fun.out_proj.weight.detach().clone().requires_grad_()
+    b = eg.fun.out_proj.bias.detach().clone().requires_grad_()
+    a = (v32.view(n_seq, 1, H, D // H) * keep.float().unsqueeze(-1)).reshape(n_seq * seq_len, D)
+    ref = a @ W.t() + b
+    ref.backward(g.float())
+    for name, x, r in zip(("o", "dv", "dW", "db"), got, (ref, v32.grad, W.grad, b.grad)):
+        assert _rel(x, r) < 2e-2, (name, _rel(x, r))
