@@ -395,11 +395,19 @@ def run_cuda(args):
                        "dead_decoder_passes": "pruned (output-identical, SURVEY.md §0.3)", "dropout": args.dropout, "cuda_graph": use_graph, "cudnn_benchmark": bool(args.cudnn_benchmark),
                        "optimizer": "fused flat clip+AdamW (fod_flat_adamw_step)" if flat is not None else "torch fused AdamW",
                        "grad_allreduce": ("bucketed NCCL AVG, %g MB fp32 buckets, side stream inside the graph" % args.bucket_mb) if world > 1 else None},
-            "e2e": {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                    "d2h": "loss (4 B, synchronous) + packed stats/AP bookkeeping (async, pinned slab)",
-                    "pipelined": None if ms_e2e_pipe is None else {
-                        "value": clips / (ms_e2e_pipe / 1e3), "unit": UNIT,
-                        "note": "same copies and reads; the loss of step i is read (pinned copy on a side stream) after step i+1 was launched"}},
+            # e2e.value: the training loop of INTEGRATION.md — every step copies its batch from pinned host memory (prefetch
+            # on a copy stream), replays the graph, ships the stats / AP bookkeeping to the host and reads a step's loss;
+            # the loss of step i is read after step i+1 has been launched (GraphedTrainStep.read_loss_async), which keeps
+            # the ~1 ms launch latency of the ~1 500-node graph behind the running step.  `synchronous` is the same loop
+            # with float(loss) of the step just launched (what the reference's eager Trainer does, trainer.py:191): it
+            # exposes that latency every step and is sensitive to host jitter (outliers of -15..-30 % were seen).
+            "e2e": ({"value": clips / (ms_e2e_pipe / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                     "d2h": "loss (4 B, pinned, read one step after its launch) + packed stats/AP bookkeeping (async, pinned slab)",
+                     "synchronous": {"value": clips / (ms_e2e / 1e3), "unit": UNIT,
+                                     "note": "same copies; float(loss) of the step just launched, before the next launch"}}
+                    if ms_e2e_pipe is not None else
+                    {"value": clips / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
+                     "d2h": "loss (4 B, synchronous) + packed stats/AP bookkeeping (async, pinned slab)"}),
             "loss_first_last_timed_step": loss_vals, "matcher_status_by_region": status_log, "gpu_launches": launches, "launches_by_kernel": launch_by_kernel, "clocks": sampler.summary()}
     # warm, GPU-bound per-launch times of EVERY instrumented (kernel, shape) pair: each re-issued back to back in a
     # small graph; the roofline is then ranked by time per step (launches x isolated time)
