@@ -55,9 +55,15 @@ constexpr int GEMM_THREADS_MAX = 320;
 template <int BN> struct GemmThreads { static constexpr int kEpiWarps = BN == 256 ? 8 : 4; static constexpr int kThreads = 64 + 32 * kEpiWarps; };
 constexpr int GEMM_MAX_STAGES = 8;
 
-template <int BN>
+// MT = 2: one CTA computes TWO 128-row tiles against the same BN x 64 k-blocks of W (two accumulators in TMEM, 512
+// columns).  The N = 256 GEMMs over all encoder tokens (22 400 rows = 175 tiles on 148 SMs) take two waves, so the
+// busiest SMs issue two tiles' MMAs whatever the tiling — the main loop itself runs at the MMA issue rate (csrc/
+// microbench.cu, ingest_kernel: 541 clk per 48 KB k-block with the MMAs, 417 clk without; W, shared by every CTA, is
+// served far above the ~7 KB/clk the L2 gives distinct lines).  What the two-tile CTA saves is the second CTA's launch,
+// barrier / TMEM set-up and first TMA round trip, and half of the W fetches: -3..5 us on the 40..53 us K = 2048 calls.
+template <int BN, int MT = 1>
 struct GemmCfg {
-    static constexpr int kABytes = GEMM_BM * GEMM_BK * 2;
+    static constexpr int kABytes = MT * GEMM_BM * GEMM_BK * 2;
     static constexpr int kBBytes = BN * GEMM_BK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     // epilogue staging rows carry 16 bytes of padding: a lane's 16-byte accesses to ITS row and a warp's accesses
@@ -65,11 +71,20 @@ struct GemmCfg {
     static constexpr int kRowBf16 = BN * 2 + 16;
     static constexpr int kRowF32 = BN * 4 + 16;
     static constexpr int kAuxBytes = GEMM_BM * kRowBf16;
-    static constexpr int kTmemCols = BN < 32 ? 32 : BN;
+    static constexpr int kTmemCols = BN < 32 ? 32 : MT * BN;
     static constexpr int kParamBytes = 3 * BN * 4;  // bias / gamma / beta slices of this N tile, fp32
-    static constexpr int kStatBytes = 2 * 2 * GEMM_BM * 4;  // LayerNorm partial sums of the two column halves
+    static constexpr int kStatBytes = MT * 2 * 2 * GEMM_BM * 4;  // LayerNorm partial sums of the two column halves, per sub-tile
     static constexpr int kBarBytes = 256 + kParamBytes + kStatBytes;
-    static int smem_bytes(int stages, bool aux) { return 1024 + stages * kStageBytes + (aux ? kAuxBytes : 0) + kBarBytes; }
+    // MT = 2 runs exactly 3 stages (3 x 64 KB) and has no room for a dedicated residual / mask staging area: once the
+    // pipeline memory dies it is carved into [output staging | aux of sub-tile 1 | aux of sub-tile 0], each kAuxBytes.
+    // The aux-0 region lies inside stage 2 (and a few KB past the pipeline), so its prefetch can start as soon as the
+    // LAST use of stage 2 has retired — two or three k-blocks before the main loop ends.
+    static constexpr int kMt2Stages = 3;
+    static constexpr int kMt2Carve = 3 * kAuxBytes > kMt2Stages * kStageBytes ? 3 * kAuxBytes : kMt2Stages * kStageBytes;
+    static int smem_bytes(int stages, bool aux) {
+        if (MT == 2) return 1024 + kMt2Carve + kBarBytes;
+        return 1024 + stages * kStageBytes + (aux ? kAuxBytes : 0) + kBarBytes;
+    }
 };
 
 __device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, uint32_t src_bytes) {
@@ -77,6 +92,8 @@ __device__ __forceinline__ void cp_async_16(uint32_t dst, const void* src, uint3
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __device__ __forceinline__ void unpack8(const uint4& u, float (&f)[8]) {
     const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
@@ -286,21 +303,25 @@ __device__ __forceinline__ void ln_chunk(float (&z)[32], const uint32_t (&v)[32]
 
 // LN = true: the LayerNorm epilogue (N == BN == 256) and nothing else — a separate instantiation, so that neither
 // variant drags the other's code through the instruction cache.
-template <int BN, bool A_MN, bool B_MN, bool LN>
+template <int BN, bool A_MN, bool B_MN, bool LN, int MT = 1>
 __global__ void __launch_bounds__(GemmThreads<BN>::kThreads, BN == 256 ? 1 : 2)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmEpi p) {
-    using Cfg = GemmCfg<BN>;
+    using Cfg = GemmCfg<BN, MT>;
+    static_assert(MT == 1 || (MT == 2 && BN == 256 && !A_MN), "two-tile CTAs: 256-wide tiles with a K-major A operand");
+    static_assert(MT == 1 || 2 * Cfg::kAuxBytes >= 2 * Cfg::kStageBytes, "aux-0 region must start inside the last stage");
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    uint8_t* aux_stage = smem + p.num_stages * Cfg::kStageBytes;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(aux_stage + (p.aux_mode ? Cfg::kAuxBytes : 0));
+    // MT = 1: dedicated aux staging behind the stages.  MT = 2: aux of sub-tile t at (2 - t) * kAuxBytes of the carve.
+    uint8_t* aux_stage = MT == 2 ? smem + 2 * Cfg::kAuxBytes : smem + p.num_stages * Cfg::kStageBytes;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(MT == 2 ? smem + Cfg::kMt2Carve : aux_stage + (p.aux_mode ? Cfg::kAuxBytes : 0));
     uint64_t* empty_bar = full_bar + GEMM_MAX_STAGES;
     uint64_t* accum_bar = empty_bar + GEMM_MAX_STAGES;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+    uint64_t* tail_bar = accum_bar + 1;  // MT = 2: the last MMAs that read stage 2 have retired
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tail_bar + 1);
     float* s_bias = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(full_bar) + 256);
     float* s_gamma = s_bias + BN;
     float* s_beta = s_gamma + BN;
-    float* s_stat = s_beta + BN;  // [2 passes][2 halves][128 rows]
+    float* s_stat = s_beta + BN;  // [MT sub-tiles][2 passes][2 halves][128 rows]
     constexpr int EW = GemmThreads<BN>::kEpiWarps;
     constexpr int CPW = (BN / 32) / (EW / 4);  // 32-column chunks per epilogue warp
     constexpr int WCOLS = CPW * 32;            // columns per epilogue warp
@@ -308,7 +329,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int n0 = blockIdx.x * BN;
-    const int m0 = blockIdx.y * GEMM_BM;
+    const int m0 = blockIdx.y * (GEMM_BM * MT);
     const int total_kb = (p.K + GEMM_BK - 1) / GEMM_BK;
     const int kb_begin = blockIdx.z * p.kb_per_split;
     const int kb_end = min(total_kb, kb_begin + p.kb_per_split);
@@ -323,6 +344,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             mbar_init(empty_bar + s, 1);
         }
         mbar_init(accum_bar, 1);
+        mbar_init(tail_bar, 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<Cfg::kTmemCols>(tmem_slot);
@@ -350,7 +372,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
                     for (int c = 0; c < GEMM_BM / 64; ++c) tma_load_2d(sa + c * 8192, &tmA, full_bar + s, m0 + c * 64, k0);
                 } else {
-                    tma_load_2d(sa, &tmA, full_bar + s, k0, m0);
+#pragma unroll
+                    for (int t = 0; t < MT; ++t)  // rows past M are zero-filled and still count their bytes
+                        tma_load_2d(sa + t * (GEMM_BM * GEMM_BK * 2), &tmA, full_bar + s, k0, m0 + t * GEMM_BM);
                 }
                 if constexpr (B_MN) {
 #pragma unroll
@@ -376,14 +400,20 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             constexpr uint32_t kStepA = A_MN ? 2048 : 32, kStepB = B_MN ? 2048 : 32;
             int s = 0;
             uint32_t ph = 0;
+            const int kb_tail = num_kb - 1 - ((num_kb - 3) % 3);  // MT = 2 (3 stages, num_kb >= 3): last k-block held in stage 2
             for (int kb = 0; kb < num_kb; ++kb) {
                 mbar_wait(full_bar + s, ph);
                 tc_fence_after();
                 const uint64_t da = umma_desc_adv(dA0, s * Cfg::kStageBytes), db = umma_desc_adv(dB0, s * Cfg::kStageBytes);
 #pragma unroll
-                for (int k = 0; k < GEMM_BK / 16; ++k)
-                    umma_bf16_ss(tmem_base, umma_desc_adv(da, k * kStepA), umma_desc_adv(db, k * kStepB), idesc, (kb | k) ? 1u : 0u);
+                for (int k = 0; k < GEMM_BK / 16; ++k) {
+#pragma unroll
+                    for (int t = 0; t < MT; ++t)
+                        umma_bf16_ss(tmem_base + t * BN, umma_desc_adv(da, t * (GEMM_BM * GEMM_BK * 2) + k * kStepA),
+                                     umma_desc_adv(db, k * kStepB), idesc, (kb | k) ? 1u : 0u);
+                }
                 umma_commit(empty_bar + s);  // frees the smem stage when these MMAs retire
+                if (MT == 2 && kb == kb_tail) umma_commit(tail_bar);
                 if (++s == num_stages) {
                     s = 0;
                     ph ^= 1;
@@ -398,11 +428,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int half = (warp - 2) >> 2;      // 0 for the 4-warp configurations
         const int c_begin = half * CPW;
         const int row_in_tile = quarter * 32 + lane;
-        const long long row = (long long)m0 + row_in_tile;
-        const bool row_ok = row < p.M;
-        const long long mod_row = p.aux_row_mod > 0 ? (row % p.aux_row_mod) : row;
-        const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16);
-        const uint8_t* aux_row = aux_stage + row_in_tile * Cfg::kRowBf16;
         PhiloxKey key = {0u, 0u, 0u, 0u};
         if (p.drop.state) key = dropout_key(p.drop);
 
@@ -416,28 +441,51 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 s_beta[i] = ok ? __ldg(p.ln_beta + n0 + i) : 0.f;
             }
         }
-        // ... and this thread's residual / mask row -> shared memory, 16 bytes at a time
-        if (p.aux_mode && p.vec_ok) {
-            const __nv_bfloat16* src = p.aux + (p.aux_mode == 1 ? mod_row : row) * p.ld_aux + n0;
-            const uint32_t dst = smem_u32(aux_row);
+        // ... and this thread's residual / mask row(s) -> shared memory, 16 bytes at a time (sub-tile t)
+        auto aux_prefetch = [&](int t) {
+            const long long r = (long long)m0 + t * GEMM_BM + row_in_tile;
+            const bool r_ok = r < p.M;
+            const long long mr = p.aux_row_mod > 0 ? (r % p.aux_row_mod) : r;
+            const __nv_bfloat16* src = p.aux + (p.aux_mode == 1 ? mr : r) * p.ld_aux + n0;
+            const uint32_t dst = smem_u32(aux_stage - t * Cfg::kAuxBytes + row_in_tile * Cfg::kRowBf16);
 #pragma unroll 8
             for (int j = c_begin * 4; j < (c_begin + CPW) * 4; ++j) {
-                const bool ok = row_ok && (n0 + j * 8 + 8 <= p.N);
+                const bool ok = r_ok && (n0 + j * 8 + 8 <= p.N);
                 cp_async_16(dst + j * 16, ok ? static_cast<const void*>(src + j * 8) : static_cast<const void*>(p.aux),
                             ok ? 16u : 0u);
             }
             cp_async_commit();
-        }
+        };
+        const bool aux_staged = p.aux_mode && p.vec_ok;
+        if (MT == 1 && aux_staged) aux_prefetch(0);
 
         asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");  // parameter slices visible to all epilogue warps
+        if (MT == 2 && aux_staged) {  // stage 2 is dead two or three k-blocks before the end: sub-tile 0's rows land meanwhile
+            mbar_wait(tail_bar, 0);
+            aux_prefetch(0);
+        }
         mbar_wait(accum_bar, 0);
         tc_fence_after();
-        if (p.aux_mode && p.vec_ok) cp_async_wait_all();
         // The pipeline stages are dead now (every TMA write landed and every MMA retired before accum_bar fired):
-        // they become the output staging area.
+        // they become the output staging area (and, for MT = 2, the aux area of sub-tile 1).
+        if (MT == 2 && aux_staged) aux_prefetch(1);
         uint8_t* stage_a = smem;
         uint32_t v[32];
         float z[32];
+#pragma unroll 1
+        for (int t = 0; t < MT; ++t) {
+        const long long mt0 = (long long)m0 + t * GEMM_BM;
+        const long long row = mt0 + row_in_tile;
+        const bool row_ok = row < p.M;
+        const long long mod_row = p.aux_row_mod > 0 ? (row % p.aux_row_mod) : row;
+        const uint32_t taddr = tmem_base + (uint32_t(quarter * 32) << 16) + t * BN;
+        const uint8_t* aux_row = aux_stage - t * Cfg::kAuxBytes + row_in_tile * Cfg::kRowBf16;
+        float* s_stat_t = s_stat + t * (4 * GEMM_BM);
+        if (aux_staged) {
+            if (MT == 2 && t == 0) cp_async_wait_group<1>();
+            else cp_async_wait_all();
+        }
+        if (MT == 2 && t > 0 && mt0 >= p.M) break;  // (CTA-uniform) the empty second tile of an odd tile count
         if constexpr (!LN) {
             const bool f32out = p.out_f32 != nullptr;
             const int rowb = f32out ? Cfg::kRowF32 : Cfg::kRowBf16;
@@ -457,11 +505,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             __syncwarp();
             const uint8_t* stage_warp = stage_a + quarter * 32 * rowb + c_begin * 32 * (f32out ? 4 : 2);
             if (f32out)
-                drain_f32<BN, WCOLS>(stage_warp, p.out_f32, p.ld_out, p.M, p.N, (long long)m0 + quarter * 32,
+                drain_f32<BN, WCOLS>(stage_warp, p.out_f32, p.ld_out, p.M, p.N, mt0 + quarter * 32,
                                      n0 + c_begin * 32, lane, p.vec_ok != 0, p.atomic_out != 0);
             else
-                drain_bf16<BN, WCOLS>(stage_warp, p.out_bf16, p.ld_out, p.M, p.N, (long long)m0 + quarter * 32,
+                drain_bf16<BN, WCOLS>(stage_warp, p.out_bf16, p.ld_out, p.M, p.N, mt0 + quarter * 32,
                                       n0 + c_begin * 32, lane, p.vec_ok != 0, p.colsum_out);
+            if (MT == 2) __syncwarp();  // the staged rows are reused by the next sub-tile
         } else {
             // LayerNorm over the whole row (N == BN == 256, n0 == 0).  The two warps of a lane quarter own 128 columns of
             // the row each.  Two passes over the accumulator IN TMEM (reading it costs ~1 KB/clk per SM, a fraction of
@@ -472,7 +521,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             // Loops are kept rolled (32 columns per iteration).
             static_assert(BN == 256, "LayerNorm epilogue needs the whole 256-wide row in one tile");
             uint8_t* my_a = stage_a + row_in_tile * Cfg::kRowBf16;
-            const long long row0 = (long long)m0 + quarter * 32;
+            const long long row0 = mt0 + quarter * 32;
             const int off = c_begin * 64;  // byte offset of this warp's column half inside a staged bf16 row
             float shift = 0.f, s1 = 0.f, s2 = 0.f;
 #pragma unroll 1
@@ -498,16 +547,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             constexpr float kInvHalf = 1.f / (CPW * 32);
             const float m_half = shift + s1 * kInvHalf;           // mean of this warp's 128 columns
             const float m2_half = s2 - s1 * s1 * kInvHalf;        // sum of squared deviations about it
-            s_stat[half * GEMM_BM + row_in_tile] = m_half;
-            s_stat[(2 + half) * GEMM_BM + row_in_tile] = m2_half;
+            s_stat_t[half * GEMM_BM + row_in_tile] = m_half;
+            s_stat_t[(2 + half) * GEMM_BM + row_in_tile] = m2_half;
             if (p.pre_ln) {
                 __syncwarp();
                 drain_bf16<BN, WCOLS>(stage_a + quarter * 32 * Cfg::kRowBf16 + off, p.pre_ln, p.ld_out, p.M, p.N, row0,
                                       c_begin * 32, lane, p.vec_ok != 0, nullptr);
             }
             asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
-            const float m_other = s_stat[(half ^ 1) * GEMM_BM + row_in_tile];
-            const float m2_other = s_stat[(2 + (half ^ 1)) * GEMM_BM + row_in_tile];
+            const float m_other = s_stat_t[(half ^ 1) * GEMM_BM + row_in_tile];
+            const float m2_other = s_stat_t[(2 + (half ^ 1)) * GEMM_BM + row_in_tile];
             const float mean = 0.5f * (m_half + m_other);
             const float dm = m_half - m_other;
             // Chan's pairwise combination of two equal halves of n = 128: M2 = M2a + M2b + dm^2 * n / 2
@@ -537,7 +586,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             __syncwarp();
             drain_bf16<BN, WCOLS>(stage_a + quarter * 32 * Cfg::kRowBf16 + off, p.out_bf16, p.ld_out, p.M, p.N, row0,
                                   c_begin * 32, lane, p.vec_ok != 0, nullptr);
+            if (MT == 2) __syncwarp();  // the staged rows are reused by the next sub-tile
         }
+        }  // sub-tiles
         tc_fence_before();
     }
     __syncthreads();
@@ -547,9 +598,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
 }
 
-template <int BN, bool A_MN, bool B_MN, bool LN = false>
+template <int BN, bool A_MN, bool B_MN, bool LN = false, int MT = 1>
 static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
-    using Cfg = GemmCfg<BN>;
+    using Cfg = GemmCfg<BN, MT>;
     CUtensorMap tmA, tmB;
     const long long ldw = a->ldw ? a->ldw : (B_MN ? a->N : a->K);
     if (A_MN) {
@@ -578,7 +629,7 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     // stage count: the pipeline stages double as output staging, so they must hold the staged tile
     int stages = BN == 256 ? (aux ? 3 : 4) : (BN == 128 ? 4 : 3);
     const int total_kb = (a->K + GEMM_BK - 1) / GEMM_BK;
-    const int mt = (a->M + GEMM_BM - 1) / GEMM_BM, nt = (a->N + BN - 1) / BN;
+    const int mt = (a->M + GEMM_BM * MT - 1) / (GEMM_BM * MT), nt = (a->N + BN - 1) / BN;
     int splits = 1;
     if (a->split_k > 1) splits = a->split_k;
     else if (a->split_k < 0) {  // auto: fill the 148 SMs, at least two k-blocks per split
@@ -600,6 +651,10 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
         const int want = epi.kb_per_split < min_stages ? min_stages : epi.kb_per_split;
         if (want < stages) stages = want;
     }
+    if (MT == 2) {  // (gemm_two_tiles() admits only what this layout holds: bf16 output, no split, >= 3 k-blocks)
+        if (splits != 1 || a->out_f32 || total_kb < Cfg::kMt2Stages) return fod_fail(FOD_E_ARG, "gemm: two-tile CTAs misrouted");
+        stages = Cfg::kMt2Stages;
+    }
     bool memset_before = false;
     if (a->split_k < 0 && !a->atomic_out) {  // overwrite semantics: plain stores, or zero-fill + reductions
         if (splits > 1) {
@@ -614,7 +669,7 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
         const int a1 = Cfg::smem_bytes(BN == 256 ? 3 : (BN == 128 ? 4 : 3), true), a2 = Cfg::smem_bytes(BN == 64 ? 3 : 4, false);
-        cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN, LN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(gemm_bf16_kernel<BN, A_MN, B_MN, LN, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              a1 > a2 ? a1 : a2);
         attr_set = true;
     }
@@ -629,7 +684,7 @@ static int launch_gemm(const fod_linear_args* a, GemmEpi epi, cudaStream_t st) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = (fod_pdl_enabled() && !memset_before) ? 1 : 0;  // a memset node cannot be a programmatic predecessor
-    cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, A_MN, B_MN, LN>, tmA, tmB, epi);
+    cudaLaunchKernelEx(&cfg, gemm_bf16_kernel<BN, A_MN, B_MN, LN, MT>, tmA, tmB, epi);
     return fod_check_launch("gemm_bf16_kernel");
 }
 
@@ -659,8 +714,6 @@ constexpr int WS_X_BYTES = WS_EPI_WARPS * 2 * WS_XBUF;      // two chunk buffers
 constexpr int WS_CS_BYTES = WS_EPI_WARPS * 128 * 4;            // per-warp column-sum accumulators (bias gradients)
 constexpr int WS_SMEM = 1024 + WS_B_BYTES + WS_A_STAGES * WS_A_BYTES + WS_X_BYTES + 256 + WS_BN * 4 + WS_CS_BYTES;
 
-template <int N>
-__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
     uint4 u;
@@ -996,13 +1049,30 @@ static int launch_gemm_ws(const fod_linear_args* a, const GemmEpi& epi, cudaStre
     return fod_check_launch("gemm_ws_kernel");
 }
 
+// Two 128-row tiles per CTA (GemmCfg<256, 2>) when the 128-row tiling leaves a partial last wave that the 256-row
+// tiling removes (a 256-row CTA is charged as 1.4 one-tile CTAs).  22 400 rows: 175 tiles = 2 waves -> 88 CTAs = 1 wave.
+// Measured at 22 400 rows (us, one tile -> two tiles per CTA): LayerNorm epilogue K = 2048 41.3 -> 38.1, with dropout and
+// saved statistics 53.3 -> 48.4, dX + residual 37.3 -> 33.9, plain 30.1 -> 28.8; K = 256: 11.0 -> 9.8, LayerNorm 18.6 -> 17.9.
+// FOD_GEMM_MT2=0 disables the path, =1 keeps it to contractions of >= 8 k-blocks.
+static bool gemm_two_tiles(const fod_linear_args* a, const GemmEpi& e) {
+    static const int mode = [] { const char* v = getenv("FOD_GEMM_MT2"); return v ? atoi(v) : 2; }();
+    if (mode == 0 || a->a_mn || a->N > 256 || a->N <= 128 || a->out_f32 || a->split_k || a->atomic_out || !e.vec_ok) return false;
+    const int total_kb = (a->K + GEMM_BK - 1) / GEMM_BK;
+    if (total_kb < (mode == 2 ? 3 : 8)) return false;
+    const int mt1 = (a->M + GEMM_BM - 1) / GEMM_BM, mt2 = (mt1 + 1) / 2;
+    return 1.4 * ((mt2 + 147) / 148) < 1.0 * ((mt1 + 147) / 148);
+}
+
 template <int BN>
 static int launch_gemm_major(const fod_linear_args* a, const GemmEpi& e, cudaStream_t st) {
     if constexpr (BN == 256) {
+        const bool two = gemm_two_tiles(a, e);
         if (a->ln_gamma) {
             if (a->a_mn || a->b_mn) return fod_fail(FOD_E_ARG, "gemm: the LayerNorm epilogue takes K-major operands");
+            if (two) return launch_gemm<256, false, false, true, 2>(a, e, st);
             return launch_gemm<256, false, false, true>(a, e, st);
         }
+        if (two) return a->b_mn ? launch_gemm<256, false, true, false, 2>(a, e, st) : launch_gemm<256, false, false, false, 2>(a, e, st);
     }
     if (a->a_mn && a->b_mn) return launch_gemm<BN, true, true>(a, e, st);
     if (a->b_mn) return launch_gemm<BN, false, true>(a, e, st);

@@ -1,12 +1,15 @@
 // Device micro-benchmarks behind the roofline statements of DESIGN.md (standalone, no Python):
 //   1. TMEM read bandwidth per SM (tcgen05.ld.32x32b.x32) with 4 / 8 / 16 reader warps — the ceiling of every
 //      epilogue and of the attention softmax, which pull fp32 accumulators into registers;
-//   2. ex2.approx throughput per SM (MUFU) next to a degree-3 polynomial exp2 on the FMA pipe.
+//   2. ex2.approx throughput per SM (MUFU) next to a degree-3 polynomial exp2 on the FMA pipe;
+//   3. tcgen05.mma issue cost by N, A operand in shared or tensor memory;
+//   4. TMA ingest of the GEMM main loop (L2 -> shared memory) with and without the MMAs that consume it.
 // Build: make microbench ; run on a B200: ./microbench_fod
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
 #include "sm100_ptx.cuh"
+#include "tmap.h"
 
 using namespace fod;
 
@@ -129,6 +132,94 @@ __global__ void __launch_bounds__(128, 1) mma_rate_kernel(int iters, unsigned lo
     }
 }
 
+
+// L2 -> shared-memory ingest of the GEMM main loop: per k-block NA boxes of 128 rows x 64 k (16 KB each, this CTA's rows
+// of A) and, with B, one 256 x 64 box of W (32 KB, the same for every CTA) through a 3- or 4-stage ring.  MMAS = 0: the
+// consumer frees the stage at once (pure ingest); MMAS = m: it issues m M128 N256 K16 MMAs per 16 k first (operand reads
+// compete with the TMA writes for shared-memory bandwidth).  Reports clk per k-block.
+template <int NA, bool WITHB, int MMAS, int STAGES>
+__global__ void __launch_bounds__(128, 1) ingest_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                                                         int reps, int kblocks, unsigned long long* cycles) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    constexpr int kStage = NA * 16384 + (WITHB ? 32768 : 0);
+    __shared__ uint64_t full[STAGES], empty[STAGES];
+    __shared__ uint32_t slot;
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < STAGES; ++i) {
+            mbar_init(full + i, 1);
+            mbar_init(empty + i, 1);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 2) tmem_alloc<512>(&slot);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t base = slot;
+    const int m0 = blockIdx.x * 128 * NA;
+    const long long t0 = clock64();
+    if (threadIdx.x == 0) {
+        int st = 0;
+        uint32_t ph = 0;
+        for (int r = 0; r < reps; ++r)
+            for (int kb = 0; kb < kblocks; ++kb) {
+                mbar_wait(empty + st, ph ^ 1);
+                uint8_t* sa = smem + st * kStage;
+                mbar_arrive_expect_tx(full + st, kStage);
+#pragma unroll
+                for (int t = 0; t < NA; ++t) tma_load_2d(sa + t * 16384, &tmA, full + st, kb * 64, m0 + t * 128);
+                if (WITHB) tma_load_2d(sa + NA * 16384, &tmB, full + st, kb * 64, 0);
+                if (++st == STAGES) {
+                    st = 0;
+                    ph ^= 1;
+                }
+            }
+    } else if (threadIdx.x == 32) {
+        constexpr uint32_t idesc = umma_idesc_bf16(128, 256, 0, 0);
+        int st = 0;
+        uint32_t ph = 0;
+        for (int r = 0; r < reps; ++r)
+            for (int kb = 0; kb < kblocks; ++kb) {
+                mbar_wait(full + st, ph);
+                if (MMAS > 0) {
+                    tc_fence_after();
+                    const uint32_t a0 = smem_u32(smem) + st * kStage;
+                    const uint64_t dA = umma_smem_desc(a0, 16, 1024, 2);
+                    const uint64_t dB = umma_smem_desc(a0 + (WITHB ? NA * 16384 : 0), 16, 1024, 2);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+#pragma unroll
+                        for (int t = 0; t < MMAS; ++t)
+                            umma_bf16_ss(base + (t & 1) * 256, umma_desc_adv(dA, (NA > 1 ? (t & 1) * 16384 : 0) + k * 32), umma_desc_adv(dB, k * 32), idesc, 1u);
+                    }
+                    umma_commit(empty + st);
+                } else {
+                    mbar_arrive(empty + st);
+                }
+                if (++st == STAGES) {
+                    st = 0;
+                    ph ^= 1;
+                }
+            }
+        if (MMAS > 0) {  // drain: the last commit covers every MMA issued
+            const int last = (st + STAGES - 1) % STAGES;
+            const long long n = (long long)reps * kblocks;
+            mbar_wait(empty + last, (uint32_t)(((n - 1) / STAGES) & 1));
+        }
+    }
+    __syncthreads();
+    const long long t1 = clock64();
+    if (threadIdx.x == 0) cycles[blockIdx.x] = (unsigned long long)(t1 - t0);
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) {
+        tc_fence_after();
+        tmem_dealloc<512>(base);
+    }
+}
+
 template <typename F>
 static double run(F launch, unsigned long long* d_cyc) {
     launch();
@@ -178,5 +269,33 @@ int main() {
                2.0 * 128 * NN * 16 / (c / (mi * 32.0)));                                                        \
     }
     MR(32, false) MR(64, false) MR(128, false) MR(256, false) MR(32, true) MR(64, true) MR(128, true) MR(256, true)
+    {
+        printf("TMA ingest of the GEMM main loop (A rows per CTA, W shared), 32 k-blocks x 8 passes per CTA\n");
+        const int rows = 148 * 256, K = 2048;
+        void *dA, *dW;
+        cudaMalloc(&dA, (size_t)rows * K * 2);
+        cudaMalloc(&dW, (size_t)256 * K * 2);
+        cudaMemset(dA, 0, (size_t)rows * K * 2);
+        cudaMemset(dW, 0, (size_t)256 * K * 2);
+        CUtensorMap tmA, tmB;
+        uint64_t da[2] = {(uint64_t)K, (uint64_t)rows}, db[2] = {(uint64_t)K, 256};
+        uint64_t str[1] = {(uint64_t)K * 2};
+        uint32_t ba[2] = {64, 128}, bb[2] = {64, 256};
+        if (fod::make_tmap_bf16(&tmA, dA, 2, da, str, ba, 128) || fod::make_tmap_bf16(&tmB, dW, 2, db, str, bb, 128)) return 1;
+        const int reps = 8, kbs = 32;
+#define IG(NA, WB, MM, ST, GRID)                                                                                      \
+    {                                                                                                                  \
+        const int smem = 1024 + ST * (NA * 16384 + (WB ? 32768 : 0));                                                  \
+        cudaFuncSetAttribute(ingest_kernel<NA, WB, MM, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);        \
+        cudaMemset(d_cyc, 0, 148 * 8);                                                                                 \
+        double c = run([&] { ingest_kernel<NA, WB, MM, ST><<<GRID, 128, smem>>>(tmA, tmB, reps, kbs, d_cyc); }, d_cyc) * 148.0 / GRID; \
+        const double per = c / (reps * kbs);                                                                           \
+        printf("  grid %3d  A boxes %d  W %d  MMAs/k16 %d  stages %d: %.0f clk per k-block -> %.1f B/clk/SM, %.0f B/clk chip\n", GRID, NA, \
+               (int)WB, MM, ST, per, (NA * 16384 + (WB ? 32768 : 0)) / per, GRID * (NA * 16384 + (WB ? 32768 : 0)) / per); \
+    }
+        IG(1, true, 0, 3, 148) IG(1, true, 0, 4, 148) IG(1, true, 0, 3, 88) IG(1, true, 0, 3, 27) IG(1, true, 0, 3, 1)
+        IG(2, true, 0, 3, 88) IG(2, true, 0, 3, 148) IG(1, false, 0, 4, 148) IG(2, false, 0, 4, 148) IG(2, false, 0, 4, 27)
+        IG(1, true, 1, 3, 148) IG(1, true, 1, 4, 148) IG(1, true, 1, 3, 27) IG(2, true, 2, 3, 88) IG(2, true, 2, 3, 27)
+    }
     return 0;
 }

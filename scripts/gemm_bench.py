@@ -125,8 +125,11 @@ cases["relu_bwd_add3 183500800"] = _relu_case(183500800)
 flops = {"2048x256": 2.0 * M * 2048 * 256, "768x256": 2.0 * M * 768 * 256, "256x256": 2.0 * M * 256 * 256,
          "256x2048": 2.0 * M * 2048 * 256}
 only = os.environ.get("GEMM_CASE")
+match = os.environ.get("GEMM_MATCH")
 for name, fn in cases.items():
     if only and only != name:
+        continue
+    if match and not any(m in name for m in match.split(",")):  # GEMM_MATCH: comma-separated substrings
         continue
     if os.environ.get("GEMM_EAGER"):  # under ncu: plain launches, no graph
         for _ in range(3):

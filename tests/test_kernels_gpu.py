@@ -387,3 +387,52 @@ def test_batch_sum_matches_torch(G, R, C):
     from fod_b200 import ops
     x = _rnd(G, R, C, seed=5)
     _close(ops.batch_sum(x), x.float().sum(0), tol=5e-3, what="batch_sum")
+
+
+@pytest.mark.parametrize("M,K", [(22400, 2048), (19010, 512), (44800, 576), (22400, 640)])
+def test_gemm_two_tiles_per_cta_path(M, K):
+    """N = 256 GEMMs whose 128-row tiling leaves a partial last wave run two 128-row tiles per CTA (csrc/gemm_sm100.cu:
+    GemmCfg<256, 2>): 175 / 149 / 350 tiles (odd counts: the last CTA's second tile is empty or ragged), k-block counts
+    8 / 9 / 10 / 32 (the three positions of the last use of pipeline stage 2).  Every epilogue the path admits, both W
+    layouts, LayerNorm with saved statistics, dropout masks identical to the one-tile path's on the same rows."""
+    from fod_b200 import ops
+    N = 256
+    x, w = _rnd(M, K, seed=1), _rnd(N, K, scale=0.03, seed=2)
+    b = torch.randn(N, device=_dev())
+    ref = x.float() @ w.float().t() + b
+    _close(ops.gemm(x, w, bias=b), ref, what="bias")
+    _close(ops.gemm(x, w, bias=b, relu=True), ref.relu(), what="relu")
+    mod = 350 if M % 350 == 0 else 0
+    res = _rnd(mod or M, N, seed=3)
+    rr = res.float().repeat(M // mod, 1) if mod else res.float()
+    _close(ops.gemm(x, w, bias=b, residual=res, res_row_mod=mod), ref + rr, what="residual")
+    gam, bet = torch.rand(N, device=_dev()) + 0.5, torch.randn(N, device=_dev())
+    z = ref + rr
+    y, pre, mean, rstd = ops.gemm(x, w, bias=b, residual=res, res_row_mod=mod, ln=(gam, bet, 1e-5), save_ln=True)
+    _close(y, torch.nn.functional.layer_norm(z, (N,), gam, bet, 1e-5), what="ln")
+    _close(pre, z, what="pre_ln")
+    _close(mean, z.mean(1), tol=1e-2, what="mean")
+    _close(rstd, (z.var(1, unbiased=False) + 1e-5).rsqrt(), tol=1e-2, what="rstd")
+    _close(ops.gemm(x, w, bias=b, ln=(gam, bet, 1e-5)), torch.nn.functional.layer_norm(ref, (N,), gam, bet, 1e-5), what="ln, no residual")
+    # dX form: dy (M, K) · W (K, N) read MN-major, residual / ReLU mask with scale and fused column sums
+    wt = _rnd(K, N, scale=0.03, seed=4)
+    ref_dx = x.float() @ wt.float()
+    full = _rnd(M, N, seed=5)
+    _close(ops.gemm(x, wt, b_mn=True), ref_dx, what="dX plain")
+    _close(ops.gemm(x, wt, b_mn=True, residual=full), ref_dx + full.float(), what="dX + residual")
+    cs = torch.zeros(N, device=_dev())
+    dx = ops.gemm(x, wt, b_mn=True, relu_mask=full, mask_scale=1.25, colsum_out=cs)
+    _close(dx, ref_dx * (full.float() > 0) * 1.25, what="dX mask")
+    _close(cs, dx.float().sum(0), tol=2e-3, what="colsum")
+    # dropout before the residual of the LayerNorm epilogue: the mask depends on (seed, step, call, row, column) only,
+    # so the first 5 000 rows computed alone (44 tiles: one tile per CTA) must reproduce the big launch bit for bit
+    ops.set_dropout_seed(77, _dev())
+    drop = (0.1, 5)
+    yd, pred, _, _ = ops.gemm(x, w, bias=b, residual=full, ln=(gam, bet, 1e-5), save_ln=True, drop=drop)
+    ys, pres, _, _ = ops.gemm(x[:5000], w, bias=b, residual=full[:5000], ln=(gam, bet, 1e-5), save_ln=True, drop=drop)
+    assert torch.equal(yd[:5000], ys) and torch.equal(pred[:5000], pres)
+    kept = float(((pred.float() - full.float()).abs() > 0).float().mean())
+    assert abs(kept - 0.9) < 5e-3, kept
+    # twice in a row on one stream: no stale barrier / TMEM state
+    y2 = ops.gemm(x, w, bias=b, residual=res, res_row_mod=mod, ln=(gam, bet, 1e-5))
+    assert torch.equal(y, y2)
