@@ -1050,7 +1050,9 @@ static int launch_gemm_ws(const fod_linear_args* a, const GemmEpi& epi, cudaStre
 }
 
 // Two 128-row tiles per CTA (GemmCfg<256, 2>) when the 128-row tiling leaves a partial last wave that the 256-row
-// tiling removes (a 256-row CTA is charged as 1.4 one-tile CTAs).  22 400 rows: 175 tiles = 2 waves -> 88 CTAs = 1 wave.
+// tiling removes.  A 256-row CTA is charged as 1.9 one-tile CTAs (28.8 us for one wave of them against 30.1 / 2 us per
+// one-tile wave, plain epilogue): 22 400 rows, 175 tiles = 2 waves -> 88 CTAs = 1 wave qualifies; 44 800 rows
+// (350 tiles = 3 waves -> 175 CTAs = 2 waves) does not, and measured no different in the stage-2 step.
 // Measured at 22 400 rows (us, one tile -> two tiles per CTA): LayerNorm epilogue K = 2048 41.3 -> 38.1, with dropout and
 // saved statistics 53.3 -> 48.4, dX + residual 37.3 -> 33.9, plain 30.1 -> 28.8; K = 256: 11.0 -> 9.8, LayerNorm 18.6 -> 17.9.
 // FOD_GEMM_MT2=0 disables the path, =1 keeps it to contractions of >= 8 k-blocks.
@@ -1060,7 +1062,7 @@ static bool gemm_two_tiles(const fod_linear_args* a, const GemmEpi& e) {
     const int total_kb = (a->K + GEMM_BK - 1) / GEMM_BK;
     if (total_kb < (mode == 2 ? 3 : 8)) return false;
     const int mt1 = (a->M + GEMM_BM - 1) / GEMM_BM, mt2 = (mt1 + 1) / 2;
-    return 1.4 * ((mt2 + 147) / 148) < 1.0 * ((mt1 + 147) / 148);
+    return 1.9 * ((mt2 + 147) / 148) < 1.0 * ((mt1 + 147) / 148);
 }
 
 template <int BN>
