@@ -502,6 +502,56 @@ extern "C" int fod_frames_to_nhwc_bf16(const float* video, int64_t stride_b, int
     return fod::fod_check_launch("frames_to_nhwc_bf16_kernel");
 }
 
+// The same frames as (N, H, W + 8, 4) bf16: pixel x at padded column x + 3, channel 3 and the 3 + 5 border columns zero —
+// the layout fod_stem_conv7x7s2_p4 reads through one overlapping-window tensor map (csrc/stemconv_sm100.cu).  One
+// thread writes 8 padded columns (64 contiguous bytes); every element of `out` is written, borders included.
+namespace fod {
+__global__ void __launch_bounds__(256)
+frames_to_nhwc4p_bf16_kernel(const float* __restrict__ video, long long stride_b, long long stride_t, int T, int H, int W,
+                             __nv_bfloat16* __restrict__ out, long long groups) {
+    const long long hw = (long long)H * W;
+    const int wg = (W + 8) / 8;
+    for (long long g = (long long)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += (long long)gridDim.x * blockDim.x) {
+        const int xg = (int)(g % wg);
+        const long long r = g / wg;          // frame * H + row
+        const int y = (int)(r % H);
+        const long long n = r / H;           // frame index b * T + t
+        const float* src = video + (n / T) * stride_b + (n % T) * stride_t + (long long)y * W;
+        const int x0 = xg * 8 - 3;
+        uint4* dst = reinterpret_cast<uint4*>(out + (r * (long long)(W + 8) + xg * 8) * 4);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {  // two pixels per 16-byte store
+            float f[2][3];
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const int x = x0 + 2 * q + i;
+                const bool ok = x >= 0 && x < W;
+#pragma unroll
+                for (int ch = 0; ch < 3; ++ch) f[i][ch] = ok ? __ldg(src + ch * hw + x) : 0.f;
+            }
+            uint4 u;
+            u.x = pack_bf16x2(f[0][0], f[0][1]);
+            u.y = pack_bf16x2(f[0][2], 0.f);
+            u.z = pack_bf16x2(f[1][0], f[1][1]);
+            u.w = pack_bf16x2(f[1][2], 0.f);
+            dst[q] = u;
+        }
+    }
+}
+}  // namespace fod
+
+extern "C" int fod_frames_to_nhwc4p_bf16(const float* video, int64_t stride_b, int64_t stride_t, int32_t B, int32_t T,
+                                         int32_t H, int32_t W, void* out, void* stream) {
+    if (!video || !out || B <= 0 || T <= 0 || H <= 0 || W <= 0) return fod_fail(FOD_E_ARG, "frames_to_nhwc4p: null/empty");
+    if (W % 8 || (reinterpret_cast<uintptr_t>(out) & 15)) return fod_fail(FOD_E_ARG, "frames_to_nhwc4p: W % 8 == 0 and a 16-byte aligned output needed");
+    const long long groups = (long long)B * T * H * ((W + 8) / 8);
+    long long blocks = (groups + 255) / 256;
+    if (blocks > 148LL * 16) blocks = 148LL * 16;
+    fod::frames_to_nhwc4p_bf16_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+        video, stride_b, stride_t, T, H, W, reinterpret_cast<__nv_bfloat16*>(out), groups);
+    return fod::fod_check_launch("frames_to_nhwc4p_bf16_kernel");
+}
+
 // ---------------------------------------------------------------- fused ReLU backward (+ gradient add) for the backbone
 // out = (a [+ b]) * (y > 0), flat bf16 arrays of n elements (n % 8 == 0, identical layouts).  In a bottleneck's backward
 // the gradient of the block output arrives as two addends (the conv1 input gradient and the identity-path gradient of

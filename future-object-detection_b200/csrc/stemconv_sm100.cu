@@ -13,8 +13,10 @@
 //   folded shift, applies ReLU and writes the pixel's 64 channels (128 contiguous bytes, NHWC).
 // Persistent CTAs, two per SM, so one CTA's operand assembly overlaps the other's MMA + epilogue.
 // HBM-bound in the limit: reads the image once (6 B/pixel), writes 128 B per output pixel (275 MB for the bench step).
+#include <cstdlib>
 #include "fod_internal.h"
 #include "sm100_ptx.cuh"
+#include "tmap.h"
 
 namespace fod {
 
@@ -176,6 +178,232 @@ stem_conv7x7s2_kernel(const StemParams p) {
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Second form: the operand tile comes straight from TMA (no thread-built im2col).  The image is stored NHWC with FOUR
+// channels (the fourth zero) and explicit zero columns left and right: (N, H, W + 8, 4) bf16, pixel x of the image at
+// padded column x + 3.  For one kernel row the 7 x 3 inputs of output pixel ox are then the 32 contiguous elements
+// (8 pixels x 4 channels, 64 bytes; the 8th pixel and every 4th channel meet zero weights) that start at padded column
+// 2 ox — 16 bytes further for every output pixel.  A tiled tensor map whose second dimension has a 16-byte stride under
+// a 64-byte innermost extent describes exactly that overlapping window (csrc/tmaprobe.cu checks it on the device), and
+// splitting the image rows into (parity, row / 2) turns the stride-2 row walk into a dense box:
+//     dims [k = 32][ox][row parity = 2][row / 2][n], box [32][16][1][11][1] -> [11 half-rows][16 pixels][64 B], SWIZZLE_64B:
+// any 8 consecutive half-rows of it are the K-major A operand of one kernel row as they land, and the kernel rows of one
+// parity (1,3,5 / 0,2,4,6) are the SAME box read one half-row further down (two boxes = 22 KB per tile, not seven).  Rows above / below the image and tiles hanging over the right
+// edge are zero-filled by the TMA unit.  K = 7 x 32 = 224: 14 MMAs (M128 N64 K16) per 8 x 16-pixel tile.
+//   warp 0: TMA producer, the two parity boxes of a tile on one barrier, 5-tile ring
+//   warp 1: TMEM allocator + MMA issuer, two accumulators (2 x 64 columns): tile i+1 is multiplied while tile i drains
+//   warps 2-5: epilogue — accumulator row -> +shift, ReLU -> bf16 -> SWIZZLE_128B staging tile -> ONE TMA store of
+//              the tile's [8][16][64] block (clipped at the image edges by the unit).
+// Persistent, one CTA per SM.  Bound: the 128 B per output pixel it writes (HBM) — 14 MMAs at the 52-clk issue floor
+// are 730 clk per 16 KB tile, i.e. ~6 TB/s over 148 SMs.
+constexpr int S4_STAGES = 5;                     // ring of whole tiles
+constexpr int S4_BOX_ROWS = 11;                  // half-rows per box: 8 output rows + 3 (odd kernel rows 0,2,4,6 share one box)
+constexpr int S4_BOX_BYTES = S4_BOX_ROWS * 16 * 64;  // 11 KB: [11 half-rows][16 pixels][64 B]
+constexpr int S4_A_BYTES = 2 * S4_BOX_BYTES;     // even-parity box (kernel rows 1,3,5) + odd-parity box (0,2,4,6)
+constexpr int S4_B_BYTES = 7 * 64 * 64;          // weights: 7 kernel rows x [64 out][32 k]
+constexpr int S4_OUT_BYTES = 128 * 128;          // staged output tile
+constexpr int S4_SMEM = S4_STAGES * S4_A_BYTES + S4_B_BYTES + 2 * S4_OUT_BYTES + 64 * 4 + 512 + 1024;
+constexpr int S4_THREADS = 192;
+
+struct Stem4Params {
+    const __nv_bfloat16* wk;  // (64, 224): [o][kh*32 + kw*4 + c] = W[o][c][kh][kw] * s[o] (kw < 7, c < 3), zeros elsewhere
+    const float* bias;
+    int tiles_x, tiles_y, tiles;
+};
+
+__global__ void __launch_bounds__(S4_THREADS, 1)
+stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmY, const Stem4Params p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t* sA = smem;
+    uint8_t* sB = sA + S4_STAGES * S4_A_BYTES;
+    uint8_t* sOut = sB + S4_B_BYTES;
+    float* sBias = reinterpret_cast<float*>(sOut + 2 * S4_OUT_BYTES);
+    uint64_t* full = reinterpret_cast<uint64_t*>(sBias + 64);
+    uint64_t* empty = full + S4_STAGES;
+    uint64_t* acc_full = empty + S4_STAGES;
+    uint64_t* acc_empty = acc_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        tma_prefetch_desc(&tmX);
+        tma_prefetch_desc(&tmY);
+        for (int s = 0; s < S4_STAGES; ++s) {
+            mbar_init(full + s, 1);
+            mbar_init(empty + s, 1);
+        }
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(acc_full + b, 1);
+            mbar_init(acc_empty + b, 4);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<128>(tmem_slot);
+    // weights -> 7 swizzled [64][64 B] tiles (once per CTA); folded shift
+    for (int c = tid; c < 64 * 28; c += S4_THREADS) {
+        const int o = c / 28, ch = c - o * 28;  // 28 chunks of 8 k per output channel
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.wk + (long long)o * 224) + ch);
+        *reinterpret_cast<uint4*>(sB + (ch >> 2) * (64 * 64) + swz_off<64>(o, ch & 3)) = v;
+    }
+    if (tid < 64) sBias[tid] = p.bias[tid];
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int s = 0;
+            uint32_t ph = 0;
+            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x) {
+                const int tx = tile % p.tiles_x;
+                const int t2 = tile / p.tiles_x;
+                const int ty = t2 % p.tiles_y;
+                const int n = t2 / p.tiles_y;
+                mbar_wait(empty + s, ph ^ 1);
+                mbar_arrive_expect_tx(full + s, S4_A_BYTES);
+                // input row 2 oy - 3 + kh = 2 (oy + off) + par: kh = 1,3,5 -> par 0, off -1,0,1; kh = 0,2,4,6 -> par 1, off -2..1
+                tma_load_5d(sA + s * S4_A_BYTES, &tmX, full + s, 0, tx * 16, 0, ty * 8 - 1, n);
+                tma_load_5d(sA + s * S4_A_BYTES + S4_BOX_BYTES, &tmX, full + s, 0, tx * 16, 1, ty * 8 - 2, n);
+                if (++s == S4_STAGES) {
+                    s = 0;
+                    ph ^= 1;
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 0);
+            const uint64_t dA0 = umma_smem_desc(smem_u32(sA), 16, 512, 4);   // [128][64 B] SWIZZLE_64B, 8-row groups 512 B apart
+            const uint64_t dB0 = umma_smem_desc(smem_u32(sB), 16, 512, 4);
+            int s = 0, it = 0;
+            uint32_t ph = 0;
+            for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+                const int buf = it & 1;
+                mbar_wait(acc_empty + buf, ((it >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + buf * 64;
+                mbar_wait(full + s, ph);
+                tc_fence_after();
+#pragma unroll
+                for (int kh = 0; kh < 7; ++kh) {
+                    // kernel row kh starts (kh >> 1) half-rows (1 KB each: 16 pixels x 64 B, a multiple of the 512-byte
+                    // swizzle period) into the box of its parity
+                    const uint64_t da = umma_desc_adv(dA0, s * S4_A_BYTES + ((kh & 1) ? 0 : S4_BOX_BYTES) + (kh >> 1) * 1024);
+                    const uint64_t db = umma_desc_adv(dB0, kh * (64 * 64));
+                    umma_bf16_ss(d_tmem, da, db, idesc, kh ? 1u : 0u);
+                    umma_bf16_ss(d_tmem, umma_desc_adv(da, 32), umma_desc_adv(db, 32), idesc, 1u);
+                }
+                umma_commit(empty + s);
+                umma_commit(acc_full + buf);
+                if (++s == S4_STAGES) {
+                    s = 0;
+                    ph ^= 1;
+                }
+            }
+        }
+    } else {
+        const int quarter = warp & 3;                 // TMEM lane quarter of this warp
+        const int row = quarter * 32 + lane;          // pixel (row >> 4, row & 15) of the tile
+        const uint32_t lane_off = uint32_t(quarter * 32) << 16;
+        const bool leader = tid == 64;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
+            const int buf = it & 1;
+            mbar_wait(acc_full + buf, (it >> 1) & 1);
+            tc_fence_after();
+            uint32_t acc[2][32];
+            tmem_ld_32x32b_x32(tmem_base + buf * 64 + lane_off, acc[0]);
+            tmem_ld_32x32b_x32(tmem_base + buf * 64 + lane_off + 32, acc[1]);
+            tmem_ld_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(acc_empty + buf);  // the MMA warp may overwrite this accumulator
+            // the staging tile `buf` was read by the store issued two tiles ago: the leader waited for it (below)
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            uint8_t* so = sOut + buf * S4_OUT_BYTES;
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    float f[8];
+#pragma unroll
+                    for (int t = 0; t < 8; ++t) f[t] = fmaxf(__uint_as_float(acc[h][q * 8 + t]) + sBias[h * 32 + q * 8 + t], 0.f);
+                    uint4 u;
+                    u.x = pack_bf16x2(f[0], f[1]);
+                    u.y = pack_bf16x2(f[2], f[3]);
+                    u.z = pack_bf16x2(f[4], f[5]);
+                    u.w = pack_bf16x2(f[6], f[7]);
+                    *reinterpret_cast<uint4*>(so + swz_off<128>(row, h * 4 + q)) = u;
+                }
+            fence_proxy_async_smem();
+            asm volatile("bar.sync 2, 128;" ::: "memory");
+            if (leader) {
+                const int tx = tile % p.tiles_x;
+                const int t2 = tile / p.tiles_x;
+                const int ty = t2 % p.tiles_y;
+                const int n = t2 / p.tiles_y;
+                tma_store_4d(&tmY, so, 0, tx * 16, ty * 8, n);
+                bulk_commit();
+                asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");  // the OTHER staging tile is free again
+            }
+        }
+        if (leader) bulk_wait0();
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc<128>(tmem_base);
+    }
+}
+
+}  // namespace fod
+
+extern "C" int fod_stem_conv7x7s2_p4(const void* x4p, const void* wk4, const float* bias, void* y, int32_t N, int32_t H,
+                                     int32_t W, void* stream) {
+    using namespace fod;
+    if (!x4p || !wk4 || !bias || !y || N <= 0 || H <= 0 || W <= 0) return fod_fail(FOD_E_ARG, "stem_conv_p4: null/empty");
+    if ((W % 8) || (H % 2)) return fod_fail(FOD_E_ARG, "stem_conv_p4: W must be a multiple of 8 and H even");
+    if ((reinterpret_cast<uintptr_t>(x4p) | reinterpret_cast<uintptr_t>(wk4) | reinterpret_cast<uintptr_t>(y)) & 15)
+        return fod_fail(FOD_E_ARG, "stem_conv_p4: x / wk / y must be 16-byte aligned");
+    const int OH = H / 2, OW = W / 2;
+    const long long pitch = (long long)(W + 8) * 8;  // bytes per padded image row
+    CUtensorMap tmX, tmY;
+    {
+        uint64_t dims[5] = {32, (uint64_t)OW, 2, (uint64_t)H / 2, (uint64_t)N};
+        uint64_t str[4] = {16, (uint64_t)pitch, 2ull * pitch, (uint64_t)H * pitch};
+        uint32_t box[5] = {32, 16, 1, (uint32_t)S4_BOX_ROWS, 1};
+        if (make_tmap_bf16(&tmX, x4p, 5, dims, str, box, 64)) return fod_fail(FOD_E_TMAP, "stem_conv_p4: tmap X");
+    }
+    {
+        uint64_t dims[4] = {64, (uint64_t)OW, (uint64_t)OH, (uint64_t)N};
+        uint64_t str[3] = {128, (uint64_t)OW * 128, (uint64_t)OH * OW * 128};
+        uint32_t box[4] = {64, 16, 8, 1};
+        if (make_tmap_bf16(&tmY, y, 4, dims, str, box, 128)) return fod_fail(FOD_E_TMAP, "stem_conv_p4: tmap Y");
+    }
+    Stem4Params p;
+    p.wk = reinterpret_cast<const __nv_bfloat16*>(wk4);
+    p.bias = bias;
+    p.tiles_x = (OW + 15) / 16;
+    p.tiles_y = (OH + 7) / 8;
+    const long long tiles = (long long)N * p.tiles_x * p.tiles_y;
+    if (tiles > 0x7fffffffLL) return fod_fail(FOD_E_ARG, "stem_conv_p4: too many tiles");
+    p.tiles = (int)tiles;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(stem_conv7x7s2_p4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S4_SMEM);
+        attr_set = true;
+    }
+    const int grid = (int)(tiles < 148 ? tiles : 148);
+    stem_conv7x7s2_p4_kernel<<<grid, S4_THREADS, S4_SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(tmX, tmY, p);
+    return fod_check_launch("stem_conv7x7s2_p4_kernel");
+}
+
+namespace fod {
 }  // namespace fod
 
 extern "C" int fod_stem_conv7x7s2(const void* x, const void* wk, const float* bias, void* y, int32_t N, int32_t H, int32_t W,

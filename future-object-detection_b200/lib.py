@@ -9,7 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfod_b200.so")
-ABI_VERSION = 11
+ABI_VERSION = 12
 
 FOD_OK, FOD_E_ARG, FOD_E_TMAP, FOD_E_LAUNCH, FOD_E_NUMERIC = 0, 1, 2, 3, 4
 
@@ -125,6 +125,8 @@ SYMBOLS = {
     "fod_frames_to_nhwc_bf16": (C.c_int, [_VP, _I64, _I64, _I32, _I32, _I32, _I32, _VP, _VP]),
     "fod_relu_bwd_add": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_stem_conv7x7s2": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),
+    "fod_stem_conv7x7s2_p4": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),
+    "fod_frames_to_nhwc4p_bf16": (C.c_int, [_VP, _I64, _I64, _I32, _I32, _I32, _I32, _VP, _VP]),
     "fod_fold_conv_weights": (C.c_int, [_VP, _I32, _I64, _VP]),
     "fod_conv_wgrad_unfold": (C.c_int, [_VP, _VP, _VP, _I32, _I32, _I32, _VP]),
     "fod_targets_compact": (C.c_int, [_VP, _VP, _VP, _VP, _VP, _VP, _VP, _I32, _I32, _F, _F, _VP]),

@@ -425,7 +425,21 @@ class CDetrBackbone(nn.Module):
         b = self.body
         pre = self._prefold(x)
         c1 = b["conv1"]
-        if (x.is_cuda and x.dtype == BF16 and not x.requires_grad and not c1.weight.requires_grad and c1.bias is None
+        padded = isinstance(x, ops.PaddedFrames)
+        if padded and (c1.weight.requires_grad or c1.bias is not None or tuple(c1.weight.shape) != (64, 3, 7, 7)
+                       or (c1.stride, c1.padding) != ((2, 2), (3, 3)) or x.h % 2):
+            x, padded = x.nchw().contiguous(memory_format=torch.channels_last), False  # not the frozen ResNet stem
+        if padded:
+            # frozen stem, operand tiles fetched by TMA from the padded 4-channel frames (csrc/stemconv_sm100.cu)
+            s1, t1 = b["bn1"].fold()
+            w1 = c1.weight
+            key = (w1._version, s1._version, t1._version, w1.data_ptr(), s1.data_ptr())
+            c = getattr(w1, "_fod_stem4", None)
+            if c is None or c[0] != key:
+                c = (key, ops.stem_weights4(w1, s1), t1.detach().float().contiguous())
+                w1._fod_stem4 = c
+            x = ops.stem_conv7x7s2_p4(x, c[1], c[2])
+        elif (x.is_cuda and x.dtype == BF16 and not x.requires_grad and not c1.weight.requires_grad and c1.bias is None
                 and tuple(c1.weight.shape) == (64, 3, 7, 7) and (c1.stride, c1.padding) == ((2, 2), (3, 3))
                 and x.shape[3] % 8 == 0 and x.is_contiguous(memory_format=torch.channels_last)):
             # frozen stem (paper.py:102-109): hand-written implicit-GEMM kernel, operands cached on the version counters
@@ -515,9 +529,14 @@ class CDetrBackbone(nn.Module):
 
     def forward_tokens(self, images):
         """(N,3,H,W) -> tokens (N*h*w, hidden) bf16 in (n, h, w) row order, plus (h, w)."""
-        x = images.contiguous(memory_format=torch.channels_last)
+        if isinstance(images, ops.PaddedFrames):
+            x = images if (self.fold_frozen_bn and self.compute_dtype == BF16) else images.nchw()
+        else:
+            x = images
+        if not isinstance(x, ops.PaddedFrames):
+            x = x.contiguous(memory_format=torch.channels_last)
         if self.fold_frozen_bn:
-            f = self._body_folded(x.to(self.compute_dtype))
+            f = self._body_folded(x if isinstance(x, ops.PaddedFrames) else x.to(self.compute_dtype))
         else:
             with torch.autocast("cuda", dtype=self.compute_dtype, enabled=self.compute_dtype != torch.float32):
                 f = self.body(x)["0"]

@@ -436,6 +436,38 @@ def frames_to_nhwc_bf16(video, frames=None):
     return out.permute(0, 3, 1, 2)  # logical (N, 3, H, W), channels-last strides
 
 
+class PaddedFrames:
+    """Frames in the layout the TMA stem convolution reads (fod_frames_to_nhwc4p_bf16): `buf` (N, H, W + 8, 4) bf16 with
+    pixel x at padded column x + 3, zero fourth channel and zero border columns.  `nchw()` is the plain (N, 3, H, W)
+    view of the same memory for every other consumer."""
+
+    def __init__(self, buf, h, w):
+        self.buf, self.h, self.w = buf, h, w
+        self.shape = (buf.shape[0], 3, h, w)
+        self.device, self.dtype, self.is_cuda, self.requires_grad = buf.device, buf.dtype, buf.is_cuda, False
+
+    def nchw(self):
+        return self.buf[:, :, 3:3 + self.w, :3].permute(0, 3, 1, 2)
+
+
+def frames_to_nhwc4p_bf16(video, frames=None):
+    """video (B, L, 3, H, W) fp32 with dense (3, H, W) frames -> PaddedFrames of the first `frames` (default L) frames of
+    every clip, in one pass."""
+    L = lib.load()
+    b, l, c, h, w = video.shape
+    t = l if frames is None else frames
+    assert video.dtype == torch.float32 and c == 3 and 0 < t <= l and video.stride()[2:] == (h * w, w, 1) and w % 8 == 0
+    out = torch.empty((b * t, h, w + 8, 4), dtype=BF16, device=video.device)
+    _t = prof.begin()
+    args = (_p(video), video.stride(0), video.stride(1), b, t, h, w, _p(out))
+    call = lambda: L.fod_frames_to_nhwc4p_bf16(*args, _stream())
+    lib.check(call(), "fod_frames_to_nhwc4p_bf16")
+    prof.end(_t, "frames_to_nhwc4p_%dx%dx%d" % (b * t, h, w), 0.0, (12.0 * w + 8.0 * (w + 8)) * b * t * h,
+             replay=call if _t is not None else None, keep=(video, out))
+    LAUNCH_COUNTS["frames_to_nhwc4p_bf16_kernel"] += 1
+    return PaddedFrames(out, h, w)
+
+
 def relu_bwd_add(a, b, y):
     """(a [+ b]) * (y > 0) in one pass; a, b, y bf16 CUDA tensors of one shape AND one memory layout (dense)."""
     L = lib.load()
@@ -462,6 +494,36 @@ def stem_weights(w, scale):
     wk = torch.zeros((64, 7, 24), dtype=torch.float32, device=w.device)
     wk[:, :, 1:22] = wf
     return torch.cat([wk.reshape(64, 168), torch.zeros((64, 24), device=w.device)], 1).to(BF16).contiguous()
+
+
+def stem_weights4(w, scale):
+    """(64,3,7,7) fp32 conv weight and (64) fold scale -> the (64,224) bf16 operand of fod_stem_conv7x7s2_p4:
+    [o][kh*32 + kw*4 + c] = w[o][c][kh][kw] * scale[o] (kw < 7, c < 3), zeros elsewhere."""
+    assert tuple(w.shape) == (64, 3, 7, 7)
+    wf = (w.detach().float() * scale.view(-1, 1, 1, 1)).permute(0, 2, 3, 1)  # [o][kh][kw][c]
+    wk = torch.zeros((64, 7, 8, 4), dtype=torch.float32, device=w.device)
+    wk[:, :, :7, :3] = wf
+    return wk.reshape(64, 224).to(BF16).contiguous()
+
+
+def stem_conv7x7s2_p4(frames, wk4, bias):
+    """relu(conv7x7/s2/p3(x, W·s) + t) for PaddedFrames -> channels_last (N,64,H/2,W/2); operand tiles by TMA."""
+    L = lib.load()
+    buf, h, w = frames.buf, frames.h, frames.w
+    _chk_bf16(buf, "stem x4p")
+    _chk_bf16(wk4, "stem wk4")
+    n = buf.shape[0]
+    assert buf.is_contiguous() and tuple(buf.shape) == (n, h, w + 8, 4) and w % 8 == 0 and h % 2 == 0
+    assert tuple(wk4.shape) == (64, 224) and wk4.is_contiguous() and bias.dtype == torch.float32 and bias.numel() == 64
+    oh, ow = h // 2, w // 2
+    y = torch.empty((n, 64, oh, ow), dtype=BF16, device=buf.device, memory_format=torch.channels_last)
+    _t = prof.begin()
+    call = lambda: L.fod_stem_conv7x7s2_p4(_p(buf), _p(wk4), _p(bias), _p(y), n, h, w, _stream())
+    lib.check(call(), "fod_stem_conv7x7s2_p4")
+    prof.end(_t, "stem_conv7x7s2_%dx%d" % (h, w), 2.0 * n * oh * ow * 64 * 147, 2.0 * (buf.numel() + y.numel()),
+             replay=call if _t is not None else None, keep=(buf, wk4, bias, y))
+    LAUNCH_COUNTS["stem_conv7x7s2_p4_kernel"] += 1
+    return y
 
 
 def stem_conv7x7s2(x, wk, bias):

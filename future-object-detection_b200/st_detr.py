@@ -81,7 +81,8 @@ class SeparateEncoder(nn.Module):
                 and images.stride()[2:] == (ih * iw, iw, 1) and images.stride(0) % 4 == 0 and images.stride(1) % 4 == 0
                 and (ih * iw) % 4 == 0 and images.data_ptr() % 16 == 0):
             # (B, T, 3, H, W) fp32 planar (possibly a frame slice of the loader's tensor) -> channels-last bf16 in one pass
-            frames = ops.frames_to_nhwc_bf16(images)
+            # (the padded 4-channel form feeds the TMA stem convolution; odd heights keep the 3-channel form)
+            frames = ops.frames_to_nhwc4p_bf16(images) if (ih % 2 == 0 and _STEM_P4) else ops.frames_to_nhwc_bf16(images)
         else:
             frames = images.flatten(0, 1)
         x, h, w = self.backbone.forward_tokens(frames)
@@ -392,6 +393,7 @@ class SpatioTemporalDETR(nn.Module):
 # Measured at 8 GPUs on one box: device-timed step unchanged (28.44 / 28.46 vs 28.52 / 28.47 ms), end-to-end
 # throughput WORSE (8 430 -> 7 070-7 740 clips/s: ranks that launch late now stall everyone at the first kernel), so
 # the reference's placement inside the criterion stays the default.
+_STEM_P4 = os.environ.get("FOD_STEM_P4", "1") != "0"  # 0: thread-assembled stem convolution (A/B switch)
 _EARLY_NUM_BOXES = int(os.environ.get("FOD_EARLY_NUM_BOXES", "0")) != 0
 
 

@@ -189,6 +189,10 @@ int fod_batch_sum(const void* x, void* out, int64_t G, int64_t n, void* stream);
  * planes are dense (H*W), W % 8 == 0.  One pass instead of torch's slice copy + channels_last copy + cast. */
 int fod_frames_to_nhwc_bf16(const float* video, int64_t stride_b, int64_t stride_t, int32_t B, int32_t T, int32_t H,
                             int32_t W, void* out, void* stream);
+/* The same frames in the layout fod_stem_conv7x7s2_p4 reads: out (B*T, H, W + 8, 4) bf16 — pixel x at padded column
+ * x + 3, the fourth channel and the 3 left / 5 right border columns zero (all written by this call).  W % 8 == 0. */
+int fod_frames_to_nhwc4p_bf16(const float* video, int64_t stride_b, int64_t stride_t, int32_t B, int32_t T, int32_t H,
+                              int32_t W, void* out, void* stream);
 
 /* Fused ReLU backward with an optional gradient add for the backbone's bottleneck blocks: out = (a [+ b]) * (y > 0) on
  * flat bf16 arrays of n elements with identical layouts (n % 8 == 0, 16-byte aligned).  Replaces autograd's gradient
@@ -202,6 +206,12 @@ int fod_relu_bwd_add(const void* a, const void* b /* or NULL */, const void* y, 
  * zeros elsewhere; bias (64) fp32 = folded shift; y (N,(H-1)/2+1,(W-1)/2+1,64) bf16 NHWC.  Implicit GEMM on tcgen05. */
 int fod_stem_conv7x7s2(const void* x, const void* wk, const float* bias, void* y, int32_t N, int32_t H, int32_t W,
                        void* stream);
+/* The same convolution with the operand tile fetched by TMA instead of assembled by the threads (same reference lines).
+ * x4p (N, H, W + 8, 4) bf16 as written by fod_frames_to_nhwc4p_bf16 (H even, W % 8 == 0); wk4 (64, 224) bf16 with
+ * wk4[o][kh*32 + kw*4 + c] = W[o][c][kh][kw]*scale[o] for kw < 7, c < 3 and zeros elsewhere; bias (64) fp32;
+ * y (N, H/2, W/2, 64) bf16 NHWC.  One overlapping-window tensor map yields the im2col rows of a kernel row directly. */
+int fod_stem_conv7x7s2_p4(const void* x4p, const void* wk4, const float* bias, void* y, int32_t N, int32_t H, int32_t W,
+                          void* stream);
 
 /* Frozen-BatchNorm folding of the trainable backbone convolutions (ConditionalDETR/models/backbone.py:53-63 applies
  * y = conv(x, W)*s + t with frozen s, t; the cuDNN conv runs on W*s).  One descriptor per conv, the table lives in

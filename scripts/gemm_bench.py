@@ -122,6 +122,38 @@ cases["attn_fwd 32x1400"] = _attn_case(32, 1400, False, False)
 cases["attn_bwd 32x1400"] = _attn_case(32, 1400, False, True)
 cases["relu_bwd_add3 183500800"] = _relu_case(183500800)
 
+
+def _stem_case(p4):
+    st = {}
+
+    def run():
+        if not st:
+            st["v"] = torch.randn(64, 1, 3, 448, 800, device=dev)
+            w, s_ = torch.randn(64, 3, 7, 7, device=dev) * 0.1, torch.rand(64, device=dev) + 0.5
+            st["t"] = torch.randn(64, device=dev)
+            if p4:
+                st["x"], st["w"] = ops.frames_to_nhwc4p_bf16(st["v"]), ops.stem_weights4(w, s_)
+            else:
+                st["x"], st["w"] = ops.frames_to_nhwc_bf16(st["v"]), ops.stem_weights(w, s_)
+        return (ops.stem_conv7x7s2_p4 if p4 else ops.stem_conv7x7s2)(st["x"], st["w"], st["t"])
+    return run
+
+
+def _frames_case(p4):
+    st = {}
+
+    def run():
+        if not st:
+            st["v"] = torch.randn(32, 3, 3, 448, 800, device=dev)
+        return (ops.frames_to_nhwc4p_bf16 if p4 else ops.frames_to_nhwc_bf16)(st["v"], frames=2)
+    return run
+
+
+cases["stem 64x448x800 threads"] = _stem_case(False)
+cases["stem 64x448x800 tma"] = _stem_case(True)
+cases["frames 64x448x800 nhwc3"] = _frames_case(False)
+cases["frames 64x448x800 nhwc4p"] = _frames_case(True)
+
 flops = {"2048x256": 2.0 * M * 2048 * 256, "768x256": 2.0 * M * 768 * 256, "256x256": 2.0 * M * 256 * 256,
          "256x2048": 2.0 * M * 2048 * 256}
 only = os.environ.get("GEMM_CASE")

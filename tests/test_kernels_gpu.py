@@ -436,3 +436,48 @@ def test_gemm_two_tiles_per_cta_path(M, K):
     # twice in a row on one stream: no stale barrier / TMEM state
     y2 = ops.gemm(x, w, bias=b, residual=res, res_row_mod=mod, ln=(gam, bet, 1e-5))
     assert torch.equal(y, y2)
+
+
+@pytest.mark.parametrize("B,L,H,W", [(2, 3, 64, 96), (1, 4, 448, 800), (3, 2, 30, 8)])
+def test_frames_to_nhwc4p_bf16_matches_torch(B, L, H, W):
+    """The padded 4-channel input layout of the TMA stem convolution: image pixels bit-equal to torch's cast, every
+    border column and the fourth channel zero (also on a buffer that held garbage: the kernel writes all of it)."""
+    from fod_b200 import ops
+    video = torch.randn(B, L, 3, H, W, device=_dev())
+    part = video[:, :-1] if L > 1 else video
+    junk = torch.full((part.shape[0] * part.shape[1] * H * (W + 8) * 4,), float("nan"), dtype=BF, device=_dev())
+    del junk  # the next allocation of this size reuses the block
+    pf = ops.frames_to_nhwc4p_bf16(part)
+    assert tuple(pf.buf.shape) == (part.shape[0] * part.shape[1], H, W + 8, 4)
+    assert torch.equal(pf.nchw(), part.flatten(0, 1).to(BF))
+    assert float(pf.buf[:, :, :3].abs().max()) == 0 and float(pf.buf[:, :, W + 3:].abs().max()) == 0
+    assert float(pf.buf[..., 3].abs().max()) == 0
+
+
+@pytest.mark.parametrize("N,H,W", [(2, 64, 80), (1, 448, 800), (3, 70, 88), (5, 2, 8), (2, 896, 1600)])
+def test_stem_conv7x7s2_tma_operand_form_matches_torch(N, H, W):
+    """fod_stem_conv7x7s2_p4 (operand tiles fetched by one overlapping-window tensor map, TMA store of the output tile)
+    == relu(conv2d(x, W*s) + t) of torch fp32 on the same bf16-rounded image and weights — ragged tiles on the right /
+    bottom (W/2 = 44, H/2 = 35), all four borders, more tiles than CTAs — and bit-equal to the thread-assembled kernel."""
+    from fod_b200 import ops
+    torch.manual_seed(22)
+    video = torch.randn(N, 1, 3, H, W, device="cuda")
+    pf = ops.frames_to_nhwc4p_bf16(video)
+    x = pf.nchw().contiguous(memory_format=torch.channels_last)
+    w = torch.randn(64, 3, 7, 7, device="cuda") * 0.1
+    s = torch.rand(64, device="cuda") + 0.5
+    t = torch.randn(64, device="cuda")
+    wk4 = ops.stem_weights4(w, s)
+    assert wk4.shape == (64, 224)
+    y = ops.stem_conv7x7s2_p4(pf, wk4, t)
+    wq = (w * s.view(-1, 1, 1, 1)).to(BF).float()
+    ref = torch.nn.functional.conv2d(x.float(), wq, t, stride=2, padding=3).relu()
+    assert y.shape == ref.shape and y.is_contiguous(memory_format=torch.channels_last)
+    _close(y, ref, what="stem conv (TMA operands)")
+    y_old = ops.stem_conv7x7s2(x, ops.stem_weights(w, s), t)
+    assert float((y.float() - y_old.float()).abs().max()) <= 2 ** -6 * float(ref.abs().max())  # same products, other summation order
+    pf.buf[:, :, 3:3 + W, :3] = 1.0
+    y1 = ops.stem_conv7x7s2_p4(pf, wk4, t)
+    ref1 = torch.nn.functional.conv2d(torch.ones_like(x).float(), wq, t, stride=2, padding=3).relu()
+    _close(y1, ref1, tol=1e-2, what="stem conv borders")
+    assert torch.equal(y1, ops.stem_conv7x7s2_p4(pf, wk4, t))  # second launch: no stale barrier / TMEM state
