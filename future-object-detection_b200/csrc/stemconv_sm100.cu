@@ -203,28 +203,70 @@ constexpr int S4_BOX_BYTES = S4_BOX_ROWS * 16 * 64;  // 11 KB: [11 half-rows][16
 constexpr int S4_A_BYTES = 2 * S4_BOX_BYTES;     // even-parity box (kernel rows 1,3,5) + odd-parity box (0,2,4,6)
 constexpr int S4_B_BYTES = 7 * 64 * 64;          // weights: 7 kernel rows x [64 out][32 k]
 constexpr int S4_OUT_BYTES = 128 * 128;          // staged output tile
-constexpr int S4_SMEM = S4_STAGES * S4_A_BYTES + S4_B_BYTES + 2 * S4_OUT_BYTES + 64 * 4 + 512 + 1024;
 constexpr int S4_THREADS = 192;
+// RAW form: the tile is 16 output rows x 8 pixels and shared memory holds the image half-rows AS THEY ARE (256 B each:
+// the 22 padded columns the 8 pixels touch, rounded up to the box), not their im2col expansion.  The expansion is done by
+// the MMA's own operand addressing: with the un-swizzled K-major layout a matrix descriptor places element (m, k) at
+//     start + (m / 8) * SBO + (m % 8) * 16 + (k / 8) * LBO + (k % 8) * 2   bytes,
+// and LBO = 16, SBO = 256 (one half-row per 8-pixel group) make that start + y * 256 + x * 16 + k * 2: the overlapping
+// 64-byte window of output pixel (y, x).  Two boxes of 19 half-rows per tile (9.5 KB instead of 22 KB, 38 row requests
+// of 256 B for the TMA unit instead of 352 of 64 B, which is what bounded the expanded form at ~1 500 clk per tile).
+constexpr int S4R_BOX_ROWS = 19;
+constexpr int S4R_ROW_BYTES = 256;
+constexpr int S4R_BOX_BYTES = S4R_BOX_ROWS * S4R_ROW_BYTES;
+constexpr int S4R_A_BYTES = 2 * S4R_BOX_BYTES;
 
 struct Stem4Params {
     const __nv_bfloat16* wk;  // (64, 224): [o][kh*32 + kw*4 + c] = W[o][c][kh][kw] * s[o] (kw < 7, c < 3), zeros elsewhere
     const float* bias;
+    __nv_bfloat16* pooled;    // POOL: (N, PH, PW, 64) output of the fused 3x3 / stride 2 / pad 1 max-pool
     int tiles_x, tiles_y, tiles;
+    int OH, OW, PH, PW;       // convolution / pooled output extents
 };
 
-__global__ void __launch_bounds__(S4_THREADS, 1)
+// POOL form (RAW tiles only): the max-pool that follows the stem (torchvision resnet `maxpool`, kernel 3, stride 2,
+// padding 1) is taken inside the epilogue, so the 64-channel convolution output — 128 B per pixel, 734 MB for the bench
+// step, whose WRITE alone costs 190 us at the 3.9 TB/s a B200 sustains for pure stores (scripts/bw_probe.py) — never
+// leaves the SM; only the pooled quarter of it does.  A tile of 16 x 8 convolution outputs that starts at an odd row and
+// column (14 ty - 1, 6 tx - 1) contains every input of a 7 x 3 block of pooled pixels: tiles overlap by two rows / columns
+// (21 pooled pixels from 128 convolution outputs, 1.5x the MMAs — still below what the store cost).  Convolution
+// positions outside the image are skipped in the maximum (everything kept is >= 0 after the ReLU).
+constexpr int S4P_PH = 7, S4P_PW = 3;
+
+// POOL runs TWO epilogue groups of four warps (tiles alternate between them, one TMEM accumulator and one staging tile
+// each): with the pooling pass the epilogue, not the MMAs, is the longest stage of a tile.
+template <bool POOL, int G> constexpr int s4_threads() { return POOL ? 64 + 128 * G : S4_THREADS; }
+template <bool RAW, bool POOL, int G> constexpr int s4_smem() {
+    // (the non-POOL forms request the expanded form's stage bytes either way: more than half an SM's shared memory, so the
+    // 148 persistent CTAs land one per SM — with the smaller RAW request two fit, some SMs got two and the launch took 288 us
+    // instead of 242)
+    return ((S4_STAGES * S4_A_BYTES + 1023) & ~1023) + S4_B_BYTES + (POOL ? G : 2) * S4_OUT_BYTES + 64 * 4 + 512 + 1024;
+}
+
+template <bool RAW, bool POOL, int G>
+__global__ void __launch_bounds__(s4_threads<POOL, G>(), 1)
 stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmY, const Stem4Params p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    constexpr int A_BYTES = RAW ? S4R_A_BYTES : S4_A_BYTES;
+    constexpr int BOX_BYTES = RAW ? S4R_BOX_BYTES : S4_BOX_BYTES;
+    constexpr int TW = RAW ? 8 : 16, TH = RAW ? 16 : 8;   // output tile (pixels x rows), M = 128 either way
+    static_assert(RAW || !POOL, "the fused max-pool works on the 16 x 8 tiles of the RAW form");
+    // first convolution row / column of tile (ty, tx)
+    constexpr int SY = POOL ? 2 * S4P_PH : TH, SX = POOL ? 2 * S4P_PW : TW, O0 = POOL ? -1 : 0;
     uint8_t* sA = smem;
-    uint8_t* sB = sA + S4_STAGES * S4_A_BYTES;
+    constexpr int NB = POOL ? G : 2;                      // TMEM accumulators (64 columns each) = staging tiles
+    constexpr int TCOLS = NB <= 2 ? 128 : 256;
+    static_assert(NB <= 4, "barrier block holds four accumulator barriers");
+    // (1 KB-aligned: the SWIZZLE_128B staging tiles follow; the non-POOL forms keep the expanded form's stage region)
+    uint8_t* sB = sA + ((S4_STAGES * S4_A_BYTES + 1023) & ~1023);
     uint8_t* sOut = sB + S4_B_BYTES;
-    float* sBias = reinterpret_cast<float*>(sOut + 2 * S4_OUT_BYTES);
+    float* sBias = reinterpret_cast<float*>(sOut + NB * S4_OUT_BYTES);
     uint64_t* full = reinterpret_cast<uint64_t*>(sBias + 64);
     uint64_t* empty = full + S4_STAGES;
     uint64_t* acc_full = empty + S4_STAGES;
-    uint64_t* acc_empty = acc_full + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+    uint64_t* acc_empty = acc_full + 4;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 4);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
@@ -234,15 +276,15 @@ stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
             mbar_init(full + s, 1);
             mbar_init(empty + s, 1);
         }
-        for (int b = 0; b < 2; ++b) {
+        for (int b = 0; b < NB; ++b) {
             mbar_init(acc_full + b, 1);
             mbar_init(acc_empty + b, 4);
         }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc<128>(tmem_slot);
+    if (warp == 1) tmem_alloc<TCOLS>(tmem_slot);
     // weights -> 7 swizzled [64][64 B] tiles (once per CTA); folded shift
-    for (int c = tid; c < 64 * 28; c += S4_THREADS) {
+    for (int c = tid; c < 64 * 28; c += s4_threads<POOL, G>()) {
         const int o = c / 28, ch = c - o * 28;  // 28 chunks of 8 k per output channel
         const uint4 v = __ldg(reinterpret_cast<const uint4*>(p.wk + (long long)o * 224) + ch);
         *reinterpret_cast<uint4*>(sB + (ch >> 2) * (64 * 64) + swz_off<64>(o, ch & 3)) = v;
@@ -264,10 +306,16 @@ stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
                 const int ty = t2 % p.tiles_y;
                 const int n = t2 / p.tiles_y;
                 mbar_wait(empty + s, ph ^ 1);
-                mbar_arrive_expect_tx(full + s, S4_A_BYTES);
+                mbar_arrive_expect_tx(full + s, A_BYTES);
                 // input row 2 oy - 3 + kh = 2 (oy + off) + par: kh = 1,3,5 -> par 0, off -1,0,1; kh = 0,2,4,6 -> par 1, off -2..1
-                tma_load_5d(sA + s * S4_A_BYTES, &tmX, full + s, 0, tx * 16, 0, ty * 8 - 1, n);
-                tma_load_5d(sA + s * S4_A_BYTES + S4_BOX_BYTES, &tmX, full + s, 0, tx * 16, 1, ty * 8 - 2, n);
+                if constexpr (RAW) {  // [element of the padded row][parity][row / 2][n]: 8 output pixels start at padded column 16 tx
+                    const int r0 = ty * SY + O0, c0 = tx * SX + O0;   // (padded column of output column c0: 2 c0, 4 channels each)
+                    tma_load_4d(sA + s * A_BYTES, &tmX, full + s, c0 * 8, 0, r0 - 1, n);
+                    tma_load_4d(sA + s * A_BYTES + BOX_BYTES, &tmX, full + s, c0 * 8, 1, r0 - 2, n);
+                } else {
+                    tma_load_5d(sA + s * A_BYTES, &tmX, full + s, 0, tx * TW, 0, ty * TH - 1, n);
+                    tma_load_5d(sA + s * A_BYTES + BOX_BYTES, &tmX, full + s, 0, tx * TW, 1, ty * TH - 2, n);
+                }
                 if (++s == S4_STAGES) {
                     s = 0;
                     ph ^= 1;
@@ -277,13 +325,14 @@ stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     } else if (warp == 1) {
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc_bf16(128, 64, 0, 0);
-            const uint64_t dA0 = umma_smem_desc(smem_u32(sA), 16, 512, 4);   // [128][64 B] SWIZZLE_64B, 8-row groups 512 B apart
+            // expanded form: [128][64 B] SWIZZLE_64B, 8-row groups 512 B apart; RAW: un-swizzled, LBO 16 / SBO 256 (see above)
+            const uint64_t dA0 = RAW ? umma_smem_desc(smem_u32(sA), 16, S4R_ROW_BYTES, 0) : umma_smem_desc(smem_u32(sA), 16, 512, 4);
             const uint64_t dB0 = umma_smem_desc(smem_u32(sB), 16, 512, 4);
             int s = 0, it = 0;
             uint32_t ph = 0;
             for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
-                const int buf = it & 1;
-                mbar_wait(acc_empty + buf, ((it >> 1) & 1) ^ 1);
+                const int buf = it % NB;
+                mbar_wait(acc_empty + buf, ((it / NB) & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + buf * 64;
                 mbar_wait(full + s, ph);
@@ -292,7 +341,7 @@ stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
                 for (int kh = 0; kh < 7; ++kh) {
                     // kernel row kh starts (kh >> 1) half-rows (1 KB each: 16 pixels x 64 B, a multiple of the 512-byte
                     // swizzle period) into the box of its parity
-                    const uint64_t da = umma_desc_adv(dA0, s * S4_A_BYTES + ((kh & 1) ? 0 : S4_BOX_BYTES) + (kh >> 1) * 1024);
+                    const uint64_t da = umma_desc_adv(dA0, s * A_BYTES + ((kh & 1) ? 0 : BOX_BYTES) + (kh >> 1) * (RAW ? S4R_ROW_BYTES : 1024));
                     const uint64_t db = umma_desc_adv(dB0, kh * (64 * 64));
                     umma_bf16_ss(d_tmem, da, db, idesc, kh ? 1u : 0u);
                     umma_bf16_ss(d_tmem, umma_desc_adv(da, 32), umma_desc_adv(db, 32), idesc, 1u);
@@ -307,13 +356,34 @@ stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
         }
     } else {
         const int quarter = warp & 3;                 // TMEM lane quarter of this warp
-        const int row = quarter * 32 + lane;          // pixel (row >> 4, row & 15) of the tile
+        const int row = quarter * 32 + lane;          // pixel (row / TW, row % TW) of the tile
         const uint32_t lane_off = uint32_t(quarter * 32) << 16;
         const bool leader = tid == 64;
-        int it = 0;
-        for (int tile = blockIdx.x; tile < p.tiles; tile += gridDim.x, ++it) {
-            const int buf = it & 1;
-            mbar_wait(acc_full + buf, (it >> 1) & 1);
+        constexpr int GROUPS = POOL ? G : 1;
+        const int group = (warp - 2) >> 2;            // 0 unless POOL
+        const int gtid = tid - 64 - group * 128;
+        const int bar_a = 1 + 2 * group, bar_b = 2 + 2 * group;
+        // POOL: this thread's (pooled pixel, 16-byte channel chunk) items — the same in every tile — with the nine staged
+        // addresses of each window precomputed
+        uint32_t p_off[2][9];
+        int p_rel[2], p_pr[2], p_pc[2];
+        bool p_on[2];
+        if constexpr (POOL) {
+#pragma unroll
+            for (int j = 0; j < 2; ++j) {
+                const int item = gtid + 128 * j, q = item & 7, pp = item >> 3;
+                p_on[j] = item < S4P_PH * S4P_PW * 8;
+                p_pr[j] = pp / S4P_PW;
+                p_pc[j] = pp - p_pr[j] * S4P_PW;
+#pragma unroll
+                for (int d = 0; d < 9; ++d)
+                    p_off[j][d] = p_on[j] ? swz_off<128>((2 * p_pr[j] + d / 3) * TW + 2 * p_pc[j] + d % 3, q) : 0u;
+                p_rel[j] = (p_pr[j] * p.PW + p_pc[j]) * 64 + q * 8;
+            }
+        }
+        for (int it = group, tile = blockIdx.x + group * gridDim.x; tile < p.tiles; tile += GROUPS * gridDim.x, it += GROUPS) {
+            const int buf = it % NB;                  // (POOL: == group)
+            mbar_wait(acc_full + buf, (it / NB) & 1);
             tc_fence_after();
             uint32_t acc[2][32];
             tmem_ld_32x32b_x32(tmem_base + buf * 64 + lane_off, acc[0]);
@@ -323,7 +393,7 @@ stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
             __syncwarp();
             if (lane == 0) mbar_arrive(acc_empty + buf);  // the MMA warp may overwrite this accumulator
             // the staging tile `buf` was read by the store issued two tiles ago: the leader waited for it (below)
-            asm volatile("bar.sync 1, 128;" ::: "memory");
+            asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
             uint8_t* so = sOut + buf * S4_OUT_BYTES;
 #pragma unroll
             for (int h = 0; h < 2; ++h)
@@ -339,14 +409,68 @@ stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
                     u.w = pack_bf16x2(f[6], f[7]);
                     *reinterpret_cast<uint4*>(so + swz_off<128>(row, h * 4 + q)) = u;
                 }
-            fence_proxy_async_smem();
+            if constexpr (!POOL) fence_proxy_async_smem();
+            if constexpr (POOL) {
+                asm volatile("bar.sync %0, 128;" ::"r"(bar_b) : "memory");  // the staged tile is complete
+                const int tx = tile % p.tiles_x;
+                const int t2 = tile / p.tiles_x;
+                const int ty = t2 % p.tiles_y;
+                const int n = t2 / p.tiles_y;
+                const int r0 = ty * SY + O0, c0 = tx * SX + O0;
+                const __nv_bfloat162 zero = __floats2bfloat162_rn(0.f, 0.f);
+                if (r0 >= 0 && r0 + 2 * S4P_PH < p.OH && c0 >= 0 && c0 + 2 * S4P_PW < p.OW && ty * S4P_PH + S4P_PH <= p.PH &&
+                    tx * S4P_PW + S4P_PW <= p.PW) {  // interior tile (CTA-uniform): every window complete
+                    __nv_bfloat16* blk = p.pooled + (((long long)n * p.PH + ty * S4P_PH) * p.PW + tx * S4P_PW) * 64;
+#pragma unroll
+                    for (int j = 0; j < 2; ++j) {
+                        if (!p_on[j]) continue;
+                        uint4 v[9];
+#pragma unroll
+                        for (int d = 0; d < 9; ++d) v[d] = *reinterpret_cast<const uint4*>(so + p_off[j][d]);
+                        __nv_bfloat162* hb = reinterpret_cast<__nv_bfloat162*>(&v[0]);
+#pragma unroll
+                        for (int d = 1; d < 9; ++d) {
+                            const __nv_bfloat162* hv = reinterpret_cast<const __nv_bfloat162*>(&v[d]);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) hb[e] = __hmax2(hb[e], hv[e]);
+                        }
+                        *reinterpret_cast<uint4*>(blk + p_rel[j]) = v[0];
+                    }
+                    continue;
+                }
+                for (int item = gtid; item < S4P_PH * S4P_PW * 8; item += 128) {
+                    const int q = item & 7, pp = item >> 3;
+                    const int pr = pp / S4P_PW, pc = pp - pr * S4P_PW;
+                    const int py = ty * S4P_PH + pr, px = tx * S4P_PW + pc;
+                    if (py >= p.PH || px >= p.PW) continue;
+                    uint4 best = make_uint4(0u, 0u, 0u, 0u);
+                    __nv_bfloat162* hb = reinterpret_cast<__nv_bfloat162*>(&best);
+                    hb[0] = hb[1] = hb[2] = hb[3] = zero;
+#pragma unroll
+                    for (int dy = 0; dy < 3; ++dy) {
+                        const int lr = 2 * pr + dy;
+                        if (r0 + lr < 0 || r0 + lr >= p.OH) continue;
+#pragma unroll
+                        for (int dx = 0; dx < 3; ++dx) {
+                            const int lc = 2 * pc + dx;
+                            if (c0 + lc < 0 || c0 + lc >= p.OW) continue;
+                            const uint4 v = *reinterpret_cast<const uint4*>(so + swz_off<128>(lr * TW + lc, q));
+                            const __nv_bfloat162* hv = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) hb[j] = __hmax2(hb[j], hv[j]);
+                        }
+                    }
+                    *reinterpret_cast<uint4*>(p.pooled + (((long long)n * p.PH + py) * p.PW + px) * 64 + q * 8) = best;
+                }
+                continue;  // (this group's next bar_a orders these reads before its staging tile is written again)
+            }
             asm volatile("bar.sync 2, 128;" ::: "memory");
             if (leader) {
                 const int tx = tile % p.tiles_x;
                 const int t2 = tile / p.tiles_x;
                 const int ty = t2 % p.tiles_y;
                 const int n = t2 / p.tiles_y;
-                tma_store_4d(&tmY, so, 0, tx * 16, ty * 8, n);
+                tma_store_4d(&tmY, so, 0, tx * TW, ty * TH, n);
                 bulk_commit();
                 asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");  // the OTHER staging tile is free again
             }
@@ -357,7 +481,7 @@ stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
     __syncthreads();
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc<128>(tmem_base);
+        tmem_dealloc<TCOLS>(tmem_base);
     }
 }
 
@@ -372,8 +496,15 @@ extern "C" int fod_stem_conv7x7s2_p4(const void* x4p, const void* wk4, const flo
         return fod_fail(FOD_E_ARG, "stem_conv_p4: x / wk / y must be 16-byte aligned");
     const int OH = H / 2, OW = W / 2;
     const long long pitch = (long long)(W + 8) * 8;  // bytes per padded image row
+    static const bool raw = [] { const char* e = getenv("FOD_STEM_RAW"); return e ? atoi(e) != 0 : true; }();
+    const int TW = raw ? 8 : 16, TH = raw ? 16 : 8;
     CUtensorMap tmX, tmY;
-    {
+    if (raw) {
+        uint64_t dims[4] = {(uint64_t)(W + 8) * 4, 2, (uint64_t)H / 2, (uint64_t)N};
+        uint64_t str[3] = {(uint64_t)pitch, 2ull * pitch, (uint64_t)H * pitch};
+        uint32_t box[4] = {S4R_ROW_BYTES / 2, 1, (uint32_t)S4R_BOX_ROWS, 1};
+        if (make_tmap_bf16(&tmX, x4p, 4, dims, str, box, 0)) return fod_fail(FOD_E_TMAP, "stem_conv_p4: tmap X (rows)");
+    } else {
         uint64_t dims[5] = {32, (uint64_t)OW, 2, (uint64_t)H / 2, (uint64_t)N};
         uint64_t str[4] = {16, (uint64_t)pitch, 2ull * pitch, (uint64_t)H * pitch};
         uint32_t box[5] = {32, 16, 1, (uint32_t)S4_BOX_ROWS, 1};
@@ -382,25 +513,73 @@ extern "C" int fod_stem_conv7x7s2_p4(const void* x4p, const void* wk4, const flo
     {
         uint64_t dims[4] = {64, (uint64_t)OW, (uint64_t)OH, (uint64_t)N};
         uint64_t str[3] = {128, (uint64_t)OW * 128, (uint64_t)OH * OW * 128};
-        uint32_t box[4] = {64, 16, 8, 1};
+        uint32_t box[4] = {64, (uint32_t)TW, (uint32_t)TH, 1};
         if (make_tmap_bf16(&tmY, y, 4, dims, str, box, 128)) return fod_fail(FOD_E_TMAP, "stem_conv_p4: tmap Y");
     }
     Stem4Params p;
     p.wk = reinterpret_cast<const __nv_bfloat16*>(wk4);
     p.bias = bias;
-    p.tiles_x = (OW + 15) / 16;
-    p.tiles_y = (OH + 7) / 8;
+    p.tiles_x = (OW + TW - 1) / TW;
+    p.tiles_y = (OH + TH - 1) / TH;
+    p.pooled = nullptr;
+    p.OH = OH; p.OW = OW; p.PH = p.PW = 0;
     const long long tiles = (long long)N * p.tiles_x * p.tiles_y;
     if (tiles > 0x7fffffffLL) return fod_fail(FOD_E_ARG, "stem_conv_p4: too many tiles");
     p.tiles = (int)tiles;
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(stem_conv7x7s2_p4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, S4_SMEM);
+        cudaFuncSetAttribute(stem_conv7x7s2_p4_kernel<true, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, s4_smem<true, false, 1>());
+        cudaFuncSetAttribute(stem_conv7x7s2_p4_kernel<false, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, s4_smem<false, false, 1>());
         attr_set = true;
     }
     const int grid = (int)(tiles < 148 ? tiles : 148);
-    stem_conv7x7s2_p4_kernel<<<grid, S4_THREADS, S4_SMEM, reinterpret_cast<cudaStream_t>(stream)>>>(tmX, tmY, p);
+    if (raw) stem_conv7x7s2_p4_kernel<true, false, 1><<<grid, S4_THREADS, s4_smem<true, false, 1>(), reinterpret_cast<cudaStream_t>(stream)>>>(tmX, tmY, p);
+    else stem_conv7x7s2_p4_kernel<false, false, 1><<<grid, S4_THREADS, s4_smem<false, false, 1>(), reinterpret_cast<cudaStream_t>(stream)>>>(tmX, tmY, p);
     return fod_check_launch("stem_conv7x7s2_p4_kernel");
+}
+
+extern "C" int fod_stem_conv_pool_p4(const void* x4p, const void* wk4, const float* bias, void* y, int32_t N, int32_t H,
+                                     int32_t W, void* stream) {
+    using namespace fod;
+    if (!x4p || !wk4 || !bias || !y || N <= 0 || H <= 0 || W <= 0) return fod_fail(FOD_E_ARG, "stem_conv_pool: null/empty");
+    if ((W % 8) || (H % 2)) return fod_fail(FOD_E_ARG, "stem_conv_pool: W must be a multiple of 8 and H even");
+    if ((reinterpret_cast<uintptr_t>(x4p) | reinterpret_cast<uintptr_t>(wk4) | reinterpret_cast<uintptr_t>(y)) & 15)
+        return fod_fail(FOD_E_ARG, "stem_conv_pool: x / wk / y must be 16-byte aligned");
+    const int OH = H / 2, OW = W / 2;
+    const long long pitch = (long long)(W + 8) * 8;
+    CUtensorMap tmX;
+    {
+        uint64_t dims[4] = {(uint64_t)(W + 8) * 4, 2, (uint64_t)H / 2, (uint64_t)N};
+        uint64_t str[3] = {(uint64_t)pitch, 2ull * pitch, (uint64_t)H * pitch};
+        uint32_t box[4] = {S4R_ROW_BYTES / 2, 1, (uint32_t)S4R_BOX_ROWS, 1};
+        if (make_tmap_bf16(&tmX, x4p, 4, dims, str, box, 0)) return fod_fail(FOD_E_TMAP, "stem_conv_pool: tmap X");
+    }
+    Stem4Params p;
+    p.wk = reinterpret_cast<const __nv_bfloat16*>(wk4);
+    p.bias = bias;
+    p.pooled = reinterpret_cast<__nv_bfloat16*>(y);
+    p.OH = OH; p.OW = OW;
+    p.PH = (OH - 1) / 2 + 1;
+    p.PW = (OW - 1) / 2 + 1;
+    p.tiles_x = (p.PW + S4P_PW - 1) / S4P_PW;
+    p.tiles_y = (p.PH + S4P_PH - 1) / S4P_PH;
+    const long long tiles = (long long)N * p.tiles_x * p.tiles_y;
+    if (tiles > 0x7fffffffLL) return fod_fail(FOD_E_ARG, "stem_conv_pool: too many tiles");
+    p.tiles = (int)tiles;
+    static const int groups = [] { const char* e = getenv("FOD_STEM_GROUPS"); return e ? atoi(e) : 3; }();
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(stem_conv7x7s2_p4_kernel<true, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, s4_smem<true, true, 2>());
+        cudaFuncSetAttribute(stem_conv7x7s2_p4_kernel<true, true, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, s4_smem<true, true, 3>());
+        cudaFuncSetAttribute(stem_conv7x7s2_p4_kernel<true, true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, s4_smem<true, true, 4>());
+        attr_set = true;
+    }
+    const int grid = (int)(tiles < 148 ? tiles : 148);
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+    if (groups == 2) stem_conv7x7s2_p4_kernel<true, true, 2><<<grid, s4_threads<true, 2>(), s4_smem<true, true, 2>(), st>>>(tmX, tmX, p);
+    else if (groups == 4) stem_conv7x7s2_p4_kernel<true, true, 4><<<grid, s4_threads<true, 4>(), s4_smem<true, true, 4>(), st>>>(tmX, tmX, p);
+    else stem_conv7x7s2_p4_kernel<true, true, 3><<<grid, s4_threads<true, 3>(), s4_smem<true, true, 3>(), st>>>(tmX, tmX, p);
+    return fod_check_launch("stem_conv_pool_p4_kernel");
 }
 
 namespace fod {

@@ -126,6 +126,7 @@ SYMBOLS = {
     "fod_relu_bwd_add": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_stem_conv7x7s2": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),
     "fod_stem_conv7x7s2_p4": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),
+    "fod_stem_conv_pool_p4": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),
     "fod_frames_to_nhwc4p_bf16": (C.c_int, [_VP, _I64, _I64, _I32, _I32, _I32, _I32, _VP, _VP]),
     "fod_fold_conv_weights": (C.c_int, [_VP, _I32, _I64, _VP]),
     "fod_conv_wgrad_unfold": (C.c_int, [_VP, _VP, _VP, _I32, _I32, _I32, _VP]),

@@ -16,6 +16,8 @@ dropout-free numerics, which is what the parity tests compare.
 """
 import math
 
+import os
+
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
@@ -425,6 +427,7 @@ class CDetrBackbone(nn.Module):
         b = self.body
         pre = self._prefold(x)
         c1 = b["conv1"]
+        pooled = False
         padded = isinstance(x, ops.PaddedFrames)
         if padded and (c1.weight.requires_grad or c1.bias is not None or tuple(c1.weight.shape) != (64, 3, 7, 7)
                        or (c1.stride, c1.padding) != ((2, 2), (3, 3)) or x.h % 2):
@@ -438,7 +441,11 @@ class CDetrBackbone(nn.Module):
             if c is None or c[0] != key:
                 c = (key, ops.stem_weights4(w1, s1), t1.detach().float().contiguous())
                 w1._fod_stem4 = c
-            x = ops.stem_conv7x7s2_p4(x, c[1], c[2])
+            mp = b["maxpool"]
+            if (mp.kernel_size, mp.stride, mp.padding) == (3, 2, 1) and _STEM_POOL:
+                x, pooled = ops.stem_conv_pool_p4(x, c[1], c[2]), True  # conv + bn + relu + maxpool, one kernel
+            else:
+                x = ops.stem_conv7x7s2_p4(x, c[1], c[2])
         elif (x.is_cuda and x.dtype == BF16 and not x.requires_grad and not c1.weight.requires_grad and c1.bias is None
                 and tuple(c1.weight.shape) == (64, 3, 7, 7) and (c1.stride, c1.padding) == ((2, 2), (3, 3))
                 and x.shape[3] % 8 == 0 and x.is_contiguous(memory_format=torch.channels_last)):
@@ -454,7 +461,9 @@ class CDetrBackbone(nn.Module):
         else:
             x = _conv_bn(x, c1, b["bn1"], True)
         mp = b["maxpool"]
-        if (not x.requires_grad and x.is_cuda and x.dtype == BF16 and (mp.kernel_size, mp.stride, mp.padding) == (3, 2, 1)
+        if pooled:
+            pass
+        elif (not x.requires_grad and x.is_cuda and x.dtype == BF16 and (mp.kernel_size, mp.stride, mp.padding) == (3, 2, 1)
                 and x.is_contiguous(memory_format=torch.channels_last)):
             x = ops.maxpool3x3s2_nhwc(x)  # frozen stem (paper.py:102-109): forward only, one HBM-bound kernel
         else:
@@ -553,6 +562,9 @@ class CDetrBackbone(nn.Module):
 
 
 # ------------------------------------------------------------------------------------------------ encoder
+_STEM_POOL = os.environ.get("FOD_STEM_POOL", "1") != "0"  # 0: stem convolution and max-pool as two kernels (A/B switch)
+
+
 class _InProjMHA(nn.Module):
     """Parameter holder with torch.nn.MultiheadAttention's names (transformer.py:404): packed in-proj + out_proj."""
 

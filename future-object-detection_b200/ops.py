@@ -526,6 +526,27 @@ def stem_conv7x7s2_p4(frames, wk4, bias):
     return y
 
 
+def stem_conv_pool_p4(frames, wk4, bias):
+    """maxpool3x3/s2/p1(relu(conv7x7/s2/p3(x, W·s) + t)) for PaddedFrames in ONE kernel -> channels_last (N,64,PH,PW)."""
+    L = lib.load()
+    buf, h, w = frames.buf, frames.h, frames.w
+    _chk_bf16(buf, "stem x4p")
+    _chk_bf16(wk4, "stem wk4")
+    n = buf.shape[0]
+    assert buf.is_contiguous() and tuple(buf.shape) == (n, h, w + 8, 4) and w % 8 == 0 and h % 2 == 0
+    assert tuple(wk4.shape) == (64, 224) and wk4.is_contiguous() and bias.dtype == torch.float32 and bias.numel() == 64
+    oh, ow = h // 2, w // 2
+    ph, pw = (oh - 1) // 2 + 1, (ow - 1) // 2 + 1
+    y = torch.empty((n, 64, ph, pw), dtype=BF16, device=buf.device, memory_format=torch.channels_last)
+    _t = prof.begin()
+    call = lambda: L.fod_stem_conv_pool_p4(_p(buf), _p(wk4), _p(bias), _p(y), n, h, w, _stream())
+    lib.check(call(), "fod_stem_conv_pool_p4")
+    prof.end(_t, "stem_conv_pool_%dx%d" % (h, w), 2.0 * n * oh * ow * 64 * 147, 2.0 * (buf.numel() + y.numel()),
+             replay=call if _t is not None else None, keep=(buf, wk4, bias, y))
+    LAUNCH_COUNTS["stem_conv_pool_p4_kernel"] += 1
+    return y
+
+
 def stem_conv7x7s2(x, wk, bias):
     """relu(conv7x7/s2/p3(x, W·s) + t) for a channels_last bf16 (N,3,H,W) image batch -> channels_last (N,64,OH,OW)."""
     L = lib.load()

@@ -212,6 +212,12 @@ int fod_stem_conv7x7s2(const void* x, const void* wk, const float* bias, void* y
  * y (N, H/2, W/2, 64) bf16 NHWC.  One overlapping-window tensor map yields the im2col rows of a kernel row directly. */
 int fod_stem_conv7x7s2_p4(const void* x4p, const void* wk4, const float* bias, void* y, int32_t N, int32_t H, int32_t W,
                           void* stream);
+/* The stem convolution AND the max-pool that follows it (torchvision resnet `maxpool`, kernel 3 / stride 2 / pad 1:
+ * ConditionalDETR/models/backbone.py:88-96; frozen, forward only: paper.py:102-109) in one kernel: the 64-channel
+ * convolution output stays on chip, y is the pooled (N, (H/2-1)/2+1, (W/2-1)/2+1, 64) bf16 NHWC tensor.  Operands as
+ * for fod_stem_conv7x7s2_p4.  Equal to fod_maxpool3x3s2_nhwc(fod_stem_conv7x7s2_p4(x)) bit for bit. */
+int fod_stem_conv_pool_p4(const void* x4p, const void* wk4, const float* bias, void* y, int32_t N, int32_t H, int32_t W,
+                          void* stream);
 
 /* Frozen-BatchNorm folding of the trainable backbone convolutions (ConditionalDETR/models/backbone.py:53-63 applies
  * y = conv(x, W)*s + t with frozen s, t; the cuDNN conv runs on W*s).  One descriptor per conv, the table lives in

@@ -151,6 +151,25 @@ def _frames_case(p4):
 
 cases["stem 64x448x800 threads"] = _stem_case(False)
 cases["stem 64x448x800 tma"] = _stem_case(True)
+
+
+def _stem_pool_case(fused):
+    st = {}
+
+    def run():
+        if not st:
+            st["v"] = torch.randn(64, 1, 3, 448, 800, device=dev)
+            w, s_ = torch.randn(64, 3, 7, 7, device=dev) * 0.1, torch.rand(64, device=dev) + 0.5
+            st["t"] = torch.randn(64, device=dev)
+            st["x"], st["w"] = ops.frames_to_nhwc4p_bf16(st["v"]), ops.stem_weights4(w, s_)
+        if fused:
+            return ops.stem_conv_pool_p4(st["x"], st["w"], st["t"])
+        return ops.maxpool3x3s2_nhwc(ops.stem_conv7x7s2_p4(st["x"], st["w"], st["t"]))
+    return run
+
+
+cases["stem+pool 64x448x800 two kernels"] = _stem_pool_case(False)
+cases["stem+pool 64x448x800 fused"] = _stem_pool_case(True)
 cases["frames 64x448x800 nhwc3"] = _frames_case(False)
 cases["frames 64x448x800 nhwc4p"] = _frames_case(True)
 

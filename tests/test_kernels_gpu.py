@@ -481,3 +481,26 @@ def test_stem_conv7x7s2_tma_operand_form_matches_torch(N, H, W):
     ref1 = torch.nn.functional.conv2d(torch.ones_like(x).float(), wq, t, stride=2, padding=3).relu()
     _close(y1, ref1, tol=1e-2, what="stem conv borders")
     assert torch.equal(y1, ops.stem_conv7x7s2_p4(pf, wk4, t))  # second launch: no stale barrier / TMEM state
+
+
+@pytest.mark.parametrize("N,H,W", [(2, 64, 80), (1, 448, 800), (3, 70, 88), (5, 2, 8), (2, 896, 1600), (1, 30, 16)])
+def test_stem_conv_with_fused_maxpool_equals_the_two_kernels(N, H, W):
+    """fod_stem_conv_pool_p4 (the 3x3 / stride 2 / pad 1 max-pool taken inside the convolution's epilogue, overlapping
+    16 x 8 tiles) is bit-equal to fod_maxpool3x3s2_nhwc(fod_stem_conv7x7s2_p4(x)) and matches torch fp32 — odd pooled
+    extents (18 x 22), a one-row image, all borders."""
+    from fod_b200 import ops
+    torch.manual_seed(23)
+    pf = ops.frames_to_nhwc4p_bf16(torch.randn(N, 1, 3, H, W, device="cuda"))
+    w = torch.randn(64, 3, 7, 7, device="cuda") * 0.1
+    s = torch.rand(64, device="cuda") + 0.5
+    t = torch.randn(64, device="cuda")
+    wk4 = ops.stem_weights4(w, s)
+    y = ops.stem_conv_pool_p4(pf, wk4, t)
+    two = ops.maxpool3x3s2_nhwc(ops.stem_conv7x7s2_p4(pf, wk4, t))
+    assert y.shape == two.shape and y.is_contiguous(memory_format=torch.channels_last)
+    assert torch.equal(y, two)
+    x = pf.nchw().float()
+    wq = (w * s.view(-1, 1, 1, 1)).to(BF).float()
+    ref = torch.nn.functional.max_pool2d(torch.nn.functional.conv2d(x, wq, t, stride=2, padding=3).relu(), 3, 2, 1)
+    _close(y, ref, what="stem conv + maxpool")
+    assert torch.equal(y, ops.stem_conv_pool_p4(pf, wk4, t))
