@@ -506,6 +506,7 @@ extern "C" int fod_frames_to_nhwc_bf16(const float* video, int64_t stride_b, int
 // the layout fod_stem_conv7x7s2_p4 reads through one overlapping-window tensor map (csrc/stemconv_sm100.cu).  One
 // thread writes 8 padded columns (64 contiguous bytes); every element of `out` is written, borders included.
 namespace fod {
+template <bool VEC>
 __global__ void __launch_bounds__(256)
 frames_to_nhwc4p_bf16_kernel(const float* __restrict__ video, long long stride_b, long long stride_t, int T, int H, int W,
                              __nv_bfloat16* __restrict__ out, long long groups) {
@@ -519,21 +520,35 @@ frames_to_nhwc4p_bf16_kernel(const float* __restrict__ video, long long stride_b
         const float* src = video + (n / T) * stride_b + (n % T) * stride_t + (long long)y * W;
         const int x0 = xg * 8 - 3;
         uint4* dst = reinterpret_cast<uint4*>(out + (r * (long long)(W + 8) + xg * 8) * 4);
+        float c[3][8];  // image columns x0 .. x0 + 7 of the three planes
+        if (VEC) {      // aligned 16-byte loads of columns [8 xg - 4, 8 xg + 8): the wanted eight are elements 1..8
+            const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {  // two pixels per 16-byte store
-            float f[2][3];
+            for (int ch = 0; ch < 3; ++ch) {
+                const float4* pl = reinterpret_cast<const float4*>(src + ch * hw + xg * 8);
+                const float4 a = xg > 0 ? __ldg(pl - 1) : z4;
+                const float4 b = xg * 8 < W ? __ldg(pl) : z4;
+                const float4 d = xg * 8 < W ? __ldg(pl + 1) : z4;
+                c[ch][0] = a.y; c[ch][1] = a.z; c[ch][2] = a.w;
+                c[ch][3] = b.x; c[ch][4] = b.y; c[ch][5] = b.z; c[ch][6] = b.w;
+                c[ch][7] = d.x;
+            }
+        } else {
 #pragma unroll
-            for (int i = 0; i < 2; ++i) {
-                const int x = x0 + 2 * q + i;
+            for (int i = 0; i < 8; ++i) {
+                const int x = x0 + i;
                 const bool ok = x >= 0 && x < W;
 #pragma unroll
-                for (int ch = 0; ch < 3; ++ch) f[i][ch] = ok ? __ldg(src + ch * hw + x) : 0.f;
+                for (int ch = 0; ch < 3; ++ch) c[ch][i] = ok ? __ldg(src + ch * hw + x) : 0.f;
             }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {  // two pixels per 16-byte store
             uint4 u;
-            u.x = pack_bf16x2(f[0][0], f[0][1]);
-            u.y = pack_bf16x2(f[0][2], 0.f);
-            u.z = pack_bf16x2(f[1][0], f[1][1]);
-            u.w = pack_bf16x2(f[1][2], 0.f);
+            u.x = pack_bf16x2(c[0][2 * q], c[1][2 * q]);
+            u.y = pack_bf16x2(c[2][2 * q], 0.f);
+            u.z = pack_bf16x2(c[0][2 * q + 1], c[1][2 * q + 1]);
+            u.w = pack_bf16x2(c[2][2 * q + 1], 0.f);
             dst[q] = u;
         }
     }
@@ -547,8 +562,13 @@ extern "C" int fod_frames_to_nhwc4p_bf16(const float* video, int64_t stride_b, i
     const long long groups = (long long)B * T * H * ((W + 8) / 8);
     long long blocks = (groups + 255) / 256;
     if (blocks > 148LL * 16) blocks = 148LL * 16;
-    fod::frames_to_nhwc4p_bf16_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
-        video, stride_b, stride_t, T, H, W, reinterpret_cast<__nv_bfloat16*>(out), groups);
+    const bool vec = !(stride_b % 4) && !(stride_t % 4) && !(((long long)H * W) % 4) && !(reinterpret_cast<uintptr_t>(video) & 15);
+    if (vec)
+        fod::frames_to_nhwc4p_bf16_kernel<true><<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+            video, stride_b, stride_t, T, H, W, reinterpret_cast<__nv_bfloat16*>(out), groups);
+    else
+        fod::frames_to_nhwc4p_bf16_kernel<false><<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+            video, stride_b, stride_t, T, H, W, reinterpret_cast<__nv_bfloat16*>(out), groups);
     return fod::fod_check_launch("frames_to_nhwc4p_bf16_kernel");
 }
 

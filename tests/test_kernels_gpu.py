@@ -452,6 +452,11 @@ def test_frames_to_nhwc4p_bf16_matches_torch(B, L, H, W):
     assert torch.equal(pf.nchw(), part.flatten(0, 1).to(BF))
     assert float(pf.buf[:, :, :3].abs().max()) == 0 and float(pf.buf[:, :, W + 3:].abs().max()) == 0
     assert float(pf.buf[..., 3].abs().max()) == 0
+    # a clip tensor that is only 4-byte aligned takes the scalar-load variant of the kernel
+    flat = torch.randn(part.numel() + 1, device=_dev())
+    odd = flat[1:].view(part.shape)
+    assert odd.data_ptr() % 16 != 0
+    assert torch.equal(ops.frames_to_nhwc4p_bf16(odd).nchw(), odd.flatten(0, 1).to(BF))
 
 
 @pytest.mark.parametrize("N,H,W", [(2, 64, 80), (1, 448, 800), (3, 70, 88), (5, 2, 8), (2, 896, 1600)])
