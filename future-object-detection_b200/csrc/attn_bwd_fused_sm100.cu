@@ -79,7 +79,9 @@ struct AttnBwdFusedParams {
     int B, H, Lq, Lk;
     int bm_q1, bm_k1, bm_q2, bm_k2, bm_v;
     float scale;
-    DropoutCfg drop;             // DROP kernels: the forward call's dropout on P, regenerated here
+    DropoutCfg drop;             // DROP kernels: the forward call's dropout on P, regenerated here (DROP == 1)
+    const uint8_t* keep_bits;    // ... or read from the bits the forward call used (DROP == 2, fod_attn_keep_bits)
+    long long keep_pitch;
     // Query groups (grid.z > 1, one-part attention longer than kMaxQT query tiles): CTA z owns query tiles
     // [z*kMaxQT, z*kMaxQT + kMaxQT) and ALL key tiles.  dQ is complete per CTA; dK / dV are partial sums over the
     // group's queries and are reduced with fp32 vector atomics into these (B,H,Lk,32) workspaces (zeroed by the host
@@ -131,7 +133,7 @@ __device__ __forceinline__ void af_red_tile(uint32_t taddr_lane, float* ws_row, 
 
 // DROP: out = dropout(P)·V in the forward pass (mask m, scale c = 1/(1-p)): dV takes P·m·c, dP = (dO·Vᵀ)·m·c, and
 // dS = P ⊙ (dP − delta) with the UNdropped P; delta = rowsum(dO ⊙ O) is unchanged.
-template <int NP, bool DROP>
+template <int NP, int DROP>
 __global__ void __launch_bounds__(AF_THREADS, 1)
 attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant__ CUtensorMap tmK1,
                       const __grid_constant__ CUtensorMap tmQ2, const __grid_constant__ CUtensorMap tmK2,
@@ -396,7 +398,7 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
 
         uint32_t vs[32], vp[32];
         PhiloxKey key = {0u, 0u, 0u, 0u};
-        if (DROP) key = dropout_key(p.drop);
+        if (DROP == 1) key = dropout_key(p.drop);
         const unsigned long long lkp8 = (unsigned long long)((p.Lk + 7) >> 3);  // Philox groups per (padded) score row
         for (int t = 0; t < ntiles; ++t) {
             const int j = t / nqt, i = t - j * nqt;
@@ -405,6 +407,11 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
             const unsigned long long g_row =
                 (((unsigned long long)b * p.H + h) * p.Lq + (unsigned long long)min((qt0 + i) * AF_T + row, p.Lq - 1)) * lkp8;
             const int kvalid = p.Lk - j * AF_T;  // >= 1
+            uint2 kb2 = make_uint2(0u, 0u);      // DROP == 2: the 64 keep bits of this thread's two 32-column chunks
+            if (DROP == 2)
+                kb2 = __ldg(reinterpret_cast<const uint2*>(
+                                p.keep_bits + (((long long)b * p.H + h) * p.Lq + min((qt0 + i) * AF_T + row, p.Lq - 1)) * p.keep_pitch) +
+                            j * 2 + half);
             if (threadIdx.x == 0) AF_STAMP(0, t, 0);
             mbar_wait(s_full, t & 1);
             tc_fence_after();
@@ -427,11 +434,14 @@ attn_bwd_fused_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_con
                 if (DROP) {
 #pragma unroll
                     for (int qd = 0; qd < 4; ++qd) {
-                        const Keep8 keep = dropout_draw8(key, g_row + (unsigned long long)(j * (AF_T / 8) + c * 4 + qd), p.drop.thresh);
+                        Keep8 keep = {{0u, 0u, 0u, 0u}, 0u};
+                        if (DROP == 1) keep = dropout_draw8(key, g_row + (unsigned long long)(j * (AF_T / 8) + c * 4 + qd), p.drop.thresh);
+                        const uint32_t kw = (cc == 0 ? kb2.x : kb2.y) >> (8 * qd);
 #pragma unroll
                         for (int e = 0; e < 8; ++e) {
                             const int idx = qd * 8 + e;
-                            const float mk = keep[e] ? p.drop.scale : 0.f;
+                            const bool kept = DROP == 1 ? keep[e] : ((kw >> e) & 1u) != 0u;
+                            const float mk = kept ? p.drop.scale : 0.f;
                             const float x = fast_exp2(fmaf(__uint_as_float(vs[idx]), sl2, -lse2));
                             const float g = fmaf(__uint_as_float(vp[idx]) * mk, p.scale, -dlt);
                             vs[idx] = __float_as_uint(x * mk);  // dropout(P): the operand of dV
@@ -634,6 +644,8 @@ int launch_attn_bwd_fused(const fod_attn_bwd_args* g, cudaStream_t st) {
     p.bm_v = has_b(a->bsv);
     p.scale = a->scale;
     p.drop = {nullptr, 0u, 0u, 1.f};
+    p.keep_bits = nullptr;
+    p.keep_pitch = 0;
     const bool drop = a->drop.rng_state && a->drop.p > 0.f;
     if (drop) {
         if (!(a->drop.p < 1.f)) return fod_fail(FOD_E_ARG, "attn_bwd: dropout p must be in [0, 1)");
@@ -641,7 +653,14 @@ int launch_attn_bwd_fused(const fod_attn_bwd_args* g, cudaStream_t st) {
         p.drop.call = (unsigned int)a->drop.call;
         p.drop.thresh = (unsigned int)(a->drop.p * 65536.f + 0.5f);
         p.drop.scale = 1.f / (1.f - a->drop.p);
+        if (a->keep_bits) {
+            if ((a->keep_pitch % 16) || a->keep_pitch < 16LL * ((a->Lk + AF_T - 1) / AF_T) || (reinterpret_cast<uintptr_t>(a->keep_bits) & 15))
+                return fod_fail(FOD_E_ARG, "attn_bwd: keep_bits needs a 16-byte aligned base and pitch >= 16 * ceil(Lk / 128), pitch % 16 == 0");
+            p.keep_bits = reinterpret_cast<const uint8_t*>(a->keep_bits);
+            p.keep_pitch = a->keep_pitch;
+        }
     }
+    const bool bits = p.keep_bits != nullptr;
     const int nqt_all = (a->Lq + AF_T - 1) / AF_T;
     const int groups = two ? 1 : (nqt_all + FusedBwdSmem<1>::kMaxQT - 1) / FusedBwdSmem<1>::kMaxQT;
     p.ws_dk = p.ws_dv = nullptr;
@@ -659,13 +678,15 @@ int launch_attn_bwd_fused(const fod_attn_bwd_args* g, cudaStream_t st) {
         }
         fod_launch(kernel, grid, dim3(AF_THREADS), (size_t)smem_bytes, st, tq1, tk1, tq2, tk2, tv, tdo, tdq1, tdq2, tdk1, tdk2, tdv, p);
     };
-    static bool attr[4] = {false, false, false, false};
+    static bool attr[6] = {false, false, false, false, false, false};
     if (two) {
-        if (drop) launch(attn_bwd_fused_kernel<2, true>, FusedBwdSmem<2>::kTotal, attr[3]);
-        else launch(attn_bwd_fused_kernel<2, false>, FusedBwdSmem<2>::kTotal, attr[2]);
+        if (drop && bits) launch(attn_bwd_fused_kernel<2, 2>, FusedBwdSmem<2>::kTotal, attr[5]);
+        else if (drop) launch(attn_bwd_fused_kernel<2, 1>, FusedBwdSmem<2>::kTotal, attr[3]);
+        else launch(attn_bwd_fused_kernel<2, 0>, FusedBwdSmem<2>::kTotal, attr[2]);
     } else {
-        if (drop) launch(attn_bwd_fused_kernel<1, true>, FusedBwdSmem<1>::kTotal, attr[1]);
-        else launch(attn_bwd_fused_kernel<1, false>, FusedBwdSmem<1>::kTotal, attr[0]);
+        if (drop && bits) launch(attn_bwd_fused_kernel<1, 2>, FusedBwdSmem<1>::kTotal, attr[4]);
+        else if (drop) launch(attn_bwd_fused_kernel<1, 1>, FusedBwdSmem<1>::kTotal, attr[1]);
+        else launch(attn_bwd_fused_kernel<1, 0>, FusedBwdSmem<1>::kTotal, attr[0]);
     }
     int rc = fod_check_launch("attn_bwd_fused_kernel");
     if (rc || groups == 1) return rc;

@@ -74,12 +74,14 @@ struct AttnParams {
     float scale_log2;                      // scale * log2(e)
     float scale;
     DropoutCfg drop;                       // DROP kernels: dropout on the softmax weights (attention.py:370)
+    const uint8_t* keep_bits;              // DROP == 2: the keep decisions, precomputed (fod_attn_keep_bits)
+    long long keep_pitch;                  // bytes per (b, h, q) row: 16 per 128-key tile
 };
 
 // DROP: train-mode dropout on P.  out = dropout(P)·V / sum(P): the row sums must be those of the UNdropped weights, so
 // they are accumulated in a register of the row's thread instead of by the [V | ones] MMA (whose L block then holds the
 // dropped sums and is ignored).  Mask element index: ((b*H + h)*Lq + q) * roundup8(Lk) + k.
-template <int NPARTS, bool DROP>
+template <int NPARTS, int DROP>  // DROP: 0 none, 1 masks drawn here (Philox), 2 masks read from keep_bits
 __global__ void __launch_bounds__(AT_THREADS, 2)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant__ CUtensorMap tmK1,
                 const __grid_constant__ CUtensorMap tmQ2, const __grid_constant__ CUtensorMap tmK2,
@@ -227,13 +229,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
         float l_reg = 0.f;         // DROP: running sum of the undropped weights of this row
         PhiloxKey key = {0u, 0u, 0u, 0u};
         unsigned long long g_row = 0;
-        if (DROP) {
+        const uint4* bits_row = nullptr;
+        if (DROP == 1) {
             key = dropout_key(p.drop);
             const unsigned long long lkp = (unsigned long long)((p.Lk + 7) & ~7);
             g_row = ((((unsigned long long)b * p.H + h) * p.Lq + (unsigned long long)min(q0 + row, p.Lq - 1)) * lkp) >> 3;
         }
+        if (DROP == 2)
+            bits_row = reinterpret_cast<const uint4*>(
+                p.keep_bits + (((long long)b * p.H + h) * p.Lq + min(q0 + row, p.Lq - 1)) * p.keep_pitch);
         uint32_t v[4][32];
         for (int j = 0; j < nkt; ++j) {
+            uint4 kb = make_uint4(0u, 0u, 0u, 0u);
+            if (DROP == 2) kb = __ldg(bits_row + j);  // 128 keep bits of this row and key tile (in flight during the wait)
             mbar_wait(s_full, j & 1);
             tc_fence_after();
 #pragma unroll
@@ -309,9 +317,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ1, const __grid_constant_
                     if (DROP) {
                         l_reg += ((e[0] + e[1]) + (e[2] + e[3])) + ((e[4] + e[5]) + (e[6] + e[7]));
                         // dropped weights are zeroed here; the 1/(1-p) of the kept ones is folded into the final 1/l
-                        const Keep8 keep = dropout_draw8(key, g_row + (unsigned long long)(j * (AT_BN / 8) + c * 4 + q), p.drop.thresh);
+                        if (DROP == 1) {
+                            const Keep8 keep = dropout_draw8(key, g_row + (unsigned long long)(j * (AT_BN / 8) + c * 4 + q), p.drop.thresh);
 #pragma unroll
-                        for (int t = 0; t < 8; ++t) e[t] = keep[t] ? e[t] : 0.f;
+                            for (int t = 0; t < 8; ++t) e[t] = keep[t] ? e[t] : 0.f;
+                        } else {
+                            const uint32_t kw = (c == 0 ? kb.x : c == 1 ? kb.y : c == 2 ? kb.z : kb.w) >> (8 * q);
+#pragma unroll
+                            for (int t = 0; t < 8; ++t) e[t] = (kw & (1u << t)) ? e[t] : 0.f;
+                        }
                     }
                     uint4 u;
                     u.x = pack_bf16x2(e[0], e[1]);
@@ -429,6 +443,8 @@ extern "C" int fod_attn_fwd(const fod_attn_args* a, void* stream) {
     p.scale = a->scale;
     p.scale_log2 = a->scale * 1.4426950408889634f;
     p.drop = {nullptr, 0u, 0u, 1.f};
+    p.keep_bits = nullptr;
+    p.keep_pitch = 0;
     const bool drop = a->drop.rng_state && a->drop.p > 0.f;
     if (drop) {
         if (!(a->drop.p < 1.f)) return fod_fail(FOD_E_ARG, "attn: dropout p must be in [0, 1)");
@@ -436,7 +452,14 @@ extern "C" int fod_attn_fwd(const fod_attn_args* a, void* stream) {
         p.drop.call = (unsigned int)a->drop.call;
         p.drop.thresh = (unsigned int)(a->drop.p * 65536.f + 0.5f);
         p.drop.scale = 1.f / (1.f - a->drop.p);
+        if (a->keep_bits) {
+            if ((a->keep_pitch % 16) || a->keep_pitch < 16LL * ((a->Lk + AT_BN - 1) / AT_BN) || (reinterpret_cast<uintptr_t>(a->keep_bits) & 15))
+                return fod_fail(FOD_E_ARG, "attn: keep_bits needs a 16-byte aligned base and pitch >= 16 * ceil(Lk / 128), pitch % 16 == 0");
+            p.keep_bits = reinterpret_cast<const uint8_t*>(a->keep_bits);
+            p.keep_pitch = a->keep_pitch;
+        }
     }
+    const bool bits = p.keep_bits != nullptr;
     cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
     dim3 grid((a->Lq + AT_BM - 1) / AT_BM, a->H, a->B);
     auto launch = [&](auto kernel, int smem_bytes, bool& attr_done) {
@@ -446,13 +469,60 @@ extern "C" int fod_attn_fwd(const fod_attn_args* a, void* stream) {
         }
         fod_launch(kernel, grid, dim3(AT_THREADS), (size_t)smem_bytes, st, tq1, tk1, tq2, tk2, tv, p);
     };
-    static bool attr[4] = {false, false, false, false};
+    static bool attr[6] = {false, false, false, false, false, false};
     if (two) {
-        if (drop) launch(attn_fwd_kernel<2, true>, AttnSmem<2>::kTotal, attr[3]);
-        else launch(attn_fwd_kernel<2, false>, AttnSmem<2>::kTotal, attr[2]);
+        if (drop && bits) launch(attn_fwd_kernel<2, 2>, AttnSmem<2>::kTotal, attr[5]);
+        else if (drop) launch(attn_fwd_kernel<2, 1>, AttnSmem<2>::kTotal, attr[3]);
+        else launch(attn_fwd_kernel<2, 0>, AttnSmem<2>::kTotal, attr[2]);
     } else {
-        if (drop) launch(attn_fwd_kernel<1, true>, AttnSmem<1>::kTotal, attr[1]);
-        else launch(attn_fwd_kernel<1, false>, AttnSmem<1>::kTotal, attr[0]);
+        if (drop && bits) launch(attn_fwd_kernel<1, 2>, AttnSmem<1>::kTotal, attr[4]);
+        else if (drop) launch(attn_fwd_kernel<1, 1>, AttnSmem<1>::kTotal, attr[1]);
+        else launch(attn_fwd_kernel<1, 0>, AttnSmem<1>::kTotal, attr[0]);
     }
     return fod_check_launch("attn_fwd_kernel");
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Keep decisions of the softmax-weight dropout for one attention call, drawn once (forward and backward read them):
+// word w of a row covers keys [32 w, 32 w + 32) = Philox groups 4 w .. 4 w + 3 of that row, byte i of the word = group
+// 4 w + i, bit t = element t of the group — the lane order of dropout_keep8 / Keep8 (csrc/dropout.cuh).
+namespace fod {
+__global__ void __launch_bounds__(256)
+attn_keep_bits_kernel(DropoutCfg d, long long rows, int lkp8, int words, uint32_t* __restrict__ out) {
+    const PhiloxKey key = dropout_key(d);
+    const long long total = rows * words;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+        const long long r = i / words;
+        const int w = (int)(i - r * words);
+        uint32_t m = 0;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+            const int grp = 4 * w + g;
+            if (grp < lkp8) m |= dropout_keep8(key, (unsigned long long)r * lkp8 + grp, d.thresh) << (8 * g);
+        }
+        out[i] = m;
+    }
+}
+}  // namespace fod
+
+extern "C" int fod_attn_keep_bits(const void* rng_state, int32_t call, float p, int64_t rows, int32_t Lk, void* out,
+                                  int64_t pitch, void* stream) {
+    using namespace fod;
+    if (!rng_state || !out || rows <= 0 || Lk <= 0) return fod_fail(FOD_E_ARG, "attn_keep_bits: null/empty");
+    if (!(p > 0.f) || !(p < 1.f)) return fod_fail(FOD_E_ARG, "attn_keep_bits: p must be in (0, 1)");
+    if ((pitch % 16) || pitch < 16LL * ((Lk + 127) / 128) || (reinterpret_cast<uintptr_t>(out) & 15))
+        return fod_fail(FOD_E_ARG, "attn_keep_bits: 16-byte aligned out, pitch % 16 == 0, pitch >= 16 * ceil(Lk / 128)");
+    DropoutCfg d;
+    d.state = reinterpret_cast<const unsigned long long*>(rng_state);
+    d.call = (unsigned int)call;
+    d.thresh = (unsigned int)(p * 65536.f + 0.5f);
+    d.scale = 1.f / (1.f - p);
+    const int words = (int)(pitch / 4);
+    const long long total = rows * words;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148LL * 16) blocks = 148LL * 16;
+    attn_keep_bits_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(d, rows, (Lk + 7) >> 3, words,
+                                                                                          reinterpret_cast<uint32_t*>(out));
+    return fod_check_launch("attn_keep_bits_kernel");
 }

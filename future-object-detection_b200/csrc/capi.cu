@@ -31,5 +31,5 @@ int fod_env_int(const char* name, int dflt) {
 }
 }  // namespace fod
 
-extern "C" int fod_version(void) { return 12; }
+extern "C" int fod_version(void) { return 13; }
 extern "C" const char* fod_last_error(void) { return fod::g_err; }

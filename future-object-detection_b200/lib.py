@@ -9,7 +9,7 @@ import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libfod_b200.so")
-ABI_VERSION = 12
+ABI_VERSION = 13
 
 FOD_OK, FOD_E_ARG, FOD_E_TMAP, FOD_E_LAUNCH, FOD_E_NUMERIC = 0, 1, 2, 3, 4
 
@@ -46,7 +46,7 @@ class AttnArgs(C.Structure):
         ("bsq1", C.c_int64), ("bsk1", C.c_int64), ("bsq2", C.c_int64), ("bsk2", C.c_int64), ("bsv", C.c_int64),
         ("bso", C.c_int64),
         ("B", C.c_int32), ("H", C.c_int32), ("Lq", C.c_int32), ("Lk", C.c_int32), ("scale", C.c_float),
-        ("pad0", C.c_int32), ("drop", Dropout),
+        ("pad0", C.c_int32), ("drop", Dropout), ("keep_bits", C.c_void_p), ("keep_pitch", C.c_int64),
     ]
 
 
@@ -126,6 +126,7 @@ SYMBOLS = {
     "fod_relu_bwd_add": (C.c_int, [_VP, _VP, _VP, _VP, _I64, _VP]),
     "fod_stem_conv7x7s2": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),
     "fod_stem_conv7x7s2_p4": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),
+    "fod_attn_keep_bits": (C.c_int, [_VP, _I32, C.c_float, _I64, _I32, _VP, _I64, _VP]),
     "fod_stem_conv_pool_p4": (C.c_int, [_VP, _VP, _VP, _VP, _I32, _I32, _I32, _VP]),
     "fod_frames_to_nhwc4p_bf16": (C.c_int, [_VP, _I64, _I64, _I32, _I32, _I32, _I32, _VP, _VP]),
     "fod_fold_conv_weights": (C.c_int, [_VP, _I32, _I64, _VP]),

@@ -8,6 +8,8 @@ import collections
 import ctypes as C
 import math
 
+import os
+
 import torch
 
 from . import lib
@@ -25,6 +27,8 @@ BF16 = torch.bfloat16
 _RNG = {}
 _CALL = [0]
 _SNAP = [None]
+_BITS_USED = []   # attention keep-bit keys of the current forward pass, in call order
+_BITS_SIDE = {}   # device -> stream the keep bits of a pass are drawn on
 
 
 def rng_state(device):
@@ -40,7 +44,7 @@ def set_dropout_seed(seed, device="cuda"):
     st.copy_(torch.tensor([int(seed), 0], dtype=torch.int64))
 
 
-def begin_forward():
+def begin_forward(training=False):
     """Start of a model forward pass (FuturePredCore.forward): dropout call ids restart at 1, and the first dropout
     site of the pass advances the device-side step counter and takes a SNAPSHOT of {seed, step}, so every pass — and
     every replay of a captured graph — draws fresh masks.  The snapshot travels with each site's (p, call id) into the
@@ -48,6 +52,34 @@ def begin_forward():
     passes (gradient accumulation) without mixing up masks."""
     _CALL[0] = 0
     _SNAP[0] = None
+    # attention keep bits (see _attn_keep_bits): what the previous forward pass needed is drawn for THIS pass up front, on a
+    # side stream, where it overlaps the backbone instead of sitting in front of every attention kernel
+    plan = list(_BITS_USED)
+    del _BITS_USED[:]
+    if training and plan and _ATTN_BITS and _BITS_PREGEN and torch.cuda.is_available():
+        dev = torch.device("cuda", torch.cuda.current_device())
+        rng_advance(dev)                       # (what the first dropout site of the pass would have done)
+        snap = _SNAP[0] = rng_state(dev).clone()
+        side = _BITS_SIDE.get(str(dev))
+        if side is None:
+            side = _BITS_SIDE[str(dev)] = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for key in plan:
+                _draw_keep_bits(snap, key, dev)
+        ev = torch.cuda.Event()
+        ev.record(side)
+        snap._fod_bits_ready = ev
+
+
+def end_forward():
+    """End of a model forward pass: joins the keep-bit side stream if no attention call of the pass did (a pass that
+    turned out to have no dropout site), so that no forked work is left dangling — a CUDA-graph capture requires it."""
+    snap = _SNAP[0]
+    ev = getattr(snap, "_fod_bits_ready", None) if snap is not None else None
+    if ev is not None:
+        torch.cuda.current_stream().wait_event(ev)
+        snap._fod_bits_ready = None
 
 
 def drop_site(p, training):
@@ -56,7 +88,7 @@ def drop_site(p, training):
         return None
     if not 0.0 < p < 1.0:
         raise ValueError("dropout probability has to be in [0, 1), got %r" % (p,))
-    if _CALL[0] == 0 or _SNAP[0] is None:
+    if _SNAP[0] is None:
         dev = torch.device("cuda", torch.cuda.current_device())
         rng_advance(dev)
         _SNAP[0] = rng_state(dev).clone()
@@ -193,6 +225,53 @@ def _fill_attn(a, q1, k1, v, q2, k2, out, lse, scale, heads, drop=None):
     a.lse = _p(lse)
     a.B, a.H, a.Lq, a.Lk, a.scale = B, heads, Lq, Lk, scale
     _fill_drop(a.drop, drop, out.device)
+    bits = _attn_keep_bits(drop, B, heads, Lq, Lk, out.device)
+    if bits is not None:
+        a.keep_bits, a.keep_pitch = _p(bits), bits.shape[1]
+
+
+_ATTN_BITS = os.environ.get("FOD_ATTN_BITS", "1") != "0"  # 0: every attention kernel draws its dropout mask itself
+_BITS_PREGEN = os.environ.get("FOD_ATTN_BITS_PREGEN", "1") != "0"  # 0: bits drawn at first use, on the compute stream
+
+
+def _draw_keep_bits(st, key, device):
+    """fod_attn_keep_bits for one attention call -> (rows, pitch) uint8, stored in the snapshot's cache."""
+    call_id, p, B, heads, Lq, Lk = key
+    cache = getattr(st, "_fod_keep_bits", None)
+    if cache is None:
+        cache = st._fod_keep_bits = {}
+    L = lib.load()
+    rows, pitch = B * heads * Lq, 16 * ((Lk + 127) // 128)
+    bits = torch.empty((rows, pitch), dtype=torch.uint8, device=device)
+    _t = prof.begin()
+    call = lambda: L.fod_attn_keep_bits(_p(st), call_id, p, rows, Lk, _p(bits), pitch, _stream())
+    lib.check(call(), "fod_attn_keep_bits")
+    prof.end(_t, "attn_keep_bits_%dx%d" % (rows, Lk), 0.0, float(rows * pitch), replay=call if _t is not None else None,
+             keep=(st, bits))
+    LAUNCH_COUNTS["attn_keep_bits_kernel"] += 1
+    cache[key] = bits
+    return bits
+
+
+def _attn_keep_bits(drop, B, heads, Lq, Lk, device):
+    """The keep decisions of one attention call's dropout as a (B*heads*Lq, pitch) byte tensor (fod_attn_keep_bits),
+    drawn once and shared by the forward and the backward kernel: cached on the forward's {seed, step} snapshot, which
+    both carry in their drop tuple and which is never written again.  None without a snapshot (the live state moves).
+    From the second training pass on the bits are already there: begin_forward() drew them on a side stream."""
+    if not _ATTN_BITS or drop is None or len(drop) < 3 or drop[2] is None or not drop[0] > 0:
+        return None
+    st = drop[2]
+    key = (drop[1], float(drop[0]), B, heads, Lq, Lk)
+    if st is _SNAP[0] and key not in _BITS_USED:
+        _BITS_USED.append(key)
+    bits = getattr(st, "_fod_keep_bits", {}).get(key)
+    if bits is None:
+        return _draw_keep_bits(st, key, device)
+    ev = getattr(st, "_fod_bits_ready", None)
+    if ev is not None:  # first consumer of bits drawn on the side stream: join it (later consumers follow in stream order)
+        torch.cuda.current_stream().wait_event(ev)
+        st._fod_bits_ready = None
+    return bits
 
 
 def attn_fwd(q1, k1, v, scale, heads=8, q2=None, k2=None, batch=None, drop=None):

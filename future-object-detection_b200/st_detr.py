@@ -115,7 +115,7 @@ class FuturePredCore(nn.Module):
 
     def forward(self, images, imu=None, temporal_offsets=None):
         assert images.dim() == 5, "expected (B, L, 3, H, W)"  # paper.py:463
-        ops.begin_forward()
+        ops.begin_forward(self.training and torch.is_grad_enabled())
         images = images[:, :-1]  # the last ("future") frame is never seen by the model (paper.py:463-468)
         if imu is not None:
             imu = imu[:, :-1]
@@ -139,6 +139,7 @@ class FuturePredCore(nn.Module):
         per_frame = x.view(b, t, s, d).transpose(0, 1).contiguous()
         frames = [per_frame[l].reshape(b * s, d) for l in range(t)]
         out = self.detector(frames, pos_bf, b, s)
+        ops.end_forward()
         moods = [["model happy" for _ in range(t + 1)] for _ in range(b)]
         return out, moods
 

@@ -114,8 +114,18 @@ typedef struct fod_attn_args {
     int32_t pad0;
     fod_dropout drop;  /* dropout on the softmax weights P (out = dropout(P)·V; lse is that of the undropped P); the
                           backward call must carry the same descriptor */
+    const void* keep_bits;  /* optional: the keep decisions of `drop` as written by fod_attn_keep_bits (NULL: the kernels
+                               draw them themselves; the bits are a cache of the same function, never a different mask) */
+    int64_t keep_pitch;     /* bytes per (b, head, query) row of keep_bits */
 } fod_attn_args;
 int fod_attn_fwd(const fod_attn_args* a, void* stream);
+/* Keep decisions of the dropout on the softmax weights (ConditionalDETR/models/attention.py:370; torch.nn.
+ * MultiheadAttention in future_od/models/transformer.py:404) for one attention call, drawn ONCE for the forward and the
+ * backward kernel: out[(b*H + h)*Lq + q][k / 8] bit (k % 8) = 1 if P[b, h, q, k] is kept under (rng_state, call, p) —
+ * exactly the decision the kernels draw on their own when keep_bits is NULL.  rows = B*H*Lq; pitch bytes per row, a
+ * multiple of 16 with pitch >= 16*ceil(Lk/128); out 16-byte aligned. */
+int fod_attn_keep_bits(const void* rng_state, int32_t call, float p, int64_t rows, int32_t Lk, void* out, int64_t pitch,
+                       void* stream);
 
 
 /* Flash attention backward (same layouts as fod_attn_fwd; recomputes S and dP on the tensor cores):

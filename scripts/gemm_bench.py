@@ -61,9 +61,11 @@ cases = {
     "dx 256x2048 plain": lambda: ops.gemm(x2048, w1, b_mn=True),
 }
 # attention / element-wise cases (one encoder layer at B = 32: 64 sequences of 350 tokens; stage 2: S = 1400)
-def _attn_case(nseq, S, drop, bwd, mode=0):
+def _attn_case(nseq, S, drop, bwd, mode=0, bits=False):
     st = {}
     d = (0.1, 9) if drop else None
+    if bits:  # a {seed, step} snapshot in the tuple: keep decisions drawn once (fod_attn_keep_bits) and cached on it
+        d = (0.1, 9, ops.rng_state(dev).clone())
 
     def run():
         if not st:  # built on first use, so a GEMM_CASE filter launches nothing else
@@ -118,6 +120,26 @@ cases["attn_fwd 64x350 drop"] = _attn_case(64, 350, True, False)
 cases["attn_fwd 64x350"] = _attn_case(64, 350, False, False)
 cases["attn_bwd 64x350 drop"] = _attn_case(64, 350, True, True)
 cases["attn_bwd 64x350"] = _attn_case(64, 350, False, True)
+cases["attn_fwd 64x350 drop bits"] = _attn_case(64, 350, True, False, bits=True)
+cases["attn_bwd 64x350 drop bits"] = _attn_case(64, 350, True, True, bits=True)
+
+
+def _bits_case(rows, lk):
+    st = {}
+
+    def run():
+        if not st:
+            st["o"] = torch.empty((rows, 16 * ((lk + 127) // 128)), dtype=torch.uint8, device=dev)
+            st["s"] = ops.rng_state(dev).clone()
+        from fod_b200 import lib as _lib
+        import ctypes as _C
+        L = _lib.load()
+        return L.fod_attn_keep_bits(_C.c_void_p(st["s"].data_ptr()), 9, 0.1, rows, lk, _C.c_void_p(st["o"].data_ptr()), st["o"].shape[1],
+                                    _C.c_void_p(torch.cuda.current_stream().cuda_stream))
+    return run
+
+
+cases["keep_bits 64x8x350x350"] = _bits_case(64 * 8 * 350, 350)
 cases["attn_fwd 32x1400"] = _attn_case(32, 1400, False, False)
 cases["attn_bwd 32x1400"] = _attn_case(32, 1400, False, True)
 cases["relu_bwd_add3 183500800"] = _relu_case(183500800)

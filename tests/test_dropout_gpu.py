@@ -395,3 +395,39 @@ def test_egodeep_head_dropout_table_equals_the_per_token_projection():
     ref.backward(g.float())
     for name, x, r in zip(("o", "dv", "dW", "db"), got, (ref, v32.grad, W.grad, b.grad)):
         assert _rel(x, r) < 2e-2, (name, _rel(x, r))
+
+
+@pytest.mark.parametrize("B,Lq,Lk,two", [(3, 350, 350, False), (2, 1400, 1400, False), (4, 128, 350, True), (2, 37, 129, False)])
+def test_attention_dropout_mask_bits_are_a_cache_of_the_drawn_masks(B, Lq, Lk, two):
+    """With a {seed, step} snapshot in the drop tuple the keep decisions are drawn once (fod_attn_keep_bits) and read by
+    the forward and the fused backward kernel; without one every kernel draws them itself.  Same function of (seed,
+    step, call, element) either way: outputs and gradients must be bit-identical, ragged key tails included."""
+    from fod_b200 import ops
+    ops.set_dropout_seed(4242, _dev())
+    H, D = 8, 256
+    q1, k1, v = _rnd(B, Lq, D, seed=1), _rnd(B, Lk, D, seed=2), _rnd(B, Lk, D, seed=3)
+    q2, k2 = (_rnd(B, Lq, D, seed=4), _rnd(Lk, D, seed=5)) if two else (None, None)
+    scale = (64 if two else 32) ** -0.5
+    snap = ops.rng_state(_dev()).clone()
+    drawn, cached = (P, 11), (P, 11, snap)
+    o1, l1 = ops.attn_fwd(q1, k1, v, scale, H, q2=q2, k2=k2, drop=drawn)
+    n0 = ops.LAUNCH_COUNTS["attn_keep_bits_kernel"]
+    o2, l2 = ops.attn_fwd(q1, k1, v, scale, H, q2=q2, k2=k2, drop=cached)
+    assert ops.LAUNCH_COUNTS["attn_keep_bits_kernel"] == n0 + 1
+    assert torch.equal(o1, o2) and torch.equal(l1, l2)
+    do = _rnd(B, Lq, D, seed=6)
+    g1 = ops.attn_bwd(q1, k1, v, o1, l1, do, scale, H, q2=q2, k2=k2, drop=drawn)
+    g2 = ops.attn_bwd(q1, k1, v, o2, l2, do, scale, H, q2=q2, k2=k2, drop=cached)
+    assert ops.LAUNCH_COUNTS["attn_keep_bits_kernel"] == n0 + 1  # the backward found the forward's bits
+    for a, b in zip(g1, g2):
+        assert (a is None) == (b is None)
+        if a is not None:
+            assert torch.equal(a, b)
+    # the bits themselves: keep rate, and zero weight on dropped entries is visible in the forward output changing
+    bits = snap._fod_keep_bits[(11, float(P), B, H, Lq, Lk)]
+    assert bits.shape == (B * H * Lq, 16 * ((Lk + 127) // 128))
+    valid = torch.zeros(bits.shape[1] * 8, dtype=torch.bool, device=_dev())
+    valid[:Lk] = True
+    unpacked = ((bits.unsqueeze(-1) >> torch.arange(8, device=_dev(), dtype=torch.uint8)) & 1).flatten(1).bool()
+    rate = float(unpacked[:, valid].float().mean())
+    assert abs(rate - (1 - P)) < 5 * (P * (1 - P) / unpacked[:, valid].numel()) ** 0.5 + 2e-5, rate
