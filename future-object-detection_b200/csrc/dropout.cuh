@@ -3,7 +3,8 @@
 // (p = 0.1 on the attention weights, ConditionalDETR/models/attention.py:370 and torch.nn.MultiheadAttention; after every
 // sub-block and inside the FFNs, future_od/models/transformer.py:201,207,234,271,285,310,405-412).
 //
-// Nothing is stored: forward and backward regenerate the same mask from
+// No activation-sized mask is stored: forward and backward evaluate the same function (the attention kernels may read
+// it from a 1-bit-per-weight cache, fod_attn_keep_bits) of
 //   key     = the run's 64-bit seed                      (device memory: fod_rng_state.seed)
 //   counter = (element group, step, call site)          step lives in device memory too and is advanced once per
 //                                                        training step (fod_rng_advance), so a captured CUDA graph draws
