@@ -189,14 +189,16 @@ stem_conv7x7s2_kernel(const StemParams p) {
 // splitting the image rows into (parity, row / 2) turns the stride-2 row walk into a dense box:
 //     dims [k = 32][ox][row parity = 2][row / 2][n], box [32][16][1][11][1] -> [11 half-rows][16 pixels][64 B], SWIZZLE_64B:
 // any 8 consecutive half-rows of it are the K-major A operand of one kernel row as they land, and the kernel rows of one
-// parity (1,3,5 / 0,2,4,6) are the SAME box read one half-row further down (two boxes = 22 KB per tile, not seven).  Rows above / below the image and tiles hanging over the right
-// edge are zero-filled by the TMA unit.  K = 7 x 32 = 224: 14 MMAs (M128 N64 K16) per 8 x 16-pixel tile.
+// parity (1,3,5 / 0,2,4,6) are the SAME box read one half-row further down (two boxes = 22 KB per tile, not seven).
+// Rows above / below the image and tiles hanging over the right edge are zero-filled by the TMA unit.
+// K = 7 x 32 = 224: 14 MMAs (M128 N64 K16) per 8 x 16-pixel tile.
 //   warp 0: TMA producer, the two parity boxes of a tile on one barrier, 5-tile ring
 //   warp 1: TMEM allocator + MMA issuer, two accumulators (2 x 64 columns): tile i+1 is multiplied while tile i drains
 //   warps 2-5: epilogue — accumulator row -> +shift, ReLU -> bf16 -> SWIZZLE_128B staging tile -> ONE TMA store of
 //              the tile's [8][16][64] block (clipped at the image edges by the unit).
-// Persistent, one CTA per SM.  Bound: the 128 B per output pixel it writes (HBM) — 14 MMAs at the 52-clk issue floor
-// are 730 clk per 16 KB tile, i.e. ~6 TB/s over 148 SMs.
+// Persistent, one CTA per SM.  Measured (64 frames 448x800): 243 us = 1 520 clk per tile against 730 clk of MMA issue — the
+// 128 B per output pixel leave at 3.0 TB/s where a B200 sustains 3.9 TB/s for pure stores (scripts/bw_probe.py), which
+// is why the POOL form below exists.
 constexpr int S4_STAGES = 5;                     // ring of whole tiles
 constexpr int S4_BOX_ROWS = 11;                  // half-rows per box: 8 output rows + 3 (odd kernel rows 0,2,4,6 share one box)
 constexpr int S4_BOX_BYTES = S4_BOX_ROWS * 16 * 64;  // 11 KB: [11 half-rows][16 pixels][64 B]
@@ -233,13 +235,13 @@ struct Stem4Params {
 // positions outside the image are skipped in the maximum (everything kept is >= 0 after the ReLU).
 constexpr int S4P_PH = 7, S4P_PW = 3;
 
-// POOL runs TWO epilogue groups of four warps (tiles alternate between them, one TMEM accumulator and one staging tile
-// each): with the pooling pass the epilogue, not the MMAs, is the longest stage of a tile.
+// POOL runs G (default 3) epilogue groups of four warps (tiles go round-robin, one TMEM accumulator and one staging tile
+// per group): with one group the pooling pass made the epilogue the longest stage of a tile (830 us; 2 groups 399,
+// 3 groups 375, 4 groups 377 — beyond three the shared-memory traffic of MMA operands + staging + pooling binds).
 template <bool POOL, int G> constexpr int s4_threads() { return POOL ? 64 + 128 * G : S4_THREADS; }
 template <bool RAW, bool POOL, int G> constexpr int s4_smem() {
-    // (the non-POOL forms request the expanded form's stage bytes either way: more than half an SM's shared memory, so the
-    // 148 persistent CTAs land one per SM — with the smaller RAW request two fit, some SMs got two and the launch took 288 us
-    // instead of 242)
+    // (every form keeps the expanded form's stage region, RAW stages being less than half of it: with the weights and
+    // staging tiles placed right behind the smaller RAW ring the un-pooled launch took 288 us instead of 243, reproducibly)
     return ((S4_STAGES * S4_A_BYTES + 1023) & ~1023) + S4_B_BYTES + (POOL ? G : 2) * S4_OUT_BYTES + 64 * 4 + 512 + 1024;
 }
 
