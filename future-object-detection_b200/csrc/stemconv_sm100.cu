@@ -403,7 +403,12 @@ stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
                 for (int q = 0; q < 4; ++q) {
                     float f[8];
 #pragma unroll
-                    for (int t = 0; t < 8; ++t) f[t] = fmaxf(__uint_as_float(acc[h][q * 8 + t]) + sBias[h * 32 + q * 8 + t], 0.f);
+                    for (int t = 0; t < 8; ++t) {
+                        // POOL: the ReLU is the zero the pooled maximum starts from (max and bf16 rounding are monotone:
+                        // max_i bf16(relu(x_i)) == max(0, max_i bf16(x_i)) bit for bit)
+                        const float x = __uint_as_float(acc[h][q * 8 + t]) + sBias[h * 32 + q * 8 + t];
+                        f[t] = POOL ? x : fmaxf(x, 0.f);
+                    }
                     uint4 u;
                     u.x = pack_bf16x2(f[0], f[1]);
                     u.y = pack_bf16x2(f[2], f[3]);
@@ -436,6 +441,8 @@ stem_conv7x7s2_p4_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
 #pragma unroll
                             for (int e = 0; e < 4; ++e) hb[e] = __hmax2(hb[e], hv[e]);
                         }
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) hb[e] = __hmax2(hb[e], zero);  // the ReLU
                         *reinterpret_cast<uint4*>(blk + p_rel[j]) = v[0];
                     }
                     continue;
