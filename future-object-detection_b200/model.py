@@ -562,6 +562,8 @@ class CDetrBackbone(nn.Module):
 
 
 # ------------------------------------------------------------------------------------------------ encoder
+_EGO_BIAS_ROW = os.environ.get("FOD_EGO_BIAS_ROW", "1") != "0"  # 0: out_proj bias of the egodeep table product as baddbmm addend
+_EGO_K = 16
 _STEM_POOL = os.environ.get("FOD_STEM_POOL", "1") != "0"  # 0: stem convolution and max-pool as two kernels (A/B switch)
 
 
@@ -687,11 +689,20 @@ class EgodeepAttention(nn.Module):
     def _out_proj_of_masked_heads(self, v, keep):
         """v (n_seq, D) value rows, keep (n_seq, seq_len, H) per-token head multipliers -> out_proj(v with heads scaled)
         for every token, (n_seq*seq_len, D) bf16, through the (n_seq, H, D) table of per-head out_proj contributions."""
-        n_seq, seq_len, h = keep.shape
-        d = v.shape[1]
+        n_seq, seq_len, kw = keep.shape
+        h, d = self.heads, v.shape[1]
         op = self.fun.out_proj
         table = torch.einsum("shk,ohk->sho", v.float().view(n_seq, h, d // h), op.weight.view(d, h, d // h)).to(BF16)
-        return torch.baddbmm(op.bias.to(BF16).view(1, 1, d), keep, table).view(n_seq * seq_len, d)
+        if not _EGO_BIAS_ROW:
+            return torch.baddbmm(op.bias.to(BF16).view(1, 1, d), keep[..., :h], table).view(n_seq * seq_len, d)
+        # The bias rides as one more table row against a column of ones (K padded to 16 for the library's aligned
+        # kernels): as baddbmm's broadcast addend its gradient was a separate reduction of the whole (n_seq, seq_len, D)
+        # gradient — 35 us per layer at 64 x 350 tokens — which the table-gradient product now does on the way.
+        if kw == h:
+            keep = F.pad(keep, (0, _EGO_K - h))
+            keep[..., h] = 1
+        rows = (table, op.bias.to(BF16).view(1, 1, d).expand(n_seq, 1, d), table.new_zeros((n_seq, _EGO_K - h - 1, d)))
+        return torch.bmm(keep, torch.cat(rows, dim=1)).view(n_seq * seq_len, d)
 
     def forward_single_key_dropout(self, ego, n_seq, seq_len):
         """ego (n_seq, D) -> per-TOKEN update (n_seq*seq_len, D) with dropout on.  The softmax weight over one key is
@@ -704,7 +715,12 @@ class EgodeepAttention(nn.Module):
         #   out_proj(a_token) = sum_h keep[token, h] * (W_o[:, head h] · v_seq[head h]) + b_o = keep_token (1 x H) · M_seq (H x D) + b_o:
         # the per-sequence table M is 8 rows (tiny torch ops), and the per-token out_proj GEMM (K = 256), its input, its
         # dX / dW GEMMs and the mask multiply become one K = 8 batched library product and its transpose in backward.
-        keep = (torch.rand((n_seq, seq_len, h), device=ego.device) >= self.p).to(BF16) * (1.0 / (1.0 - self.p))
+        if _EGO_BIAS_ROW:  # columns [0, h): head multipliers; column h: the ones that carry the out_proj bias; rest: zero
+            keep = (torch.rand((n_seq, seq_len, _EGO_K), device=ego.device) >= self.p).to(BF16) * (1.0 / (1.0 - self.p))
+            keep[..., h:] = 0
+            keep[..., h] = 1
+        else:
+            keep = (torch.rand((n_seq, seq_len, h), device=ego.device) >= self.p).to(BF16) * (1.0 / (1.0 - self.p))
         o = self._post(self._out_proj_of_masked_heads(v, keep))
         dead = [p for m in (self.query_content, self.query_pos, self.key) for p in m.parameters() if p.requires_grad]
         return _ZeroGrad.apply(o, *dead) if dead and torch.is_grad_enabled() else o
